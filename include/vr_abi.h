@@ -1,0 +1,192 @@
+/* vr_abi.h - C ABI of the B200 ray-march engine (libvr_b200.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of raphiniert-com/volume_renderer: the
+ * per-pixel ray march.  Every entry point replaces one command of the reference's mex gateway
+ * `volumeRender(cmd, handle, ...)` (reference: src/C/mex/render.cpp:50-277) or one of its two
+ * helper mex files.  The gateway (mex/volumeRender_mex.cpp in this repo) only unpacks mxArrays
+ * into the plain pointers below; ALL argument re-ordering the reference does while unpacking
+ * (axis reversal of positions, element sizes and the rotation matrix) happens behind this ABI,
+ * so the arrays are passed exactly as MATLAB hands them over.
+ *
+ * Conventions
+ *  - plain C types only, no exceptions / longjmp across the boundary; every call returns a
+ *    vr_status, the message is available from vr_last_error().
+ *  - all state is context-local (the reference keeps process-wide globals,
+ *    volumeRender_kernel.cu:55-120); a context is bound to one CUDA device.
+ *  - host volume memory is borrowed for the duration of the call only (render.cpp:96-98 borrows
+ *    MATLAB's buffer through mxGetPropertyShared, volumeRender.cpp:310).
+ *  - MATLAB layout everywhere: column-major, dims[0] = size(Data,1) is the fastest axis and
+ *    becomes texture x (volumeRender.cpp:338-339).
+ */
+#ifndef VR_ABI_H_
+#define VR_ABI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define VR_API __declspec(dllexport)
+#else
+#define VR_API __attribute__((visibility("default")))
+#endif
+
+#define VR_ABI_VERSION 1
+
+/* Opaque persistent context = the reference's mm::MManager behind a class_handle
+ * (src/C/vr/mm/mmanager.hxx:25-105, src/C/vr/mm/class_handle.hpp:42-62). */
+typedef struct vr_ctx vr_ctx;
+
+typedef enum vr_status {
+  VR_OK = 0,
+  VR_ERR_INVALID_ARGUMENT = 1,  /* mexErrMsgTxt("insufficient parameter!") etc., render.cpp:51-56,136-140 */
+  VR_ERR_INVALID_HANDLE = 2,    /* "Handle not valid.", class_handle.hpp:69-70 */
+  VR_ERR_INSUFFICIENT_VRAM = 3, /* "insufficient free VRAM!", mmanager.hxx:161-172 */
+  VR_ERR_CUDA = 4,              /* CUDA runtime error (the reference drops these in release, common.h:46) */
+  VR_ERR_NO_DEVICE = 5,         /* no CUDA device / wrong architecture: there is NO CPU fallback */
+  VR_ERR_UNSUPPORTED = 6
+} vr_status;
+
+typedef enum vr_dtype {
+  VR_DTYPE_F32 = 0,  /* the reference's only type (volumeRender.h:26) */
+  VR_DTYPE_BF16 = 1  /* storage only, arithmetic stays fp32 */
+} vr_dtype;
+
+typedef enum vr_memspace {
+  VR_MEM_HOST = 0,   /* pageable or pinned host memory (the MATLAB case) */
+  VR_MEM_DEVICE = 1  /* already resident on this context's device (C harness / pipelines) */
+} vr_memspace;
+
+/* One MATLAB `Volume` object as mxMake_volume reads it (volumeRender.cpp:307-342):
+ * Data pointer + dims, TimeLastUpdate.  memory_size is derived (volumeRender.cpp:71-72). */
+typedef struct vr_volume {
+  const void *data;
+  uint64_t dims[3];     /* size(Data,1), size(Data,2), size(Data,3); 1 for a 2-D array */
+  uint64_t last_update; /* Volume.TimeLastUpdate (ms timestamp, Volume.m:225-238) */
+  int32_t dtype;        /* vr_dtype */
+  int32_t memspace;     /* vr_memspace */
+} vr_volume;
+
+/* One MATLAB `LightSource` (LightSource.m:31-37): single 1x3 Position and Color exactly as
+ * stored in MATLAB.  Position is axis-reversed internally like render.cpp:162-168. */
+typedef struct vr_light {
+  float position[3];
+  float color[3];
+} vr_light;
+
+/* Counters of the last vr_render*/
+typedef struct vr_stats {
+  double kernel_ms;          /* device time of the ray-march launch(es), CUDA events */
+  double upload_ms;          /* device time of uploads done by the last vr_sync_volumes */
+  uint64_t samples_marched;  /* iterations of the loop volumeRender_kernel.cu:435-493 (skipped ones count) */
+  uint64_t samples_shaded;   /* iterations that actually sampled/shaded (not elided by empty-space skipping) */
+  uint64_t rays_hit;         /* pixels whose ray hit the box */
+  uint64_t bytes_resident;   /* device bytes owned by the context */
+  uint64_t bytes_uploaded;   /* host->device bytes moved by the last vr_sync_volumes / vr_render */
+  uint32_t kernel_launches;  /* kernels launched by the last vr_render */
+  uint32_t uploads;          /* volume uploads done by the last vr_sync_volumes */
+} vr_stats;
+
+/* ---- 'new'  (render.cpp:58-65) -------------------------------------------------------- */
+/* Creates a context on the current CUDA device (or $VR_DEVICE).  The reference picks the
+ * "max GFLOPS" device (volumeRender.cpp:77-87,163-220); one process per GPU makes that moot. */
+VR_API vr_status vr_create(vr_ctx **out_ctx);
+VR_API vr_status vr_create_on_device(vr_ctx **out_ctx, int device);
+
+/* ---- 'delete'  (render.cpp:72-79, class_handle.hpp:79-83) ------------------------------ */
+/* Frees everything the context owns.  Unlike ~MManager (mmanager.hxx:103-105) it does NOT call
+ * cudaDeviceReset().  Tolerates a stale / already deleted handle (VolumeRender.m memClear then
+ * delete double-deletes, VolumeRender.m:184-186,230-237): returns VR_ERR_INVALID_HANDLE. */
+VR_API vr_status vr_destroy(vr_ctx *ctx);
+
+/* ---- 'mem_info'  (render.cpp:85-87, mmanager.hxx:218-284) ------------------------------ */
+/* Writes the NUL-terminated report into buf (truncated to cap); *needed gets the full length. */
+VR_API vr_status vr_mem_info(vr_ctx *ctx, char *buf, size_t cap, size_t *needed);
+
+/* ---- 'sync_volumes'  (render.cpp:93-129, mmanager.hxx:178-201, kernel.cu:739-867) ------- */
+/* Argument order is the mex's: emission, REFLECTION, absorption.  gx/gy/gz all non-NULL = the
+ * nrhs==9 form (gradient lookup); all NULL = the nrhs==6 form (resetGradients, on-the-fly). */
+VR_API vr_status vr_sync_volumes(vr_ctx *ctx, uint64_t time_last_mem_sync,
+                                 const vr_volume *emission, const vr_volume *reflection,
+                                 const vr_volume *absorption, const vr_volume *gradient_x,
+                                 const vr_volume *gradient_y, const vr_volume *gradient_z);
+
+/* ---- 'render'  (render.cpp:134-277) --------------------------------------------------- */
+/* lights / illumination: NULL mirrors the `logical` placeholders (render.cpp:145-146): the
+ *   light set and LUT of the previous render stay in force (none on a fresh context).
+ * factors        single[3] = [FactorEmission, FactorReflection, FactorAbsorption]  (VolumeRender.m:558)
+ * element_size_um single[3] = ElementSizeUm as in MATLAB (reversed inside, render.cpp:195)
+ * resolution     uint64[2] = [H, W]                                                (render.cpp:196,237-243)
+ * rotation       single[9] = flip(RotationMatrix), column-major                    (render.cpp:211-219)
+ * props          single[3] = [CameraXOffset, FocalLength, DistanceToObject]        (render.cpp:220-221)
+ * color          single[3]                                                         (render.cpp:240)
+ * out_image      H*W*3 floats, MATLAB H x W x 3 single (column-major planar, kernel.cu:496-506) */
+VR_API vr_status vr_render(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
+                           const vr_volume *illumination, const float factors[3],
+                           const float element_size_um[3], const uint64_t resolution[2],
+                           const float rotation[9], const float props[3],
+                           float opacity_threshold, const float color[3], float *out_image);
+
+/* Same call, but the image stays on the device: d_out_image is a device pointer to H*W*3 floats
+ * and the work is enqueued on `cuda_stream` (a cudaStream_t, NULL = the context's stream) without
+ * a host synchronisation.  This is the entry for pipelines that post-process on the GPU. */
+VR_API vr_status vr_render_device(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
+                                  const vr_volume *illumination, const float factors[3],
+                                  const float element_size_um[3], const uint64_t resolution[2],
+                                  const float rotation[9], const float props[3],
+                                  float opacity_threshold, const float color[3],
+                                  float *d_out_image, void *cuda_stream);
+
+/* ---- HenyeyGreenstein(n[,g]) mex  (src/C/mex/HenyeyGreenstein.cc:29-96) ---------------- */
+/* n^3 floats, index k = c*n*n + a*n + b (HenyeyGreenstein.cc:86); evaluated on the GPU. */
+VR_API vr_status vr_henyey_greenstein(uint32_t n, float g, float *out_lut);
+
+/* ---- timestamp() mex  (src/C/mex/timestamp.cpp:13-33) ---------------------------------- */
+/* Milliseconds since the epoch.  The reference stores them through an int* (timestamp.cpp:25,33),
+ * i.e. only the low 32 bits reach MATLAB; truncate_like_reference != 0 reproduces that. */
+VR_API uint64_t vr_timestamp_ms(int truncate_like_reference);
+
+/* ---- errors --------------------------------------------------------------------------- */
+VR_API const char *vr_last_error(const vr_ctx *ctx); /* ctx may be NULL: last error of this thread */
+VR_API const char *vr_status_string(vr_status s);
+VR_API int vr_abi_version(void);
+
+/* ---- extensions with no reference counterpart ------------------------------------------ */
+/* Options (ints).  Defaults reproduce the reference as written. */
+typedef enum vr_option {
+  VR_OPT_FILTER_FRAC_BITS = 0,  /* 0 = fp32 trilinear weights (default); 8 = the texture unit's 1.8 fixed point */
+  VR_OPT_EMPTY_SPACE_SKIP = 1,  /* 1 (default) = exact empty-space skipping; 0 = march every sample */
+  VR_OPT_KERNEL_VARIANT = 2,    /* implementation selector; 0 = default */
+  VR_OPT_ABSORPTION_ROLE_FIX = 3, /* 0 (default) = reference as written: absorption samples the emission texture
+                                     (kernel.cu:80); 1 = sample the uploaded absorption volume */
+  VR_OPT_PART_RANK = 4,         /* image-space partition: this context renders tiles t with t % nranks == rank */
+  VR_OPT_PART_NRANKS = 5,
+  VR_OPT_TILE_W = 6,            /* partition tile size in pixels */
+  VR_OPT_TILE_H = 7,
+  VR_OPT_BRICK_LAYOUT = 8,      /* 1 = bricked resident layout (default), 0 = linear */
+  VR_OPT_COUNT_SAMPLES = 9      /* 1 (default) = maintain vr_stats sample counters */
+} vr_option;
+VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
+VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);
+VR_API vr_status vr_get_stats(vr_ctx *ctx, vr_stats *out);
+/* Work of later calls is enqueued on this cudaStream_t (NULL = legacy default stream). */
+VR_API vr_status vr_set_stream(vr_ctx *ctx, void *cuda_stream);
+VR_API vr_status vr_get_device(vr_ctx *ctx, int *device);
+
+/* Device-side synthetic "ViBE-Z-shaped" volume generator; fills d_out (device
+ * pointer, dims[0] fastest) so that 1024^3+ test volumes never cross PCIe.  kind: 0 = brain
+ * ellipsoid with value noise, 1 = sparse tubes.  The host twin lives in the test suite. */
+VR_API vr_status vr_synth_volume(vr_ctx *ctx, int kind, uint32_t seed, const uint64_t dims[3],
+                                 int32_t dtype, void *d_out);
+/* Device memory helpers for callers without a CUDA runtime binding (C harness, ctypes). */
+VR_API vr_status vr_device_alloc(vr_ctx *ctx, size_t bytes, void **d_ptr);
+VR_API vr_status vr_device_free(vr_ctx *ctx, void *d_ptr);
+VR_API vr_status vr_device_download(vr_ctx *ctx, void *host_dst, const void *d_src, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VR_ABI_H_ */

@@ -1,0 +1,630 @@
+/* oracle.cpp - CPU restatement of the reference's ray-march path.  TEST INFRASTRUCTURE ONLY
+ * (see oracle.h).  Written from the reference's behaviour, statement by statement, with the
+ * reference line each block follows cited as `kernel.cu:N` (= src/C/vr/volumeRender_kernel.cu),
+ * `vr.cpp:N` (= src/C/vr/volumeRender.cpp), `render.cpp:N` (= src/C/mex/render.cpp),
+ * `mm.hxx:N` (= src/C/vr/mm/mmanager.hxx), `hg.cc:N` (= src/C/mex/HenyeyGreenstein.cc) and
+ * `helper_math.h:N` (= lib/cuda-samples/Common/helper_math.h).
+ *
+ * Arithmetic is fp32 throughout, in the reference's operation order.  Where the reference
+ * relies on hardware (texture filtering, MUFU intrinsics) the rule used here is stated at the
+ * function.  Build with -ffp-contract=off for the checker (oracle/Makefile).
+ */
+#include "oracle.h"
+
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+struct f3 {
+  float x, y, z;
+};
+inline f3 mk(float x, float y, float z) { return f3{x, y, z}; }
+inline f3 operator+(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline f3 operator-(f3 a, f3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline f3 operator*(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+inline f3 operator*(f3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+inline f3 operator*(float s, f3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+/* helper_math.h:1264-1267 */
+inline float dot(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+/* helper_math.h:1307-1310 */
+inline float length(f3 v) { return sqrtf(dot(v, v)); }
+/* helper_math.h:1325-1328: v * rsqrtf(dot(v,v)).  rsqrtf(0)=+inf so normalize(0) = NaN, kept. */
+inline f3 normalize(f3 v) {
+  float invLen = 1.0f / sqrtf(dot(v, v));
+  return v * invLen;
+}
+
+const float PI_F = 3.14159265358979323846f; /* kernel.cu:20 */
+
+enum Slot { S_EM = 0, S_AB = 1, S_RE = 2, S_DX = 3, S_DY = 4, S_DZ = 5, S_LIGHT = 6, S_N = 7 }; /* vr.h:152-160 */
+
+/* vr::Volume (vr.h:62-71) + operator== (vr.cpp:24-26) */
+struct HostVol {
+  const float *data = nullptr;
+  uint64_t w = 0, h = 0, d = 0;
+  uint64_t bytes = 0;
+  uint64_t last_update = 0;
+};
+inline bool same(const HostVol &a, const HostVol &b) {
+  return a.data == b.data && a.last_update == b.last_update && a.bytes == b.bytes;
+}
+HostVol make_volume(const vr_volume *v) { /* vr.cpp:65-76, 307-342 */
+  HostVol r;
+  if (!v) return r;
+  r.data = static_cast<const float *>(v->data);
+  r.w = v->dims[0];
+  r.h = v->dims[1];
+  r.d = v->dims[2];
+  r.bytes = r.w * r.h * r.d * sizeof(float);
+  r.last_update = v->last_update;
+  return r;
+}
+
+/* A texture reference bound to a cudaArray (kernel.cu:90-120, 522-554): normalized coordinates,
+ * linear filter, clamp addressing.  `bound == false` models an unbound texture reference; the
+ * reference's behaviour is then undefined, the oracle (and the product) read 0. */
+struct Tex {
+  std::vector<float> own;
+  const float *p = nullptr;
+  uint64_t w = 0, h = 0, d = 0;
+  bool bound = false;
+};
+
+struct Light {
+  f3 position, color;
+};
+
+/* CUDA Programming Guide, "Texture Fetching / Linear Filtering" (the contract of
+ * cudaFilterModeLinear + normalized coords + clamp, kernel.cu:544-548):
+ *   xB = x*N - 0.5 ; i = floor(xB) ; a = frac(xB) ; taps clamped to [0,N-1];
+ *   tex = sum of the 8 taps weighted (1-a|a)(1-b|b)(1-c|c).
+ * frac_bits == 8 rounds a,b,c to the texture unit's 1.8 fixed point (round to nearest), the
+ * default 0 keeps fp32 weights (the definition of "render math").
+ * NaN coordinate rule: a NaN coordinate is treated as 0 (what the texture unit's float->fixed
+ * conversion does; verified on B200 by tests/probes).  Interpolation is written
+ * as nested a + f*(b-a) lerps so constant data filters to exactly that constant.
+ */
+struct Axis {
+  int64_t i0, i1;
+  float f;
+};
+inline Axis axis(float x, uint64_t n, int frac_bits) {
+  if (!(x == x)) x = 0.0f; /* NaN -> 0 */
+  float xb = x * (float)n - 0.5f;
+  /* keep the float->int conversion defined for huge / infinite coordinates */
+  if (xb < -2.0f) xb = -2.0f;
+  if (xb > (float)n + 1.0f) xb = (float)n + 1.0f;
+  float fl = floorf(xb);
+  float f = xb - fl;
+  if (frac_bits > 0) {
+    float q = (float)(1 << frac_bits);
+    f = floorf(f * q + 0.5f) / q;
+  }
+  int64_t i = (int64_t)fl;
+  int64_t hi = (int64_t)n - 1;
+  Axis a;
+  a.i0 = i < 0 ? 0 : (i > hi ? hi : i);
+  a.i1 = i + 1 < 0 ? 0 : (i + 1 > hi ? hi : i + 1);
+  a.f = f;
+  return a;
+}
+inline float lerp(float a, float b, float f) { return a + f * (b - a); }
+
+inline float tex3d_raw(const float *p, uint64_t w, uint64_t h, uint64_t d, float x, float y, float z,
+                       int frac_bits) {
+  Axis ax = axis(x, w, frac_bits), ay = axis(y, h, frac_bits), az = axis(z, d, frac_bits);
+  const uint64_t sy = w, sz = w * h;
+  const float *z0 = p + az.i0 * sz, *z1 = p + az.i1 * sz;
+  float c000 = z0[ay.i0 * sy + ax.i0], c100 = z0[ay.i0 * sy + ax.i1];
+  float c010 = z0[ay.i1 * sy + ax.i0], c110 = z0[ay.i1 * sy + ax.i1];
+  float c001 = z1[ay.i0 * sy + ax.i0], c101 = z1[ay.i0 * sy + ax.i1];
+  float c011 = z1[ay.i1 * sy + ax.i0], c111 = z1[ay.i1 * sy + ax.i1];
+  float c00 = lerp(c000, c100, ax.f), c10 = lerp(c010, c110, ax.f);
+  float c01 = lerp(c001, c101, ax.f), c11 = lerp(c011, c111, ax.f);
+  float c0 = lerp(c00, c10, ay.f), c1 = lerp(c01, c11, ay.f);
+  return lerp(c0, c1, az.f);
+}
+inline float tex3d(const Tex &t, float x, float y, float z, int frac_bits) {
+  if (!t.bound || !t.p || t.w == 0 || t.h == 0 || t.d == 0) return 0.0f;
+  return tex3d_raw(t.p, t.w, t.h, t.d, x, y, z, frac_bits);
+}
+
+/* vr::RenderOptions (vr.h:81-109) */
+struct Options {
+  uint64_t image_width, image_height;
+  float factor_emission, factor_absorption, factor_reflection;
+  f3 boxmin, boxmax;
+  f3 m[4]; /* float4x3: rows 0..2 camera axes, row 3 = (camXOffset, focal, objDist) */
+  float opacity_threshold, tstep;
+};
+
+/* vr.cpp:125-145 */
+void init_box_tstep(uint64_t w, uint64_t h, uint64_t d, f3 es, f3 *boxmin, f3 *boxmax, float *tstep) {
+  *boxmax = mk(1.f, (es.y * h) / ((float)w * es.x), (es.z * d) / ((float)w * es.x));
+  *boxmin = -1.f * (*boxmax);
+  f3 diagonals = mk(sqrtf((float)(w * w + h * h)), sqrtf((float)(h * h + d * d)), sqrtf((float)(w * w + d * d)));
+  /* named maxDiagonal in the reference but it is the MINIMUM (fminf, vr.cpp:141) */
+  float maxDiagonal = fminf(diagonals.x, fminf(diagonals.y, diagonals.z));
+  *tstep = 1.f / (2.2f * maxDiagonal);
+}
+
+} // namespace
+
+struct orc_ctx {
+  /* mm::MManager (mm.hxx:25-100) */
+  uint64_t timeLastMemSync = 0;
+  HostVol host[S_N];
+  bool arr[S_N] = {false, false, false, false, false, false, false}; /* ptr_d_volume* != 0 */
+  /* device globals (kernel.cu:55-120) */
+  Tex tex[S_N];
+  int idxEm = S_EM, idxAb = S_EM /* sic, kernel.cu:80 */, idxRe = S_RE;
+  int gradientMethod = 0; /* dc_activeGradientMethod, kernel.cu:55 */
+  std::vector<Light> lights; /* d_lightSources + c_numLightSources (zero-initialised constant) */
+  /* oracle switches */
+  int frac_bits = 0;
+  int absorption_role_fix = 0;
+  int borrow = 0;
+  int threads = 0;
+  int fast_exp = 1;
+  /* bookkeeping */
+  uint64_t uploads[S_N] = {0, 0, 0, 0, 0, 0, 0};
+  orc_stats stats{};
+  std::string err;
+};
+
+namespace {
+
+/* createTextureFromVolume (kernel.cu:522-554): cudaMalloc3DArray + cudaMemcpy3D + bind. */
+void upload(orc_ctx *c, int slot, const HostVol &v) {
+  Tex &t = c->tex[slot];
+  t.w = v.w;
+  t.h = v.h;
+  t.d = v.d;
+  size_t n = (size_t)(v.w * v.h * v.d);
+  if (c->borrow) {
+    t.own.clear();
+    t.own.shrink_to_fit();
+    t.p = v.data;
+  } else {
+    t.own.assign(v.data, v.data + n);
+    t.p = t.own.data();
+  }
+  t.bound = (v.data != nullptr && n > 0);
+  c->arr[slot] = true;
+  c->uploads[slot]++;
+}
+/* syncVolume (kernel.cu:659-672): whatever the flag, the old array is released when present
+ * and createTextureFromVolume then sees a null array, so the volume is ALWAYS (re)uploaded. */
+void syncVolume(orc_ctx *c, int slot, const HostVol &v, bool /*aAllocateMemory*/) { upload(c, slot, v); }
+/* referenceTexture (kernel.cu:631-648): unbind + drop the array pointer (leaks it), then
+ * redirect the role index. */
+void referenceTexture(orc_ctx *c, int slot, int *idx, int assigned) {
+  if (c->arr[slot]) {
+    c->tex[slot].bound = false;
+    c->tex[slot].own.clear();
+    c->tex[slot].p = nullptr;
+    c->arr[slot] = false;
+  }
+  *idx = assigned;
+}
+
+/* syncWithDevice (kernel.cu:739-867), statement by statement. */
+void syncWithDevice(orc_ctx *c) {
+  const HostVol &Em = c->host[S_EM], &Ab = c->host[S_AB], &Re = c->host[S_RE];
+  const uint64_t T = c->timeLastMemSync;
+  const bool simEmAb = same(Em, Ab), simEmRe = same(Em, Re), simAbRe = same(Ab, Re); /* :744-746 */
+  const bool reqEm = (Em.last_update > T) || (T == 0); /* :749-751 */
+  const bool reqAb = (Ab.last_update > T) || (T == 0);
+  const bool reqRe = (Re.last_update > T) || (T == 0);
+  bool updEm = false, updAb = false, updRe = false;
+
+  if (reqEm) { /* :765-792 */
+    if (!updEm) {
+      syncVolume(c, S_EM, Em, updEm);
+      updEm = true;
+    }
+    if (simEmRe && !updRe) {
+      referenceTexture(c, S_RE, &c->idxRe, S_EM);
+      updRe = true;
+    }
+    if (simEmAb && !updAb) {
+      referenceTexture(c, S_AB, &c->idxAb, S_EM);
+      updAb = true;
+    }
+  }
+  if (reqAb) { /* :794-828 */
+    if (!updAb) {
+      syncVolume(c, S_AB, Ab, updAb);
+      updAb = true;
+    }
+    if (simAbRe && !updRe) {
+      referenceTexture(c, S_RE, &c->idxRe, S_AB);
+      updRe = true;
+    }
+    if (simEmAb && !updEm) {
+      /* :818-819 passes tex_emission but stores the result into d_aVolumeAbsorption */
+      if (c->arr[S_AB]) {
+        c->tex[S_EM].bound = false;
+        c->tex[S_EM].own.clear();
+        c->tex[S_EM].p = nullptr;
+      }
+      c->arr[S_AB] = false;
+      c->idxEm = S_AB;
+      updEm = true;
+    }
+  }
+  if (reqRe) { /* :830-863 */
+    if (!updRe) {
+      syncVolume(c, S_RE, Re, reqRe);
+      updRe = true;
+    }
+    if (simAbRe && !updAb) {
+      referenceTexture(c, S_AB, &c->idxAb, S_RE);
+      updAb = true;
+    }
+    if (simEmAb && !updEm) {
+      referenceTexture(c, S_EM, &c->idxEm, S_RE);
+      updEm = true;
+    }
+  }
+}
+
+/* MManager::resetGradients (mm.hxx:206-213).  The device arrays are only "freed" when one of
+ * the pointers is already null (inverted test) - i.e. never for live ones - and the textures
+ * stay bound; only the host descriptors are cleared. */
+void resetGradients(orc_ctx *c) {
+  c->host[S_DX] = HostVol();
+  c->host[S_DY] = HostVol();
+  c->host[S_DZ] = HostVol();
+}
+
+/* MManager::sync (mm.hxx:178-201) */
+void mm_sync(orc_ctx *c) {
+  if ((c->host[S_DX].last_update == 0 && c->arr[S_DX]) || (c->host[S_DY].last_update == 0 && c->arr[S_DY]) ||
+      (c->host[S_DZ].last_update == 0 && c->arr[S_DZ]))
+    resetGradients(c);
+  syncWithDevice(c);
+  if (c->host[S_DX].last_update != 0 && c->host[S_DY].last_update != 0 && c->host[S_DZ].last_update != 0) {
+    /* setGradientTextures (kernel.cu:703-722) */
+    syncVolume(c, S_DX, c->host[S_DX], true);
+    syncVolume(c, S_DY, c->host[S_DY], true);
+    syncVolume(c, S_DZ, c->host[S_DZ], true);
+    c->gradientMethod = 1;
+  }
+}
+
+struct Frame {
+  Options o;
+  f3 color;
+  f3 gradientStep;
+  const Tex *texEm, *texAb, *texRe; /* getTexture(d_idx*) (kernel.cu:127-144) */
+  const Tex *texEmissionDirect;     /* tex_emission as computeGradient uses it (kernel.cu:225-248) */
+  const Tex *texDx, *texDy, *texDz, *texLight;
+  const Light *lights;
+  size_t numLights;
+  int gradientMethod;
+  int frac_bits;
+  int fast_exp;
+};
+
+/* intersectBox (kernel.cu:155-199) */
+inline bool intersectBox(f3 origin, f3 direction, f3 boxmin, f3 boxmax, float *tnear, float *tfar) {
+  int sign[3];
+  f3 parameters[2] = {boxmin, boxmax};
+  f3 inv = mk(1.f / direction.x, 1.f / direction.y, 1.f / direction.z);
+  sign[0] = (inv.x < 0);
+  sign[1] = (inv.y < 0);
+  sign[2] = (inv.z < 0);
+  float tmin, tmax, tymin, tymax, tzmin, tzmax;
+  tmin = (parameters[sign[0]].x - origin.x) * inv.x;
+  tmax = (parameters[1 - sign[0]].x - origin.x) * inv.x;
+  tymin = (parameters[sign[1]].y - origin.y) * inv.y;
+  tymax = (parameters[1 - sign[1]].y - origin.y) * inv.y;
+  if ((tmin > tymax) || (tymin > tmax)) return false;
+  if (tymin > tmin) tmin = tymin;
+  if (tymax < tmax) tmax = tymax;
+  tzmin = (parameters[sign[2]].z - origin.z) * inv.z;
+  tzmax = (parameters[1 - sign[2]].z - origin.z) * inv.z;
+  if ((tmin > tzmax) || (tzmin > tmax)) return false;
+  if (tzmin > tmin) tmin = tzmin;
+  if (tzmax < tmax) tmax = tzmax;
+  *tnear = tmin;
+  *tfar = tmax;
+  return true;
+}
+
+/* computeGradient (kernel.cu:212-253): central differences on tex_emission itself */
+inline f3 computeGradient(const Frame &F, f3 pos, f3 step, f3 boxmin, f3 boxScale) {
+  f3 g, s1, s2;
+  s1 = (pos + mk(step.x, 0, 0) - boxmin) * boxScale;
+  s2 = (pos - mk(step.x, 0, 0) - boxmin) * boxScale;
+  g.x = tex3d(*F.texEmissionDirect, s1.x, s1.y, s1.z, F.frac_bits) - tex3d(*F.texEmissionDirect, s2.x, s2.y, s2.z, F.frac_bits);
+  s1 = (pos + mk(0, step.y, 0) - boxmin) * boxScale;
+  s2 = (pos - mk(0, step.y, 0) - boxmin) * boxScale;
+  g.y = tex3d(*F.texEmissionDirect, s1.x, s1.y, s1.z, F.frac_bits) - tex3d(*F.texEmissionDirect, s2.x, s2.y, s2.z, F.frac_bits);
+  s1 = (pos + mk(0, 0, step.z) - boxmin) * boxScale;
+  s2 = (pos - mk(0, 0, step.z) - boxmin) * boxScale;
+  g.z = tex3d(*F.texEmissionDirect, s1.x, s1.y, s1.z, F.frac_bits) - tex3d(*F.texEmissionDirect, s2.x, s2.y, s2.z, F.frac_bits);
+  return g * mk(0.5f, 0.5f, 0.5f);
+}
+/* lookupGradient (kernel.cu:266-276) */
+inline f3 lookupGradient(const Frame &F, f3 ps) {
+  return mk(tex3d(*F.texDx, ps.x, ps.y, ps.z, F.frac_bits), tex3d(*F.texDy, ps.x, ps.y, ps.z, F.frac_bits),
+            tex3d(*F.texDz, ps.x, ps.y, ps.z, F.frac_bits));
+}
+/* angle (kernel.cu:284-287) */
+inline float angle(f3 a, f3 b) { return acosf(dot(a, b) / (length(a) * length(b))); }
+
+/* shade (kernel.cu:308-353) */
+inline f3 shade(const Frame &F, f3 ps, f3 pos, f3 viewPos, f3 boxmin, f3 boxScale) {
+  f3 grad = F.gradientMethod == 0 ? computeGradient(F, pos, F.gradientStep, boxmin, boxScale) : lookupGradient(F, ps);
+  const f3 N = -1.f * normalize(grad);
+  f3 result = mk(0.f, 0.f, 0.f);
+  for (size_t i = 0; i < F.numLights; ++i) {
+    const Light &L = F.lights[i];
+    f3 lightOut = L.position - pos;
+    f3 lightIn = viewPos - pos;
+    float alpha = angle(N, lightIn) / PI_F;
+    float beta = angle(N, lightOut) / PI_F;
+    f3 lightOutProj = lightOut - (dot(lightOut, N) * N);
+    f3 lightInProj = lightIn - (dot(lightIn, N) * N);
+    float gamma = angle(lightInProj, lightOutProj) / PI_F;
+    float reflection = F.o.factor_reflection * tex3d(*F.texRe, ps.x, ps.y, ps.z, F.frac_bits);
+    float light = tex3d(*F.texLight, alpha, beta, gamma, F.frac_bits);
+    result = result + reflection * light * L.color * F.color;
+  }
+  return result;
+}
+
+/* d_render for one pixel (kernel.cu:365-507).  Returns the number of loop iterations, or -1
+ * when the ray misses the box (pixel not written). */
+inline int64_t render_pixel(const Frame &F, uint32_t x, uint32_t y, float rgb[3]) {
+  const Options &o = F.o;
+  const float tstep = o.tstep;
+  const f3 boxMin = o.boxmin, boxMax = o.boxmax;
+  float u = (x / (float)o.image_width) * 2.0f - 1.0f; /* :388-390 */
+  float ratio = o.image_height / (float)o.image_width;
+  float v = (y / (float)o.image_height) * 2.0f * ratio - 1.0f * ratio;
+  const f3 d = boxMax - boxMin;
+  const f3 boxScale = mk(1.f / d.x, 1.f / d.y, 1.f / d.z); /* :396 */
+  const float cameraXOffset = o.m[3].x, focalLength = o.m[3].y, objectDistance = o.m[3].z;
+  const f3 xVector = o.m[0], yVector = o.m[1], zVector = o.m[2];
+  const f3 vCameraOffset = cameraXOffset * xVector;
+  const f3 origin = vCameraOffset + (-1.f * objectDistance * zVector);                           /* :410 */
+  const f3 direction = normalize(u * normalize(xVector) + v * yVector + focalLength * zVector); /* :412-413 */
+  float tnear = 0, tfar = 0;
+  if (!intersectBox(origin, direction, boxMin, boxMax, &tnear, &tfar)) return -1;
+  if (tnear < 0.0f) tnear = 0.0f;
+  float sx = 0, sy = 0, sz = 0, sw = 0; /* float4 sum */
+  float t = tnear;
+  f3 pos = origin + direction * tnear;
+  f3 step = direction * tstep;
+  int64_t n = 0;
+  while (true) {
+    ++n;
+    f3 ps = (pos - boxMin) * boxScale;                                               /* :437 */
+    float emission = o.factor_emission * tex3d(*F.texEm, ps.x, ps.y, ps.z, F.frac_bits); /* :444-447 */
+    float absorption = o.factor_absorption * tex3d(*F.texAb, ps.x, ps.y, ps.z, F.frac_bits);
+    /* :455-456  __expf(x) = ex2.approx(x*log2e); exp2f keeps that decomposition */
+    float alpha = F.fast_exp ? 1 - exp2f((-absorption * tstep) * 1.4426950408889634f) : 1 - expf(-absorption * tstep);
+    f3 colored = mk(emission, emission, emission) * tstep * F.color;              /* :459-460 */
+    f3 illumination = shade(F, ps, pos, origin, boxMin, boxScale);               /* :462-464 */
+    f3 illuminated = colored + illumination;
+    float shx = illuminated.x * alpha, shy = illuminated.y * alpha, shz = illuminated.z * alpha; /* :477-479 */
+    float k = 1 - sw; /* :482  sum = (1 - sum.w) * shaded + sum */
+    sx = k * shx + sx;
+    sy = k * shy + sy;
+    sz = k * shz + sz;
+    sw = k * alpha + sw;
+    if (sw > o.opacity_threshold) break; /* :485 */
+    t += tstep;                          /* :488-492 */
+    if (t > tfar) break;
+    pos = pos + step;
+  }
+  rgb[0] = sx;
+  rgb[1] = sy;
+  rgb[2] = sz;
+  return n;
+}
+
+} // namespace
+
+extern "C" {
+
+orc_ctx *orc_create(void) { return new orc_ctx(); }
+void orc_destroy(orc_ctx *c) { delete c; }
+
+int orc_set_option(orc_ctx *c, int option, int64_t value) {
+  switch (option) {
+  case ORC_OPT_FILTER_FRAC_BITS: c->frac_bits = (int)value; return 0;
+  case ORC_OPT_ABSORPTION_ROLE_FIX: c->absorption_role_fix = (int)value; return 0;
+  case ORC_OPT_BORROW_HOST_DATA: c->borrow = (int)value; return 0;
+  case ORC_OPT_THREADS: c->threads = (int)value; return 0;
+  case ORC_OPT_FAST_EXP: c->fast_exp = (int)value; return 0;
+  }
+  c->err = "unknown option";
+  return 1;
+}
+
+/* 'sync_volumes' (render.cpp:93-129) */
+int orc_sync_volumes(orc_ctx *c, uint64_t T, const vr_volume *em, const vr_volume *re, const vr_volume *ab,
+                     const vr_volume *gx, const vr_volume *gy, const vr_volume *gz) {
+  if (!em || !re || !ab) {
+    c->err = "sync_volumes: emission, reflection and absorption are required";
+    return 1;
+  }
+  c->timeLastMemSync = T;       /* :94 */
+  c->host[S_EM] = make_volume(em); /* :96-98 */
+  c->host[S_RE] = make_volume(re);
+  c->host[S_AB] = make_volume(ab);
+  int tmp = 0; /* gradientCompute */
+  if (gx && gy && gz) { /* nrhs == 9, :105-110 */
+    c->host[S_DX] = make_volume(gx);
+    c->host[S_DY] = make_volume(gy);
+    c->host[S_DZ] = make_volume(gz);
+    tmp = 1;
+  } else { /* nrhs == 6, :111-113 */
+    resetGradients(c);
+  }
+  c->gradientMethod = tmp; /* setGradientMethod, :121 */
+  mm_sync(c);              /* :122 */
+  return 0;
+}
+
+int orc_render(orc_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+               const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
+               const float props[3], float thr, const float color[3], const uint64_t *window, float *out) {
+  if (lights && illumination) { /* render.cpp:145-191 */
+    c->host[S_LIGHT] = make_volume(illumination);
+    c->lights.resize(n_lights);
+    for (size_t l = 0; l < n_lights; ++l) {
+      /* make_float3Inv on Position (render.cpp:167), plain make_float3 on Color */
+      c->lights[l].position = mk(lights[l].position[2], lights[l].position[1], lights[l].position[0]);
+      c->lights[l].color = mk(lights[l].color[0], lights[l].color[1], lights[l].color[2]);
+    }
+    /* setIlluminationTexture -> syncVolume: always re-uploads (kernel.cu:682-689) */
+    syncVolume(c, S_LIGHT, c->host[S_LIGHT], true);
+  }
+  const HostVol &E = c->host[S_EM];
+  if (E.w == 0 || E.h == 0 || E.d == 0) {
+    c->err = "render: no emission volume synced";
+    return 1;
+  }
+  Frame F;
+  Options &o = F.o;
+  const uint64_t H = res[0], W = res[1]; /* render.cpp:196,243 */
+  o.image_width = W;
+  o.image_height = H;
+  o.factor_emission = factors[0]; /* render.cpp:243-244 with initRender's (Em, Re, Ab) order, vr.cpp:112-117 */
+  o.factor_reflection = factors[1];
+  o.factor_absorption = factors[2];
+  f3 esz = mk(es[2], es[1], es[0]); /* make_float3Inv, render.cpp:195 */
+  init_box_tstep(E.w, E.h, E.d, esz, &o.boxmin, &o.boxmax, &o.tstep);
+  o.m[0] = mk(R[2], R[1], R[0]); /* render.cpp:211-219 */
+  o.m[1] = mk(R[5], R[4], R[3]);
+  o.m[2] = mk(R[8], R[7], R[6]);
+  o.m[3] = mk(props[0], props[1], props[2]);
+  o.opacity_threshold = thr;
+  F.color = mk(color[0], color[1], color[2]);
+  F.gradientStep = mk(1.f / E.w, 1.f / E.h, 1.f / E.d); /* vr.cpp:273-275 */
+  F.texEm = &c->tex[c->idxEm];
+  F.texAb = &c->tex[c->absorption_role_fix ? (c->tex[S_AB].bound ? S_AB : c->idxAb) : c->idxAb];
+  F.texRe = &c->tex[c->idxRe];
+  F.texEmissionDirect = &c->tex[S_EM];
+  F.texDx = &c->tex[S_DX];
+  F.texDy = &c->tex[S_DY];
+  F.texDz = &c->tex[S_DZ];
+  F.texLight = &c->tex[S_LIGHT];
+  F.lights = c->lights.data();
+  F.numLights = c->lights.size();
+  F.gradientMethod = c->gradientMethod;
+  F.frac_bits = c->frac_bits;
+  F.fast_exp = c->fast_exp;
+
+  const size_t size = (size_t)W * H;
+  memset(out, 0, size * 3 * sizeof(float)); /* cudaMemset, vr.cpp:271 */
+  uint64_t x0 = 0, x1 = W, y0 = 0, y1 = H;
+  if (window) {
+    x0 = window[0];
+    x1 = window[1] < W ? window[1] : W;
+    y0 = window[2];
+    y1 = window[3] < H ? window[3] : H;
+  }
+  int nthreads = 1;
+#ifdef _OPENMP
+  nthreads = c->threads > 0 ? c->threads : omp_get_max_threads();
+#endif
+  uint64_t samples = 0, hits = 0;
+  auto t0 = std::chrono::steady_clock::now();
+  /* 16x16 pixel tiles like the reference's launch (render.cpp:236-238), dynamic schedule */
+  const int64_t tx0 = x0 / 16, tx1 = (x1 + 15) / 16, ty0 = y0 / 16, ty1 = (y1 + 15) / 16;
+  const int64_t ntx = tx1 - tx0, nty = ty1 - ty0;
+#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads) reduction(+ : samples, hits)
+  for (int64_t tile = 0; tile < ntx * nty; ++tile) {
+    const uint64_t bx = (tx0 + tile % ntx) * 16, by = (ty0 + tile / ntx) * 16;
+    for (uint64_t y = by; y < by + 16; ++y)
+      for (uint64_t x = bx; x < bx + 16; ++x) {
+        if (x < x0 || x >= x1 || y < y0 || y >= y1) continue;
+        float rgb[3];
+        int64_t n = render_pixel(F, (uint32_t)x, (uint32_t)y, rgb);
+        if (n < 0) continue;
+        samples += (uint64_t)n;
+        hits += 1;
+        size_t k = (size_t)x * H + y; /* kernel.cu:501 */
+        out[k] = rgb[0];
+        out[k + size] = rgb[1];
+        out[k + size * 2] = rgb[2];
+      }
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  c->stats.samples_marched = samples;
+  c->stats.rays_hit = hits;
+  c->stats.seconds = std::chrono::duration<double>(t1 - t0).count();
+  c->stats.threads = nthreads;
+  return 0;
+}
+
+void orc_get_state(const orc_ctx *c, orc_state *s) {
+  s->idx_emission = c->idxEm;
+  s->idx_absorption = c->idxAb;
+  s->idx_reflection = c->idxRe;
+  s->gradient_method = c->gradientMethod;
+  for (int i = 0; i < S_N; ++i) {
+    s->bound[i] = c->tex[i].bound ? 1 : 0;
+    s->uploads[i] = c->uploads[i];
+  }
+  s->num_lights = c->lights.size();
+}
+void orc_get_stats(const orc_ctx *c, orc_stats *s) { *s = c->stats; }
+
+void orc_init_render(const uint64_t dims[3], const float es_xyz[3], float boxmin[3], float boxmax[3], float *tstep) {
+  f3 mn, mx;
+  init_box_tstep(dims[0], dims[1], dims[2], mk(es_xyz[0], es_xyz[1], es_xyz[2]), &mn, &mx, tstep);
+  boxmin[0] = mn.x, boxmin[1] = mn.y, boxmin[2] = mn.z;
+  boxmax[0] = mx.x, boxmax[1] = mx.y, boxmax[2] = mx.z;
+}
+
+/* HenyeyGreenstein(n, g) (hg.cc:47-91, float3.h:74-104) */
+void orc_henyey_greenstein(uint32_t n, float aG, float *out) {
+  const float PI = ((float)3.141592653589793238462643383279502884197169399375105820); /* hg.cc:18 */
+  float frac_half = PI / n;
+  int pageSize = n * n;
+  for (int c = 0; c < (int)n; ++c) {
+    float gamma = c * frac_half;
+    for (int a = 0; a < (int)n; ++a) {
+      float alpha = a * frac_half;
+      f3 lightOut = mk(sinf(alpha), 0, cosf(alpha));
+      for (int b = 0; b < (int)n; ++b) {
+        float beta = b * frac_half;
+        f3 lightIn = mk(sinf(beta), 0, cosf(beta));
+        /* rotateAroundX(gamma) * lightOut (float3.h:74-104) */
+        float s = sinf(gamma), co = cosf(gamma);
+        f3 r;
+        r.x = 1 * lightOut.x + 0 * lightOut.y + 0 * lightOut.z;
+        r.y = 0 * lightOut.x + co * lightOut.y + s * lightOut.z;
+        r.z = 0 * lightOut.x + -s * lightOut.y + co * lightOut.z;
+        float cosTheta = dot(r, lightIn);
+        float numerator = (1.f - powf(aG, 2.f));
+        float denominator = sqrtf(powf((1.f + powf(aG, 2.f) - (2.f * aG * cosTheta)), 3.f));
+        int k = c * pageSize + a * n + b;
+        out[k] = 1.f / (4.f * PI) * (numerator / denominator);
+      }
+    }
+  }
+}
+
+float orc_tex3d(const float *data, uint64_t w, uint64_t h, uint64_t d, float x, float y, float z, int frac_bits) {
+  return tex3d_raw(data, w, h, d, x, y, z, frac_bits);
+}
+
+const char *orc_last_error(const orc_ctx *c) { return c ? c->err.c_str() : ""; }
+
+} // extern "C"
