@@ -1,0 +1,522 @@
+#!/usr/bin/env python
+"""bench.py - the headline benchmark of BASELINE.json: Gsamples/s and frames/s of the ray march.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's render math on host cores
+
+Workload (BASELINE.json configs[1], "example1_grad-shaped"): synthetic ViBE-Z-shaped 1024^3 fp32
+emission volume E, reflection R = E^2, a distinct half-resolution absorption volume A (resident;
+as written the reference samples absorption from E), precomputed gradient volumes
+Gx,Gy,Gz = MATLAB gradient(E), 2 Henyey-Greenstein lights, 2048x2048 mono image, camera of
+examples/example1_grad.m.  One step = one frame; the camera turns 1 degree per step
+(example2-style) so no frame is a replay of the previous one.
+
+N > 1: image-space mode - every rank holds all volumes, 64x64 tiles are dealt round-robin to the
+ranks, partial images are SUM-reduced to rank 0 over NCCL inside the timed region (strong
+scaling of one frame).
+"""
+import argparse
+import ctypes as C
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED = 0x5EED01BE
+B_GATHER_LOOKUP_L2 = 256  # gradient volumes, (6 + L) * 32 B per sample at L = 2
+B_GATHER_COMPUTE_L1 = 320  # on-the-fly gradient, (9 + L) * 32 B per sample at L = 1
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--size", type=int, default=1024, help="volume edge (default 1024 = the metric's config)")
+    p.add_argument("--image", type=int, default=2048, help="image edge (default 2048)")
+    p.add_argument("--gradient", default="lookup", choices=["lookup", "compute"])
+    p.add_argument("--lights", type=int, default=2)
+    p.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    p.add_argument("--variant", type=int, default=0)
+    p.add_argument("--skip", type=int, default=1)
+    p.add_argument("--tile", type=int, default=64)
+    return p.parse_args()
+
+
+# ---- the scene (examples/example1_grad.m:36-51,79-82 on synthetic data) ---------------------------
+def rotation(alpha, beta, gamma, R=None):
+    """VolumeRender.rotate (VolumeRender.m:239-262)"""
+    c, s = lambda a: math.cos(math.radians(a)), lambda a: math.sin(math.radians(a))
+    Rx = np.array([[1, 0, 0], [0, c(alpha), -s(alpha)], [0, s(alpha), c(alpha)]])
+    Ry = np.array([[c(beta), 0, s(beta)], [0, 1, 0], [-s(beta), 0, c(beta)]])
+    Rz = np.array([[c(gamma), -s(gamma), 0], [s(gamma), c(gamma), 0], [0, 0, 1]])
+    R = np.eye(3) if R is None else R
+    return R @ Rx @ Ry @ Rz
+
+
+class Scene:
+    def __init__(self, args):
+        self.W = self.H = args.image
+        self.factors = np.array([0.1, 0.1, 0.4], dtype=np.float32)  # [fEm, fRe, fAb] second pass of example1_grad.m:79-82
+        self.es = np.array([1, 1, 1], dtype=np.float32)
+        self.res = np.array([self.H, self.W], dtype=np.uint64)
+        self.props = np.array([0.0, 3.0, 6.0], dtype=np.float32)  # CameraXOffset, FocalLength, DistanceToObject
+        self.thr = 0.9
+        self.color = np.array([1, 1, 1], dtype=np.float32)
+        self.R0 = rotation(125, 25, 0)
+        lights = [([500, 1000, 550], [0, 1, 1]), ([550, 1000, 500], [1, 0, 1])][: args.lights]
+        self.lights = lights
+
+    def rot(self, step):
+        R = rotation(0, float(step), 0, self.R0)
+        return np.asfortranarray(np.flipud(R).astype(np.float32))  # flip(RotationMatrix), VolumeRender.m:560
+
+
+def f32p(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+# ---- clocks during the timed region ----------------------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            if ts < t0 or ts > t1 + 0.2:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0])), mx.append(float(f[1])), power.append(float(f[2]))
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- oracle (CPU) legs: cpu_baseline of the b200 arm, and the whole reference arm --------------------
+def oracle_lib():
+    import ctypes
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import vrt
+
+    return vrt, ctypes
+
+
+def mem_available_gib():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable"):
+                return int(line.split()[1]) / (1024.0 * 1024.0)
+    except Exception:
+        pass
+    return 0.0
+
+
+class CpuRender:
+    """The reference's per-ray render math (oracle/oracle.cpp, OpenMP over 16x16 tiles, all host
+    cores) on host copies of the workload's volumes."""
+
+    def __init__(self, scene, args, vols):
+        vrt, _ = oracle_lib()
+        self.vrt = vrt
+        self.scene = scene
+        from volume_renderer_b200 import _abi, api
+
+        self.abi, self.api = _abi, api
+        self.lib = vrt.oracle(fast=True)
+        self.h = C.c_void_p(self.lib.orc_create())
+        self.lib.orc_set_option(self.h, vrt.ORC_OPT_BORROW_HOST_DATA, 1)
+        self.keep = []
+        self.vols = vols
+        vs = {k: (_abi.volume_struct(v, 1, self.keep) if v is not None else None) for k, v in vols.items()}
+        ptr = lambda k: C.byref(vs[k]) if vs.get(k) is not None else None
+        rc = self.lib.orc_sync_volumes(self.h, 0, ptr("E"), ptr("R"), ptr("A"), ptr("Gx"), ptr("Gy"), ptr("Gz"))
+        assert rc == 0, self.lib.orc_last_error(self.h)
+        self.lut = vrt.oracle_lut(64)
+        self.lutv = _abi.volume_struct(self.lut, 1, self.keep)
+        self.lights = (_abi.VrLight * len(scene.lights))()
+        for i, (p, c) in enumerate(scene.lights):
+            self.lights[i].position[:] = p
+            self.lights[i].color[:] = c
+        self.out = np.zeros((scene.H, scene.W, 3), dtype=np.float32, order="F")
+
+    def render_window(self, step, half):
+        s = self.scene
+        cx, cy = s.W // 2, s.H // 2
+        win = (C.c_uint64 * 4)(max(cx - half, 0), min(cx + half, s.W), max(cy - half, 0), min(cy + half, s.H))
+        rot = s.rot(step)
+        n = len(s.lights)
+        rc = self.lib.orc_render(self.h, self.lights if n else None, n, C.byref(self.lutv) if n else None, f32p(s.factors), f32p(s.es),
+                                 s.res.ctypes.data_as(C.POINTER(C.c_uint64)), f32p(rot), f32p(s.props), C.c_float(s.thr), f32p(s.color),
+                                 win, self.out.ctypes.data)
+        assert rc == 0
+        st = self.vrt.OrcStats()
+        self.lib.orc_get_stats(self.h, C.byref(st))
+        return st.samples_marched, st.seconds, st.threads
+
+    def calibrated_half(self, target_s):
+        """Window half-size so that one window costs about target_s seconds."""
+        n, sec, _ = self.render_window(0, 16)
+        rate = n / max(sec, 1e-6)
+        per_px = n / (32.0 * 32.0)
+        px = max(rate * target_s / max(per_px, 1.0), 1024.0)
+        half = int(min(math.sqrt(px) / 2, self.scene.W // 2))
+        return max(16, half)
+
+
+def host_volumes_cpu(args):
+    """Generate the workload's volumes on the host with the oracle's bit-identical twins of the
+    device generators (no GPU involved): used by the reference arm."""
+    vrt, _ = oracle_lib()
+    lib = vrt.oracle(fast=False)
+    n = args.size
+    dims = (C.c_uint64 * 3)(n, n, n)
+    E = np.zeros((n, n, n), dtype=np.float32, order="F")
+    lib.orc_synth_volume.argtypes = [C.c_int, C.c_uint32, C.POINTER(C.c_uint64), C.c_void_p]
+    lib.orc_volume_gradient.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)] + [C.c_void_p] * 3
+    lib.orc_synth_volume(0, SEED, dims, E.ctypes.data)
+    A = np.asfortranarray(E[::2, ::2, ::2])  # distinct half-resolution absorption volume, normalised
+    A = np.asfortranarray((A - A.min()) / (A.max() - A.min()))
+    vols = {"E": E, "R": np.asfortranarray(E * E), "A": A}
+    if args.gradient == "lookup":
+        g = [np.zeros((n, n, n), dtype=np.float32, order="F") for _ in range(3)]
+        lib.orc_volume_gradient(E.ctypes.data, dims, g[0].ctypes.data, g[1].ctypes.data, g[2].ctypes.data)
+        vols.update({"Gx": g[0], "Gy": g[1], "Gz": g[2]})
+    return vols
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    scene = Scene(args)
+    need = (5 if args.gradient == "lookup" else 2) * 4.0 * args.size ** 3 / 2 ** 30
+    size_used = args.size
+    if mem_available_gib() < need * 1.5 + 4:
+        args.size = 512
+    vols = host_volumes_cpu(args)
+    cpu = CpuRender(scene, args, vols)
+    half = cpu.calibrated_half(10.0)
+    for w in range(args.warmup):
+        cpu.render_window(w, 16)
+    tot_n, tot_s, threads = 0, 0.0, 1
+    for k in range(args.steps):
+        n, sec, threads = cpu.render_window(k, half)
+        tot_n += n
+        tot_s += sec
+    value = tot_n / tot_s / 1e9
+    sample = "centred %dx%d pixel window of each %dx%d frame over the %d^3 volume, %d frames" % (2 * half, 2 * half, scene.W, scene.H, args.size, args.steps)
+    line = {
+        "impl": "reference", "metric": "Gsamples/s (%d^2 image, %d^3 vol)" % (args.image, size_used), "value": value, "unit": "Gsamples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, scene, size_used),
+        "cpu_baseline": {"value": value, "unit": "Gsamples/s", "cores": int(threads), "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Gsamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, scene, size=None):
+    size = size or args.size
+    return {
+        "workload": "example1_grad-shaped: %d^3 %s synthetic ViBE-Z-like E (+R=E^2, A, %s), %d HG light(s), %dx%d mono, F=3 D=6 thr=0.9, +1deg/step" % (
+            size, args.dtype, "Gx,Gy,Gz gradient lookup" if args.gradient == "lookup" else "on-the-fly gradient", len(scene.lights), scene.W, scene.H),
+        "volume": [size] * 3, "image": [scene.W, scene.H], "gradient": args.gradient, "lights": len(scene.lights),
+        "multi_gpu": "image-space tiles %dx%d round-robin, NCCL sum-reduce to rank 0" % (args.tile, args.tile),
+        "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames",
+    }
+
+
+# ---- the CUDA arm ---------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from volume_renderer_b200 import _abi, multigpu
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = _abi.lib()
+    ctx = C.c_void_p()
+    _abi.check(lib.vr_create_on_device(C.byref(ctx), local))
+    stream = torch.cuda.current_stream()
+    _abi.check(lib.vr_set_stream(ctx, C.c_void_p(stream.cuda_stream)), ctx)
+    _abi.check(lib.vr_set_option(ctx, _abi.OPT_KERNEL_VARIANT, args.variant), ctx)
+    _abi.check(lib.vr_set_option(ctx, _abi.OPT_EMPTY_SPACE_SKIP, args.skip), ctx)
+    multigpu.configure_partition(ctx, rank, world, args.tile, args.tile)
+    scene = Scene(args)
+    n = args.size
+    dt = _abi.DTYPE_F32 if args.dtype == "f32" else _abi.DTYPE_BF16
+    tdt = torch.float32 if dt == _abi.DTYPE_F32 else torch.bfloat16
+    dims = (C.c_uint64 * 3)(n, n, n)
+    dev = torch.device("cuda", local)
+
+    # synthetic volumes generated straight into HBM (torch only owns the memory)
+    E = torch.empty(n * n * n, dtype=tdt, device=dev)
+    _abi.check(lib.vr_synth_volume(ctx, 0, SEED, dims, dt, C.c_void_p(E.data_ptr())), ctx)
+    Rv = E * E
+    m = n // 2
+    A = E.view(n, n, n)[::2, ::2, ::2].contiguous().view(-1)  # distinct half-resolution absorption volume
+    A = (A - A.min()) / (A.max() - A.min())
+    keep = [E, Rv, A]
+
+    def vol(t, d, stamp):
+        v = _abi.VrVolume()
+        v.data = t.data_ptr()
+        v.dims[0], v.dims[1], v.dims[2] = d
+        v.last_update = stamp
+        v.dtype = dt
+        v.memspace = _abi.MEM_DEVICE
+        return v
+
+    vE, vR, vA = vol(E, (n, n, n), 1), vol(Rv, (n, n, n), 2), vol(A, (m, m, m), 3)
+    g = [None, None, None]
+    if args.gradient == "lookup":
+        G = [torch.empty(n * n * n, dtype=tdt, device=dev) for _ in range(3)]
+        _abi.check(lib.vr_volume_gradient(ctx, C.byref(vE), _abi.MEM_DEVICE, *[C.c_void_p(t.data_ptr()) for t in G]), ctx)
+        keep += G
+        g = [vol(G[i], (n, n, n), 4 + i) for i in range(3)]
+    t_up = time.perf_counter()
+    _abi.check(lib.vr_sync_volumes(ctx, 0, C.byref(vE), C.byref(vR), C.byref(vA), *[C.byref(x) if x is not None else None for x in g]), ctx)
+    torch.cuda.synchronize()
+    t_up = time.perf_counter() - t_up
+
+    # LUT: HenyeyGreenstein(64) generated on the GPU, then handed over as the MATLAB array it would be
+    lut = np.zeros(64 * 64 * 64, dtype=np.float32)
+    _abi.check(lib.vr_henyey_greenstein(64, 0.8, lut.ctypes.data))
+    lutv = _abi.VrVolume()
+    lutv.data = lut.ctypes.data
+    lutv.dims[0] = lutv.dims[1] = lutv.dims[2] = 64
+    lutv.last_update = 9
+    lutv.dtype = _abi.DTYPE_F32
+    lutv.memspace = _abi.MEM_HOST
+    nl = len(scene.lights)
+    lights = (_abi.VrLight * max(nl, 1))()
+    for i, (p, c) in enumerate(scene.lights):
+        lights[i].position[:] = p
+        lights[i].color[:] = c
+    d_img = torch.zeros(scene.W * scene.H * 3, dtype=torch.float32, device=dev)
+    h_img = torch.zeros(scene.W * scene.H * 3, dtype=torch.float32).pin_memory()
+    resp = scene.res.ctypes.data_as(C.POINTER(C.c_uint64))
+
+    def frame_device(step):
+        rot = scene.rot(step)
+        _abi.check(lib.vr_render_device(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
+                                        f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color), C.c_void_p(d_img.data_ptr()),
+                                        C.c_void_p(stream.cuda_stream)), ctx)
+        if world > 1:
+            multigpu.combine_partials(d_img, 0)
+
+    def stats():
+        s = _abi.VrStats()
+        _abi.check(lib.vr_get_stats(ctx, C.byref(s)), ctx)
+        return s
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident leg: `value` ----
+    for w in range(args.warmup):
+        frame_device(-1 - w)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    samples = shaded = 0
+    kernel_ms = []
+    launches = 0
+    t0 = time.time()
+    barrier()
+    ev[0].record(stream)
+    for k in range(args.steps):
+        frame_device(k)
+        ev[k + 1].record(stream)
+        s = stats()  # synchronises this rank's stream; per-frame counters
+        samples += s.samples_marched
+        shaded += s.samples_shaded
+        kernel_ms.append(s.kernel_ms)
+        launches += s.kernel_launches
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    ms = ev[0].elapsed_time(ev[args.steps])
+    tot = torch.tensor([ms, float(samples), float(shaded), float(launches), max(kernel_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = tot.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        ms = float(mx[0])
+        kmax = float(mx[4])
+    else:
+        kmax = max(kernel_ms)
+    samples_all, shaded_all, launches_all = float(tot[1]), float(tot[2]), int(tot[3])
+    value = samples_all / (ms * 1e-3) / 1e9
+
+    # ---- end-to-end leg through the public C ABI call with HOST buffers ----
+    # every step: 'sync_volumes' (nothing dirty -> nothing moves, the persistent-volume design of
+    # the reference, example2.m) + 'render' with host-side parameters and a device->host read of
+    # the frame.  N > 1: partials are reduced to rank 0 first, rank 0 reads the frame back.
+    out_host = np.zeros(scene.W * scene.H * 3, dtype=np.float32)
+    stamp_sync = 100
+
+    def frame_e2e(step):
+        _abi.check(lib.vr_sync_volumes(ctx, stamp_sync, C.byref(vE), C.byref(vR), C.byref(vA), *[C.byref(x) if x is not None else None for x in g]), ctx)
+        if world == 1:
+            rot = scene.rot(step)
+            _abi.check(lib.vr_render(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
+                                     f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color), out_host.ctypes.data), ctx)
+        else:
+            frame_device(step)
+            if rank == 0:
+                h_img.copy_(d_img, non_blocking=True)
+            torch.cuda.synchronize()
+
+    for w in range(max(1, args.warmup // 2)):
+        frame_e2e(-1 - w)
+    barrier()
+    e_samples = 0
+    te = time.perf_counter()
+    for k in range(args.steps):
+        frame_e2e(k)
+        e_samples += stats().samples_marched
+    barrier()
+    te = time.perf_counter() - te
+    e = torch.tensor([te, float(e_samples)], dtype=torch.float64, device=dev)
+    if world > 1:
+        emx = e.clone()
+        dist.all_reduce(emx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e, op=dist.ReduceOp.SUM)
+        te = float(emx[0])
+    e2e_value = float(e[1]) / te / 1e9
+    h2d = 9 * 4 + 3 * 4 * 4 + 8 * 2 + nl * 24 + 6 * 40  # rotation, factors/es/props/color, resolution, lights, volume descriptors
+    d2h = scene.W * scene.H * 3 * 4
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s"
+    bps = B_GATHER_LOOKUP_L2 if args.gradient == "lookup" else B_GATHER_COMPUTE_L1
+    if args.gradient == "lookup":
+        bps = (6 + len(scene.lights)) * 32
+    else:
+        bps = (9 + len(scene.lights)) * 32
+    kavg_ms = float(np.mean(kernel_ms))
+    per_launch_shaded = shaded / max(args.steps, 1)  # rank 0's launches
+    per_launch_marched = samples / max(args.steps, 1)
+    achieved = per_launch_shaded * bps / (kavg_ms * 1e-3) / 1e9
+    roofline = {
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "peak_source": peak_src,
+        "bytes_per_sample": bps, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
+        "achieved_if_every_marched_sample_gathered": per_launch_marched * bps / (kavg_ms * 1e-3) / 1e9,
+        "note": "algorithmic GATHER bytes (SURVEY 8(d)) of the samples that were actually shaded; the gather is served by L1/L2, so the HBM peak is a reference line, not a ceiling",
+    }
+    line = {
+        "metric": "Gsamples/s (%d^2 image, %d^3 vol)" % (args.image, args.size), "value": value, "unit": "Gsamples/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": workload_config(args, scene),
+        "frames_per_s": args.steps / (ms * 1e-3), "gsamples_shaded_per_s": shaded_all / (ms * 1e-3) / 1e9,
+        "samples_per_frame": samples_all / args.steps, "upload_s": t_up,
+        "e2e": {"value": e2e_value, "unit": "Gsamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "frames_per_s": args.steps / te,
+                "note": "vr_sync_volumes + vr_render through the C ABI with host parameter/output buffers; volumes persistent (uploaded once, %0.2f s)" % t_up},
+        "gpu_launches": launches_all, "clocks": clocks, "roofline": roofline,
+    }
+
+    # ---- cpu_baseline: the oracle on host copies of the same volumes, bounded sample ----
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m)
+        except Exception as ex:  # the bench line must still print
+            line["cpu_baseline"] = {"value": None, "unit": "Gsamples/s", "cores": 0, "kind": "port", "sample": "failed: %r" % (ex,)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m):
+    import torch
+
+    need = (5 if G is not None else 2) * 4.0 * n ** 3 / 2 ** 30
+    if mem_available_gib() < need * 1.3 + 8 or E.dtype != torch.float32:
+        # not enough host memory for copies of the full volumes: same scene on a 512^3 twin
+        a2 = argparse.Namespace(**vars(args))
+        a2.size = 512
+        vols = host_volumes_cpu(a2)
+        note = "512^3 twin of the volume (host memory too small for the %d^3 copies)" % n
+    else:
+        def host(t, d):  # the flat tensors are in MATLAB order (dims[0] fastest)
+            return t.cpu().numpy().reshape(d, order="F")
+
+        vols = {"E": host(E, (n, n, n)), "R": host(Rv, (n, n, n)), "A": host(A, (m, m, m))}
+        if G is not None:
+            vols.update({"Gx": host(G[0], (n, n, n)), "Gy": host(G[1], (n, n, n)), "Gz": host(G[2], (n, n, n))})
+        note = "the same %d^3 volumes copied back from the GPU" % n
+    cpu = CpuRender(scene, args, vols)
+    half = cpu.calibrated_half(args.cpu_seconds)
+    nsm, sec, threads = cpu.render_window(0, half)
+    return {"value": nsm / sec / 1e9, "unit": "Gsamples/s", "cores": int(threads), "kind": "port",
+            "sample": "frame 0, centred %dx%d pixel window of the %dx%d image, %s; %.1f s of CPU time, %d samples" % (2 * half, 2 * half, scene.W, scene.H, note, sec, nsm)}
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))

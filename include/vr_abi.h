@@ -181,6 +181,12 @@ VR_API vr_status vr_get_device(vr_ctx *ctx, int *device);
  * ellipsoid with value noise, 1 = sparse tubes.  The host twin lives in the test suite. */
 VR_API vr_status vr_synth_volume(vr_ctx *ctx, int kind, uint32_t seed, const uint64_t dims[3],
                                  int32_t dtype, void *d_out);
+/* Volume.grad (src/matlab/VolumeRender/Volume.m:181-205), i.e. MATLAB's [gx,gy,gz] = gradient(Data):
+ * unit spacing, central differences inside, one-sided at the ends; gx = derivative along dim 2,
+ * gy along dim 1, gz along dim 3.  `in` may be host or device memory; the three outputs (same
+ * dims and dtype as `in`) live in `out_memspace`.  SURVEY 8(f) row 3: saves 3 volume uploads. */
+VR_API vr_status vr_volume_gradient(vr_ctx *ctx, const vr_volume *in, int32_t out_memspace, void *gx, void *gy,
+                                    void *gz);
 /* Device memory helpers for callers without a CUDA runtime binding (C harness, ctypes). */
 VR_API vr_status vr_device_alloc(vr_ctx *ctx, size_t bytes, void **d_ptr);
 VR_API vr_status vr_device_free(vr_ctx *ctx, void *d_ptr);

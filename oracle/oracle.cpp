@@ -628,3 +628,105 @@ float orc_tex3d(const float *data, uint64_t w, uint64_t h, uint64_t d, float x, 
 const char *orc_last_error(const orc_ctx *c) { return c ? c->err.c_str() : ""; }
 
 } // extern "C"
+
+/* ---- synthetic volumes + MATLAB gradient: CPU twins of the product's device generators --------
+ * (volume_renderer_b200/csrc/resident_kernels.cu k_synth / k_gradient).  Same formulas, written
+ * for a strict-IEEE build (no contraction), so the results are bit-identical to the device's
+ * explicit round-to-nearest intrinsics.  They give the reference arm of bench.py and the tests
+ * the same input data without a GPU. */
+namespace {
+inline uint32_t hash_u32(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x7feb352du;
+  x ^= x >> 15;
+  x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
+}
+inline uint32_t hash3(uint32_t i, uint32_t j, uint32_t k, uint32_t seed) {
+  return hash_u32(i * 0x9e3779b1u ^ hash_u32(j * 0x85ebca77u ^ hash_u32(k * 0xc2b2ae3du ^ seed)));
+}
+inline float u01(uint32_t h) { return (float)(h >> 8) * (1.0f / 16777216.0f); }
+inline float smooth(float f) { return (f * f) * (3.0f - 2.0f * f); }
+inline float value_noise(float px, float py, float pz, uint32_t seed) {
+  const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+  const uint32_t i = (uint32_t)(int)fx, j = (uint32_t)(int)fy, k = (uint32_t)(int)fz;
+  const float wx = smooth(px - fx), wy = smooth(py - fy), wz = smooth(pz - fz);
+  const float c000 = u01(hash3(i, j, k, seed)), c100 = u01(hash3(i + 1, j, k, seed));
+  const float c010 = u01(hash3(i, j + 1, k, seed)), c110 = u01(hash3(i + 1, j + 1, k, seed));
+  const float c001 = u01(hash3(i, j, k + 1, seed)), c101 = u01(hash3(i + 1, j, k + 1, seed));
+  const float c011 = u01(hash3(i, j + 1, k + 1, seed)), c111 = u01(hash3(i + 1, j + 1, k + 1, seed));
+  const float c00 = lerp(c000, c100, wx), c10 = lerp(c010, c110, wx);
+  const float c01 = lerp(c001, c101, wx), c11 = lerp(c011, c111, wx);
+  return lerp(lerp(c00, c10, wy), lerp(c01, c11, wy), wz);
+}
+inline float ncoord(int i, int n) { return (((float)i + 0.5f) / (float)n) * 2.0f - 1.0f; }
+inline float synth_brain(int x, int y, int z, int w, int h, int d, uint32_t seed) {
+  const float u = ncoord(x, w), v = ncoord(y, h), s = ncoord(z, d);
+  const float a = u / 0.8f, b = v / 0.55f, c = s / 0.4f;
+  const float r2 = (a * a + b * b) + c * c;
+  if (!(r2 < 1.0f)) return 0.0f;
+  const float m = smooth(fminf((1.0f - r2) * 4.0f, 1.0f));
+  const float qx = (u + 1.0f) * 0.5f, qy = (v + 1.0f) * 0.5f, qz = (s + 1.0f) * 0.5f;
+  const float n0 = value_noise(qx * 8.0f, qy * 8.0f, qz * 8.0f, seed);
+  const float n1 = value_noise(qx * 16.0f, qy * 16.0f, qz * 16.0f, seed + 1u);
+  const float n2 = value_noise(qx * 32.0f, qy * 32.0f, qz * 32.0f, seed + 2u);
+  const float nz = (0.5f * n0 + 0.3f * n1) + 0.2f * n2;
+  const float val = m * (0.6f + 0.4f * nz);
+  return fminf(fmaxf(val, 0.0f), 1.0f);
+}
+inline float synth_tubes(int x, int y, int z, int w, int h, int d, uint32_t seed) {
+  const float px = ncoord(x, w), py = ncoord(y, h), pz = ncoord(z, d);
+  const float vox = 2.0f / (float)w;
+  float best = 0.0f;
+  for (uint32_t t = 0; t < 200; ++t) {
+    const uint32_t s = seed ^ (t * 0x632be5abu);
+    const float ax = u01(hash_u32(s + 1u)) * 1.6f - 0.8f, ay = u01(hash_u32(s + 2u)) * 1.6f - 0.8f, az = u01(hash_u32(s + 3u)) * 1.6f - 0.8f;
+    const float dx = u01(hash_u32(s + 4u)) * 0.8f - 0.4f, dy = u01(hash_u32(s + 5u)) * 0.8f - 0.4f, dz = u01(hash_u32(s + 6u)) * 0.8f - 0.4f;
+    const float rad = (3.0f + u01(hash_u32(s + 7u)) * 3.0f) * vox;
+    const float ex = px - ax, ey = py - ay, ez = pz - az;
+    const float dd = (dx * dx + dy * dy) + dz * dz;
+    const float ed = (ex * dx + ey * dy) + ez * dz;
+    const float tt = fminf(fmaxf(ed / fmaxf(dd, 1e-12f), 0.0f), 1.0f);
+    const float cx = ex - tt * dx, cy = ey - tt * dy, cz = ez - tt * dz;
+    const float dist = sqrtf((cx * cx + cy * cy) + cz * cz);
+    const float edge = 1.5f * vox;
+    const float vv = fminf(fmaxf((rad - dist) / edge, 0.0f), 1.0f);
+    best = fmaxf(best, vv);
+  }
+  return best;
+}
+/* MATLAB gradient() along one axis, unit spacing: central inside, one-sided at the ends, 0 for a
+ * singleton axis */
+inline float grad1(const float *p, int64_t i, int64_t n, int64_t stride) {
+  if (n < 2) return 0.0f;
+  if (i == 0) return p[stride] - p[0];
+  if (i == n - 1) return p[0] - p[-stride];
+  return (p[stride] - p[-stride]) / 2.0f;
+}
+} // namespace
+
+extern "C" {
+void orc_synth_volume(int kind, uint32_t seed, const uint64_t dims[3], float *out) {
+  const int w = (int)dims[0], h = (int)dims[1], d = (int)dims[2];
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int z = 0; z < d; ++z)
+    for (int y = 0; y < h; ++y)
+      for (int x = 0; x < w; ++x)
+        out[((size_t)z * h + y) * w + x] = kind == 0 ? synth_brain(x, y, z, w, h, d, seed) : synth_tubes(x, y, z, w, h, d, seed);
+}
+/* Volume.grad (Volume.m:181-205): [gx, gy, gz] = gradient(Data) - gx is the derivative along
+ * MATLAB dim 2, gy along dim 1, gz along dim 3. */
+void orc_volume_gradient(const float *in, const uint64_t dims[3], float *gx, float *gy, float *gz) {
+  const int64_t w = (int64_t)dims[0], h = (int64_t)dims[1], d = (int64_t)dims[2];
+#pragma omp parallel for schedule(static)
+  for (int64_t z = 0; z < d; ++z)
+    for (int64_t y = 0; y < h; ++y)
+      for (int64_t x = 0; x < w; ++x) {
+        const size_t k = ((size_t)z * h + y) * w + x;
+        gy[k] = grad1(in + k, x, w, 1);
+        gx[k] = grad1(in + k, y, h, w);
+        gz[k] = grad1(in + k, z, d, w * h);
+      }
+}
+} // extern "C"

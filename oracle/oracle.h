@@ -83,6 +83,10 @@ void orc_henyey_greenstein(uint32_t n, float g, float *out);
 float orc_tex3d(const float *data, uint64_t w, uint64_t h, uint64_t d, float x, float y, float z,
                 int frac_bits);
 
+/* CPU twins of vr_synth_volume / vr_volume_gradient (bit-identical; MATLAB layout) */
+void orc_synth_volume(int kind, uint32_t seed, const uint64_t dims[3], float *out);
+void orc_volume_gradient(const float *in, const uint64_t dims[3], float *gx, float *gy, float *gz);
+
 const char *orc_last_error(const orc_ctx *ctx);
 
 #ifdef __cplusplus

@@ -1,0 +1,154 @@
+/* host_emul.cpp - TEST INFRASTRUCTURE: runs the product's per-lane device code
+ * (volume_renderer_b200/csrc/raymarch_core.h, every function is __host__ __device__) on the CPU,
+ * lane-serially, over padded (bricked) storage built here with the same geometry rules as
+ * context.cu / resident_kernels.cu.  It lets the `-m "not gpu"` suite compare the very
+ * arithmetic the kernel executes with the oracle before any GPU time is spent.  It is not a
+ * product path: nothing under volume_renderer_b200/ builds or loads it.
+ */
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "../include/vr_abi.h"
+#include "../volume_renderer_b200/csrc/raymarch_core.h"
+#include "../volume_renderer_b200/csrc/render_setup.h"
+
+using namespace vrb;
+
+namespace {
+
+struct HostTex {
+  std::vector<float> store;
+  std::vector<uint32_t> occ;
+  TexDesc t{};
+  int ocx = 0, ocy = 0, ocz = 0;
+};
+
+template <int LAYOUT>
+void build(HostTex &T, const float *src, int w, int h, int d, bool with_occ) {
+  memset(&T.t, 0, sizeof T.t);
+  if (!src || w == 0) {
+    T.t.kind = TEX_UNBOUND;
+    return;
+  }
+  if (w == 1 && h == 1 && d == 1) {
+    T.t.kind = TEX_CONST;
+    T.t.cval = src[0];
+    T.t.w = T.t.h = T.t.d = 1;
+    return;
+  }
+  const uint64_t pw = w + 2, ph = h + 2, pd = d + 2;
+  uint64_t elems;
+  if (LAYOUT == LAYOUT_BRICK) {
+    const uint64_t nbx = (pw + 7) / 8, nby = (ph + 7) / 8, nbz = (pd + 7) / 8;
+    T.t.sy = (uint32_t)(nbx * 512), T.t.sz = (uint32_t)(nbx * nby * 512);
+    elems = nbx * nby * nbz * 512;
+  } else {
+    T.t.sy = (uint32_t)pw, T.t.sz = (uint32_t)(pw * ph);
+    elems = pw * ph * pd;
+  }
+  T.store.assign(elems, 0.0f);
+  typedef Addr<LAYOUT> A;
+  for (int Z = 0; Z < (int)pd; ++Z)
+    for (int Y = 0; Y < (int)ph; ++Y)
+      for (int X = 0; X < (int)pw; ++X) {
+        const int sx = X - 1 < 0 ? 0 : (X - 1 > w - 1 ? w - 1 : X - 1);
+        const int sy = Y - 1 < 0 ? 0 : (Y - 1 > h - 1 ? h - 1 : Y - 1);
+        const int sz = Z - 1 < 0 ? 0 : (Z - 1 > d - 1 ? d - 1 : Z - 1);
+        T.store[A::x(X) + A::y(Y, T.t.sy) + A::z(Z, T.t.sz)] = src[((size_t)sz * h + sy) * w + sx];
+      }
+  T.t.p = T.store.data();
+  T.t.w = w, T.t.h = h, T.t.d = d;
+  T.t.fw = (float)w, T.t.fh = (float)h, T.t.fd = (float)d;
+  T.t.kind = TEX_VOLUME;
+  if (with_occ) {
+    const int dil = 2;
+    T.ocx = (w + 7) / 8, T.ocy = (h + 7) / 8, T.ocz = (d + 7) / 8;
+    T.occ.assign(((size_t)T.ocx * T.ocy * T.ocz + 31) / 32, 0u);
+    for (int cz = 0; cz < T.ocz; ++cz)
+      for (int cy = 0; cy < T.ocy; ++cy)
+        for (int cx = 0; cx < T.ocx; ++cx) {
+          bool any = false;
+          for (int z = cz * 8 - dil; z <= cz * 8 + 7 + dil && !any; ++z)
+            for (int y = cy * 8 - dil; y <= cy * 8 + 7 + dil && !any; ++y)
+              for (int x = cx * 8 - dil; x <= cx * 8 + 7 + dil && !any; ++x) {
+                const int sx = x < 0 ? 0 : (x > w - 1 ? w - 1 : x), sy = y < 0 ? 0 : (y > h - 1 ? h - 1 : y),
+                          sz = z < 0 ? 0 : (z > d - 1 ? d - 1 : z);
+                any = !(src[((size_t)sz * h + sy) * w + sx] == 0.0f);
+              }
+          const size_t cell = ((size_t)cz * T.ocy + cy) * T.ocx + cx;
+          if (any) T.occ[cell >> 5] |= 1u << (cell & 31);
+        }
+  }
+}
+
+template <int GRAD, int LAYOUT>
+void run(const KernelParams &P, float *out, uint64_t *stats) {
+  const size_t size = (size_t)P.W * P.H;
+  memset(out, 0, size * 3 * sizeof(float));
+  uint64_t marched = 0, shaded = 0, hits = 0;
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : marched, shaded, hits)
+  for (int64_t x = 0; x < P.W; ++x)
+    for (int y = 0; y < P.H; ++y) {
+      float rgb[3];
+      uint32_t m = 0, s = 0;
+      if (!march_pixel<GRAD, LAYOUT, ElemF32>(P, (uint32_t)x, (uint32_t)y, rgb, m, s)) continue;
+      const size_t k = (size_t)x * P.H + y;
+      out[k] = rgb[0], out[k + size] = rgb[1], out[k + 2 * size] = rgb[2];
+      marched += m, shaded += s, hits += 1;
+    }
+  if (stats) stats[0] = marched, stats[1] = shaded, stats[2] = hits;
+}
+
+template <int LAYOUT>
+int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr_volume *gy, const vr_volume *gz,
+         const vr_volume *lut, const vr_light *lights, size_t n_lights, const float factors[3], const float es[3],
+         const uint64_t res[2], const float R[9], const float props[3], float thr, const float color[3], int skip,
+         int frac_bits, float *out, uint64_t *stats) {
+  HostTex Em, Re, Gx, Gy, Gz, Lut;
+  auto ptr = [](const vr_volume *v) { return v ? static_cast<const float *>(v->data) : nullptr; };
+  auto dim = [](const vr_volume *v, int i) { return v ? (int)v->dims[i] : 0; };
+  build<LAYOUT>(Em, ptr(em), dim(em, 0), dim(em, 1), dim(em, 2), true);
+  build<LAYOUT>(Re, ptr(re), dim(re, 0), dim(re, 1), dim(re, 2), false);
+  build<LAYOUT>(Gx, ptr(gx), dim(gx, 0), dim(gx, 1), dim(gx, 2), false);
+  build<LAYOUT>(Gy, ptr(gy), dim(gy, 0), dim(gy, 1), dim(gy, 2), false);
+  build<LAYOUT>(Gz, ptr(gz), dim(gz, 0), dim(gz, 1), dim(gz, 2), false);
+  build<LAYOUT_LINEAR>(Lut, ptr(lut), dim(lut, 0), dim(lut, 1), dim(lut, 2), false);
+  KernelParams P;
+  memset(&P, 0, sizeof P);
+  setup_frame(P, factors, es, res[1], res[0], R, props, thr, color, em->dims[0], em->dims[1], em->dims[2]);
+  P.em = P.ab = P.em_direct = Em.t;  // Em = Ab aliased, the examples' case
+  P.ab_is_em = 1;
+  P.re = Re.t;
+  P.gx = Gx.t, P.gy = Gy.t, P.gz = Gz.t;
+  P.lut = Lut.t;
+  P.gradient_method = gx ? 1 : 0;
+  P.frac_bits = frac_bits;
+  P.skip = skip && Em.t.kind == TEX_VOLUME;
+  P.occ = Em.occ.data(), P.ocx = Em.ocx, P.ocy = Em.ocy, P.ocz = Em.ocz;
+  P.count = 1;
+  P.n_lights = lut ? (int)n_lights : 0;
+  if (P.n_lights > MAX_PARAM_LIGHTS) return 2;
+  for (int i = 0; i < P.n_lights; ++i) {
+    P.lights[i][0] = lights[i].position[2], P.lights[i][1] = lights[i].position[1], P.lights[i][2] = lights[i].position[0];
+    memcpy(P.lights[i] + 3, lights[i].color, 12);
+  }
+  if (P.gradient_method)
+    run<1, LAYOUT>(P, out, stats);
+  else
+    run<0, LAYOUT>(P, out, stats);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int emul_render(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr_volume *gy,
+                           const vr_volume *gz, const vr_volume *lut, const vr_light *lights, size_t n_lights,
+                           const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
+                           const float props[3], float thr, const float color[3], int layout, int skip, int frac_bits,
+                           float *out, uint64_t *stats) {
+  if (!em) return 1;
+  if (layout == LAYOUT_BRICK)
+    return emul<LAYOUT_BRICK>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, out, stats);
+  return emul<LAYOUT_LINEAR>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, out, stats);
+}

@@ -1,0 +1,235 @@
+"""GPU parity: the CUDA path through the C ABI (Python mirror of the MATLAB classes -> ctypes ->
+libvr_b200.so) against the oracle on the same seeded inputs.  Tolerance from BASELINE.json:
+max abs error <= 1e-3 on RGB normalised to [0,1] (vrt.TOL), PSNR reported."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import vrt
+from volume_renderer_b200 import _abi, api
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lut():
+    return api.HenyeyGreenstein(64)
+
+
+@pytest.fixture(scope="module")
+def brain64():
+    return vrt.synth_brain((64, 64, 64))
+
+
+def _pair(vol, res, lights, lut, **kw):
+    gpu = vrt.example1_scene(api.VolumeRender, vol, res, lights=lights, lut=lut, **kw)
+    orc = vrt.example1_scene(vrt.OracleVolumeRender, vol, res, lights=lights, lut=lut, **kw)
+    return gpu, orc
+
+
+def _check(gpu, orc, tol=vrt.TOL, same_samples=True):
+    img, ref = gpu.render(), orc.render()
+    m = vrt.compare(img, ref)
+    print(m)
+    assert np.isfinite(img).all()
+    assert m["max_abs_norm"] <= tol, m
+    if same_samples and isinstance(gpu, api.VolumeRender) and gpu.CameraXOffset == 0:
+        assert gpu.stats()["samples_marched"] == orc._backend.stats(orc.objectHandle).samples_marched
+    return img, ref
+
+
+def test_hg_lut_matches_reference_lut(lut):
+    ref = vrt.oracle_lut(64)
+    rel = np.abs(lut - ref) / np.abs(ref)
+    assert rel.max() < 2e-4, rel.max()  # device sinf/cosf vs glibc; the LUT is data for both sides
+    assert np.abs(lut - ref).max() / ref.max() < 1e-5
+
+
+@pytest.mark.parametrize("lights", [0, 1, 2])
+def test_example1_shape(brain64, lut, lights):
+    gpu, orc = _pair(brain64, (160, 128), lights, lut)
+    if lights == 0:
+        gpu.LightSources = False
+        orc.LightSources = False
+    _check(gpu, orc)
+
+
+@pytest.mark.parametrize("brick,skip", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_layout_and_skipping_are_invisible(brain64, lut, brick, skip):
+    gpu, orc = _pair(brain64, (128, 128), 1, lut)
+    gpu.setOption(_abi.OPT_BRICK_LAYOUT, brick)
+    gpu.setOption(_abi.OPT_EMPTY_SPACE_SKIP, skip)
+    img, _ = _check(gpu, orc)
+    base = vrt.example1_scene(api.VolumeRender, brain64, (128, 128), lights=1, lut=lut)
+    base.setOption(_abi.OPT_BRICK_LAYOUT, 0)
+    base.setOption(_abi.OPT_EMPTY_SPACE_SKIP, 0)
+    assert np.array_equal(img, base.render())  # bit-identical across layouts / skipping
+
+
+def test_anisotropic_volume_and_element_size(lut):
+    vol = vrt.synth_brain((80, 56, 40))
+    gpu, orc = _pair(vol, (128, 96), 1, lut)
+    for r in (gpu, orc):
+        r.ElementSizeUm = [1.0, 0.8, 2.5]
+    _check(gpu, orc)
+
+
+def test_gradient_volumes_lookup(brain64, lut):
+    gpu, orc = _pair(brain64, (128, 128), 2, lut)
+    for r in (gpu, orc):
+        gx, gy, gz = r.VolumeEmission.grad()
+        r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
+        r.FactorEmission, r.FactorAbsorption, r.FactorReflection = 0.1, 0.4, 0.1
+        r.Color = [1, 1, 1]
+    _check(gpu, orc)
+    # example1_grad.m:94-95: reset, render again with on-the-fly gradients
+    for r in (gpu, orc):
+        r.resetGradientVolumes()
+    _check(gpu, orc)
+
+
+def test_distinct_absorption_and_reflection_volumes(brain64, lut):
+    """example1.m:65-70 second pass: a distinct absorption volume is uploaded but, as written,
+    the kernel keeps sampling emission; with the role fix it samples absorption."""
+    for fix in (0, 1):
+        gpu, orc = _pair(brain64, (96, 96), 1, lut)
+        ab = np.asfortranarray(np.sqrt(brain64))
+        re = np.asfortranarray(brain64 * brain64)
+        for r in (gpu, orc):
+            r.VolumeAbsorption = api.Volume(ab)
+            r.VolumeReflection = api.Volume(re)
+        gpu.setOption(_abi.OPT_ABSORPTION_ROLE_FIX, fix)
+        orc._backend.lib.orc_set_option(orc.objectHandle, vrt.ORC_OPT_ABSORPTION_ROLE_FIX, fix)
+        _check(gpu, orc)
+
+
+def test_stereo_red_cyan_and_side_by_side(lut):
+    vol = vrt.synth_brain((48, 48, 48))
+    for mode in (api.StereoRenderMode.RedCyan, api.StereoRenderMode.LeftRightHorizontal):
+        gpu, orc = _pair(vol, (128, 96), 1, lut)
+        for r in (gpu, orc):
+            r.CameraXOffset = 0.06
+            r.FocalLength = 4.5
+            r.StereoOutput = mode
+        _check(gpu, orc)
+
+
+def test_filter_frac_bits_8(brain64, lut):
+    gpu, orc = _pair(brain64, (96, 96), 1, lut)
+    gpu.setOption(_abi.OPT_FILTER_FRAC_BITS, 8)
+    orc._backend.lib.orc_set_option(orc.objectHandle, vrt.ORC_OPT_FILTER_FRAC_BITS, 8)
+    _check(gpu, orc)
+
+
+def test_persistent_volumes_rotation_movie(brain64, lut):
+    """example2.m:53-66: volumes uploaded on the first frame only."""
+    gpu, orc = _pair(brain64, (96, 64), 1, lut)
+    uploads = []
+    for _ in range(3):
+        for r in (gpu, orc):
+            r.rotate(0, 30, 0)
+        _check(gpu, orc)
+        s = gpu.stats()
+        uploads.append(s["uploads"])
+    assert uploads[0] >= 1 and uploads[1:] == [0, 0], uploads  # later frames: nothing dirty, nothing moves
+
+
+def test_dirty_volume_is_reuploaded(brain64, lut):
+    """example3.m:145-161: writing into Data stamps the volume -> re-upload, new pixels."""
+    gpu, orc = _pair(brain64.copy(order="F"), (96, 96), 1, lut)
+    _check(gpu, orc)
+    for r in (gpu, orc):
+        d = r.VolumeEmission.Data
+        d[: d.shape[0] // 2, :, :] = d[: d.shape[0] // 2, :, :] * np.float32(0.2)
+    _check(gpu, orc)
+
+
+def test_upload_state_machine_matches_oracle(brain64, lut):
+    """Same sync sequences through both state machines (kernel.cu:739-867): role redirects and
+    which textures end up bound are observable through the rendered pixels."""
+    a = brain64
+    b = np.asfortranarray(np.sqrt(a))
+    c = np.asfortranarray(a * a)
+    seqs = [
+        ["EEE"], ["EEC", "EEC"], ["ABC", "ABC"], ["AAC", "ABC", "AAC"], ["ABB", "ABB"], ["ABA"],
+    ]
+    data = {"A": a, "B": b, "C": c, "E": a}
+    for seq in seqs:
+        gpu, orc = _pair(a, (64, 64), 1, lut)
+        for step in seq:
+            for r in (gpu, orc):
+                vols = {}
+                for ch in set(step):
+                    vols[ch] = api.Volume(data[ch])
+                r.VolumeEmission, r.VolumeAbsorption, r.VolumeReflection = vols[step[0]], vols[step[1]], vols[step[2]]
+            _check(gpu, orc)
+
+
+def test_edge_cases(lut):
+    # 2-D "volume", tiny volume, 1x1x1 constant everything, camera inside the box, odd image sizes
+    flat = np.asfortranarray(np.random.default_rng(1).random((40, 24), dtype=np.float32))
+    gpu, orc = _pair(flat, (70, 50), 1, lut)
+    _check(gpu, orc)
+    tiny = np.asfortranarray(np.random.default_rng(2).random((2, 3, 2), dtype=np.float32))
+    gpu, orc = _pair(tiny, (33, 17), 2, lut)
+    _check(gpu, orc)
+    gpu, orc = _pair(vrt.synth_brain((32, 32, 32)), (64, 64), 1, lut)
+    for r in (gpu, orc):
+        r.DistanceToObject = 0.5  # origin inside the box: tnear clamps to 0
+    _check(gpu, orc)
+
+
+def test_constant_volume_zero_gradient_nan_rule(lut):
+    """Constant emission -> zero gradient -> NaN normal -> NaN LUT coordinates, which the texture
+    unit (and both implementations) treat as 0."""
+    vol = np.full((16, 16, 16), 0.5, dtype=np.float32, order="F")
+    gpu, orc = _pair(vol, (64, 64), 1, lut)
+    _check(gpu, orc)
+
+
+def test_image_space_partition_is_bit_identical(brain64, lut):
+    full = vrt.example1_scene(api.VolumeRender, brain64, (192, 160), lights=1, lut=lut).render()
+    for nranks in (2, 4, 8):
+        acc = np.zeros_like(full)
+        samples = 0
+        for rank in range(nranks):
+            r = vrt.example1_scene(api.VolumeRender, brain64, (192, 160), lights=1, lut=lut)
+            r.setOption(_abi.OPT_TILE_W, 32)
+            r.setOption(_abi.OPT_TILE_H, 32)
+            r.setOption(_abi.OPT_PART_RANK, rank)
+            r.setOption(_abi.OPT_PART_NRANKS, nranks)
+            part = r.render()
+            assert not (np.logical_and(acc != 0, part != 0)).any()
+            acc += part
+            samples += r.stats()["samples_marched"]
+        assert np.array_equal(acc, full)
+
+
+def test_device_resident_input_and_synth_twin(lut):
+    """vr_synth_volume writes the volume straight into HBM; its numpy twin reproduces it bit for
+    bit, and a VR_MEM_DEVICE volume renders like the same data uploaded from the host."""
+    lib = _abi.lib()
+    r = api.VolumeRender()
+    dims = (C.c_uint64 * 3)(40, 48, 56)
+    for kind, twin in ((0, vrt.synth_brain), (1, vrt.synth_tubes)):
+        ptr = C.c_void_p()
+        _abi.check(lib.vr_device_alloc(r.objectHandle, 40 * 48 * 56 * 4, C.byref(ptr)), r.objectHandle)
+        _abi.check(lib.vr_synth_volume(r.objectHandle, kind, vrt.SEED, dims, _abi.DTYPE_F32, ptr), r.objectHandle)
+        host = np.zeros((40, 48, 56), dtype=np.float32, order="F")
+        _abi.check(lib.vr_device_download(r.objectHandle, host.ctypes.data, ptr, host.nbytes), r.objectHandle)
+        ref = twin((40, 48, 56))
+        assert np.array_equal(host, ref), (kind, np.abs(host - ref).max())
+        _abi.check(lib.vr_device_free(r.objectHandle, ptr), r.objectHandle)
+
+
+def test_errors_are_returned_not_thrown_across_the_abi():
+    lib = _abi.lib()
+    assert lib.vr_destroy(C.c_void_p(0x1234)) == 2  # VR_ERR_INVALID_HANDLE
+    r = api.VolumeRender()
+    h = r.objectHandle
+    r.memClear()
+    assert lib.vr_destroy(h) == 2  # stale handle after memClear (VolumeRender.m:230-237)
+    object.__setattr__(r, "objectHandle", None)
+    with pytest.raises(ValueError):
+        api.HenyeyGreenstein(8, 1.5)

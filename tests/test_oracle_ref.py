@@ -1,0 +1,267 @@
+"""Pins of the oracle: bit-equality with the reference's own CPU sources compiled
+unmodified into oracle/_ref (HenyeyGreenstein.cc, volumeRender.cpp, timestamp.cpp), and analytic
+scenes with closed-form answers.  The reference ships no golden vectors or tests of its own."""
+import ctypes as C
+import math
+import os
+
+import numpy as np
+import pytest
+
+import vrt
+from volume_renderer_b200 import api
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    lib = vrt.ref_cpu()
+    if lib is None:
+        pytest.skip("oracle/_ref not built and /root/reference absent")
+    return lib
+
+
+@pytest.mark.parametrize("n,g", [(64, None), (64, 0.8), (16, -0.3), (8, 0.0), (5, 1.0)])
+def test_hg_lut_bit_equal_to_reference(ref, n, g):
+    mine = np.zeros(n ** 3, dtype=np.float32)
+    vrt.oracle().orc_henyey_greenstein(n, 0.8 if g is None else g, mine.ctypes.data)
+    theirs = np.zeros(n ** 3, dtype=np.float32)
+    err = C.create_string_buffer(256)
+    assert ref.ref_henyey_greenstein(n, 0 if g is None else 1, 0.0 if g is None else g, theirs.ctypes.data, err, 256) == 0, err.value
+    assert np.array_equal(mine.view(np.uint32), theirs.view(np.uint32))
+
+
+def test_hg_reference_rejects_bad_g(ref):
+    out = np.zeros(8, dtype=np.float32)
+    err = C.create_string_buffer(256)
+    assert ref.ref_henyey_greenstein(2, 1, 1.5, out.ctypes.data, err, 256) == 1
+    assert b"[-1,1]" in err.value
+
+
+def test_hg_lut_golden_fixture():
+    """tests/golden/hg_lut_64_g0.8.npy was produced by the reference's own HenyeyGreenstein.cc
+    (tests/golden/make_golden.py); it travels to the GPU box where /root/reference does not exist."""
+    gold = np.load(os.path.join(GOLDEN, "hg_lut_64_g0.8.npy"))
+    mine = vrt.oracle_lut(64, 0.8)
+    assert np.array_equal(mine.view(np.uint32), gold.view(np.uint32))
+
+
+@pytest.mark.parametrize("dims,es", [((64, 64, 64), (1, 1, 1)), ((1024, 1024, 1024), (1, 1, 1)), ((300, 200, 100), (0.5, 0.25, 2.0)),
+                                      ((7, 130, 31), (1.0, 3.0, 0.1)), ((40, 24, 1), (1, 1, 1))])
+def test_init_render_bit_equal_to_reference(ref, dims, es):
+    d3 = (C.c_uint64 * 3)(*dims)
+    esx = (C.c_float * 3)(*es)
+    bmin, bmax, tstep = (C.c_float * 3)(), (C.c_float * 3)(), C.c_float()
+    vrt.oracle().orc_init_render(d3, esx, bmin, bmax, C.byref(tstep))
+    ext, mem = (C.c_uint64 * 3)(), C.c_uint64()
+    rmin, rmax, rt, fo = (C.c_float * 3)(), (C.c_float * 3)(), C.c_float(), (C.c_float * 3)()
+    factors = (C.c_float * 3)(0.5, 0.25, 0.125)
+    data = np.zeros(1, dtype=np.float32)
+    nd = 3 if dims[2] > 1 else 2
+    ref.ref_init_render(data.ctypes.data, d3, nd, 7, esx, 640, 480, factors, 0.9, ext, C.byref(mem), rmin, rmax, C.byref(rt), fo)
+    assert list(ext) == list(dims) and mem.value == dims[0] * dims[1] * dims[2] * 4
+    assert np.array_equal(np.array(bmin[:], dtype=np.float32).view(np.uint32), np.array(rmin[:], dtype=np.float32).view(np.uint32))
+    assert np.array_equal(np.array(bmax[:], dtype=np.float32).view(np.uint32), np.array(rmax[:], dtype=np.float32).view(np.uint32))
+    assert np.float32(tstep.value).view(np.uint32) == np.float32(rt.value).view(np.uint32)
+    assert list(fo) == [0.5, 0.125, 0.25]  # initRender(em, re, ab) -> options (em, ab, re)
+
+
+def test_init_render_golden_fixture():
+    gold = np.load(os.path.join(GOLDEN, "init_render.npz"))
+    for dims, es, bmax, tstep in zip(gold["dims"], gold["es"], gold["boxmax"], gold["tstep"]):
+        d3 = (C.c_uint64 * 3)(*[int(x) for x in dims])
+        esx = (C.c_float * 3)(*[float(x) for x in es])
+        bmin, bm, t = (C.c_float * 3)(), (C.c_float * 3)(), C.c_float()
+        vrt.oracle().orc_init_render(d3, esx, bmin, bm, C.byref(t))
+        assert np.array_equal(np.array(bm[:], dtype=np.float32).view(np.uint32), bmax.view(np.uint32))
+        assert np.float32(t.value).view(np.uint32) == tstep.view(np.uint32)
+
+
+def test_volume_equality_rule_matches_reference(ref):
+    a = np.zeros(8, dtype=np.float32)
+    b = np.zeros(8, dtype=np.float32)
+    d = (C.c_uint64 * 3)(2, 2, 2)
+    d2 = (C.c_uint64 * 3)(2, 2, 1)
+    assert ref.ref_volume_equal(a.ctypes.data, 5, d, a.ctypes.data, 5, d) == 1
+    assert ref.ref_volume_equal(a.ctypes.data, 5, d, a.ctypes.data, 6, d) == 0  # last_update takes part
+    assert ref.ref_volume_equal(a.ctypes.data, 5, d, b.ctypes.data, 5, d) == 0
+    assert ref.ref_volume_equal(a.ctypes.data, 5, d, a.ctypes.data, 5, d2) == 0  # memory_size takes part
+
+
+def test_timestamp_reference_truncates_to_32_bits(ref):
+    t = ref.ref_timestamp()
+    now = int(__import__("time").time() * 1000)
+    assert t < 2 ** 32 and abs((now & 0xFFFFFFFF) - t) < 5000  # timestamp.cpp:25 writes through int*
+
+
+# ---- software tex3D ---------------------------------------------------------------------------
+def test_tex3d_linear_ramp_and_clamp():
+    lib = vrt.oracle()
+    w, h, d = 9, 7, 5
+    x, y, z = np.meshgrid(np.arange(w), np.arange(h), np.arange(d), indexing="ij")
+    vol = np.asfortranarray((2 * x + 3 * y + 5 * z).astype(np.float32))
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        u = rng.random(3)
+        # texel-centre convention: value at normalised u is ramp(u*N - 0.5) inside the centres' hull
+        p = np.clip(u * [w, h, d] - 0.5, 0, [w - 1, h - 1, d - 1])
+        want = 2 * p[0] + 3 * p[1] + 5 * p[2]
+        got = lib.orc_tex3d(vol.ctypes.data, w, h, d, u[0], u[1], u[2], 0)
+        assert abs(got - want) < 1e-4
+    assert lib.orc_tex3d(vol.ctypes.data, w, h, d, -3.0, -1.0, -0.1, 0) == vol[0, 0, 0]
+    assert lib.orc_tex3d(vol.ctypes.data, w, h, d, 7.0, 1.5, 1.01, 0) == vol[-1, -1, -1]
+    assert lib.orc_tex3d(vol.ctypes.data, w, h, d, float("nan"), float("nan"), float("nan"), 0) == vol[0, 0, 0]  # NaN -> 0
+
+
+def test_tex3d_8bit_weights_bracket_fp32():
+    lib = vrt.oracle()
+    vol = np.asfortranarray(np.random.default_rng(3).random((6, 6, 6), dtype=np.float32))
+    for u in np.random.default_rng(4).random((100, 3)):
+        a = lib.orc_tex3d(vol.ctypes.data, 6, 6, 6, u[0], u[1], u[2], 0)
+        b = lib.orc_tex3d(vol.ctypes.data, 6, 6, 6, u[0], u[1], u[2], 8)
+        assert abs(a - b) <= 3 * (1 / 512) * 1.0 + 1e-6
+
+
+# ---- analytic scenes ----------------------------------------------------------------------------
+def _const_scene(value, n=8, res=(32, 32), thr=2.0, fEm=1.0, fAb=1.0):
+    r = vrt.OracleVolumeRender()
+    r.FocalLength, r.DistanceToObject = 3.0, 6.0
+    r.OpacityThreshold = thr
+    r.ImageResolution = list(res)
+    v = api.Volume(np.full((n, n, n), value, dtype=np.float32, order="F"))
+    r.VolumeEmission = v
+    r.VolumeAbsorption = v
+    r.FactorEmission, r.FactorAbsorption, r.FactorReflection = fEm, fAb, 1.0
+    r.Color = [1.0, 0.5, 0.25]
+    return r
+
+
+def test_constant_medium_beer_lambert_closed_form():
+    """No lights: per sample alpha = 1 - exp(-fAb*v*tstep), colour c = fEm*v*tstep*color; after n
+    samples the under operator gives C_n = c * (1 - (1-alpha)^n) (geometric series) - kernel.cu:455-482."""
+    v, n = 0.75, 8
+    r = _const_scene(v, n)
+    with pytest.warns(UserWarning):
+        img = r.render()
+    st = r._backend.stats(r.objectHandle)
+    tstep = 1.0 / (2.2 * math.sqrt(2 * n * n))
+    alpha = 1 - math.exp(-v * tstep)
+    H, W = img.shape[:2]
+    # centre pixel looks along -z through the cube: chord 2 -> floor(2/tstep)+1 samples (+-1 for rounding)
+    c = img[H // 2, W // 2]
+    ns = 2.0 / tstep
+    want = v * tstep * (1 - (1 - alpha) ** ns)
+    assert abs(c[0] - want) / want < 2e-2
+    assert np.allclose(c[1] / c[0], 0.5, rtol=1e-5) and np.allclose(c[2] / c[0], 0.25, rtol=1e-5)
+    assert st.rays_hit > 0 and st.samples_marched >= st.rays_hit
+    assert (img[0, 0] == 0).all()  # corner rays miss the box: pixel never written
+
+
+def test_early_termination_sample_count():
+    """sum.w > thr stops the ray (kernel.cu:485): with alpha per sample a, n = first n with 1-(1-a)^n > thr."""
+    v, n = 1.0, 8
+    fAb = 5.0
+    r = _const_scene(v, n, res=(16, 16), thr=0.5, fAb=fAb)
+    with pytest.warns(UserWarning):
+        img = r.render()
+    tstep = np.float32(1.0) / (np.float32(2.2) * np.float32(math.sqrt(2 * n * n)))
+    a = 1 - math.exp(-fAb * v * float(tstep))
+    want = math.floor(math.log(0.5) / math.log(1 - a)) + 1
+    st = r._backend.stats(r.objectHandle)
+    # every ray stops after exactly `want` samples, except grazing rays whose chord is shorter
+    assert want * (st.rays_hit - 8) <= st.samples_marched <= want * st.rays_hit and want >= 3
+    assert np.isfinite(img).all()
+
+
+def test_zero_volume_renders_black_but_marches():
+    r = _const_scene(0.0, 8)
+    with pytest.warns(UserWarning):
+        img = r.render()
+    assert (img == 0).all()
+    assert r._backend.stats(r.objectHandle).samples_marched > 0
+
+
+def test_output_layout_is_matlab_hxwx3():
+    vol = vrt.synth_brain((24, 24, 24))
+    r = vrt.example1_scene(vrt.OracleVolumeRender, vol, (48, 32), lights=1)  # ImageResolution = [W, H]
+    img = r.render()
+    assert img.shape == (32, 48, 3) and img.flags.f_contiguous
+
+
+# ---- the upload / aliasing state machine (kernel.cu:739-867) --------------------------------------
+def _sync(r, em, ab, re):
+    r.VolumeEmission, r.VolumeAbsorption, r.VolumeReflection = em, ab, re
+    r.syncVolumes()
+    return r._backend.state(r.objectHandle)
+
+
+def test_absorption_role_is_stuck_on_emission():
+    """d_idxAbsorption starts as `emission` (kernel.cu:80) and a distinct absorption upload never
+    moves it."""
+    a, b, c = (api.Volume(np.random.default_rng(i).random((4, 4, 4), dtype=np.float32)) for i in range(3))
+    r = vrt.OracleVolumeRender()
+    s = _sync(r, a, b, c)
+    assert (s.idx_emission, s.idx_absorption, s.idx_reflection) == (0, 0, 2)
+    assert list(s.bound[:3]) == [1, 1, 1] and list(s.uploads[:3]) == [1, 1, 1]
+    s = _sync(r, a, b, c)  # re-assignment stamps all three -> all re-uploaded
+    assert list(s.uploads[:3]) == [2, 2, 2]
+    r.syncVolumes()  # nothing dirty
+    assert list(r._backend.state(r.objectHandle).uploads[:3]) == [2, 2, 2]
+
+
+def test_aliased_emission_absorption_uploads_once():
+    a = api.Volume(np.random.default_rng(0).random((4, 4, 4), dtype=np.float32))
+    r = vrt.OracleVolumeRender()
+    r.VolumeEmission = a
+    r.VolumeAbsorption = a  # same object: the second assignment re-stamps it, both roles see one stamp
+    r.syncVolumes()
+    s = r._backend.state(r.objectHandle)
+    assert (s.idx_emission, s.idx_absorption, s.idx_reflection) == (0, 0, 2)
+    assert list(s.uploads[:3]) == [1, 0, 1] and list(s.bound[:3]) == [1, 0, 1]
+
+
+def test_reflection_only_dirty_hazard_is_restated_literally():
+    """Em == Ab clean, only Reflection dirty: kernel.cu:853-855 unbinds tex_emission and redirects
+    the emission role to the reflection texture."""
+    a = api.Volume(np.random.default_rng(0).random((4, 4, 4), dtype=np.float32))
+    r = vrt.OracleVolumeRender()
+    r.VolumeEmission = a
+    r.VolumeAbsorption = a
+    r.syncVolumes()
+    r.VolumeReflection = api.Volume(np.random.default_rng(1).random((4, 4, 4), dtype=np.float32))
+    r.syncVolumes()
+    s = r._backend.state(r.objectHandle)
+    assert s.idx_emission == 2 and s.bound[0] == 0
+
+
+def test_gradient_volumes_switch_method_and_reset():
+    vol = vrt.synth_brain((16, 16, 16))
+    r = vrt.example1_scene(vrt.OracleVolumeRender, vol, (32, 32), lights=1)
+    r.syncVolumes()
+    assert r._backend.state(r.objectHandle).gradient_method == 0
+    gx, gy, gz = r.VolumeEmission.grad()
+    r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
+    r.syncVolumes()
+    s = r._backend.state(r.objectHandle)
+    assert s.gradient_method == 1 and list(s.bound[3:6]) == [1, 1, 1]
+    r.resetGradientVolumes()
+    r.syncVolumes()
+    assert r._backend.state(r.objectHandle).gradient_method == 0
+
+
+def test_synth_and_gradient_twins_agree_with_numpy():
+    lib = vrt.oracle()
+    dims = (20, 24, 28)
+    d3 = (C.c_uint64 * 3)(*dims)
+    lib.orc_synth_volume.argtypes = [C.c_int, C.c_uint32, C.POINTER(C.c_uint64), C.c_void_p]
+    lib.orc_volume_gradient.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)] + [C.c_void_p] * 3
+    for kind, twin in ((0, vrt.synth_brain), (1, vrt.synth_tubes)):
+        out = np.zeros(dims, dtype=np.float32, order="F")
+        lib.orc_synth_volume(kind, vrt.SEED, d3, out.ctypes.data)
+        assert np.array_equal(out, twin(dims))
+    v = vrt.synth_brain(dims)
+    g = [np.zeros_like(v) for _ in range(3)]
+    lib.orc_volume_gradient(v.ctypes.data, d3, g[0].ctypes.data, g[1].ctypes.data, g[2].ctypes.data)
+    for mine, theirs in zip(g, api.Volume(v).grad()):
+        assert np.array_equal(mine, np.asarray(theirs.Data))

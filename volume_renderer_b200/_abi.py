@@ -101,6 +101,7 @@ def declare(lib):
         "vr_set_stream": ([vp, vp], C.c_int),
         "vr_get_device": ([vp, P(C.c_int)], C.c_int),
         "vr_synth_volume": ([vp, C.c_int, C.c_uint32, u64p, C.c_int32, vp], C.c_int),
+        "vr_volume_gradient": ([vp, P(VrVolume), C.c_int32, vp, vp, vp], C.c_int),
         "vr_device_alloc": ([vp, C.c_size_t, P(vp)], C.c_int),
         "vr_device_free": ([vp, vp], C.c_int),
         "vr_device_download": ([vp, vp, vp, C.c_size_t], C.c_int),

@@ -238,6 +238,15 @@ class _CudaBackend:
         _abi.check(_abi.lib().vr_render(h, *args[0], out.ctypes.data), h)
         return out
 
+    # extensions with no mex counterpart (include/vr_abi.h, "extensions")
+    def stats(self, h):
+        s = _abi.VrStats()
+        _abi.check(_abi.lib().vr_get_stats(h, C.byref(s)), h)
+        return s.as_dict()
+
+    def set_option(self, h, option, value):
+        _abi.check(_abi.lib().vr_set_option(h, int(option), int(value)), h)
+
 
 def _render_args(lights, lut, factors, es, res, rot, props, thr, color):
     """Pack the 'render' arguments the way MATLAB lays them out in memory (render.cpp:142-240)."""
@@ -377,6 +386,14 @@ class VolumeRender:
         s = self._backend.mem_info(self.objectHandle)
         print(s, end="")
         return s
+
+    def stats(self):
+        """Counters of the last render (vr_get_stats); no MATLAB counterpart."""
+        return self._backend.stats(self.objectHandle)
+
+    def setOption(self, option, value):
+        """vr_set_option; no MATLAB counterpart (defaults reproduce the reference as written)."""
+        self._backend.set_option(self.objectHandle, option, value)
 
     def memClear(self):
         """VolumeRender.m:230-237: 'delete' on the handle; the later destructor hits a stale handle."""

@@ -1,0 +1,886 @@
+// context.cu - the C ABI of include/vr_abi.h: persistent context, volume residency, render.
+//
+// Replaces, behind the same command protocol, the reference's host runtime for the ray-march
+// path: mm::MManager (src/C/vr/mm/mmanager.hxx), syncWithDevice and friends
+// (src/C/vr/volumeRender_kernel.cu:522-867), vr::initRender / vr::render
+// (src/C/vr/volumeRender.cpp:112-300) and the argument marshalling of the mex gateway
+// (src/C/mex/render.cpp:93-277).  Differences by design: context-local state instead of process
+// globals, volumes resident as padded bricks in HBM instead of cudaArrays, one persistent image
+// buffer / light block instead of a per-frame cudaMalloc, every CUDA error checked and returned.
+// There is no CPU path in here: without a B200 every call fails with VR_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "../../include/vr_abi.h"
+#include "raymarch_launch.h"
+#include "render_setup.h"
+#include "vr_types.h"
+
+using namespace vrb;
+
+namespace {
+
+thread_local std::string tl_error;
+std::mutex g_registry_mutex;
+std::set<const vr_ctx *> g_registry;  // live contexts: lets a stale handle be recognised
+
+// vr::Volume (volumeRender.h:62-71) and its operator== (volumeRender.cpp:24-26)
+struct HostVol {
+  const void *data = nullptr;
+  uint64_t w = 0, h = 0, d = 0;
+  uint64_t bytes = 0;
+  uint64_t last_update = 0;
+  int dtype = VR_DTYPE_F32;
+  int memspace = VR_MEM_HOST;
+};
+inline bool same(const HostVol &a, const HostVol &b) {
+  return a.data == b.data && a.last_update == b.last_update && a.bytes == b.bytes;
+}
+inline size_t elem_size(int dtype) { return dtype == VR_DTYPE_BF16 ? 2 : 4; }
+HostVol make_volume(const vr_volume *v) {
+  HostVol r;
+  if (!v) return r;
+  r.data = v->data;
+  r.w = v->dims[0], r.h = v->dims[1], r.d = v->dims[2];
+  r.dtype = v->dtype;
+  r.memspace = v->memspace;
+  r.bytes = r.w * r.h * r.d * elem_size(r.dtype);
+  r.last_update = v->last_update;
+  return r;
+}
+
+// One texture slot = what a bound texture reference + its cudaArray was (kernel.cu:90-120).
+struct Resident {
+  void *storage = nullptr;  // padded (bricked) voxels
+  size_t storage_bytes = 0;
+  uint32_t *occ = nullptr;  // occupancy bit grid
+  size_t occ_bytes = 0;
+  int ocx = 0, ocy = 0, ocz = 0;
+  int w = 0, h = 0, d = 0;
+  int dtype = VR_DTYPE_F32;
+  int layout = LAYOUT_LINEAR;
+  uint32_t sy = 0, sz = 0;
+  int kind = TEX_UNBOUND;
+  float cval = 0.0f;
+  HostVol src;  // what was uploaded (identity: pointer, timestamp, bytes)
+};
+
+}  // namespace
+
+struct vr_ctx {
+  uint32_t magic = 0xB200F0A5u;
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evu0 = nullptr, evu1 = nullptr;
+  // mm::MManager state (mmanager.hxx:25-100)
+  uint64_t timeLastMemSync = 0;
+  HostVol host[S_N];
+  bool arr[S_N] = {false, false, false, false, false, false, false};  // ptr_d_volume* != 0
+  // device globals of the reference (kernel.cu:55-120), context-local here
+  Resident tex[S_N];
+  int idxEm = S_EM, idxAb = S_EM /* sic: kernel.cu:80 initialises d_idxAbsorption to emission */, idxRe = S_RE;
+  int gradientMethod = 0;
+  std::vector<vr_light> lights;  // positions already axis-reversed (render.cpp:167)
+  float *d_lights_more = nullptr;
+  size_t lights_more_cap = 0;
+  // persistent buffers
+  float *d_image = nullptr;
+  size_t image_cap = 0;
+  void *d_stage = nullptr;
+  size_t stage_cap = 0;
+  unsigned int *d_counter = nullptr;      // work counter + padding
+  unsigned long long *d_stats = nullptr;  // 3 counters
+  unsigned long long *h_stats = nullptr;  // pinned
+  // options
+  int64_t opt[16];
+  // bookkeeping
+  vr_stats stats{};
+  bool stats_pending = false;
+  bool timing_pending = false;
+  std::string err;
+};
+
+namespace {
+
+vr_status fail(vr_ctx *c, vr_status s, const char *fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  tl_error = buf;
+  if (c) c->err = buf;
+  return s;
+}
+#define VR_CUDA(c, call)                                                                                      \
+  do {                                                                                                        \
+    cudaError_t e_ = (call);                                                                                  \
+    if (e_ != cudaSuccess)                                                                                    \
+      return fail(c, e_ == cudaErrorMemoryAllocation ? VR_ERR_INSUFFICIENT_VRAM : VR_ERR_CUDA, "%s: %s (%s:%d)", #call, \
+                  cudaGetErrorString(e_), __FILE__, __LINE__);                                                \
+  } while (0)
+#define VR_TRY(expr)                 \
+  do {                               \
+    vr_status s_ = (expr);           \
+    if (s_ != VR_OK) return s_;      \
+  } while (0)
+
+bool live(const vr_ctx *c) {
+  if (!c) return false;
+  std::lock_guard<std::mutex> g(g_registry_mutex);
+  return g_registry.count(c) != 0 && c->magic == 0xB200F0A5u;
+}
+#define VR_CHECK_HANDLE(c) \
+  if (!live(c)) return fail(nullptr, VR_ERR_INVALID_HANDLE, "Handle not valid.")
+
+void release(vr_ctx *c, Resident &r) {
+  if (r.storage) cudaFree(r.storage);
+  if (r.occ) cudaFree(r.occ);
+  r = Resident();
+  (void)c;
+}
+
+uint64_t resident_bytes(const vr_ctx *c) {
+  uint64_t b = 0;
+  for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes;
+  b += c->image_cap + c->stage_cap + c->lights_more_cap;
+  return b;
+}
+
+// storage geometry of a padded volume
+void geometry(int layout, uint64_t w, uint64_t h, uint64_t d, uint32_t *sy, uint32_t *sz, uint64_t *elems,
+              uint64_t *layers, uint64_t *layer_elems) {
+  const uint64_t pw = w + 2, ph = h + 2, pd = d + 2;
+  if (layout == LAYOUT_BRICK) {
+    const uint64_t nbx = (pw + 7) / 8, nby = (ph + 7) / 8, nbz = (pd + 7) / 8;
+    *sy = (uint32_t)(nbx * 512);
+    *sz = (uint32_t)(nbx * nby * 512);
+    *layers = nbz;
+    *layer_elems = nbx * nby * 512;
+  } else {
+    *sy = (uint32_t)pw;
+    *sz = (uint32_t)(pw * ph);
+    *layers = pd;
+    *layer_elems = pw * ph;
+  }
+  *elems = *layers * *layer_elems;
+}
+
+vr_status ensure_stage(vr_ctx *c, size_t bytes) {
+  if (c->stage_cap >= bytes) return VR_OK;
+  if (c->d_stage) cudaFree(c->d_stage);
+  c->d_stage = nullptr;
+  c->stage_cap = 0;
+  VR_CUDA(c, cudaMalloc(&c->d_stage, bytes));
+  c->stage_cap = bytes;
+  return VR_OK;
+}
+
+// createTextureFromVolume (kernel.cu:522-554): make `v` resident in slot `slot`.  The volume is
+// streamed in slabs of whole destination layers: H2D of the source slices a slab needs, then a
+// repack kernel that writes the padded (bricked) storage.  A 1x1x1 volume becomes a constant.
+vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
+  Resident &r = c->tex[slot];
+  release(c, r);
+  c->arr[slot] = true;
+  if (!v.data || v.w == 0 || v.h == 0 || v.d == 0) return VR_OK;  // stays unbound, reads 0
+  if (v.dtype != VR_DTYPE_F32 && v.dtype != VR_DTYPE_BF16) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown volume dtype %d", v.dtype);
+  if (v.w > 0x3fffffff || v.h > 0x3fffffff || v.d > 0x3fffffff) return fail(c, VR_ERR_UNSUPPORTED, "volume dimension too large");
+  c->stats.uploads++;
+  if (v.w == 1 && v.h == 1 && v.d == 1) {
+    uint32_t raw = 0;
+    if (v.memspace == VR_MEM_DEVICE) {
+      VR_CUDA(c, cudaMemcpyAsync(&raw, v.data, elem_size(v.dtype), cudaMemcpyDeviceToHost, c->stream));
+      VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    } else {
+      memcpy(&raw, v.data, elem_size(v.dtype));
+    }
+    if (v.dtype == VR_DTYPE_BF16) raw <<= 16;
+    memcpy(&r.cval, &raw, 4);
+    r.kind = TEX_CONST;
+    r.w = r.h = r.d = 1;
+    r.dtype = v.dtype;
+    r.src = v;
+    c->stats.bytes_uploaded += elem_size(v.dtype);
+    return VR_OK;
+  }
+  const int layout = slot == S_LIGHT ? LAYOUT_LINEAR : (c->opt[VR_OPT_BRICK_LAYOUT] ? LAYOUT_BRICK : LAYOUT_LINEAR);
+  uint64_t elems, layers, layer_elems;
+  uint32_t sy, sz;
+  geometry(layout, v.w, v.h, v.d, &sy, &sz, &elems, &layers, &layer_elems);
+  if (layer_elems > 0xffffffffull) return fail(c, VR_ERR_UNSUPPORTED, "volume slice too large for 32-bit in-layer offsets");
+  const size_t es = elem_size(v.dtype);
+  size_t free_b = 0, total_b = 0;
+  VR_CUDA(c, cudaMemGetInfo(&free_b, &total_b));
+  if (free_b < elems * es) {  // MManager::checkFreeDeviceMemory (mmanager.hxx:144-173)
+    return fail(c, VR_ERR_INSUFFICIENT_VRAM,
+                "insufficient free VRAM!\n\tTotal Memory (MB): \t%zu\n\tFree Memory (MB): \t%zu\n\tRequired memory (MB): \t%zu\n",
+                total_b >> 20, free_b >> 20, (size_t)(elems * es) >> 20);
+  }
+  VR_CUDA(c, cudaMalloc(&r.storage, elems * es));
+  r.storage_bytes = elems * es;
+  r.w = (int)v.w, r.h = (int)v.h, r.d = (int)v.d;
+  r.dtype = v.dtype;
+  r.layout = layout;
+  r.sy = sy, r.sz = sz;
+
+  RepackArgs a;
+  a.dst = r.storage;
+  a.w = r.w, a.h = r.h, a.d = r.d;
+  a.sy = sy, a.sz = sz;
+  a.layout = layout;
+  a.src_dtype = a.dst_dtype = v.dtype;
+  const uint64_t zper = layout == LAYOUT_BRICK ? 8 : 1;  // padded Z planes per layer
+  const size_t slice_bytes = (size_t)v.w * v.h * es;
+  if (v.memspace == VR_MEM_DEVICE) {
+    a.src = v.data;
+    a.src_z0 = 0;
+    a.o0 = 0, a.o1 = elems;
+    VR_CUDA(c, launch_repack(a, c->stream));
+  } else {
+    // slab = as many layers as fit a ~256 MiB staging buffer
+    const size_t budget = (size_t)256 << 20;
+    uint64_t slab_layers = budget / (slice_bytes * zper);
+    if (slab_layers < 1) slab_layers = 1;
+    if (slab_layers > layers) slab_layers = layers;
+    VR_TRY(ensure_stage(c, (size_t)(slab_layers * zper + 1) * slice_bytes));
+    for (uint64_t l0 = 0; l0 < layers; l0 += slab_layers) {
+      const uint64_t l1 = l0 + slab_layers < layers ? l0 + slab_layers : layers;
+      // padded planes [l0*zper, l1*zper) hold voxel z = clamp(Z-1)
+      int64_t z0 = (int64_t)(l0 * zper) - 1, z1 = (int64_t)(l1 * zper) - 2;
+      z0 = z0 < 0 ? 0 : (z0 > (int64_t)v.d - 1 ? (int64_t)v.d - 1 : z0);
+      z1 = z1 < 0 ? 0 : (z1 > (int64_t)v.d - 1 ? (int64_t)v.d - 1 : z1);
+      const size_t nbytes = (size_t)(z1 - z0 + 1) * slice_bytes;
+      // the staging buffer is reused: the previous slab's repack must have consumed it (same stream)
+      VR_CUDA(c, cudaMemcpyAsync(c->d_stage, static_cast<const char *>(v.data) + (size_t)z0 * slice_bytes, nbytes,
+                                 cudaMemcpyHostToDevice, c->stream));
+      a.src = c->d_stage;
+      a.src_z0 = (int)z0;
+      a.o0 = l0 * layer_elems, a.o1 = l1 * layer_elems;
+      VR_CUDA(c, launch_repack(a, c->stream));
+      c->stats.bytes_uploaded += nbytes;
+    }
+  }
+  r.kind = TEX_VOLUME;
+  r.src = v;
+  if (slot != S_LIGHT) {
+    r.ocx = (r.w + 7) / 8, r.ocy = (r.h + 7) / 8, r.ocz = (r.d + 7) / 8;
+    const uint64_t ncell = (uint64_t)r.ocx * r.ocy * r.ocz;
+    r.occ_bytes = (size_t)((ncell + 31) / 32) * 4;
+    VR_CUDA(c, cudaMalloc(&r.occ, r.occ_bytes));
+    VR_CUDA(c, cudaMemsetAsync(r.occ, 0, r.occ_bytes, c->stream));
+    TexDesc t{};
+    t.p = r.storage, t.w = r.w, t.h = r.h, t.d = r.d, t.sy = r.sy, t.sz = r.sz, t.kind = r.kind;
+    VR_CUDA(c, launch_occupancy(t, r.layout, r.dtype, r.occ, r.ocx, r.ocy, r.ocz, 2, c->stream));
+  }
+  return VR_OK;
+}
+
+// syncVolume (kernel.cu:659-672): whatever the flag says, the old array is released and the
+// volume is uploaded again.
+vr_status syncVolume(vr_ctx *c, int slot, const HostVol &v) { return upload(c, slot, v); }
+
+// The reference re-uploads the LUT on every 'render' and the three gradient volumes on every
+// 'sync_volumes' (syncVolume frees and re-creates whatever its flag says, kernel.cu:659-672 +
+// :522-541).  The data does not change between those calls unless the volume was stamped, so
+// the copy is elided when the slot already holds exactly this (pointer, timestamp, size).
+vr_status syncVolumeCached(vr_ctx *c, int slot, const HostVol &v) {
+  const Resident &r = c->tex[slot];
+  if (c->arr[slot] && r.kind != TEX_UNBOUND && same(r.src, v) && r.src.w == v.w && r.src.h == v.h && r.src.d == v.d &&
+      r.src.dtype == v.dtype && v.last_update != 0)
+    return VR_OK;
+  return upload(c, slot, v);
+}
+
+// referenceTexture (kernel.cu:631-648): unbind the slot's texture, drop its array (the reference
+// leaks it; freed here) and redirect the role index.
+void referenceTexture(vr_ctx *c, int slot, int *idx, int assigned) {
+  if (c->arr[slot]) {
+    release(c, c->tex[slot]);
+    c->arr[slot] = false;
+  }
+  *idx = assigned;
+}
+
+// syncWithDevice (kernel.cu:739-867): per-role dirty test, alias test, order Em -> Ab -> Re.
+vr_status syncWithDevice(vr_ctx *c) {
+  const HostVol &Em = c->host[S_EM], &Ab = c->host[S_AB], &Re = c->host[S_RE];
+  const uint64_t T = c->timeLastMemSync;
+  const bool simEmAb = same(Em, Ab), simEmRe = same(Em, Re), simAbRe = same(Ab, Re);
+  const bool reqEm = Em.last_update > T || T == 0;
+  const bool reqAb = Ab.last_update > T || T == 0;
+  const bool reqRe = Re.last_update > T || T == 0;
+  bool updEm = false, updAb = false, updRe = false;
+  if (reqEm) {
+    VR_TRY(syncVolume(c, S_EM, Em));
+    updEm = true;
+    if (simEmRe && !updRe) referenceTexture(c, S_RE, &c->idxRe, S_EM), updRe = true;
+    if (simEmAb && !updAb) referenceTexture(c, S_AB, &c->idxAb, S_EM), updAb = true;
+  }
+  if (reqAb) {
+    if (!updAb) {
+      VR_TRY(syncVolume(c, S_AB, Ab));
+      updAb = true;
+    }
+    if (simAbRe && !updRe) referenceTexture(c, S_RE, &c->idxRe, S_AB), updRe = true;
+    if (simEmAb && !updEm) {
+      // kernel.cu:818-819 hands tex_emission together with the ABSORPTION array pointer: the
+      // emission texture is unbound when an absorption array exists, that pointer is dropped,
+      // and the emission role is redirected to the absorption texture.
+      if (c->arr[S_AB]) release(c, c->tex[S_EM]);
+      c->arr[S_AB] = false;
+      c->idxEm = S_AB;
+      updEm = true;
+    }
+  }
+  if (reqRe) {
+    if (!updRe) {
+      VR_TRY(syncVolume(c, S_RE, Re));
+      updRe = true;
+    }
+    if (simAbRe && !updAb) referenceTexture(c, S_AB, &c->idxAb, S_RE), updAb = true;
+    if (simEmAb && !updEm) referenceTexture(c, S_EM, &c->idxEm, S_RE), updEm = true;
+  }
+  return VR_OK;
+}
+
+// MManager::resetGradients (mmanager.hxx:206-213): only the host descriptors are cleared; the
+// device arrays of live gradient volumes stay (inverted null test) - here they are kept too, so
+// that the sampled data matches; they are released when the context dies or they are replaced.
+void resetGradients(vr_ctx *c) {
+  c->host[S_DX] = HostVol();
+  c->host[S_DY] = HostVol();
+  c->host[S_DZ] = HostVol();
+}
+
+// MManager::sync (mmanager.hxx:178-201)
+vr_status mm_sync(vr_ctx *c) {
+  if ((c->host[S_DX].last_update == 0 && c->arr[S_DX]) || (c->host[S_DY].last_update == 0 && c->arr[S_DY]) ||
+      (c->host[S_DZ].last_update == 0 && c->arr[S_DZ]))
+    resetGradients(c);
+  VR_TRY(syncWithDevice(c));
+  if (c->host[S_DX].last_update != 0 && c->host[S_DY].last_update != 0 && c->host[S_DZ].last_update != 0) {
+    // setGradientTextures (kernel.cu:703-722)
+    VR_TRY(syncVolumeCached(c, S_DX, c->host[S_DX]));
+    VR_TRY(syncVolumeCached(c, S_DY, c->host[S_DY]));
+    VR_TRY(syncVolumeCached(c, S_DZ, c->host[S_DZ]));
+    c->gradientMethod = 1;
+  }
+  return VR_OK;
+}
+
+// MManager::getRequiredMemory (mmanager.hxx:110-134)
+uint64_t required_memory(const vr_ctx *c) {
+  const HostVol &Em = c->host[S_EM], &Ab = c->host[S_AB], &Re = c->host[S_RE];
+  uint64_t need = Em.bytes;
+  if (!same(Em, Ab) && !same(Re, Ab)) need += Ab.bytes;
+  if (!same(Em, Re) && !same(Re, Ab)) need += Re.bytes;
+  need += c->host[S_DX].bytes + c->host[S_DY].bytes + c->host[S_DZ].bytes;
+  return need;
+}
+
+vr_status check_free(vr_ctx *c, uint64_t need) {
+  size_t free_b = 0, total_b = 0;
+  VR_CUDA(c, cudaMemGetInfo(&free_b, &total_b));
+  if (free_b < need)
+    return fail(c, VR_ERR_INSUFFICIENT_VRAM,
+                "insufficient free VRAM!\n\tTotal Memory (MB): \t%zu\n\tFree Memory (MB): \t%zu\n\tRequired memory (MB): \t%zu\n",
+                total_b >> 20, free_b >> 20, (size_t)need >> 20);
+  return VR_OK;
+}
+
+TexDesc describe(const Resident &r) {
+  TexDesc t{};
+  t.p = r.storage;
+  t.w = r.w, t.h = r.h, t.d = r.d;
+  t.fw = (float)r.w, t.fh = (float)r.h, t.fd = (float)r.d;
+  t.sy = r.sy, t.sz = r.sz;
+  t.kind = r.kind;
+  t.cval = r.cval;
+  return t;
+}
+
+vr_status set_device(vr_ctx *c) {
+  VR_CUDA(c, cudaSetDevice(c->device));
+  return VR_OK;
+}
+
+vr_status collect(vr_ctx *c) {
+  if (!c->stats_pending && !c->timing_pending) return VR_OK;
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->timing_pending) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.kernel_ms = ms;
+    c->timing_pending = false;
+  }
+  if (c->stats_pending) {
+    c->stats.samples_marched = c->h_stats[0];
+    c->stats.samples_shaded = c->h_stats[1];
+    c->stats.rays_hit = c->h_stats[2];
+    c->stats_pending = false;
+  }
+  return VR_OK;
+}
+
+// 'render' minus the read-back: marshal like render.cpp:142-245, set up like vr::initRender
+// (volumeRender.cpp:112-156) and vr::render (:264-277), launch on the context's stream.
+vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+                        const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
+                        const float props[3], float thr, const float color[3], float *d_out, cudaStream_t stream) {
+  if (!factors || !es || !res || !R || !props || !color) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
+  c->stats.bytes_uploaded = 0;
+  if (lights && illumination) {  // render.cpp:145-191; a logical placeholder keeps the previous set
+    c->host[S_LIGHT] = make_volume(illumination);
+    c->lights.resize(n_lights);
+    for (size_t l = 0; l < n_lights; ++l) {
+      vr_light &o = c->lights[l];
+      // make_float3Inv on Position (render.cpp:167), plain order on Color
+      o.position[0] = lights[l].position[2], o.position[1] = lights[l].position[1], o.position[2] = lights[l].position[0];
+      memcpy(o.color, lights[l].color, sizeof o.color);
+    }
+    // setIlluminationTexture (kernel.cu:682-689) tests `last_update > timeLastMemSync` but
+    // syncVolume re-uploads regardless of its flag; the LUT is tiny, the data is what matters.
+    VR_TRY(syncVolumeCached(c, S_LIGHT, c->host[S_LIGHT]));
+  }
+  const HostVol &E = c->host[S_EM];
+  if (E.w == 0 || E.h == 0 || E.d == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: no emission volume synced");
+  const uint64_t H = res[0], W = res[1];  // render.cpp:196,243
+  if (H == 0 || W == 0 || H > 0x7fffffff || W > 0x7fffffff || W * H > 0xffffffffull)
+    return fail(c, VR_ERR_INVALID_ARGUMENT, "render: bad resolution");
+
+  KernelParams P;
+  memset(&P, 0, sizeof P);
+  P.out = d_out;
+  setup_frame(P, factors, es, W, H, R, props, thr, color, E.w, E.h, E.d);
+
+  // role -> texture through the redirect indices (kernel.cu:127-144)
+  int sEm = c->idxEm, sAb = c->idxAb, sRe = c->idxRe;
+  if (c->opt[VR_OPT_ABSORPTION_ROLE_FIX] && c->tex[S_AB].kind != TEX_UNBOUND) sAb = S_AB;
+  P.em = describe(c->tex[sEm]);
+  P.ab = describe(c->tex[sAb]);
+  P.re = describe(c->tex[sRe]);
+  P.em_direct = describe(c->tex[S_EM]);
+  P.gx = describe(c->tex[S_DX]);
+  P.gy = describe(c->tex[S_DY]);
+  P.gz = describe(c->tex[S_DZ]);
+  P.lut = describe(c->tex[S_LIGHT]);
+  P.ab_is_em = sAb == sEm;
+  P.re_is_em = sRe == sEm;
+  P.gradient_method = c->gradientMethod;
+  P.frac_bits = (int)c->opt[VR_OPT_FILTER_FRAC_BITS];
+  P.count = (int)c->opt[VR_OPT_COUNT_SAMPLES];
+  // all volume textures of one launch must share element type and layout
+  int dtype = -1, layout = -1;
+  const int used[] = {sEm, sAb, sRe, S_EM, S_DX, S_DY, S_DZ};
+  for (int s : used) {
+    const Resident &r = c->tex[s];
+    if (r.kind != TEX_VOLUME) continue;
+    if (dtype < 0) dtype = r.dtype, layout = r.layout;
+    if (dtype != r.dtype || layout != r.layout)
+      return fail(c, VR_ERR_UNSUPPORTED, "volumes of one render must share dtype and layout (slot %d differs)", s);
+  }
+  if (dtype < 0) dtype = VR_DTYPE_F32, layout = LAYOUT_LINEAR;
+  const Resident &rab = c->tex[sAb];
+  P.skip = c->opt[VR_OPT_EMPTY_SPACE_SKIP] && rab.kind == TEX_VOLUME && rab.occ;
+  P.occ = rab.occ, P.ocx = rab.ocx, P.ocy = rab.ocy, P.ocz = rab.ocz;
+
+  // lights
+  P.n_lights = (int)c->lights.size();
+  for (int i = 0; i < P.n_lights && i < MAX_PARAM_LIGHTS; ++i) {
+    memcpy(P.lights[i], c->lights[i].position, 12);
+    memcpy(P.lights[i] + 3, c->lights[i].color, 12);
+  }
+  if (P.n_lights > MAX_PARAM_LIGHTS) {
+    const size_t need = (size_t)(P.n_lights - MAX_PARAM_LIGHTS) * 24;
+    if (c->lights_more_cap < need) {
+      if (c->d_lights_more) cudaFree(c->d_lights_more);
+      c->d_lights_more = nullptr, c->lights_more_cap = 0;
+      VR_CUDA(c, cudaMalloc(&c->d_lights_more, need));
+      c->lights_more_cap = need;
+    }
+    VR_CUDA(c, cudaMemcpyAsync(c->d_lights_more, c->lights.data() + MAX_PARAM_LIGHTS, need, cudaMemcpyHostToDevice, stream));
+    P.lights_more = c->d_lights_more;
+  }
+  if (P.n_lights > 0 && c->tex[S_LIGHT].kind == TEX_UNBOUND) {
+    // lights without a LUT cannot happen through render.cpp (both or neither); keep it defined
+    P.n_lights = 0;
+  }
+
+  // image-space partition
+  P.part_rank = (int)c->opt[VR_OPT_PART_RANK];
+  P.part_nranks = (int)c->opt[VR_OPT_PART_NRANKS];
+  if (P.part_nranks < 1 || P.part_rank < 0 || P.part_rank >= P.part_nranks) return fail(c, VR_ERR_INVALID_ARGUMENT, "bad partition %d/%d", P.part_rank, P.part_nranks);
+  P.tile_w = (int)c->opt[VR_OPT_TILE_W], P.tile_h = (int)c->opt[VR_OPT_TILE_H];
+  if (P.tile_w < 8 || P.tile_h < 4 || P.tile_w % 8 || P.tile_h % 4) return fail(c, VR_ERR_INVALID_ARGUMENT, "tile must be a multiple of 8x4");
+  P.ntx = (P.W + P.tile_w - 1) / P.tile_w, P.nty = (P.H + P.tile_h - 1) / P.tile_h;
+  P.wt_x = P.tile_w / 8, P.wt_y = P.tile_h / 4;
+  const uint64_t ntiles = (uint64_t)P.ntx * P.nty;
+  const uint64_t owned = ntiles > (uint64_t)P.part_rank ? (ntiles - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0;
+  P.num_owned = (uint32_t)owned;
+  const uint64_t work = owned * P.wt_x * P.wt_y;
+  if (work > 0xfffffff0ull) return fail(c, VR_ERR_UNSUPPORTED, "too many work items");
+  P.num_work = (uint32_t)work;
+  P.work_counter = c->d_counter;
+  P.stats = c->d_stats;
+
+  // cudaMemset of the image (volumeRender.cpp:271): pixels whose ray misses the box stay 0
+  VR_CUDA(c, cudaMemsetAsync(d_out, 0, (size_t)W * H * 3 * sizeof(float), stream));
+  VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
+  VR_CUDA(c, cudaMemsetAsync(c->d_stats, 0, 3 * sizeof(unsigned long long), stream));
+  VR_CUDA(c, cudaEventRecord(c->ev0, stream));
+  if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, (int)c->opt[VR_OPT_KERNEL_VARIANT], stream, c->sm_count));
+  VR_CUDA(c, cudaEventRecord(c->ev1, stream));
+  if (P.count) {
+    VR_CUDA(c, cudaMemcpyAsync(c->h_stats, c->d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    c->stats_pending = true;
+  }
+  c->timing_pending = true;
+  c->stats.kernel_launches = P.num_work > 0 ? 1 : 0;
+  return VR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+vr_status vr_create_on_device(vr_ctx **out, int device) {
+  if (!out) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: null output");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) return fail(nullptr, VR_ERR_NO_DEVICE, "no CUDA device (%s); there is no CPU fallback", cudaGetErrorString(e));
+  if (device < 0) {
+    const char *env = getenv("VR_DEVICE");
+    if (env) {
+      device = atoi(env);
+    } else if (cudaGetDevice(&device) != cudaSuccess) {
+      device = 0;
+    }
+  }
+  if (device >= n) return fail(nullptr, VR_ERR_NO_DEVICE, "device %d of %d does not exist", device, n);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail(nullptr, VR_ERR_NO_DEVICE, "cannot query device %d", device);
+  if (prop.major != 10) return fail(nullptr, VR_ERR_NO_DEVICE, "device %d is sm_%d%d; this library holds sm_100a code only", device, prop.major, prop.minor);
+  vr_ctx *c = new vr_ctx();
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  memset(c->opt, 0, sizeof c->opt);
+  c->opt[VR_OPT_EMPTY_SPACE_SKIP] = 1;
+  c->opt[VR_OPT_PART_NRANKS] = 1;
+  c->opt[VR_OPT_TILE_W] = 64;
+  c->opt[VR_OPT_TILE_H] = 64;
+  c->opt[VR_OPT_BRICK_LAYOUT] = 1;
+  c->opt[VR_OPT_COUNT_SAMPLES] = 1;
+  cudaError_t ce = cudaSetDevice(device);
+  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  c->own_stream = ce == cudaSuccess;
+  if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev0);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu0);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu1);
+  if (ce == cudaSuccess) ce = cudaMalloc(&c->d_counter, 64);
+  if (ce == cudaSuccess) ce = cudaMalloc(&c->d_stats, 64);
+  if (ce == cudaSuccess) ce = cudaMallocHost(&c->h_stats, 64);
+  if (ce != cudaSuccess) {
+    vr_status s = fail(nullptr, VR_ERR_CUDA, "vr_create: %s", cudaGetErrorString(ce));
+    delete c;
+    return s;
+  }
+  {
+    std::lock_guard<std::mutex> g(g_registry_mutex);
+    g_registry.insert(c);
+  }
+  *out = c;
+  return VR_OK;
+}
+vr_status vr_create(vr_ctx **out) { return vr_create_on_device(out, -1); }
+
+vr_status vr_destroy(vr_ctx *c) {
+  {
+    std::lock_guard<std::mutex> g(g_registry_mutex);
+    if (!c || !g_registry.count(c)) {
+      tl_error = "Handle not valid.";
+      return VR_ERR_INVALID_HANDLE;
+    }
+    g_registry.erase(c);
+  }
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (int i = 0; i < S_N; ++i) release(c, c->tex[i]);
+  if (c->d_image) cudaFree(c->d_image);
+  if (c->d_stage) cudaFree(c->d_stage);
+  if (c->d_lights_more) cudaFree(c->d_lights_more);
+  if (c->d_counter) cudaFree(c->d_counter);
+  if (c->d_stats) cudaFree(c->d_stats);
+  if (c->h_stats) cudaFreeHost(c->h_stats);
+  cudaEventDestroy(c->ev0), cudaEventDestroy(c->ev1), cudaEventDestroy(c->evu0), cudaEventDestroy(c->evu1);
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  c->magic = 0;
+  delete c;
+  return VR_OK;
+}
+
+vr_status vr_mem_info(vr_ctx *c, char *buf, size_t cap, size_t *needed) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  size_t free_b = 0, total_b = 0;
+  VR_CUDA(c, cudaMemGetInfo(&free_b, &total_b));
+  const double MB = 1024.0 * 1024.0;
+  std::string s;
+  char line[512];
+  auto add = [&](const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(line, sizeof line, fmt, ap);
+    va_end(ap);
+    s += line;
+  };
+  // same report as MManager::memInfo (mmanager.hxx:218-284), device pointers = resident storage
+  add("Memory Information\n------------------------------\nlast sync (timestamp): %llu\n\n", (unsigned long long)c->timeLastMemSync);
+  add("\tGPU %d\n\t---\n\t\tTotal Memory (MB): \t%g\n\t\tFree Memory (MB): \t%g\n\t\tUsed Memory (MB): \t%g\n\n", c->device, total_b / MB,
+      free_b / MB, (total_b - free_b) / MB);
+  add("\t\tVolumes\n\t\t-------\n");
+  const char *names[S_N] = {"Emission", "Absorption", "Reflection", "dX", "dY", "dZ", "light"};
+  for (int i = 0; i < S_N; ++i)
+    add("\t\t%s (MB): %g ptr: %p resident (MB): %g\n", names[i], c->host[i].bytes / MB, c->tex[i].storage, c->tex[i].storage_bytes / MB);
+  add("\t\trole -> texture: Em->%s Ab->%s Re->%s, gradient method: %s\n", names[c->idxEm], names[c->idxAb], names[c->idxRe],
+      c->gradientMethod ? "lookup" : "compute");
+  add("\n\t\tSimilarity of Volumes\n\t\t---------------------\n\t\t\tEm\tAb\tRe\n\t\tEm\t1\t\n\t\tAb\t%d\t1\n\t\tRe\t%d\t%d\t1\n\n",
+      (int)same(c->host[S_EM], c->host[S_AB]), (int)same(c->host[S_EM], c->host[S_RE]), (int)same(c->host[S_AB], c->host[S_RE]));
+  if (needed) *needed = s.size();
+  if (buf && cap) {
+    const size_t n = s.size() < cap - 1 ? s.size() : cap - 1;
+    memcpy(buf, s.data(), n);
+    buf[n] = 0;
+  }
+  return VR_OK;
+}
+
+vr_status vr_sync_volumes(vr_ctx *c, uint64_t T, const vr_volume *em, const vr_volume *re, const vr_volume *ab,
+                          const vr_volume *gx, const vr_volume *gy, const vr_volume *gz) {
+  VR_CHECK_HANDLE(c);
+  if (!em || !re || !ab) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
+  const int ng = (gx != nullptr) + (gy != nullptr) + (gz != nullptr);
+  if (ng != 0 && ng != 3) return fail(c, VR_ERR_INVALID_ARGUMENT, "gradient volumes: pass all three or none");
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  c->stats.uploads = 0;
+  c->stats.bytes_uploaded = 0;
+  c->timeLastMemSync = T;  // render.cpp:94
+  c->host[S_EM] = make_volume(em);
+  c->host[S_RE] = make_volume(re);
+  c->host[S_AB] = make_volume(ab);
+  int method = 0;
+  if (ng == 3) {  // nrhs == 9 (render.cpp:105-110)
+    c->host[S_DX] = make_volume(gx);
+    c->host[S_DY] = make_volume(gy);
+    c->host[S_DZ] = make_volume(gz);
+    method = 1;
+  } else {  // nrhs == 6 (render.cpp:111-113)
+    resetGradients(c);
+  }
+  VR_TRY(check_free(c, 0));  // the per-upload check in upload() is the binding one (old copies are freed first)
+  (void)required_memory;
+  c->gradientMethod = method;  // setGradientMethod (render.cpp:121)
+  VR_CUDA(c, cudaEventRecord(c->evu0, c->stream));
+  VR_TRY(mm_sync(c));  // render.cpp:122
+  VR_CUDA(c, cudaEventRecord(c->evu1, c->stream));
+  // host memory is only borrowed for the duration of the call
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->evu0, c->evu1);
+  c->stats.upload_ms = ms;
+  c->stats.bytes_resident = resident_bytes(c);
+  return VR_OK;
+}
+
+vr_status vr_render_device(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+                           const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
+                           const float props[3], float thr, const float color[3], float *d_out, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  if (!d_out) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: null output");
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  return render_common(c, lights, n_lights, illumination, factors, es, res, R, props, thr, color, d_out, s);
+}
+
+vr_status vr_render(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+                    const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
+                    const float props[3], float thr, const float color[3], float *out) {
+  VR_CHECK_HANDLE(c);
+  if (!out || !res) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  const size_t bytes = (size_t)res[0] * res[1] * 3 * sizeof(float);
+  if (bytes == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: bad resolution");
+  if (c->image_cap < bytes) {
+    if (c->d_image) cudaFree(c->d_image);
+    c->d_image = nullptr, c->image_cap = 0;
+    VR_CUDA(c, cudaMalloc(&c->d_image, bytes));
+    c->image_cap = bytes;
+  }
+  VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, R, props, thr, color, c->d_image, c->stream));
+  // cudaDeviceSynchronize + cudaMemcpy D2H (volumeRender.cpp:280-281)
+  VR_CUDA(c, cudaMemcpyAsync(out, c->d_image, bytes, cudaMemcpyDeviceToHost, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  VR_TRY(collect(c));
+  c->stats.bytes_resident = resident_bytes(c);
+  return VR_OK;
+}
+
+vr_status vr_henyey_greenstein(uint32_t n, float g, float *out) {
+  if (!out || n == 0 || n > 1024) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "HenyeyGreenstein: bad size");
+  if (g > 1.0f || g < -1.0f) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "g must be in interval [-1,1]");  // HenyeyGreenstein.cc:44-45
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(nullptr, VR_ERR_NO_DEVICE, "no CUDA device; there is no CPU fallback");
+  float *d = nullptr;
+  const size_t bytes = (size_t)n * n * n * sizeof(float);
+  VR_CUDA(nullptr, cudaMalloc(&d, bytes));
+  cudaError_t e = launch_hg_lut(d, n, g, nullptr);
+  if (e == cudaSuccess) e = cudaMemcpy(out, d, bytes, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(nullptr, VR_ERR_CUDA, "HenyeyGreenstein: %s", cudaGetErrorString(e));
+  return VR_OK;
+}
+
+uint64_t vr_timestamp_ms(int truncate_like_reference) {
+  const uint64_t ms = (uint64_t)std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::system_clock::now().time_since_epoch()).count();
+  return truncate_like_reference ? (ms & 0xffffffffull) : ms;
+}
+
+const char *vr_last_error(const vr_ctx *c) {
+  if (c && live(c)) return c->err.c_str();
+  return tl_error.c_str();
+}
+const char *vr_status_string(vr_status s) {
+  switch (s) {
+  case VR_OK: return "VR_OK";
+  case VR_ERR_INVALID_ARGUMENT: return "VR_ERR_INVALID_ARGUMENT";
+  case VR_ERR_INVALID_HANDLE: return "VR_ERR_INVALID_HANDLE";
+  case VR_ERR_INSUFFICIENT_VRAM: return "VR_ERR_INSUFFICIENT_VRAM";
+  case VR_ERR_CUDA: return "VR_ERR_CUDA";
+  case VR_ERR_NO_DEVICE: return "VR_ERR_NO_DEVICE";
+  case VR_ERR_UNSUPPORTED: return "VR_ERR_UNSUPPORTED";
+  }
+  return "?";
+}
+int vr_abi_version(void) { return VR_ABI_VERSION; }
+
+vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
+  VR_CHECK_HANDLE(c);
+  if (option < 0 || option > VR_OPT_COUNT_SAMPLES) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
+  c->opt[option] = value;
+  return VR_OK;
+}
+vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
+  VR_CHECK_HANDLE(c);
+  if (option < 0 || option > VR_OPT_COUNT_SAMPLES || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  *value = c->opt[option];
+  return VR_OK;
+}
+vr_status vr_get_stats(vr_ctx *c, vr_stats *out) {
+  VR_CHECK_HANDLE(c);
+  if (!out) return fail(c, VR_ERR_INVALID_ARGUMENT, "null stats");
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  c->stats.bytes_resident = resident_bytes(c);
+  *out = c->stats;
+  return VR_OK;
+}
+vr_status vr_set_stream(vr_ctx *c, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  c->own_stream = false;
+  c->stream = (cudaStream_t)cuda_stream;
+  return VR_OK;
+}
+vr_status vr_get_device(vr_ctx *c, int *device) {
+  VR_CHECK_HANDLE(c);
+  if (device) *device = c->device;
+  return VR_OK;
+}
+
+vr_status vr_synth_volume(vr_ctx *c, int kind, uint32_t seed, const uint64_t dims[3], int32_t dtype, void *d_out) {
+  VR_CHECK_HANDLE(c);
+  if (!dims || !d_out || kind < 0 || kind > 1 || (dtype != VR_DTYPE_F32 && dtype != VR_DTYPE_BF16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "synth: bad argument");
+  VR_TRY(set_device(c));
+  VR_CUDA(c, launch_synth(d_out, kind, seed, (int)dims[0], (int)dims[1], (int)dims[2], dtype, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
+vr_status vr_volume_gradient(vr_ctx *c, const vr_volume *in, int32_t out_memspace, void *gx, void *gy, void *gz) {
+  VR_CHECK_HANDLE(c);
+  if (!in || !in->data || !gx || !gy || !gz) return fail(c, VR_ERR_INVALID_ARGUMENT, "gradient: null argument");
+  if (in->dtype != VR_DTYPE_F32 && in->dtype != VR_DTYPE_BF16) return fail(c, VR_ERR_INVALID_ARGUMENT, "gradient: bad dtype");
+  VR_TRY(set_device(c));
+  const uint64_t w = in->dims[0], h = in->dims[1], d = in->dims[2];
+  if (w == 0 || h == 0 || d == 0 || w > 0x7fffffff || h > 0x7fffffff || d > 0x7fffffff) return fail(c, VR_ERR_INVALID_ARGUMENT, "gradient: bad dims");
+  const size_t bytes = (size_t)w * h * d * elem_size(in->dtype);
+  void *tmp[4] = {nullptr, nullptr, nullptr, nullptr};
+  auto cleanup = [&]() {
+    for (void *p : tmp)
+      if (p) cudaFree(p);
+  };
+  const void *d_in = in->data;
+  void *d_out[3] = {gx, gy, gz};
+  cudaError_t e = cudaSuccess;
+  if (in->memspace == VR_MEM_HOST) {
+    e = cudaMalloc(&tmp[0], bytes);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(tmp[0], in->data, bytes, cudaMemcpyHostToDevice, c->stream);
+    d_in = tmp[0];
+  }
+  if (out_memspace == VR_MEM_HOST)
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) {
+      e = cudaMalloc(&tmp[1 + i], bytes);
+      d_out[i] = tmp[1 + i];
+    }
+  if (e == cudaSuccess) e = launch_gradient(d_in, (int)w, (int)h, (int)d, in->dtype, d_out[0], d_out[1], d_out[2], c->stream);
+  if (out_memspace == VR_MEM_HOST) {
+    void *host[3] = {gx, gy, gz};
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = cudaMemcpyAsync(host[i], d_out[i], bytes, cudaMemcpyDeviceToHost, c->stream);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cleanup();
+  if (e != cudaSuccess)
+    return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_INSUFFICIENT_VRAM : VR_ERR_CUDA, "gradient: %s", cudaGetErrorString(e));
+  return VR_OK;
+}
+vr_status vr_device_alloc(vr_ctx *c, size_t bytes, void **d_ptr) {
+  VR_CHECK_HANDLE(c);
+  if (!d_ptr) return fail(c, VR_ERR_INVALID_ARGUMENT, "null pointer");
+  VR_TRY(set_device(c));
+  VR_CUDA(c, cudaMalloc(d_ptr, bytes));
+  return VR_OK;
+}
+vr_status vr_device_free(vr_ctx *c, void *d_ptr) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  VR_CUDA(c, cudaFree(d_ptr));
+  return VR_OK;
+}
+vr_status vr_device_download(vr_ctx *c, void *host_dst, const void *d_src, size_t bytes) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  VR_CUDA(c, cudaMemcpyAsync(host_dst, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
+
+}  // extern "C"

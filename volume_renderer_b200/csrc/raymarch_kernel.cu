@@ -1,0 +1,119 @@
+// raymarch_kernel.cu - the ray-march kernel for sm_100a and its launcher.
+//
+// Replaces d_render<<<grid,16x16>>> (src/C/vr/volumeRender_kernel.cu:365-507, launched at :590).
+// Design:
+//  * persistent grid: (SMs x resident blocks) blocks of 8 warps; every warp pulls 8x4-pixel
+//    work items from a global atomic counter, so long and short rays balance across the chip;
+//  * per warp a "while-while" loop: lanes first run the cheap empty-space phase (serial
+//    t/pos recurrences only) until they stand on a sample that can contribute, then all such
+//    lanes execute the shading phase together; __any_sync ends the tile when every lane has
+//    terminated (early ray termination or t > tfar);
+//  * volumes are padded (bricked) arrays read through the read-only path; no tensor cores, the
+//    path is gather + fp32 accumulate.
+#include <cuda_runtime.h>
+
+#include "raymarch_core.h"
+#include "raymarch_launch.h"
+
+namespace vrb {
+
+static constexpr int kBlockThreads = 256;
+static constexpr unsigned kFull = 0xffffffffu;
+
+template <int GRAD, int LAYOUT, typename E>
+__global__ void __launch_bounds__(kBlockThreads) k_raymarch(const __grid_constant__ KernelParams P) {
+  const int lane = threadIdx.x & 31;
+  const F3 origin = ray_origin(P);
+  const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
+  const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);
+  const uint32_t wt_per_tile = (uint32_t)(P.wt_x * P.wt_y);
+  unsigned long long tot_marched = 0, tot_shaded = 0, tot_hits = 0;
+
+  for (;;) {
+    uint32_t w = 0;
+    if (lane == 0) w = atomicAdd(P.work_counter, 1u);
+    w = __shfl_sync(kFull, w, 0);
+    if (w >= P.num_work) break;
+    // work item -> pixel
+    const uint32_t owned = w / wt_per_tile, sub = w - owned * wt_per_tile;
+    const uint32_t tile = (uint32_t)P.part_rank + owned * (uint32_t)P.part_nranks;
+    const uint32_t ty = tile / (uint32_t)P.ntx, tx = tile - ty * (uint32_t)P.ntx;
+    const uint32_t sy = sub / (uint32_t)P.wt_x, sx = sub - sy * (uint32_t)P.wt_x;
+    const uint32_t x = tx * P.tile_w + sx * 8 + (lane & 7);
+    const uint32_t y = ty * P.tile_h + sy * 4 + (lane >> 3);
+
+    Ray r;
+    bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, x, y, origin, r);
+    bool active = hit;
+    F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
+    if (active && P.skip) skip_setup(P, r, bscale, dq, inv_dq);
+
+    while (__any_sync(kFull, active)) {
+      if (active && P.skip) active = skip_empty(P, r, bmin, bscale, dq, inv_dq);
+      if (active) {
+        shade_sample<GRAD, LAYOUT, E>(P, origin, r);
+        active = ray_advance(P, r);
+      }
+    }
+    if (hit) {
+      // column-major planar H x W x 3 (kernel.cu:496-506); lanes of a warp cover 4 consecutive y
+      const size_t size = (size_t)P.W * P.H, k = (size_t)x * P.H + y;
+      P.out[k] = r.sx;
+      P.out[k + size] = r.sy;
+      P.out[k + 2 * size] = r.sz;
+      tot_marched += r.n_marched;
+      tot_shaded += r.n_shaded;
+      tot_hits += 1;
+    }
+  }
+  if (P.count) {
+    for (int o = 16; o > 0; o >>= 1) {
+      tot_marched += __shfl_xor_sync(kFull, tot_marched, o);
+      tot_shaded += __shfl_xor_sync(kFull, tot_shaded, o);
+      tot_hits += __shfl_xor_sync(kFull, tot_hits, o);
+    }
+    if (lane == 0) {
+      atomicAdd(P.stats + 0, tot_marched);
+      atomicAdd(P.stats + 1, tot_shaded);
+      atomicAdd(P.stats + 2, tot_hits);
+    }
+  }
+}
+
+template <int GRAD, int LAYOUT, typename E>
+static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E>, kBlockThreads, 0);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  // persistent grid: a whole number of waves, never more warps than work items
+  long long blocks = (long long)sm_count * per_sm;
+  const long long need = ((long long)P.num_work + (kBlockThreads / 32) - 1) / (kBlockThreads / 32);
+  if (blocks > need) blocks = need;
+  if (blocks < 1) blocks = 1;
+  k_raymarch<GRAD, LAYOUT, E><<<(unsigned)blocks, kBlockThreads, 0, stream>>>(P);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, int variant, cudaStream_t stream, int sm_count) {
+  (void)variant;
+  const int g = P.gradient_method ? 1 : 0;
+#define VR_CASE(G, L, EL) return launch_one<G, L, EL>(P, stream, sm_count)
+  if (dtype == 0) {
+    if (layout == LAYOUT_BRICK) {
+      if (g) VR_CASE(1, LAYOUT_BRICK, ElemF32);
+      VR_CASE(0, LAYOUT_BRICK, ElemF32);
+    }
+    if (g) VR_CASE(1, LAYOUT_LINEAR, ElemF32);
+    VR_CASE(0, LAYOUT_LINEAR, ElemF32);
+  }
+  if (layout == LAYOUT_BRICK) {
+    if (g) VR_CASE(1, LAYOUT_BRICK, ElemBF16);
+    VR_CASE(0, LAYOUT_BRICK, ElemBF16);
+  }
+  if (g) VR_CASE(1, LAYOUT_LINEAR, ElemBF16);
+  VR_CASE(0, LAYOUT_LINEAR, ElemBF16);
+#undef VR_CASE
+}
+
+}  // namespace vrb

@@ -1,0 +1,46 @@
+// raymarch_launch.h - host-callable launchers of the device code (kernels live in the .cu files).
+#ifndef RAYMARCH_LAUNCH_H_
+#define RAYMARCH_LAUNCH_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "vr_types.h"
+
+namespace vrb {
+
+// raymarch_kernel.cu: the ray march.  layout / dtype describe the volume textures of the launch
+// (all volume slots of one launch share them; the LUT is always fp32 linear).
+cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, int variant, cudaStream_t stream,
+                            int sm_count);
+
+// resident_kernels.cu: everything that builds the resident representation of a volume.
+struct RepackArgs {
+  void *dst;           // padded (bricked) storage of the whole volume
+  const void *src;     // staged source slices, MATLAB layout (dims[0] fastest)
+  int w, h, d;         // voxel dims
+  int src_z0;          // z index of the first staged slice
+  uint64_t o0, o1;     // destination element range [o0, o1) to produce
+  uint32_t sy, sz;     // destination strides (see TexDesc)
+  int layout;          // LAYOUT_*
+  int src_dtype;       // vr_dtype of src
+  int dst_dtype;       // vr_dtype of dst
+};
+cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream);
+
+// occupancy bit grid: bit set when any voxel of the 8^3 macro cell dilated by `dilate` voxels is
+// non-zero (read from the padded storage).
+cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *occ, int ocx, int ocy, int ocz,
+                             int dilate, cudaStream_t stream);
+
+// Henyey-Greenstein LUT (HenyeyGreenstein.cc:47-91): n^3 floats on the device.
+cudaError_t launch_hg_lut(float *d_out, uint32_t n, float g, cudaStream_t stream);
+
+// synthetic ViBE-Z-shaped volumes; kind 0 = brain, 1 = tubes
+cudaError_t launch_synth(void *d_out, int kind, uint32_t seed, int w, int h, int d, int dtype, cudaStream_t stream);
+
+// MATLAB gradient() of a MATLAB-layout volume (Volume.m:181-205): gx = d/d dim2, gy = d/d dim1, gz = d/d dim3
+cudaError_t launch_gradient(const void *d_in, int w, int h, int d, int dtype, void *gx, void *gy, void *gz, cudaStream_t stream);
+
+}  // namespace vrb
+#endif

@@ -1,0 +1,283 @@
+// resident_kernels.cu - kernels that build what stays resident in HBM between renders:
+//   * repack: MATLAB-layout slices -> padded (bricked) storage (replaces cudaMalloc3DArray +
+//     cudaMemcpy3D into an opaque cudaArray, src/C/vr/volumeRender_kernel.cu:522-554)
+//   * occupancy: the empty-space bit grid of a resident volume (no reference counterpart)
+//   * hg_lut: the Henyey-Greenstein table (src/C/mex/HenyeyGreenstein.cc:47-91) on the GPU
+//   * synth: seeded synthetic ViBE-Z-shaped volumes generated straight into HBM
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include "raymarch_core.h"
+#include "raymarch_launch.h"
+
+namespace vrb {
+
+// ---- repack ---------------------------------------------------------------------------------
+__device__ __forceinline__ float load_src(const void *p, size_t i, int dtype) {
+  if (dtype == 0) return __ldg(static_cast<const float *>(p) + i);
+  return __uint_as_float((uint32_t)__ldg(static_cast<const uint16_t *>(p) + i) << 16);
+}
+__device__ __forceinline__ void store_dst(void *p, size_t i, int dtype, float v) {
+  if (dtype == 0) {
+    static_cast<float *>(p)[i] = v;
+  } else {
+    static_cast<__nv_bfloat16 *>(p)[i] = __float2bfloat16_rn(v);
+  }
+}
+
+// One thread per destination element, destination-offset order: a warp writes 128 contiguous
+// bytes (fp32) and reads 4 source rows of 8 voxels (bricked) or one row of 32 (linear).
+template <int LAYOUT>
+__global__ void __launch_bounds__(256) k_repack(const RepackArgs a) {
+  const uint64_t n = a.o1 - a.o0;
+  const int pw = a.w + 2, ph = a.h + 2, pd = a.d + 2;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t o = a.o0 + i;
+    int X, Y, Z;
+    if (LAYOUT == LAYOUT_BRICK) {
+      const uint64_t bz = o / a.sz;
+      const uint32_t rz = (uint32_t)(o - bz * a.sz);
+      const uint32_t by = rz / a.sy, ry = rz - by * a.sy;
+      const uint32_t bx = ry >> 9, in = ry & 511;
+      X = (int)(bx << 3) + (int)(in & 7);
+      Y = (int)(by << 3) + (int)((in >> 3) & 7);
+      Z = (int)(bz << 3) + (int)(in >> 6);
+    } else {
+      const uint64_t z = o / a.sz;
+      const uint32_t rz = (uint32_t)(o - z * a.sz);
+      Y = (int)(rz / a.sy);
+      X = (int)(rz - (uint32_t)Y * a.sy);
+      Z = (int)z;
+    }
+    float v = 0.0f;
+    if (X < pw && Y < ph && Z < pd) {
+      const int sx = min(max(X - 1, 0), a.w - 1);
+      const int sy = min(max(Y - 1, 0), a.h - 1);
+      const int sz = min(max(Z - 1, 0), a.d - 1);
+      v = load_src(a.src, ((size_t)(sz - a.src_z0) * a.h + sy) * a.w + sx, a.src_dtype);
+    }
+    store_dst(a.dst, o, a.dst_dtype, v);
+  }
+}
+
+cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream) {
+  const uint64_t n = a.o1 - a.o0;
+  if (n == 0) return cudaSuccess;
+  uint64_t blocks = (n + 255) / 256;
+  if (blocks > 148ull * 64) blocks = 148ull * 64;
+  if (a.layout == LAYOUT_BRICK)
+    k_repack<LAYOUT_BRICK><<<(unsigned)blocks, 256, 0, stream>>>(a);
+  else
+    k_repack<LAYOUT_LINEAR><<<(unsigned)blocks, 256, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
+// ---- occupancy ------------------------------------------------------------------------------
+// One warp per macro cell: scans padded voxels [8c+1-dilate, 8c+8+dilate] per axis (voxel index
+// v sits at padded index v+1; the replicated border only repeats edge voxels, so reading it is
+// harmless) and sets the cell's bit when any value is not exactly +-0.
+template <int LAYOUT, typename E>
+__global__ void __launch_bounds__(256) k_occupancy(const TexDesc t, uint32_t *occ, int ocx, int ocy, int ocz, int dilate) {
+  const int lane = threadIdx.x & 31;
+  const uint64_t ncell = (uint64_t)ocx * ocy * ocz;
+  const int span = 8 + 2 * dilate;
+  const int pw = t.w + 2, ph = t.h + 2, pd = t.d + 2;
+  for (uint64_t cell = (uint64_t)blockIdx.x * 8 + (threadIdx.x >> 5); cell < ncell; cell += (uint64_t)gridDim.x * 8) {
+    const int cx = (int)(cell % ocx), cy = (int)((cell / ocx) % ocy), cz = (int)(cell / ((uint64_t)ocx * ocy));
+    const int x0 = cx * 8 + 1 - dilate, y0 = cy * 8 + 1 - dilate, z0 = cz * 8 + 1 - dilate;
+    bool any = false;
+    const int total = span * span * span;
+    for (int i = lane; i < total && !any; i += 32) {
+      const int dx = i % span, dy = (i / span) % span, dz = i / (span * span);
+      const int X = min(max(x0 + dx, 0), pw - 1), Y = min(max(y0 + dy, 0), ph - 1), Z = min(max(z0 + dz, 0), pd - 1);
+      typedef Addr<LAYOUT> A;
+      const float v = E::load(t.p, A::x(X) + A::y(Y, t.sy) + A::z(Z, t.sz));
+      any = !(v == 0.0f);  // NaN counts as occupied
+    }
+    if (__any_sync(0xffffffffu, any) && lane == 0) atomicOr(occ + (cell >> 5), 1u << (cell & 31));
+  }
+}
+
+cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *occ, int ocx, int ocy, int ocz,
+                             int dilate, cudaStream_t stream) {
+  const uint64_t ncell = (uint64_t)ocx * ocy * ocz;
+  uint64_t blocks = (ncell + 7) / 8;
+  if (blocks > 148ull * 32) blocks = 148ull * 32;
+  if (blocks < 1) blocks = 1;
+  const unsigned g = (unsigned)blocks;
+  if (layout == LAYOUT_BRICK) {
+    if (dtype == 0)
+      k_occupancy<LAYOUT_BRICK, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+    else
+      k_occupancy<LAYOUT_BRICK, ElemBF16><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+  } else {
+    if (dtype == 0)
+      k_occupancy<LAYOUT_LINEAR, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+    else
+      k_occupancy<LAYOUT_LINEAR, ElemBF16><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+  }
+  return cudaGetLastError();
+}
+
+// ---- Henyey-Greenstein LUT --------------------------------------------------------------------
+// HenyeyGreenstein.cc:47-91: index k = c*n*n + a*n + b with gamma = c*pi/n, alpha = a*pi/n,
+// beta = b*pi/n; cos(theta) = dot(Rx(gamma) * (sin a, 0, cos a), (sin b, 0, cos b))
+//                           = sin a * sin b + cos g * cos a * cos b          (float3.h:74-104)
+// value = 1/(4 pi) * (1 - g^2) / sqrt((1 + g^2 - 2 g cos(theta))^3).  fp32 like the reference;
+// the explicit _rn intrinsics keep the reference's operation order (no FMA contraction).
+__global__ void k_hg_lut(float *out, uint32_t n, float g) {
+  const float PI = 3.14159265358979323846f;
+  const uint64_t total = (uint64_t)n * n * n;
+  const float frac = PI / (float)n;
+  for (uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t b = (uint32_t)(k % n), a = (uint32_t)((k / n) % n), c = (uint32_t)(k / ((uint64_t)n * n));
+    const float gamma = __fmul_rn((float)c, frac), alpha = __fmul_rn((float)a, frac), beta = __fmul_rn((float)b, frac);
+    const float sa = sinf(alpha), ca = cosf(alpha), sb = sinf(beta), cb = cosf(beta), cg = cosf(gamma);
+    // rotated lightOut = (sa, sin(g)*ca, cg*ca); the y component meets lightIn.y = 0
+    const float rz = __fmul_rn(cg, ca);
+    const float cosTheta = __fadd_rn(__fadd_rn(__fmul_rn(sa, sb), 0.0f), __fmul_rn(rz, cb));
+    const float g2 = __fmul_rn(g, g);
+    const float num = __fsub_rn(1.0f, g2);
+    const float base = __fsub_rn(__fadd_rn(1.0f, g2), __fmul_rn(__fmul_rn(2.0f, g), cosTheta));
+    const float den = sqrtf(__fmul_rn(__fmul_rn(base, base), base));
+    out[k] = __fmul_rn(__fdiv_rn(1.0f, __fmul_rn(4.0f, PI)), __fdiv_rn(num, den));
+  }
+}
+cudaError_t launch_hg_lut(float *d_out, uint32_t n, float g, cudaStream_t stream) {
+  const uint64_t total = (uint64_t)n * n * n;
+  uint64_t blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks < 1) blocks = 1;
+  k_hg_lut<<<(unsigned)blocks, 256, 0, stream>>>(d_out, n, g);
+  return cudaGetLastError();
+}
+
+// ---- synthetic volumes ------------------------------------------------------------------------
+// Counter-based generator: every voxel is a pure function of (x, y, z, dims, seed), written with
+// explicit round-to-nearest intrinsics and no transcendental functions so that the numpy twin in
+// tests/synth.py reproduces it bit for bit.
+__host__ __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x7feb352du;
+  x ^= x >> 15;
+  x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t hash3(uint32_t i, uint32_t j, uint32_t k, uint32_t seed) {
+  return hash_u32(i * 0x9e3779b1u ^ hash_u32(j * 0x85ebca77u ^ hash_u32(k * 0xc2b2ae3du ^ seed)));
+}
+__device__ __forceinline__ float u01(uint32_t h) { return __fmul_rn((float)(h >> 8), 1.0f / 16777216.0f); }
+__device__ __forceinline__ float lerp_rn(float a, float b, float f) { return __fadd_rn(a, __fmul_rn(f, __fsub_rn(b, a))); }
+__device__ __forceinline__ float smooth_rn(float f) {  // f*f*(3-2f)
+  return __fmul_rn(__fmul_rn(f, f), __fsub_rn(3.0f, __fmul_rn(2.0f, f)));
+}
+__device__ float value_noise(float px, float py, float pz, uint32_t seed) {
+  const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+  const uint32_t i = (uint32_t)(int)fx, j = (uint32_t)(int)fy, k = (uint32_t)(int)fz;
+  const float wx = smooth_rn(__fsub_rn(px, fx)), wy = smooth_rn(__fsub_rn(py, fy)), wz = smooth_rn(__fsub_rn(pz, fz));
+  const float c000 = u01(hash3(i, j, k, seed)), c100 = u01(hash3(i + 1, j, k, seed));
+  const float c010 = u01(hash3(i, j + 1, k, seed)), c110 = u01(hash3(i + 1, j + 1, k, seed));
+  const float c001 = u01(hash3(i, j, k + 1, seed)), c101 = u01(hash3(i + 1, j, k + 1, seed));
+  const float c011 = u01(hash3(i, j + 1, k + 1, seed)), c111 = u01(hash3(i + 1, j + 1, k + 1, seed));
+  const float c00 = lerp_rn(c000, c100, wx), c10 = lerp_rn(c010, c110, wx);
+  const float c01 = lerp_rn(c001, c101, wx), c11 = lerp_rn(c011, c111, wx);
+  return lerp_rn(lerp_rn(c00, c10, wy), lerp_rn(c01, c11, wy), wz);
+}
+// voxel-centre coordinate in [-1,1]: ((i + 0.5) / n) * 2 - 1
+__device__ __forceinline__ float ncoord(int i, int n) {
+  return __fsub_rn(__fmul_rn(__fdiv_rn(__fadd_rn((float)i, 0.5f), (float)n), 2.0f), 1.0f);
+}
+
+// kind 0: "brain" - soft-edged ellipsoid (semi-axes 0.8, 0.55, 0.4 of the box) times
+// (0.6 + 0.4 * 3-octave value noise), clamped to [0,1], exactly 0 outside the ellipsoid.
+__device__ float synth_brain(int x, int y, int z, int w, int h, int d, uint32_t seed) {
+  const float u = ncoord(x, w), v = ncoord(y, h), s = ncoord(z, d);
+  const float a = __fdiv_rn(u, 0.8f), b = __fdiv_rn(v, 0.55f), c = __fdiv_rn(s, 0.4f);
+  const float r2 = __fadd_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), __fmul_rn(c, c));
+  if (!(r2 < 1.0f)) return 0.0f;
+  const float m = smooth_rn(fminf(__fmul_rn(__fsub_rn(1.0f, r2), 4.0f), 1.0f));
+  const float qx = __fmul_rn(__fadd_rn(u, 1.0f), 0.5f), qy = __fmul_rn(__fadd_rn(v, 1.0f), 0.5f), qz = __fmul_rn(__fadd_rn(s, 1.0f), 0.5f);
+  const float n0 = value_noise(__fmul_rn(qx, 8.0f), __fmul_rn(qy, 8.0f), __fmul_rn(qz, 8.0f), seed);
+  const float n1 = value_noise(__fmul_rn(qx, 16.0f), __fmul_rn(qy, 16.0f), __fmul_rn(qz, 16.0f), seed + 1u);
+  const float n2 = value_noise(__fmul_rn(qx, 32.0f), __fmul_rn(qy, 32.0f), __fmul_rn(qz, 32.0f), seed + 2u);
+  const float nz = __fadd_rn(__fadd_rn(__fmul_rn(0.5f, n0), __fmul_rn(0.3f, n1)), __fmul_rn(0.2f, n2));
+  const float val = __fmul_rn(m, __fadd_rn(0.6f, __fmul_rn(0.4f, nz)));
+  return fminf(fmaxf(val, 0.0f), 1.0f);
+}
+
+// kind 1: "tubes" - union of 200 seeded capsules in [-1,1]^3, radius 3..6 voxels (of dim w),
+// soft edge of 1.5 voxels; exactly 0 away from every capsule.
+enum { kTubes = 200 };
+__device__ float synth_tubes(int x, int y, int z, int w, int h, int d, uint32_t seed) {
+  const float px = ncoord(x, w), py = ncoord(y, h), pz = ncoord(z, d);
+  const float vox = __fdiv_rn(2.0f, (float)w);
+  float best = 0.0f;
+  for (uint32_t t = 0; t < kTubes; ++t) {
+    const uint32_t s = seed ^ (t * 0x632be5abu);
+    const float ax = __fsub_rn(__fmul_rn(u01(hash_u32(s + 1u)), 1.6f), 0.8f);
+    const float ay = __fsub_rn(__fmul_rn(u01(hash_u32(s + 2u)), 1.6f), 0.8f);
+    const float az = __fsub_rn(__fmul_rn(u01(hash_u32(s + 3u)), 1.6f), 0.8f);
+    const float dx = __fsub_rn(__fmul_rn(u01(hash_u32(s + 4u)), 0.8f), 0.4f);
+    const float dy = __fsub_rn(__fmul_rn(u01(hash_u32(s + 5u)), 0.8f), 0.4f);
+    const float dz = __fsub_rn(__fmul_rn(u01(hash_u32(s + 6u)), 0.8f), 0.4f);
+    const float rad = __fmul_rn(__fadd_rn(3.0f, __fmul_rn(u01(hash_u32(s + 7u)), 3.0f)), vox);
+    const float ex = __fsub_rn(px, ax), ey = __fsub_rn(py, ay), ez = __fsub_rn(pz, az);
+    const float dd = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+    const float ed = __fadd_rn(__fadd_rn(__fmul_rn(ex, dx), __fmul_rn(ey, dy)), __fmul_rn(ez, dz));
+    const float tt = fminf(fmaxf(__fdiv_rn(ed, fmaxf(dd, 1e-12f)), 0.0f), 1.0f);
+    const float cx = __fsub_rn(ex, __fmul_rn(tt, dx)), cy = __fsub_rn(ey, __fmul_rn(tt, dy)), cz = __fsub_rn(ez, __fmul_rn(tt, dz));
+    const float dist = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(cx, cx), __fmul_rn(cy, cy)), __fmul_rn(cz, cz)));
+    const float edge = __fmul_rn(1.5f, vox);
+    const float vv = fminf(fmaxf(__fdiv_rn(__fsub_rn(rad, dist), edge), 0.0f), 1.0f);
+    best = fmaxf(best, vv);
+  }
+  return best;
+}
+
+__global__ void __launch_bounds__(256) k_synth(void *out, int kind, uint32_t seed, int w, int h, int d, int dtype) {
+  const uint64_t total = (uint64_t)w * h * d;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % w), y = (int)((i / w) % h), z = (int)(i / ((uint64_t)w * h));
+    const float v = kind == 0 ? synth_brain(x, y, z, w, h, d, seed) : synth_tubes(x, y, z, w, h, d, seed);
+    store_dst(out, i, dtype, v);
+  }
+}
+cudaError_t launch_synth(void *d_out, int kind, uint32_t seed, int w, int h, int d, int dtype, cudaStream_t stream) {
+  const uint64_t total = (uint64_t)w * h * d;
+  uint64_t blocks = (total + 255) / 256;
+  if (blocks > 148ull * 64) blocks = 148ull * 64;
+  if (blocks < 1) blocks = 1;
+  k_synth<<<(unsigned)blocks, 256, 0, stream>>>(d_out, kind, seed, w, h, d, dtype);
+  return cudaGetLastError();
+}
+
+// ---- MATLAB gradient() ---------------------------------------------------------------------------
+// Volume.grad (src/matlab/VolumeRender/Volume.m:181-205) calls MATLAB's gradient(Data): unit
+// spacing, central differences inside, one-sided at the ends, zero along a singleton axis; its
+// first output is the derivative along dim 2, the second along dim 1, the third along dim 3.
+__device__ __forceinline__ float grad1(const void *p, int dtype, size_t k, int64_t i, int64_t n, int64_t stride) {
+  if (n < 2) return 0.0f;
+  if (i == 0) return __fsub_rn(load_src(p, k + stride, dtype), load_src(p, k, dtype));
+  if (i == n - 1) return __fsub_rn(load_src(p, k, dtype), load_src(p, k - stride, dtype));
+  return __fdiv_rn(__fsub_rn(load_src(p, k + stride, dtype), load_src(p, k - stride, dtype)), 2.0f);
+}
+__global__ void __launch_bounds__(256) k_gradient(const void *in, int w, int h, int d, int dtype, void *gx, void *gy, void *gz) {
+  const uint64_t total = (uint64_t)w * h * d;
+  for (uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (uint64_t)gridDim.x * blockDim.x) {
+    const int x = (int)(k % w), y = (int)((k / w) % h), z = (int)(k / ((uint64_t)w * h));
+    store_dst(gy, k, dtype, grad1(in, dtype, k, x, w, 1));
+    store_dst(gx, k, dtype, grad1(in, dtype, k, y, h, w));
+    store_dst(gz, k, dtype, grad1(in, dtype, k, z, d, (int64_t)w * h));
+  }
+}
+cudaError_t launch_gradient(const void *d_in, int w, int h, int d, int dtype, void *gx, void *gy, void *gz, cudaStream_t stream) {
+  const uint64_t total = (uint64_t)w * h * d;
+  uint64_t blocks = (total + 255) / 256;
+  if (blocks > 148ull * 64) blocks = 148ull * 64;
+  if (blocks < 1) blocks = 1;
+  k_gradient<<<(unsigned)blocks, 256, 0, stream>>>(d_in, w, h, d, dtype, gx, gy, gz);
+  return cudaGetLastError();
+}
+
+}  // namespace vrb

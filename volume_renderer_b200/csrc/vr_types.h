@@ -1,0 +1,87 @@
+// vr_types.h - POD types shared by the host side (context.cu) and the kernels.
+#ifndef VR_TYPES_H_
+#define VR_TYPES_H_
+
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define VR_HD __host__ __device__ __forceinline__
+#else
+#define VR_HD inline
+#endif
+
+namespace vrb {
+
+// Texture "slots" = the reference's seven texture references (volumeRender_kernel.cu:90-120),
+// numbered like vr::VolumeType (volumeRender.h:152-160).
+enum Slot { S_EM = 0, S_AB = 1, S_RE = 2, S_DX = 3, S_DY = 4, S_DZ = 5, S_LIGHT = 6, S_N = 7 };
+
+enum TexKind {
+  TEX_UNBOUND = 0,  // unbound texture reference: reads 0 (undefined in the reference)
+  TEX_CONST = 1,    // 1x1x1 volume (the default VolumeReflection, VolumeRender.m:131): a constant
+  TEX_VOLUME = 2
+};
+
+enum Layout { LAYOUT_LINEAR = 0, LAYOUT_BRICK = 1 };
+enum { BRICK = 8, BRICK_SHIFT = 3, BRICK_MASK = 7, BRICK_ELEMS = 512 };
+enum { CELL_SHIFT = 3 };  // empty-space macro cell = 8^3 voxels
+
+// Resident volume as the kernels see it.  Storage is PADDED by one replicated voxel on every
+// side (element (X,Y,Z), X in [0,w+1], holds voxel clamp(X-1,0,w-1)...), so that clamp-to-edge
+// addressing (kernel.cu:546-548) needs no integer clamps: coordinates are clamped to [0,1] in
+// float, which gives i = floor(x*N-0.5) in [-1,N-1], and the taps i,i+1 are always stored.
+//   linear : off = X + Y*sy + Z*sz                       (sy = w+2, sz = sy*(h+2))
+//   bricked: off = (X>>3)*512 + (X&7) + (Y>>3)*sy + (Y&7)*8 + (Z>>3)*sz + (Z&7)*64
+//            (sy = nbx*512, sz = nbx*nby*512; a brick is 8x8x8 voxels = 2 KiB of fp32)
+struct TexDesc {
+  const void *p;
+  int w, h, d;
+  float fw, fh, fd;
+  uint32_t sy, sz;
+  int kind;
+  float cval;
+};
+
+enum { MAX_PARAM_LIGHTS = 8 };
+
+// Everything one ray-march launch needs; passed by value as a __grid_constant__ parameter.
+struct KernelParams {
+  float *out;  // W*H*3 floats, column-major planar: k = x*H + y (kernel.cu:496-506)
+  int W, H;
+  // image-space partition (multi-GPU): the image is cut into tile_w x tile_h tiles, tile j is
+  // rendered by the context with j % part_nranks == part_rank.
+  int part_rank, part_nranks;
+  int tile_w, tile_h, ntx, nty;
+  int wt_x, wt_y;          // warp tiles (8x4 px) per partition tile
+  uint32_t num_owned;      // partition tiles owned by this rank
+  uint32_t num_work;       // warp work items = num_owned * wt_x * wt_y
+  unsigned int *work_counter;
+  unsigned long long *stats;  // [0] samples marched, [1] samples shaded, [2] rays hit
+  // vr::RenderOptions (volumeRender.h:81-109)
+  float fEm, fAb, fRe;
+  float boxmin[3], boxmax[3];
+  float m[4][3];  // rows 0..2 camera axes, row 3 = (camXOffset, focal, objDist)
+  float thr, tstep;
+  float color[3];
+  float gstep[3];  // (1/w, 1/h, 1/d) of the emission volume (volumeRender.cpp:273-275)
+  // role -> texture, already resolved through d_idx* on the host (kernel.cu:75-85,127-144)
+  TexDesc em, ab, re;
+  TexDesc em_direct;  // tex_emission itself, as computeGradient reads it (kernel.cu:225-248)
+  TexDesc gx, gy, gz, lut;
+  int ab_is_em;  // absorption role resolves to the same texture as the emission role
+  int re_is_em;  // reflection role resolves to the same texture as the emission role
+  int gradient_method;  // 0 compute, 1 lookup (volumeRender.h:141-144)
+  int frac_bits;        // 0 = fp32 weights, 8 = 1.8 fixed point
+  int skip;             // empty-space skipping on
+  int count;            // maintain stats
+  // lights (volumeRender.h:50-55), position already axis-reversed
+  int n_lights;
+  float lights[MAX_PARAM_LIGHTS][6];
+  const float *lights_more;  // lights beyond MAX_PARAM_LIGHTS, 6 floats each (device memory)
+  // occupancy bit grid of the absorption-role texture: bit (cz*ocy+cy)*ocx+cx set = not empty
+  const uint32_t *occ;
+  int ocx, ocy, ocz;
+};
+
+}  // namespace vrb
+#endif
