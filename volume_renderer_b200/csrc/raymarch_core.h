@@ -20,7 +20,7 @@
 #if defined(__CUDA_ARCH__)
 #define VR_LDG(ptr) __ldg(ptr)
 #define VR_EXPF(x) __expf(x) /* the reference's intrinsic, kernel.cu:456 */
-#define VR_RSQRT(x) rsqrtf(x)
+#define VR_RSQRT(x) (1.0f / sqrtf(x)) /* IEEE divide + sqrt: the normal must not depend on MUFU.RSQ's last bits */
 #else
 #define VR_LDG(ptr) (*(ptr))
 #define VR_EXPF(x) exp2f((x) * 1.4426950408889634f)
