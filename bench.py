@@ -49,7 +49,7 @@ def parse():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     p.add_argument("--variant", type=int, default=0)
-    p.add_argument("--skip", type=int, default=1)
+    p.add_argument("--skip", type=int, default=2)
     p.add_argument("--tile", type=int, default=64)
     return p.parse_args()
 

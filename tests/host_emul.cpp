@@ -5,7 +5,9 @@
  * arithmetic the kernel executes with the oracle before any GPU time is spent.  It is not a
  * product path: nothing under volume_renderer_b200/ builds or loads it.
  */
+#include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -20,6 +22,7 @@ namespace {
 struct HostTex {
   std::vector<float> store;
   std::vector<uint32_t> occ;
+  std::vector<uint8_t> dist;
   TexDesc t{};
   int ocx = 0, ocy = 0, ocz = 0;
 };
@@ -79,10 +82,26 @@ void build(HostTex &T, const float *src, int w, int h, int d, bool with_occ) {
           const size_t cell = ((size_t)cz * T.ocy + cy) * T.ocx + cx;
           if (any) T.occ[cell >> 5] |= 1u << (cell & 31);
         }
+    // distance grid (resident_kernels.cu: k_dist_pass), brute force here
+    const size_t ncell = (size_t)T.ocx * T.ocy * T.ocz;
+    T.dist.assign(ncell, 255);
+    std::vector<int> occl;
+    for (size_t cell = 0; cell < ncell; ++cell)
+      if ((T.occ[cell >> 5] >> (cell & 31)) & 1u) occl.push_back((int)cell);
+    for (size_t cell = 0; cell < ncell; ++cell) {
+      const int cx = (int)(cell % T.ocx), cy = (int)((cell / T.ocx) % T.ocy), cz = (int)(cell / ((size_t)T.ocx * T.ocy));
+      int best = 255;
+      for (int o : occl) {
+        const int ox = o % T.ocx, oy = (o / T.ocx) % T.ocy, oz = o / (T.ocx * T.ocy);
+        const int dd = std::max(std::abs(cx - ox), std::max(std::abs(cy - oy), std::abs(cz - oz)));
+        best = std::min(best, dd);
+      }
+      T.dist[cell] = (uint8_t)best;
+    }
   }
 }
 
-template <int GRAD, int LAYOUT>
+template <int GRAD, int LAYOUT, int UNI>
 void run(const KernelParams &P, float *out, uint64_t *stats) {
   const size_t size = (size_t)P.W * P.H;
   memset(out, 0, size * 3 * sizeof(float));
@@ -92,7 +111,7 @@ void run(const KernelParams &P, float *out, uint64_t *stats) {
     for (int y = 0; y < P.H; ++y) {
       float rgb[3];
       uint32_t m = 0, s = 0;
-      if (!march_pixel<GRAD, LAYOUT, ElemF32>(P, (uint32_t)x, (uint32_t)y, rgb, m, s)) continue;
+      if (!march_pixel<GRAD, LAYOUT, ElemF32, UNI>(P, (uint32_t)x, (uint32_t)y, rgb, m, s)) continue;
       const size_t k = (size_t)x * P.H + y;
       out[k] = rgb[0], out[k + size] = rgb[1], out[k + 2 * size] = rgb[2];
       marched += m, shaded += s, hits += 1;
@@ -104,7 +123,7 @@ template <int LAYOUT>
 int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr_volume *gy, const vr_volume *gz,
          const vr_volume *lut, const vr_light *lights, size_t n_lights, const float factors[3], const float es[3],
          const uint64_t res[2], const float R[9], const float props[3], float thr, const float color[3], int skip,
-         int frac_bits, float *out, uint64_t *stats) {
+         int frac_bits, int variant, float *out, uint64_t *stats) {
   HostTex Em, Re, Gx, Gy, Gz, Lut;
   auto ptr = [](const vr_volume *v) { return v ? static_cast<const float *>(v->data) : nullptr; };
   auto dim = [](const vr_volume *v, int i) { return v ? (int)v->dims[i] : 0; };
@@ -124,8 +143,18 @@ int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr
   P.lut = Lut.t;
   P.gradient_method = gx ? 1 : 0;
   P.frac_bits = frac_bits;
-  P.skip = skip && Em.t.kind == TEX_VOLUME;
-  P.occ = Em.occ.data(), P.ocx = Em.ocx, P.ocy = Em.ocy, P.ocz = Em.ocz;
+  P.skip = Em.t.kind == TEX_VOLUME ? skip : 0;
+  P.occ = Em.occ.data(), P.dist = Em.dist.data(), P.ocx = Em.ocx, P.ocy = Em.ocy, P.ocz = Em.ocz;
+  // shared tap sets exactly as context.cu decides them
+  P.uniform = 1;
+  bool have_geo = false;
+  const TexDesc *vt[] = {&P.em, &P.ab, &P.re, &P.em_direct, &P.gx, &P.gy, &P.gz};
+  for (const TexDesc *t : vt) {
+    if (t->kind != TEX_VOLUME) continue;
+    if (!have_geo) P.geo = *t, P.geo.p = nullptr, have_geo = true;
+    if (t->w != P.geo.w || t->h != P.geo.h || t->d != P.geo.d || t->sy != P.geo.sy || t->sz != P.geo.sz) P.uniform = 0;
+  }
+  if (variant == 1) P.uniform = 0;
   P.count = 1;
   P.n_lights = lut ? (int)n_lights : 0;
   if (P.n_lights > MAX_PARAM_LIGHTS) return 2;
@@ -133,10 +162,11 @@ int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr
     P.lights[i][0] = lights[i].position[2], P.lights[i][1] = lights[i].position[1], P.lights[i][2] = lights[i].position[0];
     memcpy(P.lights[i] + 3, lights[i].color, 12);
   }
-  if (P.gradient_method)
-    run<1, LAYOUT>(P, out, stats);
-  else
-    run<0, LAYOUT>(P, out, stats);
+  if (P.gradient_method) {
+    if (P.uniform) run<1, LAYOUT, 1>(P, out, stats); else run<1, LAYOUT, 0>(P, out, stats);
+  } else {
+    if (P.uniform) run<0, LAYOUT, 1>(P, out, stats); else run<0, LAYOUT, 0>(P, out, stats);
+  }
   return 0;
 }
 
@@ -146,9 +176,9 @@ extern "C" int emul_render(const vr_volume *em, const vr_volume *re, const vr_vo
                            const vr_volume *gz, const vr_volume *lut, const vr_light *lights, size_t n_lights,
                            const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
                            const float props[3], float thr, const float color[3], int layout, int skip, int frac_bits,
-                           float *out, uint64_t *stats) {
+                           int variant, float *out, uint64_t *stats) {
   if (!em) return 1;
   if (layout == LAYOUT_BRICK)
-    return emul<LAYOUT_BRICK>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, out, stats);
-  return emul<LAYOUT_LINEAR>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, out, stats);
+    return emul<LAYOUT_BRICK>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, out, stats);
+  return emul<LAYOUT_LINEAR>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, out, stats);
 }

@@ -16,7 +16,7 @@ def brain():
 
 
 @pytest.mark.parametrize("layout", [0, 1])
-@pytest.mark.parametrize("skip", [0, 1])
+@pytest.mark.parametrize("skip", [0, 1, 2])
 @pytest.mark.parametrize("lights", [0, 1, 2])
 def test_on_the_fly_gradient(brain, layout, skip, lights):
     r = vrt.example1_scene(vrt.OracleVolumeRender, brain, (80, 64), lights=max(lights, 1))
@@ -36,8 +36,11 @@ def test_gradient_lookup(brain, layout):
     gx, gy, gz = r.VolumeEmission.grad()
     r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
     ref = r.render()
-    img, _ = vrt.emul_render(r, layout=layout, skip=1)
-    assert np.array_equal(img, ref)
+    o = r._backend.stats(r.objectHandle)
+    for skip, variant in ((1, 0), (2, 0), (2, 1)):
+        img, st = vrt.emul_render(r, layout=layout, skip=skip, variant=variant)
+        assert np.array_equal(img, ref)
+        assert st[0] == o.samples_marched
 
 
 def test_anisotropic_and_frac_bits():
@@ -58,7 +61,7 @@ def test_skipping_with_tubes_and_inside_camera():
     r.OpacityThreshold = 0.5
     r.FactorAbsorption = 30.0  # early ray termination does happen
     ref = r.render()
-    for skip in (0, 1):
+    for skip in (0, 1, 2):
         img, st = vrt.emul_render(r, layout=1, skip=skip)
         assert np.array_equal(img, ref)
         assert st[0] == r._backend.stats(r.objectHandle).samples_marched
@@ -83,3 +86,23 @@ def test_stereo_offset_passes():
         ref = r.p_render(off, res)
         img, _ = vrt.emul_render(r, layout=1, skip=1, resolution=res, xoffset=off)
         assert np.array_equal(img, ref)
+
+
+def test_closed_form_jumps_axis_parallel_and_zero_crossings():
+    """The exact fast-forward must survive rays whose coordinates sit at 0 / cross 0 (binade
+    borders) and rays parallel to an axis: no rotation, centre pixel looks straight down z."""
+    vol = np.zeros((48, 40, 56), dtype=np.float32, order="F")
+    vol[20:28, 16:24, 40:52] = vrt.synth_brain((8, 8, 12)) + np.float32(0.2)
+    vol[2:5, 30:36, 3:9] = 0.7
+    for dist, rot in ((6.0, (0, 0, 0)), (2.5, (90, 0, 0)), (6.0, (45, 45, 45)), (0.3, (10, 200, 5))):
+        r = vrt.example1_scene(vrt.OracleVolumeRender, vol, (65, 49), lights=1)
+        r.RotationMatrix = np.eye(3)
+        r.rotate(*rot)
+        r.DistanceToObject = dist
+        r.ElementSizeUm = [1.0, 1.3, 0.7]
+        ref = r.render()
+        o = r._backend.stats(r.objectHandle)
+        for skip in (1, 2):
+            img, st = vrt.emul_render(r, layout=1, skip=skip)
+            assert np.array_equal(img, ref), (dist, rot, skip)
+            assert st[0] == o.samples_marched and st[2] == o.rays_hit, (dist, rot, skip, st, o.samples_marched)

@@ -58,11 +58,12 @@ def test_example1_shape(brain64, lut, lights):
     _check(gpu, orc)
 
 
-@pytest.mark.parametrize("brick,skip", [(0, 0), (0, 1), (1, 0), (1, 1)])
-def test_layout_and_skipping_are_invisible(brain64, lut, brick, skip):
+@pytest.mark.parametrize("brick,skip,variant", [(0, 0, 0), (0, 1, 0), (1, 0, 1), (1, 1, 1), (0, 2, 1), (1, 2, 0)])
+def test_layout_and_skipping_are_invisible(brain64, lut, brick, skip, variant):
     gpu, orc = _pair(brain64, (128, 128), 1, lut)
     gpu.setOption(_abi.OPT_BRICK_LAYOUT, brick)
     gpu.setOption(_abi.OPT_EMPTY_SPACE_SKIP, skip)
+    gpu.setOption(_abi.OPT_KERNEL_VARIANT, variant)
     img, _ = _check(gpu, orc)
     base = vrt.example1_scene(api.VolumeRender, brain64, (128, 128), lights=1, lut=lut)
     base.setOption(_abi.OPT_BRICK_LAYOUT, 0)

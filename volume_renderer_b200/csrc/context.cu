@@ -65,6 +65,8 @@ struct Resident {
   size_t storage_bytes = 0;
   uint32_t *occ = nullptr;  // occupancy bit grid
   size_t occ_bytes = 0;
+  uint8_t *dist = nullptr;  // distance grid (cells to the nearest non-empty cell)
+  size_t dist_bytes = 0;
   int ocx = 0, ocy = 0, ocz = 0;
   int w = 0, h = 0, d = 0;
   int dtype = VR_DTYPE_F32;
@@ -148,13 +150,14 @@ bool live(const vr_ctx *c) {
 void release(vr_ctx *c, Resident &r) {
   if (r.storage) cudaFree(r.storage);
   if (r.occ) cudaFree(r.occ);
+  if (r.dist) cudaFree(r.dist);
   r = Resident();
   (void)c;
 }
 
 uint64_t resident_bytes(const vr_ctx *c) {
   uint64_t b = 0;
-  for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes;
+  for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes + c->tex[i].dist_bytes;
   b += c->image_cap + c->stage_cap + c->lights_more_cap;
   return b;
 }
@@ -284,6 +287,10 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
     TexDesc t{};
     t.p = r.storage, t.w = r.w, t.h = r.h, t.d = r.d, t.sy = r.sy, t.sz = r.sz, t.kind = r.kind;
     VR_CUDA(c, launch_occupancy(t, r.layout, r.dtype, r.occ, r.ocx, r.ocy, r.ocz, 2, c->stream));
+    r.dist_bytes = (size_t)ncell;
+    VR_CUDA(c, cudaMalloc(&r.dist, r.dist_bytes));
+    VR_TRY(ensure_stage(c, r.dist_bytes));  // scratch of the middle pass; stream order protects it
+    VR_CUDA(c, launch_distance(r.occ, r.dist, static_cast<uint8_t *>(c->d_stage), r.ocx, r.ocy, r.ocz, c->stream));
   }
   return VR_OK;
 }
@@ -493,8 +500,27 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   }
   if (dtype < 0) dtype = VR_DTYPE_F32, layout = LAYOUT_LINEAR;
   const Resident &rab = c->tex[sAb];
-  P.skip = c->opt[VR_OPT_EMPTY_SPACE_SKIP] && rab.kind == TEX_VOLUME && rab.occ;
-  P.occ = rab.occ, P.ocx = rab.ocx, P.ocy = rab.ocy, P.ocz = rab.ocz;
+  P.skip = (rab.kind == TEX_VOLUME && rab.occ && rab.dist) ? (int)c->opt[VR_OPT_EMPTY_SPACE_SKIP] : 0;
+  P.occ = rab.occ, P.dist = rab.dist, P.ocx = rab.ocx, P.ocy = rab.ocy, P.ocz = rab.ocz;
+  if (P.skip) {
+    // both skipping schemes rely on a sample moving less than half a voxel of the absorption-role
+    // texture per step (true whenever that texture is not much finer than the emission volume
+    // that defines tstep); otherwise every sample is marched
+    float mv = 0.f;
+    const float dim[3] = {P.ab.fw, P.ab.fh, P.ab.fd};
+    for (int i = 0; i < 3; ++i) mv = fmaxf(mv, P.tstep * dim[i] / (P.boxmax[i] - P.boxmin[i]));
+    if (!(mv <= 0.45f)) P.skip = 0;
+  }
+  // shared tap sets: every volume texture of the launch has the geometry of the first one
+  P.uniform = 1;
+  bool have_geo = false;
+  const TexDesc *vt[] = {&P.em, &P.ab, &P.re, &P.em_direct, &P.gx, &P.gy, &P.gz};
+  for (const TexDesc *t : vt) {
+    if (t->kind != TEX_VOLUME) continue;
+    if (!have_geo) P.geo = *t, P.geo.p = nullptr, have_geo = true;
+    if (t->w != P.geo.w || t->h != P.geo.h || t->d != P.geo.d || t->sy != P.geo.sy || t->sz != P.geo.sz) P.uniform = 0;
+  }
+  if (c->opt[VR_OPT_KERNEL_VARIANT] == 1) P.uniform = 0;  // variant 1: per-texture addressing everywhere (A/B measurements)
 
   // lights
   P.n_lights = (int)c->lights.size();
@@ -577,7 +603,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
   memset(c->opt, 0, sizeof c->opt);
-  c->opt[VR_OPT_EMPTY_SPACE_SKIP] = 1;
+  c->opt[VR_OPT_EMPTY_SPACE_SKIP] = 2;
   c->opt[VR_OPT_PART_NRANKS] = 1;
   c->opt[VR_OPT_TILE_W] = 64;
   c->opt[VR_OPT_TILE_H] = 64;

@@ -130,6 +130,58 @@ VR_HD float tex3d_any(const TexDesc &t, float x, float y, float z, int frac_bits
   return t.kind == TEX_CONST ? t.cval : 0.0f;
 }
 
+// ---- shared tap sets ---------------------------------------------------------------------
+// When every volume texture of a launch has the same geometry (the examples' case: emission,
+// reflection and the gradient volumes are all w x h x d), the eight tap offsets and the three
+// weights of a sample position are computed ONCE and reused for every volume fetched there:
+// the arithmetic per fetch is exactly tex3d_volume's, only the common subexpressions are shared.
+struct AxisTap {
+  uint32_t o0, o1;  // storage offsets contributed by the two taps of this axis
+  float f;          // weight of the high tap
+};
+template <int LAYOUT>
+VR_HD AxisTap axis_tap_x(float x, float fN, int fb) {
+  int X;
+  AxisTap a;
+  axis_setup(x, fN, fb, X, a.f);
+  a.o0 = Addr<LAYOUT>::x(X), a.o1 = Addr<LAYOUT>::x(X + 1);
+  return a;
+}
+template <int LAYOUT>
+VR_HD AxisTap axis_tap_y(float y, float fN, uint32_t sy, int fb) {
+  int Y;
+  AxisTap a;
+  axis_setup(y, fN, fb, Y, a.f);
+  a.o0 = Addr<LAYOUT>::y(Y, sy), a.o1 = Addr<LAYOUT>::y(Y + 1, sy);
+  return a;
+}
+template <int LAYOUT>
+VR_HD AxisTap axis_tap_z(float z, float fN, uint32_t sz, int fb) {
+  int Z;
+  AxisTap a;
+  axis_setup(z, fN, fb, Z, a.f);
+  a.o0 = Addr<LAYOUT>::z(Z, sz), a.o1 = Addr<LAYOUT>::z(Z + 1, sz);
+  return a;
+}
+template <typename E>
+VR_HD float taps_fetch(const void *p, const AxisTap &ax, const AxisTap &ay, const AxisTap &az) {
+  const uint32_t b00 = ay.o0 + az.o0, b10 = ay.o1 + az.o0, b01 = ay.o0 + az.o1, b11 = ay.o1 + az.o1;
+  const float c000 = E::load(p, b00 + ax.o0), c100 = E::load(p, b00 + ax.o1);
+  const float c010 = E::load(p, b10 + ax.o0), c110 = E::load(p, b10 + ax.o1);
+  const float c001 = E::load(p, b01 + ax.o0), c101 = E::load(p, b01 + ax.o1);
+  const float c011 = E::load(p, b11 + ax.o0), c111 = E::load(p, b11 + ax.o1);
+  const float c00 = lerpf(c000, c100, ax.f), c10 = lerpf(c010, c110, ax.f);
+  const float c01 = lerpf(c001, c101, ax.f), c11 = lerpf(c011, c111, ax.f);
+  return lerpf(lerpf(c00, c10, ay.f), lerpf(c01, c11, ay.f), az.f);
+}
+// any slot through a shared tap set (the slot is a volume of the common geometry, a constant,
+// or unbound)
+template <typename E>
+VR_HD float taps_any(const TexDesc &t, const AxisTap &ax, const AxisTap &ay, const AxisTap &az) {
+  if (t.kind == TEX_VOLUME) return taps_fetch<E>(t.p, ax, ay, az);
+  return t.kind == TEX_CONST ? t.cval : 0.0f;
+}
+
 // ---- ray state ---------------------------------------------------------------------------
 struct Ray {
   F3 pos, step;
@@ -189,17 +241,57 @@ VR_HD bool ray_init(const KernelParams &P, uint32_t x, uint32_t y, F3 origin, Ra
 // angle (kernel.cu:284-287)
 VR_HD float angle3(F3 a, F3 b) { return acosf(dot3(a, b) / (length3(a) * length3(b))); }
 
+// shade (kernel.cu:308-353) given the gradient and the reflection sample: N = -normalize(g),
+// then per light the three angles, the LUT fetch and the accumulation.  The reference recomputes
+// angle(N, lightIn), the projection of lightIn and the reflection fetch for every light although
+// none of them depends on the light (kernel.cu:329-344); they are evaluated once here - the same
+// operations on the same operands, so the values are those of the reference's loop.
+template <int LAYOUT>
+VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color) {
+  const int fb = P.frac_bits;
+  const F3 N = -1.0f * normalize3(g);
+  const F3 lightIn = origin - pos;
+  const float lenN = length3(N), lenIn = length3(lightIn);
+  const float a = acosf(dot3(N, lightIn) / (lenN * lenIn)) / VR_PI_F;  // angle(N, lightIn)/pi
+  const F3 lightInProj = lightIn - (dot3(lightIn, N) * N);
+  const float lenInProj = length3(lightInProj);
+  F3 illum = mk3(0.0f, 0.0f, 0.0f);
+  for (int i = 0; i < P.n_lights; ++i) {
+    const float *L = i < MAX_PARAM_LIGHTS ? P.lights[i] : P.lights_more + 6 * (i - MAX_PARAM_LIGHTS);
+    const F3 lpos = mk3(L[0], L[1], L[2]), lcol = mk3(L[3], L[4], L[5]);
+    const F3 lightOut = lpos - pos;
+    const float b = acosf(dot3(N, lightOut) / (lenN * length3(lightOut))) / VR_PI_F;
+    const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
+    const float c = acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))) / VR_PI_F;
+    // the LUT is always fp32 in the linear padded layout
+    const float light = tex3d_any<LAYOUT_LINEAR, ElemF32>(P.lut, a, b, c, fb);
+    illum = illum + reflection * light * lcol * color;  // kernel.cu:349
+  }
+  return illum;
+}
+
 // One full iteration of the loop kernel.cu:435-493 up to and including the "under" update.
 // GRAD: 0 = computeGradient (kernel.cu:212-253), 1 = lookupGradient (kernel.cu:266-276).
-template <int GRAD, int LAYOUT, typename E>
+// UNI : every volume texture of the launch shares one geometry -> shared tap sets.
+template <int GRAD, int LAYOUT, typename E, int UNI>
 VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const F3 bmin = ld3(P.boxmin), bmax = ld3(P.boxmax);
   const F3 ext = bmax - bmin;
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);  // kernel.cu:396
   const F3 ps = (r.pos - bmin) * bscale;                            // kernel.cu:437
   const int fb = P.frac_bits;
-  const float em_raw = tex3d_any<LAYOUT, E>(P.em, ps.x, ps.y, ps.z, fb);
-  const float ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, ps.x, ps.y, ps.z, fb);
+  AxisTap ax, ay, az;
+  float em_raw, ab_raw;
+  if (UNI) {
+    ax = axis_tap_x<LAYOUT>(ps.x, P.geo.fw, fb);
+    ay = axis_tap_y<LAYOUT>(ps.y, P.geo.fh, P.geo.sy, fb);
+    az = axis_tap_z<LAYOUT>(ps.z, P.geo.fd, P.geo.sz, fb);
+    em_raw = taps_any<E>(P.em, ax, ay, az);
+    ab_raw = P.ab_is_em ? em_raw : taps_any<E>(P.ab, ax, ay, az);
+  } else {
+    em_raw = tex3d_any<LAYOUT, E>(P.em, ps.x, ps.y, ps.z, fb);
+    ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, ps.x, ps.y, ps.z, fb);
+  }
   const float emission = P.fEm * em_raw;  // kernel.cu:444-447
   const float absorption = P.fAb * ab_raw;
   const float alpha = 1 - VR_EXPF(-absorption * P.tstep);  // kernel.cu:455-456
@@ -211,46 +303,52 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const F3 color = ld3(P.color);
   const F3 colored = mk3(emission, emission, emission) * P.tstep * color;  // kernel.cu:459-460
 
-  // shade (kernel.cu:308-353)
   F3 illum = mk3(0.0f, 0.0f, 0.0f);
   if (P.n_lights > 0) {
     F3 g;
-    if (GRAD == 0) {
-      const F3 gs = ld3(P.gstep);
-      F3 s1, s2;
-      s1 = (r.pos + mk3(gs.x, 0, 0) - bmin) * bscale;
-      s2 = (r.pos - mk3(gs.x, 0, 0) - bmin) * bscale;
-      g.x = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
-      s1 = (r.pos + mk3(0, gs.y, 0) - bmin) * bscale;
-      s2 = (r.pos - mk3(0, gs.y, 0) - bmin) * bscale;
-      g.y = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
-      s1 = (r.pos + mk3(0, 0, gs.z) - bmin) * bscale;
-      s2 = (r.pos - mk3(0, 0, gs.z) - bmin) * bscale;
-      g.z = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
-      g = g * mk3(0.5f, 0.5f, 0.5f);
+    float re_raw;
+    if (UNI) {
+      if (GRAD == 0) {
+        // computeGradient: the six taps differ from the sample position in ONE coordinate each
+        // ((pos.y + 0 - bmin.y) * bscale.y is ps.y bit for bit), so only that axis is set up anew.
+        const F3 gs = ld3(P.gstep);
+        const AxisTap xp = axis_tap_x<LAYOUT>((r.pos.x + gs.x - bmin.x) * bscale.x, P.geo.fw, fb);
+        const AxisTap xm = axis_tap_x<LAYOUT>((r.pos.x - gs.x - bmin.x) * bscale.x, P.geo.fw, fb);
+        g.x = taps_any<E>(P.em_direct, xp, ay, az) - taps_any<E>(P.em_direct, xm, ay, az);
+        const AxisTap yp = axis_tap_y<LAYOUT>((r.pos.y + gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, fb);
+        const AxisTap ym = axis_tap_y<LAYOUT>((r.pos.y - gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, fb);
+        g.y = taps_any<E>(P.em_direct, ax, yp, az) - taps_any<E>(P.em_direct, ax, ym, az);
+        const AxisTap zp = axis_tap_z<LAYOUT>((r.pos.z + gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, fb);
+        const AxisTap zm = axis_tap_z<LAYOUT>((r.pos.z - gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, fb);
+        g.z = taps_any<E>(P.em_direct, ax, ay, zp) - taps_any<E>(P.em_direct, ax, ay, zm);
+        g = g * mk3(0.5f, 0.5f, 0.5f);
+      } else {
+        g = mk3(taps_any<E>(P.gx, ax, ay, az), taps_any<E>(P.gy, ax, ay, az), taps_any<E>(P.gz, ax, ay, az));
+      }
+      re_raw = P.re_is_em ? em_raw : taps_any<E>(P.re, ax, ay, az);
     } else {
-      g = mk3(tex3d_any<LAYOUT, E>(P.gx, ps.x, ps.y, ps.z, fb), tex3d_any<LAYOUT, E>(P.gy, ps.x, ps.y, ps.z, fb),
-              tex3d_any<LAYOUT, E>(P.gz, ps.x, ps.y, ps.z, fb));
+      if (GRAD == 0) {
+        const F3 gs = ld3(P.gstep);
+        F3 s1, s2;
+        s1 = (r.pos + mk3(gs.x, 0, 0) - bmin) * bscale;
+        s2 = (r.pos - mk3(gs.x, 0, 0) - bmin) * bscale;
+        g.x = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
+        s1 = (r.pos + mk3(0, gs.y, 0) - bmin) * bscale;
+        s2 = (r.pos - mk3(0, gs.y, 0) - bmin) * bscale;
+        g.y = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
+        s1 = (r.pos + mk3(0, 0, gs.z) - bmin) * bscale;
+        s2 = (r.pos - mk3(0, 0, gs.z) - bmin) * bscale;
+        g.z = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
+        g = g * mk3(0.5f, 0.5f, 0.5f);
+      } else {
+        g = mk3(tex3d_any<LAYOUT, E>(P.gx, ps.x, ps.y, ps.z, fb), tex3d_any<LAYOUT, E>(P.gy, ps.x, ps.y, ps.z, fb),
+                tex3d_any<LAYOUT, E>(P.gz, ps.x, ps.y, ps.z, fb));
+      }
+      // the reflection fetch sits inside the reference's light loop (kernel.cu:342-344) but does
+      // not depend on the light: fetched once
+      re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
     }
-    const F3 N = -1.0f * normalize3(g);
-    // the reflection fetch sits inside the reference's light loop (kernel.cu:342-344) but does
-    // not depend on the light: fetched once
-    const float re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
-    const float reflection = P.fRe * re_raw;
-    const F3 lightIn = origin - r.pos;
-    for (int i = 0; i < P.n_lights; ++i) {
-      const float *L = i < MAX_PARAM_LIGHTS ? P.lights[i] : P.lights_more + 6 * (i - MAX_PARAM_LIGHTS);
-      const F3 lpos = mk3(L[0], L[1], L[2]), lcol = mk3(L[3], L[4], L[5]);
-      const F3 lightOut = lpos - r.pos;
-      const float a = angle3(N, lightIn) / VR_PI_F;
-      const float b = angle3(N, lightOut) / VR_PI_F;
-      const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
-      const F3 lightInProj = lightIn - (dot3(lightIn, N) * N);
-      const float c = angle3(lightInProj, lightOutProj) / VR_PI_F;
-      // the LUT is always fp32 in the linear padded layout
-      const float light = tex3d_any<LAYOUT_LINEAR, ElemF32>(P.lut, a, b, c, fb);
-      illum = illum + reflection * light * lcol * color;  // kernel.cu:349
-    }
+    illum = shade_lights<LAYOUT>(P, g, P.fRe * re_raw, r.pos, origin, color);
   }
   const F3 lit = colored + illum;
   const float shx = lit.x * alpha, shy = lit.y * alpha, shz = lit.z * alpha;  // kernel.cu:477-479
@@ -273,41 +371,24 @@ VR_HD bool ray_advance(const KernelParams &P, Ray &r) {
 // ---- empty-space skipping ------------------------------------------------------------------
 // A sample contributes exactly nothing when the absorption-role fetch is 0 (alpha = 1 -
 // __expf(-0) = 0 makes the premultiplied sample 0 and `sum` unchanged).  The occupancy grid has
-// one bit per 8^3 macro cell of the absorption-role texture, set when any voxel of the cell
-// DILATED BY ONE VOXEL is non-zero.  A sample whose low tap index i = floor(x*N-0.5) lies in an
-// empty cell reads only zeros.  For such a sample the lane computes how many steps keep it
-// inside the cell and runs only the reference's serial recurrences `t += tstep; pos += step`
-// (kernel.cu:488-492) for them, so positions of later samples stay bit-identical to a march
-// without skipping.  The one-voxel dilation absorbs any rounding in the step-count estimate.
-// Returns false when the ray ends inside the skipped span.
-VR_HD bool skip_empty(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, F3 dq, F3 inv_dq) {
-  for (;;) {
-    const F3 ps = (r.pos - bmin) * bscale;
-    const float qx = fminf(fmaxf(ps.x, 0.0f), 1.0f) * P.ab.fw - 0.5f;
-    const float qy = fminf(fmaxf(ps.y, 0.0f), 1.0f) * P.ab.fh - 0.5f;
-    const float qz = fminf(fmaxf(ps.z, 0.0f), 1.0f) * P.ab.fd - 0.5f;
-    int ix = (int)floorf(qx), iy = (int)floorf(qy), iz = (int)floorf(qz);
-    ix = ix < 0 ? 0 : ix, iy = iy < 0 ? 0 : iy, iz = iz < 0 ? 0 : iz;
-    const int cx = ix >> CELL_SHIFT, cy = iy >> CELL_SHIFT, cz = iz >> CELL_SHIFT;
-    const uint32_t cell = (uint32_t)((cz * P.ocy + cy) * P.ocx + cx);
-    const uint32_t word = VR_LDG(P.occ + (cell >> 5));
-    if ((word >> (cell & 31)) & 1u) return true;  // something to shade here
-    // steps until the low-tap index leaves the cell along each axis
-    const float bx = (float)((dq.x >= 0.0f ? cx + 1 : cx) << CELL_SHIFT);
-    const float by = (float)((dq.y >= 0.0f ? cy + 1 : cy) << CELL_SHIFT);
-    const float bz = (float)((dq.z >= 0.0f ? cz + 1 : cz) << CELL_SHIFT);
-    float n_exit = fminf(fminf((bx - qx) * inv_dq.x, (by - qy) * inv_dq.y), (bz - qz) * inv_dq.z);
-    n_exit = fminf(n_exit, 1048576.0f);
-    int n = (int)ceilf(n_exit);
-    n = n < 1 ? 1 : n;
-    for (int k = 0; k < n; ++k) {
-      r.n_marched++;
-      r.t += P.tstep;
-      if (r.t > r.tfar) return false;
-      r.pos = r.pos + r.step;
-    }
-  }
-}
+// one entry per 8^3 macro cell of the absorption-role texture; a cell is EMPTY when every voxel
+// of the cell DILATED BY TWO VOXELS is zero.  A sample whose low tap index i = floor(x*N-0.5)
+// lies in an empty cell reads only zeros, and so does any sample less than one voxel further
+// along (taps i, i+1).  Sample positions of later samples must stay bit-identical to a march
+// without skipping, i.e. to the reference's serial recurrences `t += tstep; pos += step`
+// (kernel.cu:488-492).  Two implementations:
+//
+//  skip == 1 (serial): the lane computes how many steps keep it inside the cell and runs the
+//    recurrences that many times.
+//  skip == 2 (closed form, default): the grid stores the Chebyshev distance (in cells) to the
+//    nearest non-empty cell, so a lane knows a whole cube of empty cells around it, and the
+//    recurrences are fast-forwarded EXACTLY: while a float stays inside one binade (same sign
+//    and exponent) repeated addition of a constant rounds the same way every time, so after
+//    two real steps v0 -> v1 -> v2 inside a binade every later value is v2 + k*(v2 - v1)
+//    exactly (the product and the sum are representable, see DESIGN.md "exact fast-forward").
+//    The lane jumps k = min(steps to leave the empty cube, steps that keep t, x, y, z inside
+//    their binades) samples at once and falls back to real steps at binade borders.
+// Both return false when the ray ends inside the skipped span.
 
 // per-ray constants of the skip phase: the ray's step in the absorption texture's voxel space
 VR_HD void skip_setup(const KernelParams &P, const Ray &r, F3 bscale, F3 &dq, F3 &inv_dq) {
@@ -316,9 +397,149 @@ VR_HD void skip_setup(const KernelParams &P, const Ray &r, F3 bscale, F3 &dq, F3
   inv_dq = mk3(dq.x != 0.0f ? 1.0f / dq.x : big, dq.y != 0.0f ? 1.0f / dq.y : big, dq.z != 0.0f ? 1.0f / dq.z : big);
 }
 
+VR_HD uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+  return __float_as_uint(f);
+#else
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return u;
+#endif
+}
+VR_HD float u2f(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(u);
+#else
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+#endif
+}
+// v0, v1, v2 are normal numbers of one binade (same sign, same exponent), or all equal
+VR_HD bool one_binade(float v0, float v1, float v2) {
+  const uint32_t e0 = f2u(v0) >> 23, e1 = f2u(v1) >> 23, e2 = f2u(v2) >> 23;
+  const uint32_t ex = e0 & 0xffu;
+  // a coordinate that does not move at all (axis-parallel ray) trivially keeps its increment of 0
+  return (e0 == e1 && e1 == e2 && ex != 0u && ex != 0xffu) || (v0 == v1 && v1 == v2);
+}
+// How many more additions of d keep v inside its binade (conservative; v normal, d a multiple of ulp(v)).
+VR_HD float binade_room(float v, float d) {
+  if (d == 0.0f) return 1.0e9f;
+  const float a = fabsf(v), lo = u2f(f2u(a) & 0x7f800000u);
+  const bool away = (d > 0.0f) == (v > 0.0f);
+  const float span = away ? (lo + lo) - a : a - lo;  // exact: both operands in/at the binade
+  return floorf(span / fabsf(d)) - 2.0f;
+}
+
+// the macro cell of the sample at r.pos and the lane's low-tap coordinates there
+struct CellAt {
+  float qx, qy, qz;
+  int cx, cy, cz;
+  uint32_t cell;
+};
+VR_HD CellAt cell_at(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale) {
+  CellAt c;
+  const F3 ps = (r.pos - bmin) * bscale;
+  c.qx = fminf(fmaxf(ps.x, 0.0f), 1.0f) * P.ab.fw - 0.5f;
+  c.qy = fminf(fmaxf(ps.y, 0.0f), 1.0f) * P.ab.fh - 0.5f;
+  c.qz = fminf(fmaxf(ps.z, 0.0f), 1.0f) * P.ab.fd - 0.5f;
+  int ix = (int)floorf(c.qx), iy = (int)floorf(c.qy), iz = (int)floorf(c.qz);
+  ix = ix < 0 ? 0 : ix, iy = iy < 0 ? 0 : iy, iz = iz < 0 ? 0 : iz;
+  c.cx = ix >> CELL_SHIFT, c.cy = iy >> CELL_SHIFT, c.cz = iz >> CELL_SHIFT;
+  c.cell = (uint32_t)((c.cz * P.ocy + c.cy) * P.ocx + c.cx);
+  return c;
+}
+// steps until the low-tap index leaves the cube of (2*rad+1)^3 cells around the cell, for a
+// per-step move of dq voxels
+VR_HD float steps_to_exit(const CellAt &c, int rad, F3 dq, F3 inv_dq) {
+  const float bx = (float)((dq.x >= 0.0f ? c.cx + 1 + rad : c.cx - rad) << CELL_SHIFT);
+  const float by = (float)((dq.y >= 0.0f ? c.cy + 1 + rad : c.cy - rad) << CELL_SHIFT);
+  const float bz = (float)((dq.z >= 0.0f ? c.cz + 1 + rad : c.cz - rad) << CELL_SHIFT);
+  return fminf(fminf((bx - c.qx) * inv_dq.x, (by - c.qy) * inv_dq.y), (bz - c.qz) * inv_dq.z);
+}
+// one iteration of the reference's loop tail for an empty sample (kernel.cu:488-492)
+VR_HD bool step_empty(const KernelParams &P, Ray &r) {
+  r.n_marched++;
+  r.t += P.tstep;
+  if (r.t > r.tfar) return false;
+  r.pos = r.pos + r.step;
+  return true;
+}
+
+VR_HD bool skip_empty_serial(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, F3 dq, F3 inv_dq) {
+  for (;;) {
+    const CellAt c = cell_at(P, r, bmin, bscale);
+    const uint32_t word = VR_LDG(P.occ + (c.cell >> 5));
+    if ((word >> (c.cell & 31)) & 1u) return true;  // something to shade here
+    float n_exit = fminf(steps_to_exit(c, 0, dq, inv_dq), 1048576.0f);
+    int n = (int)ceilf(n_exit);
+    n = n < 1 ? 1 : n;
+    for (int k = 0; k < n; ++k)
+      if (!step_empty(P, r)) return false;
+  }
+}
+
+VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale) {
+  for (;;) {
+    const CellAt c = cell_at(P, r, bmin, bscale);
+    const int dist = (int)VR_LDG(P.dist + c.cell);
+    if (dist == 0) return true;  // something to shade here
+    // two real steps: both samples are still less than one voxel past an empty cell
+    const float t0 = r.t;
+    const F3 p0 = r.pos;
+    if (!step_empty(P, r)) return false;
+    const float t1 = r.t;
+    const F3 p1 = r.pos;
+    if (!step_empty(P, r)) return false;
+    if (!(one_binade(t0, t1, r.t) && one_binade(p0.x, p1.x, r.pos.x) && one_binade(p0.y, p1.y, r.pos.y) &&
+          one_binade(p0.z, p1.z, r.pos.z)))
+      continue;  // at a binade border: keep stepping for real
+    // the increments every further addition will produce (exact differences)
+    const float dt = r.t - t1;
+    const F3 d = r.pos - p1;
+    // steps that keep the lane inside the empty cube, measured from where it stands now with the
+    // increments it will really take
+    const F3 ps = (r.pos - bmin) * bscale;
+    CellAt now = c;
+    now.qx = fminf(fmaxf(ps.x, 0.0f), 1.0f) * P.ab.fw - 0.5f;
+    now.qy = fminf(fmaxf(ps.y, 0.0f), 1.0f) * P.ab.fh - 0.5f;
+    now.qz = fminf(fmaxf(ps.z, 0.0f), 1.0f) * P.ab.fd - 0.5f;
+    const F3 dq = mk3(d.x * bscale.x * P.ab.fw, d.y * bscale.y * P.ab.fh, d.z * bscale.z * P.ab.fd);
+    const float big = 3.0e38f;
+    const F3 inv_dq = mk3(dq.x != 0.0f ? 1.0f / dq.x : big, dq.y != 0.0f ? 1.0f / dq.y : big, dq.z != 0.0f ? 1.0f / dq.z : big);
+    float kf = ceilf(steps_to_exit(now, dist - 1, dq, inv_dq));
+    kf = fminf(kf, fminf(fminf(binade_room(r.t, dt), binade_room(r.pos.x, d.x)), fminf(binade_room(r.pos.y, d.y), binade_room(r.pos.z, d.z))));
+    kf = fminf(kf, 4194304.0f);
+    if (!(kf >= 1.0f)) continue;
+    // t after kf additions; does the ray end inside the span?
+    const float t_end = r.t + kf * dt;
+    if (t_end > r.tfar) {
+      // smallest j with t + j*dt > tfar, found exactly: every t + j*dt, j <= kf, is representable
+      float j = floorf((r.tfar - r.t) / dt) + 1.0f;
+      j = fminf(fmaxf(j, 1.0f), kf);
+      while (j > 1.0f && r.t + (j - 1.0f) * dt > r.tfar) j -= 1.0f;
+      while (!(r.t + j * dt > r.tfar)) j += 1.0f;
+      r.n_marched += (uint32_t)j;
+      r.t = r.t + j * dt;
+      return false;
+    }
+    const F3 p_end = r.pos + kf * d;
+    if (!(one_binade(r.t, r.t, t_end) && one_binade(r.pos.x, r.pos.x, p_end.x) && one_binade(r.pos.y, r.pos.y, p_end.y) &&
+          one_binade(r.pos.z, r.pos.z, p_end.z)))
+      continue;  // cannot happen with the conservative room; stay exact regardless
+    r.n_marched += (uint32_t)kf;
+    r.t = t_end;
+    r.pos = p_end;
+  }
+}
+
+VR_HD bool skip_empty(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, F3 dq, F3 inv_dq) {
+  return P.skip == 2 ? skip_empty_jump(P, r, bmin, bscale) : skip_empty_serial(P, r, bmin, bscale, dq, inv_dq);
+}
+
 // The whole march of one pixel, lane-serial: what the kernel does per lane, without the warp
 // scheduling.  Used by the host emulation (tests/host_emul) and by the single-lane debug kernel.
-template <int GRAD, int LAYOUT, typename E>
+template <int GRAD, int LAYOUT, typename E, int UNI>
 VR_HD bool march_pixel(const KernelParams &P, uint32_t x, uint32_t y, float rgb[3], uint32_t &marched, uint32_t &shaded) {
   const F3 origin = ray_origin(P);
   Ray r;
@@ -331,7 +552,7 @@ VR_HD bool march_pixel(const KernelParams &P, uint32_t x, uint32_t y, float rgb[
   while (active) {
     if (P.skip) active = skip_empty(P, r, bmin, bscale, dq, inv_dq);
     if (!active) break;
-    shade_sample<GRAD, LAYOUT, E>(P, origin, r);
+    shade_sample<GRAD, LAYOUT, E, UNI>(P, origin, r);
     active = ray_advance(P, r);
   }
   rgb[0] = r.sx, rgb[1] = r.sy, rgb[2] = r.sz;

@@ -20,7 +20,7 @@ namespace vrb {
 static constexpr int kBlockThreads = 256;
 static constexpr unsigned kFull = 0xffffffffu;
 
-template <int GRAD, int LAYOUT, typename E>
+template <int GRAD, int LAYOUT, typename E, int UNI>
 __global__ void __launch_bounds__(kBlockThreads) k_raymarch(const __grid_constant__ KernelParams P) {
   const int lane = threadIdx.x & 31;
   const F3 origin = ray_origin(P);
@@ -46,12 +46,12 @@ __global__ void __launch_bounds__(kBlockThreads) k_raymarch(const __grid_constan
     bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, x, y, origin, r);
     bool active = hit;
     F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
-    if (active && P.skip) skip_setup(P, r, bscale, dq, inv_dq);
+    if (active && P.skip == 1) skip_setup(P, r, bscale, dq, inv_dq);
 
     while (__any_sync(kFull, active)) {
       if (active && P.skip) active = skip_empty(P, r, bmin, bscale, dq, inv_dq);
       if (active) {
-        shade_sample<GRAD, LAYOUT, E>(P, origin, r);
+        shade_sample<GRAD, LAYOUT, E, UNI>(P, origin, r);
         active = ray_advance(P, r);
       }
     }
@@ -80,10 +80,10 @@ __global__ void __launch_bounds__(kBlockThreads) k_raymarch(const __grid_constan
   }
 }
 
-template <int GRAD, int LAYOUT, typename E>
+template <int GRAD, int LAYOUT, typename E, int UNI>
 static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
   int per_sm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E>, kBlockThreads, 0);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E, UNI>, kBlockThreads, 0);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   // persistent grid: a whole number of waves, never more warps than work items
@@ -91,29 +91,20 @@ static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm
   const long long need = ((long long)P.num_work + (kBlockThreads / 32) - 1) / (kBlockThreads / 32);
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
-  k_raymarch<GRAD, LAYOUT, E><<<(unsigned)blocks, kBlockThreads, 0, stream>>>(P);
+  k_raymarch<GRAD, LAYOUT, E, UNI><<<(unsigned)blocks, kBlockThreads, 0, stream>>>(P);
   return cudaGetLastError();
+}
+
+template <int LAYOUT, typename E>
+static cudaError_t launch_le(const KernelParams &P, cudaStream_t stream, int sm_count) {
+  if (P.gradient_method) return P.uniform ? launch_one<1, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<1, LAYOUT, E, 0>(P, stream, sm_count);
+  return P.uniform ? launch_one<0, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<0, LAYOUT, E, 0>(P, stream, sm_count);
 }
 
 cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, int variant, cudaStream_t stream, int sm_count) {
   (void)variant;
-  const int g = P.gradient_method ? 1 : 0;
-#define VR_CASE(G, L, EL) return launch_one<G, L, EL>(P, stream, sm_count)
-  if (dtype == 0) {
-    if (layout == LAYOUT_BRICK) {
-      if (g) VR_CASE(1, LAYOUT_BRICK, ElemF32);
-      VR_CASE(0, LAYOUT_BRICK, ElemF32);
-    }
-    if (g) VR_CASE(1, LAYOUT_LINEAR, ElemF32);
-    VR_CASE(0, LAYOUT_LINEAR, ElemF32);
-  }
-  if (layout == LAYOUT_BRICK) {
-    if (g) VR_CASE(1, LAYOUT_BRICK, ElemBF16);
-    VR_CASE(0, LAYOUT_BRICK, ElemBF16);
-  }
-  if (g) VR_CASE(1, LAYOUT_LINEAR, ElemBF16);
-  VR_CASE(0, LAYOUT_LINEAR, ElemBF16);
-#undef VR_CASE
+  if (dtype == 0) return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemF32>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemF32>(P, stream, sm_count);
+  return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemBF16>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemBF16>(P, stream, sm_count);
 }
 
 }  // namespace vrb

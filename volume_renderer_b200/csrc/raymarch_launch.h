@@ -33,6 +33,10 @@ cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream);
 cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *occ, int ocx, int ocy, int ocz,
                              int dilate, cudaStream_t stream);
 
+// distance grid of an occupancy bit grid: dist[cell] = Chebyshev distance in cells to the nearest
+// set bit (0 on a set bit, capped at 255).  tmp: scratch of the same size.
+cudaError_t launch_distance(const uint32_t *occ, uint8_t *dist, uint8_t *tmp, int ocx, int ocy, int ocz, cudaStream_t stream);
+
 // Henyey-Greenstein LUT (HenyeyGreenstein.cc:47-91): n^3 floats on the device.
 cudaError_t launch_hg_lut(float *d_out, uint32_t n, float g, cudaStream_t stream);
 

@@ -119,6 +119,42 @@ cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *
   return cudaGetLastError();
 }
 
+// ---- distance grid ------------------------------------------------------------------------------
+// Chebyshev distance (in macro cells, capped at 255) from every cell to the nearest non-empty
+// cell: D(c) = min over occupied o of max(|cx-ox|, |cy-oy|, |cz-oz|).  The max-norm separates
+// exactly into three 1-D passes: Dx = distance along the row, Dxy(c) = min_k max(|k|, Dx(c + k*ey)),
+// D(c) = min_k max(|k|, Dxy(c + k*ez)).  One thread per cell; the scan stops at k = current best.
+__global__ void __launch_bounds__(256) k_dist_pass(const uint32_t *occ, const uint8_t *in, uint8_t *out, int ocx, int ocy, int ocz, int axis) {
+  const uint64_t ncell = (uint64_t)ocx * ocy * ocz;
+  for (uint64_t cell = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; cell < ncell; cell += (uint64_t)gridDim.x * blockDim.x) {
+    const int cx = (int)(cell % ocx), cy = (int)((cell / ocx) % ocy), cz = (int)(cell / ((uint64_t)ocx * ocy));
+    const int pos = axis == 0 ? cx : (axis == 1 ? cy : cz);
+    const int n = axis == 0 ? ocx : (axis == 1 ? ocy : ocz);
+    const int64_t stride = axis == 0 ? 1 : (axis == 1 ? ocx : (int64_t)ocx * ocy);
+    auto f = [&](int64_t c) -> int {
+      if (axis == 0) return ((__ldg(occ + (c >> 5)) >> (c & 31)) & 1u) ? 0 : 255;
+      return (int)__ldg(in + c);
+    };
+    int best = f((int64_t)cell);
+    for (int k = 1; k < best; ++k) {
+      if (pos - k >= 0) best = min(best, max(k, f((int64_t)cell - k * stride)));
+      if (pos + k < n) best = min(best, max(k, f((int64_t)cell + k * stride)));
+    }
+    out[cell] = (uint8_t)best;
+  }
+}
+cudaError_t launch_distance(const uint32_t *occ, uint8_t *dist, uint8_t *tmp, int ocx, int ocy, int ocz, cudaStream_t stream) {
+  const uint64_t ncell = (uint64_t)ocx * ocy * ocz;
+  uint64_t blocks = (ncell + 255) / 256;
+  if (blocks > 148ull * 32) blocks = 148ull * 32;
+  if (blocks < 1) blocks = 1;
+  const unsigned g = (unsigned)blocks;
+  k_dist_pass<<<g, 256, 0, stream>>>(occ, nullptr, dist, ocx, ocy, ocz, 0);
+  k_dist_pass<<<g, 256, 0, stream>>>(occ, dist, tmp, ocx, ocy, ocz, 1);
+  k_dist_pass<<<g, 256, 0, stream>>>(occ, tmp, dist, ocx, ocy, ocz, 2);
+  return cudaGetLastError();
+}
+
 // ---- Henyey-Greenstein LUT --------------------------------------------------------------------
 // HenyeyGreenstein.cc:47-91: index k = c*n*n + a*n + b with gamma = c*pi/n, alpha = a*pi/n,
 // beta = b*pi/n; cos(theta) = dot(Rx(gamma) * (sin a, 0, cos a), (sin b, 0, cos b))

@@ -68,11 +68,13 @@ struct KernelParams {
   TexDesc em, ab, re;
   TexDesc em_direct;  // tex_emission itself, as computeGradient reads it (kernel.cu:225-248)
   TexDesc gx, gy, gz, lut;
+  TexDesc geo;   // the geometry shared by every TEX_VOLUME slot above but the LUT (valid when `uniform`)
+  int uniform;   // all volume textures of the launch share one geometry -> shared tap sets
   int ab_is_em;  // absorption role resolves to the same texture as the emission role
   int re_is_em;  // reflection role resolves to the same texture as the emission role
   int gradient_method;  // 0 compute, 1 lookup (volumeRender.h:141-144)
   int frac_bits;        // 0 = fp32 weights, 8 = 1.8 fixed point
-  int skip;             // empty-space skipping on
+  int skip;             // empty-space skipping: 0 off, 1 serial per cell, 2 closed-form jumps (default)
   int count;            // maintain stats
   // lights (volumeRender.h:50-55), position already axis-reversed
   int n_lights;
@@ -80,6 +82,9 @@ struct KernelParams {
   const float *lights_more;  // lights beyond MAX_PARAM_LIGHTS, 6 floats each (device memory)
   // occupancy bit grid of the absorption-role texture: bit (cz*ocy+cy)*ocx+cx set = not empty
   const uint32_t *occ;
+  // the same grid as bytes: Chebyshev distance in cells to the nearest non-empty cell (0 = the
+  // cell itself is not empty, 255 = at least 255)
+  const uint8_t *dist;
   int ocx, ocy, ocz;
 };
 
