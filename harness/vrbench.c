@@ -4,7 +4,7 @@
  *
  *   vrbench [--size N] [--image W H] [--frames K] [--lights L] [--grad] [--bf16] [--stereo] [--out file.pfm]
  *
- * Links only against libvr_b200.so; nothing here touches oracle/.
+ * Links only against libvr_b200.so (no CPU fallback, no checker code).
  */
 #include <math.h>
 #include <stdio.h>

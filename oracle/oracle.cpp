@@ -116,7 +116,7 @@ inline Axis axis(float x, uint64_t n, int frac_bits) {
   a.f = f;
   return a;
 }
-inline float lerp(float a, float b, float f) { return a + f * (b - a); }
+inline float lerp(float a, float b, float f) { return fmaf(f, b - a, a); } /* a + f*(b-a), one rounding */
 
 inline float tex3d_raw(const float *p, uint64_t w, uint64_t h, uint64_t d, float x, float y, float z,
                        int frac_bits) {
@@ -656,9 +656,11 @@ inline float value_noise(float px, float py, float pz, uint32_t seed) {
   const float c010 = u01(hash3(i, j + 1, k, seed)), c110 = u01(hash3(i + 1, j + 1, k, seed));
   const float c001 = u01(hash3(i, j, k + 1, seed)), c101 = u01(hash3(i + 1, j, k + 1, seed));
   const float c011 = u01(hash3(i, j + 1, k + 1, seed)), c111 = u01(hash3(i + 1, j + 1, k + 1, seed));
-  const float c00 = lerp(c000, c100, wx), c10 = lerp(c010, c110, wx);
-  const float c01 = lerp(c001, c101, wx), c11 = lerp(c011, c111, wx);
-  return lerp(lerp(c00, c10, wy), lerp(c01, c11, wy), wz);
+  /* the generator's own lerp: three roundings, like k_synth's lerp_rn and the numpy twin */
+  auto mix = [](float a, float b, float f) { return a + f * (b - a); };
+  const float c00 = mix(c000, c100, wx), c10 = mix(c010, c110, wx);
+  const float c01 = mix(c001, c101, wx), c11 = mix(c011, c111, wx);
+  return mix(mix(c00, c10, wy), mix(c01, c11, wy), wz);
 }
 inline float ncoord(int i, int n) { return (((float)i + 0.5f) / (float)n) * 2.0f - 1.0f; }
 inline float synth_brain(int x, int y, int z, int w, int h, int d, uint32_t seed) {

@@ -182,3 +182,17 @@ extern "C" int emul_render(const vr_volume *em, const vr_volume *re, const vr_vo
     return emul<LAYOUT_BRICK>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, out, stats);
   return emul<LAYOUT_LINEAR>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, out, stats);
 }
+
+// unit-test hooks for the small numeric helpers of raymarch_core.h
+extern "C" float emul_acos_poly(float x) { return acos_poly(x); }
+extern "C" uint64_t emul_div_pi_mismatches(uint32_t first_bits, uint32_t last_bits, uint32_t stride) {
+  uint64_t bad = 0;
+  for (uint64_t u = first_bits; u <= last_bits; u += stride) {
+    float x;
+    const uint32_t b = (uint32_t)u;
+    memcpy(&x, &b, 4);
+    const float q = div_pi(x), ref = x / VR_PI_F;
+    if (!(q == ref)) ++bad;
+  }
+  return bad;
+}

@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libvr_b200.so")
+LIB_PATH = os.environ.get("VR_B200_LIB") or os.path.join(_HERE, "csrc", "libvr_b200.so")  # env: developer A/B builds
 
 VR_OK = 0
 STATUS_NAMES = {

@@ -99,7 +99,9 @@ VR_HD void axis_setup(float x, float fN, int frac_bits, int &X0, float &f) {
   if (frac_bits) f = floorf(f * 256.0f + 0.5f) * (1.0f / 256.0f);  // 1.8 fixed-point weights
   X0 = (int)fl + 1;
 }
-VR_HD float lerpf(float a, float b, float f) { return a + f * (b - a); }
+// one fused multiply-add per lerp, written explicitly so that the checker (oracle.cpp: lerp) and
+// this file round identically whatever the contraction flags are
+VR_HD float lerpf(float a, float b, float f) { return fmaf(f, b - a, a); }
 
 // tex3D on a resident volume (kind == TEX_VOLUME).
 template <int LAYOUT, typename E>
@@ -241,6 +243,48 @@ VR_HD bool ray_init(const KernelParams &P, uint32_t x, uint32_t y, F3 origin, Ra
 // angle (kernel.cu:284-287)
 VR_HD float angle3(F3 a, F3 b) { return acosf(dot3(a, b) / (length3(a) * length3(b))); }
 
+// acos for the illumination angles.  The device's own acosf and glibc's already differ in the
+// last place, so the angle is the one quantity of the march that is compared by tolerance, not
+// bit for bit; what must agree exactly is WHEN it is NaN (argument outside [-1,1] or NaN), and
+// that is preserved: sqrt of a negative number is NaN.  Abramowitz & Stegun 4.4.46,
+// acos(x) = sqrt(1-x) * P7(x) on [0,1], |error| <= 2e-8, mirrored for x < 0: 13 instructions
+// instead of ~30.  The host emulation keeps acosf (bit-equal to the checker).
+VR_HD float acos_poly(float x) {
+  const float ax = fabsf(x);
+  float s;
+#if defined(__CUDA_ARCH__)
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(1.0f - ax));
+#else
+  s = sqrtf(1.0f - ax);
+#endif
+  float p = -0.0012624911f;
+  p = fmaf(p, ax, 0.0066700901f);
+  p = fmaf(p, ax, -0.0170881256f);
+  p = fmaf(p, ax, 0.0308918810f);
+  p = fmaf(p, ax, -0.0501743046f);
+  p = fmaf(p, ax, 0.0889789874f);
+  p = fmaf(p, ax, -0.2145988016f);
+  p = fmaf(p, ax, 1.5707963050f);
+  const float r = s * p;
+  return x < 0.0f ? VR_PI_F - r : r;
+}
+VR_HD float vr_acosf(float x) {
+#if defined(__CUDA_ARCH__)
+  return acos_poly(x);
+#else
+  return acosf(x);
+#endif
+}
+// x / pi, correctly rounded, as reciprocal multiply + one exact-residual correction (3 instructions
+// instead of an IEEE divide).  Bit-equal to `x / VR_PI_F` for every float in (1e-30, 4], for 0 and
+// for NaN - checked exhaustively (tests/test_host_logic.py::test_div_pi_is_exact); the angles fed
+// to it are 0, NaN or >= 3e-4.
+VR_HD float div_pi(float x) {
+  const float rcp = 1.0f / VR_PI_F;
+  const float q0 = x * rcp;
+  return fmaf(fmaf(-q0, VR_PI_F, x), rcp, q0);
+}
+
 // shade (kernel.cu:308-353) given the gradient and the reflection sample: N = -normalize(g),
 // then per light the three angles, the LUT fetch and the accumulation.  The reference recomputes
 // angle(N, lightIn), the projection of lightIn and the reflection fetch for every light although
@@ -252,7 +296,7 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
   const F3 N = -1.0f * normalize3(g);
   const F3 lightIn = origin - pos;
   const float lenN = length3(N), lenIn = length3(lightIn);
-  const float a = acosf(dot3(N, lightIn) / (lenN * lenIn)) / VR_PI_F;  // angle(N, lightIn)/pi
+  const float a = div_pi(vr_acosf(dot3(N, lightIn) / (lenN * lenIn)));  // angle(N, lightIn)/pi
   const F3 lightInProj = lightIn - (dot3(lightIn, N) * N);
   const float lenInProj = length3(lightInProj);
   F3 illum = mk3(0.0f, 0.0f, 0.0f);
@@ -260,9 +304,9 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
     const float *L = i < MAX_PARAM_LIGHTS ? P.lights[i] : P.lights_more + 6 * (i - MAX_PARAM_LIGHTS);
     const F3 lpos = mk3(L[0], L[1], L[2]), lcol = mk3(L[3], L[4], L[5]);
     const F3 lightOut = lpos - pos;
-    const float b = acosf(dot3(N, lightOut) / (lenN * length3(lightOut))) / VR_PI_F;
+    const float b = div_pi(vr_acosf(dot3(N, lightOut) / (lenN * length3(lightOut))));
     const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
-    const float c = acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))) / VR_PI_F;
+    const float c = div_pi(vr_acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))));
     // the LUT is always fp32 in the linear padded layout
     const float light = tex3d_any<LAYOUT_LINEAR, ElemF32>(P.lut, a, b, c, fb);
     illum = illum + reflection * light * lcol * color;  // kernel.cu:349

@@ -17,11 +17,17 @@
 
 namespace vrb {
 
-static constexpr int kBlockThreads = 256;
+#ifndef VR_BLOCK_THREADS
+#define VR_BLOCK_THREADS 256
+#endif
+#ifndef VR_MIN_BLOCKS
+#define VR_MIN_BLOCKS 3
+#endif
+static constexpr int kBlockThreads = VR_BLOCK_THREADS;
 static constexpr unsigned kFull = 0xffffffffu;
 
 template <int GRAD, int LAYOUT, typename E, int UNI>
-__global__ void __launch_bounds__(kBlockThreads) k_raymarch(const __grid_constant__ KernelParams P) {
+__global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const __grid_constant__ KernelParams P) {
   const int lane = threadIdx.x & 31;
   const F3 origin = ray_origin(P);
   const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
