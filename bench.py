@@ -51,6 +51,8 @@ def parse():
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--skip", type=int, default=2)
     p.add_argument("--tile", type=int, default=64)
+    p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                   help="N > 1: p2p = every rank's kernel stores its tiles into rank 0's image over NVLink (default); nccl = SUM-reduce of partial images")
     return p.parse_args()
 
 
@@ -265,7 +267,8 @@ def workload_config(args, scene, size=None):
         "workload": "example1_grad-shaped: %d^3 %s synthetic ViBE-Z-like E (+R=E^2, A, %s), %d HG light(s), %dx%d mono, F=3 D=6 thr=0.9, +1deg/step" % (
             size, args.dtype, "Gx,Gy,Gz gradient lookup" if args.gradient == "lookup" else "on-the-fly gradient", len(scene.lights), scene.W, scene.H),
         "volume": [size] * 3, "image": [scene.W, scene.H], "gradient": args.gradient, "lights": len(scene.lights),
-        "multi_gpu": "image-space tiles %dx%d round-robin, NCCL sum-reduce to rank 0" % (args.tile, args.tile),
+        "multi_gpu": "image-space tiles %dx%d round-robin over replicated volumes; %s" % (
+            args.tile, args.tile, "kernels store their tiles straight into rank 0's image over NVLink (CUDA IPC), one barrier per frame" if args.exchange == "p2p" else "NCCL sum-reduce of partial images to rank 0"),
         "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames",
     }
 
@@ -344,16 +347,27 @@ def run_b200(args):
     for i, (p, c) in enumerate(scene.lights):
         lights[i].position[:] = p
         lights[i].color[:] = c
-    d_img = torch.zeros(scene.W * scene.H * 3, dtype=torch.float32, device=dev)
     h_img = torch.zeros(scene.W * scene.H * 3, dtype=torch.float32).pin_memory()
     resp = scene.res.ctypes.data_as(C.POINTER(C.c_uint64))
+    p2p = world > 1 and args.exchange == "p2p"
+    shared = token = d_img = None
+    if p2p:
+        # ONE image in rank 0's HBM, mapped into every rank (CUDA IPC): kernels store their tiles into it
+        shared = multigpu.SharedImage(ctx, scene.H, scene.W, rank, world, root=0)
+        out_ptr = shared.ptr
+        token = torch.zeros(1, dtype=torch.float32, device=dev)
+    else:
+        d_img = torch.zeros(scene.W * scene.H * 3, dtype=torch.float32, device=dev)
+        out_ptr = C.c_void_p(d_img.data_ptr())
 
     def frame_device(step):
         rot = scene.rot(step)
         _abi.check(lib.vr_render_device(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
-                                        f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color), C.c_void_p(d_img.data_ptr()),
+                                        f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color), out_ptr,
                                         C.c_void_p(stream.cuda_stream)), ctx)
-        if world > 1:
+        if p2p:
+            multigpu.frame_barrier(token)  # on the stream, behind the kernel: "frame complete in rank 0's image"
+        elif world > 1:
             multigpu.combine_partials(d_img, 0)
 
     def stats():
@@ -418,8 +432,13 @@ def run_b200(args):
         else:
             frame_device(step)
             if rank == 0:
-                h_img.copy_(d_img, non_blocking=True)
+                if p2p:
+                    shared.download(h_img.numpy())
+                else:
+                    h_img.copy_(d_img, non_blocking=True)
             torch.cuda.synchronize()
+            if p2p:
+                multigpu.frame_barrier(token)  # nobody overwrites the shared image while rank 0 reads it
 
     for w in range(max(1, args.warmup // 2)):
         frame_e2e(-1 - w)
@@ -441,9 +460,20 @@ def run_b200(args):
     h2d = 9 * 4 + 3 * 4 * 4 + 8 * 2 + nl * 24 + 6 * 40  # rotation, factors/es/props/color, resolution, lights, volume descriptors
     d2h = scene.W * scene.H * 3 * 4
 
-    if rank != 0:
+    def finish():
+        if shared is not None:
+            torch.cuda.synchronize()
+            dist.barrier()
+            if rank != 0:
+                shared.close()  # unmap before the owner frees
+            dist.barrier()
+            if rank == 0:
+                shared.close()
         if world > 1:
             dist.destroy_process_group()
+
+    if rank != 0:
+        finish()
         return 0
 
     peaks = {}
@@ -486,9 +516,8 @@ def run_b200(args):
             line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m)
         except Exception as ex:  # the bench line must still print
             line["cpu_baseline"] = {"value": None, "unit": "Gsamples/s", "cores": 0, "kind": "port", "sample": "failed: %r" % (ex,)}
-    print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    print(json.dumps(line), flush=True)
+    finish()
     return 0
 
 

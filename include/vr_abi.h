@@ -168,7 +168,10 @@ typedef enum vr_option {
   VR_OPT_TILE_W = 6,            /* partition tile size in pixels */
   VR_OPT_TILE_H = 7,
   VR_OPT_BRICK_LAYOUT = 8,      /* 1 = bricked resident layout (default), 0 = linear */
-  VR_OPT_COUNT_SAMPLES = 9      /* 1 (default) = maintain vr_stats sample counters */
+  VR_OPT_COUNT_SAMPLES = 9,     /* 1 (default) = maintain vr_stats sample counters */
+  VR_OPT_CLEAR_IMAGE = 10       /* 1 (default) = zero the whole output image first (volumeRender.cpp:271); 0 = only the
+                                   pixels of owned tiles are written (every owned pixel is, misses as 0): required when
+                                   several ranks render into ONE shared image */
 } vr_option;
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);
@@ -188,6 +191,14 @@ VR_API vr_status vr_synth_volume(vr_ctx *ctx, int kind, uint32_t seed, const uin
  * dims and dtype as `in`) live in `out_memspace`.  SURVEY 8(f) row 3: saves 3 volume uploads. */
 VR_API vr_status vr_volume_gradient(vr_ctx *ctx, const vr_volume *in, int32_t out_memspace, void *gx, void *gy,
                                     void *gz);
+/* Sharing one device image between the per-GPU processes of the image-space mode (CUDA IPC over
+ * NVLink peer access): the root exports the image it allocated with vr_device_alloc, every other
+ * rank opens it and passes the mapped pointer as d_out_image of vr_render_device, so the ray-march
+ * kernel stores its tiles straight into the root's HBM. handle = 64 bytes (cudaIpcMemHandle_t). */
+#define VR_IPC_HANDLE_BYTES 64
+VR_API vr_status vr_ipc_export(vr_ctx *ctx, void *d_ptr, unsigned char handle[VR_IPC_HANDLE_BYTES]);
+VR_API vr_status vr_ipc_open(vr_ctx *ctx, const unsigned char handle[VR_IPC_HANDLE_BYTES], void **d_ptr);
+VR_API vr_status vr_ipc_close(vr_ctx *ctx, void *d_ptr);
 /* Device memory helpers for callers without a CUDA runtime binding (C harness, ctypes). */
 VR_API vr_status vr_device_alloc(vr_ctx *ctx, size_t bytes, void **d_ptr);
 VR_API vr_status vr_device_free(vr_ctx *ctx, void *d_ptr);

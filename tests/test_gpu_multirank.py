@@ -1,0 +1,95 @@
+"""Image-space direct send on the GPU: several ranks render disjoint tiles into ONE image.
+
+(a) in one process: two contexts, one shared device buffer, no clear -> bit-identical to one GPU;
+(b) across two processes on cuda:0 through the CUDA IPC entry points of the C ABI (the same
+    plumbing bench.py uses over NVLink with one process per GPU), handle exchanged over gloo.
+No kernel waits on another kernel: ranks render one after the other or independently."""
+import ctypes as C
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import vrt
+from volume_renderer_b200 import _abi, api, multigpu
+
+pytestmark = pytest.mark.gpu
+RES = (192, 160)  # ImageResolution = [W, H]
+
+
+def _scene(vol, lut):
+    return vrt.example1_scene(api.VolumeRender, vol, RES, lights=1, lut=lut)
+
+
+def _render_into(r, ptr, rank, world, tile=32):
+    """p_render's argument packing (VolumeRender.m:497-583) but through vr_render_device into `ptr`."""
+    r.syncVolumes()
+    multigpu.configure_partition(r.objectHandle, rank, world, tile, tile)
+    r.setOption(_abi.OPT_CLEAR_IMAGE, 0)
+    args, keep = api._render_args(r.LightSources, r.VolumeIllumination, [r.FactorEmission, r.FactorReflection, r.FactorAbsorption],
+                                  r.ElementSizeUm, [RES[1], RES[0]], np.flipud(np.asarray(r.RotationMatrix)),
+                                  [0.0, r.FocalLength, r.DistanceToObject], r.OpacityThreshold, r.Color)
+    _abi.check(_abi.lib().vr_render_device(r.objectHandle, *args, ptr, None), r.objectHandle)
+    r.stats()  # synchronises the context's stream
+
+
+def test_two_contexts_one_image_no_clear():
+    import torch
+
+    vol = vrt.synth_brain((48, 48, 48))
+    lut = api.HenyeyGreenstein(64)
+    full = _scene(vol, lut).render()
+    # poisoned buffer: every pixel must be written by exactly one rank, misses as 0
+    buf = torch.full((full.size,), 7.0, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    ranks = [_scene(vol, lut) for _ in range(3)]
+    for rank, r in enumerate(ranks):
+        _render_into(r, C.c_void_p(buf.data_ptr()), rank, 3)
+    out = buf.cpu().numpy().reshape(full.shape, order="F")
+    assert np.array_equal(out, full)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out_path):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    vol = vrt.synth_brain((48, 48, 48))
+    lut = vrt.oracle_lut(64)
+    r = _scene(vol, lut)
+    shared = multigpu.SharedImage(r.objectHandle, RES[1], RES[0], rank, world, root=0)
+    for turn in range(world):  # one rank at a time: nothing runs concurrently on the one GPU
+        if turn == rank:
+            _render_into(r, shared.ptr, rank, world)
+        dist.barrier()
+    if rank == 0:
+        out = np.zeros((RES[1], RES[0], 3), dtype=np.float32, order="F")
+        shared.download(out)
+        np.save(out_path, out)
+    dist.barrier()
+    if rank != 0:
+        shared.close()
+    dist.barrier()
+    if rank == 0:
+        shared.close()
+    dist.destroy_process_group()
+
+
+def test_two_processes_share_the_root_image_through_cuda_ipc(tmp_path):
+    import torch.multiprocessing as mp
+
+    vol = vrt.synth_brain((48, 48, 48))
+    full = _scene(vol, vrt.oracle_lut(64)).render()
+    out = str(tmp_path / "shared.npy")
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert np.array_equal(np.load(out), full)

@@ -34,6 +34,8 @@ OPT_TILE_W = 6
 OPT_TILE_H = 7
 OPT_BRICK_LAYOUT = 8
 OPT_COUNT_SAMPLES = 9
+OPT_CLEAR_IMAGE = 10
+IPC_HANDLE_BYTES = 64
 
 
 class VrVolume(C.Structure):
@@ -102,6 +104,9 @@ def declare(lib):
         "vr_get_device": ([vp, P(C.c_int)], C.c_int),
         "vr_synth_volume": ([vp, C.c_int, C.c_uint32, u64p, C.c_int32, vp], C.c_int),
         "vr_volume_gradient": ([vp, P(VrVolume), C.c_int32, vp, vp, vp], C.c_int),
+        "vr_ipc_export": ([vp, vp, C.c_char_p], C.c_int),
+        "vr_ipc_open": ([vp, C.c_char_p, P(vp)], C.c_int),
+        "vr_ipc_close": ([vp, vp], C.c_int),
         "vr_device_alloc": ([vp, C.c_size_t, P(vp)], C.c_int),
         "vr_device_free": ([vp, vp], C.c_int),
         "vr_device_download": ([vp, vp, vp, C.c_size_t], C.c_int),

@@ -562,7 +562,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   P.stats = c->d_stats;
 
   // cudaMemset of the image (volumeRender.cpp:271): pixels whose ray misses the box stay 0
-  VR_CUDA(c, cudaMemsetAsync(d_out, 0, (size_t)W * H * 3 * sizeof(float), stream));
+  if (c->opt[VR_OPT_CLEAR_IMAGE]) VR_CUDA(c, cudaMemsetAsync(d_out, 0, (size_t)W * H * 3 * sizeof(float), stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_stats, 0, 3 * sizeof(unsigned long long), stream));
   VR_CUDA(c, cudaEventRecord(c->ev0, stream));
@@ -609,6 +609,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->opt[VR_OPT_TILE_H] = 64;
   c->opt[VR_OPT_BRICK_LAYOUT] = 1;
   c->opt[VR_OPT_COUNT_SAMPLES] = 1;
+  c->opt[VR_OPT_CLEAR_IMAGE] = 1;
   cudaError_t ce = cudaSetDevice(device);
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   c->own_stream = ce == cudaSuccess;
@@ -808,14 +809,14 @@ int vr_abi_version(void) { return VR_ABI_VERSION; }
 
 vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_COUNT_SAMPLES) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_CLEAR_IMAGE) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
   c->opt[option] = value;
   return VR_OK;
 }
 vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_COUNT_SAMPLES || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_CLEAR_IMAGE || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   *value = c->opt[option];
   return VR_OK;
 }
@@ -886,6 +887,32 @@ vr_status vr_volume_gradient(vr_ctx *c, const vr_volume *in, int32_t out_memspac
   cleanup();
   if (e != cudaSuccess)
     return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_INSUFFICIENT_VRAM : VR_ERR_CUDA, "gradient: %s", cudaGetErrorString(e));
+  return VR_OK;
+}
+vr_status vr_ipc_export(vr_ctx *c, void *d_ptr, unsigned char handle[VR_IPC_HANDLE_BYTES]) {
+  VR_CHECK_HANDLE(c);
+  if (!d_ptr || !handle) return fail(c, VR_ERR_INVALID_ARGUMENT, "ipc_export: null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == VR_IPC_HANDLE_BYTES, "handle size");
+  VR_TRY(set_device(c));
+  cudaIpcMemHandle_t h;
+  VR_CUDA(c, cudaIpcGetMemHandle(&h, d_ptr));
+  memcpy(handle, &h, sizeof h);
+  return VR_OK;
+}
+vr_status vr_ipc_open(vr_ctx *c, const unsigned char handle[VR_IPC_HANDLE_BYTES], void **d_ptr) {
+  VR_CHECK_HANDLE(c);
+  if (!d_ptr || !handle) return fail(c, VR_ERR_INVALID_ARGUMENT, "ipc_open: null argument");
+  VR_TRY(set_device(c));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  VR_CUDA(c, cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return VR_OK;
+}
+vr_status vr_ipc_close(vr_ctx *c, void *d_ptr) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  VR_CUDA(c, cudaIpcCloseMemHandle(d_ptr));
   return VR_OK;
 }
 vr_status vr_device_alloc(vr_ctx *c, size_t bytes, void **d_ptr) {

@@ -61,12 +61,17 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
         active = ray_advance(P, r);
       }
     }
-    if (hit) {
-      // column-major planar H x W x 3 (kernel.cu:496-506); lanes of a warp cover 4 consecutive y
+    if (x < (uint32_t)P.W && y < (uint32_t)P.H) {
+      // column-major planar H x W x 3 (kernel.cu:496-506); lanes of a warp cover 4 consecutive y.
+      // A ray that misses the box leaves the reference's pixel at its memset 0 (volumeRender.cpp:271):
+      // the owner of the pixel writes that 0 itself, so the image needs no clear and P.out may be
+      // another GPU's memory (image-space direct send: each rank stores its tiles into the root's image).
       const size_t size = (size_t)P.W * P.H, k = (size_t)x * P.H + y;
-      P.out[k] = r.sx;
-      P.out[k + size] = r.sy;
-      P.out[k + 2 * size] = r.sz;
+      P.out[k] = hit ? r.sx : 0.0f;
+      P.out[k + size] = hit ? r.sy : 0.0f;
+      P.out[k + 2 * size] = hit ? r.sz : 0.0f;
+    }
+    if (hit) {
       tot_marched += r.n_marched;
       tot_shaded += r.n_shaded;
       tot_hits += 1;
