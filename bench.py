@@ -38,7 +38,7 @@ B_GATHER_COMPUTE_L1 = 320  # on-the-fly gradient, (9 + L) * 32 B pe
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--steps", type=int, default=16)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--size", type=int, default=1024, help="volume edge (default 1024 = the metric's config)")
@@ -51,6 +51,8 @@ def parse():
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--skip", type=int, default=2)
     p.add_argument("--tile", type=int, default=64)
+    p.add_argument("--batch", type=int, default=8, help="frames per launch (one work queue per batch; clipped to --steps)")
+    p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                    help="N > 1: p2p = every rank's kernel stores its tiles into rank 0's image over NVLink (default); nccl = SUM-reduce of partial images")
     return p.parse_args()
@@ -269,6 +271,7 @@ def workload_config(args, scene, size=None):
         "volume": [size] * 3, "image": [scene.W, scene.H], "gradient": args.gradient, "lights": len(scene.lights),
         "multi_gpu": "image-space tiles %dx%d round-robin over replicated volumes; %s" % (
             args.tile, args.tile, "kernels store their tiles straight into rank 0's image over NVLink (CUDA IPC), one barrier per frame" if args.exchange == "p2p" else "NCCL sum-reduce of partial images to rank 0"),
+        "frames_per_launch": max(1, min(args.batch, args.steps)),
         "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames",
     }
 
@@ -296,6 +299,7 @@ def run_b200(args):
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_KERNEL_VARIANT, args.variant), ctx)
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_EMPTY_SPACE_SKIP, args.skip), ctx)
     multigpu.configure_partition(ctx, rank, world, args.tile, args.tile)
+    _abi.check(lib.vr_set_option(ctx, _abi.OPT_TILE_ORDER, args.order), ctx)
     scene = Scene(args)
     n = args.size
     dt = _abi.DTYPE_F32 if args.dtype == "f32" else _abi.DTYPE_BF16
@@ -347,28 +351,33 @@ def run_b200(args):
     for i, (p, c) in enumerate(scene.lights):
         lights[i].position[:] = p
         lights[i].color[:] = c
-    h_img = torch.zeros(scene.W * scene.H * 3, dtype=torch.float32).pin_memory()
+    B = max(1, min(args.batch, args.steps))
+    npx = scene.W * scene.H * 3
+    h_img = torch.zeros(B * npx, dtype=torch.float32).pin_memory()
     resp = scene.res.ctypes.data_as(C.POINTER(C.c_uint64))
     p2p = world > 1 and args.exchange == "p2p"
     shared = token = d_img = None
     if p2p:
-        # ONE image in rank 0's HBM, mapped into every rank (CUDA IPC): kernels store their tiles into it
-        shared = multigpu.SharedImage(ctx, scene.H, scene.W, rank, world, root=0)
-        out_ptr = shared.ptr
+        # the batch's images live in rank 0's HBM, mapped into every rank (CUDA IPC): kernels store their tiles into them
+        shared = multigpu.SharedImage(ctx, scene.H, scene.W, rank, world, root=0, count=B)
+        out_ptrs = shared.ptrs
         token = torch.zeros(1, dtype=torch.float32, device=dev)
     else:
-        d_img = torch.zeros(scene.W * scene.H * 3, dtype=torch.float32, device=dev)
-        out_ptr = C.c_void_p(d_img.data_ptr())
+        d_img = torch.zeros(B * npx, dtype=torch.float32, device=dev)
+        out_ptrs = [C.c_void_p(d_img.data_ptr() + i * npx * 4) for i in range(B)]
+    props_b = np.tile(scene.props, B).astype(np.float32)
 
-    def frame_device(step):
-        rot = scene.rot(step)
-        _abi.check(lib.vr_render_device(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
-                                        f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color), out_ptr,
-                                        C.c_void_p(stream.cuda_stream)), ctx)
+    def frame_device(step, nb=1):
+        """nb consecutive frames of the movie (camera +1 degree each) in ONE launch."""
+        rots = np.concatenate([scene.rot(step + i).reshape(-1, order="F") for i in range(nb)]).astype(np.float32)
+        outs = (C.c_void_p * nb)(*[p.value for p in out_ptrs[:nb]])
+        _abi.check(lib.vr_render_batch_device(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
+                                              nb, f32p(rots), f32p(props_b), C.c_float(scene.thr), f32p(scene.color), outs,
+                                              C.c_void_p(stream.cuda_stream)), ctx)
         if p2p:
-            multigpu.frame_barrier(token)  # on the stream, behind the kernel: "frame complete in rank 0's image"
+            multigpu.frame_barrier(token)  # on the stream, behind the kernel: "batch complete in rank 0's images"
         elif world > 1:
-            multigpu.combine_partials(d_img, 0)
+            multigpu.combine_partials(d_img[: nb * npx], 0)
 
     def stats():
         s = _abi.VrStats()
@@ -381,29 +390,29 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     # ---- device-resident leg: `value` ----
-    for w in range(args.warmup):
-        frame_device(-1 - w)
+    for w in range(0, args.warmup, B):
+        frame_device(-args.warmup + w, min(B, args.warmup - w))
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     samples = shaded = 0
     kernel_ms = []
     launches = 0
     t0 = time.time()
     barrier()
-    ev[0].record(stream)
-    for k in range(args.steps):
-        frame_device(k)
-        ev[k + 1].record(stream)
-        s = stats()  # synchronises this rank's stream; per-frame counters
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for k in range(0, args.steps, B):
+        frame_device(k, min(B, args.steps - k))
+        s = stats()  # synchronises this rank's stream; counters of the launch
         samples += s.samples_marched
         shaded += s.samples_shaded
         kernel_ms.append(s.kernel_ms)
         launches += s.kernel_launches
+    ev1.record(stream)
     barrier()
     t1 = time.time()
     clocks = sampler.stop(t0, t1) if sampler else None
-    ms = ev[0].elapsed_time(ev[args.steps])
+    ms = ev0.elapsed_time(ev1)
     tot = torch.tensor([ms, float(samples), float(shaded), float(launches), max(kernel_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         mx = tot.clone()
@@ -420,33 +429,33 @@ def run_b200(args):
     # every step: 'sync_volumes' (nothing dirty -> nothing moves, the persistent-volume design of
     # the reference, example2.m) + 'render' with host-side parameters and a device->host read of
     # the frame.  N > 1: partials are reduced to rank 0 first, rank 0 reads the frame back.
-    out_host = np.zeros(scene.W * scene.H * 3, dtype=np.float32)
     stamp_sync = 100
+    h_np = h_img.numpy()
+    host_ptrs = (C.c_void_p * B)(*[h_np.ctypes.data + i * npx * 4 for i in range(B)])
 
-    def frame_e2e(step):
+    def frame_e2e(step, nb):
         _abi.check(lib.vr_sync_volumes(ctx, stamp_sync, C.byref(vE), C.byref(vR), C.byref(vA), *[C.byref(x) if x is not None else None for x in g]), ctx)
         if world == 1:
-            rot = scene.rot(step)
-            _abi.check(lib.vr_render(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
-                                     f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color), out_host.ctypes.data), ctx)
+            rots = np.concatenate([scene.rot(step + i).reshape(-1, order="F") for i in range(nb)]).astype(np.float32)
+            _abi.check(lib.vr_render_batch(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
+                                           nb, f32p(rots), f32p(props_b), C.c_float(scene.thr), f32p(scene.color), host_ptrs), ctx)
         else:
-            frame_device(step)
+            frame_device(step, nb)
             if rank == 0:
                 if p2p:
-                    shared.download(h_img.numpy())
+                    shared.download(h_np, nb)
                 else:
-                    h_img.copy_(d_img, non_blocking=True)
+                    h_img[: nb * npx].copy_(d_img[: nb * npx], non_blocking=True)
             torch.cuda.synchronize()
             if p2p:
-                multigpu.frame_barrier(token)  # nobody overwrites the shared image while rank 0 reads it
+                multigpu.frame_barrier(token)  # nobody overwrites the shared images while rank 0 reads them
 
-    for w in range(max(1, args.warmup // 2)):
-        frame_e2e(-1 - w)
+    frame_e2e(-B, B)
     barrier()
     e_samples = 0
     te = time.perf_counter()
-    for k in range(args.steps):
-        frame_e2e(k)
+    for k in range(0, args.steps, B):
+        frame_e2e(k, min(B, args.steps - k))
         e_samples += stats().samples_marched
     barrier()
     te = time.perf_counter() - te
@@ -488,9 +497,10 @@ def run_b200(args):
         bps = (6 + len(scene.lights)) * 32
     else:
         bps = (9 + len(scene.lights)) * 32
-    kavg_ms = float(np.mean(kernel_ms))
-    per_launch_shaded = shaded / max(args.steps, 1)  # rank 0's launches
-    per_launch_marched = samples / max(args.steps, 1)
+    n_launch = max(len(kernel_ms), 1)
+    kavg_ms = float(np.sum(kernel_ms)) / n_launch
+    per_launch_shaded = shaded / n_launch  # rank 0's launches (a launch = a batch of frames)
+    per_launch_marched = samples / n_launch
     achieved = per_launch_shaded * bps / (kavg_ms * 1e-3) / 1e9
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,

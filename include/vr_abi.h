@@ -140,6 +140,24 @@ VR_API vr_status vr_render_device(vr_ctx *ctx, const vr_light *lights, size_t n_
                                   float opacity_threshold, const float color[3],
                                   float *d_out_image, void *cuda_stream);
 
+/* A batch of frames that differ only in camera (a stereo pair = the two p_render passes of
+ * VolumeRender.m:284-285; a rotation movie = the loop of examples/example2.m:59-66) in ONE launch:
+ * rotations = n_frames x single[9], props = n_frames x single[3], d_out_images = n_frames device
+ * pointers.  All frames share one work queue, so one frame's long rays overlap another's tail. */
+VR_API vr_status vr_render_batch_device(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
+                                        const vr_volume *illumination, const float factors[3],
+                                        const float element_size_um[3], const uint64_t resolution[2],
+                                        size_t n_frames, const float *rotations, const float *props,
+                                        float opacity_threshold, const float color[3],
+                                        float *const *d_out_images, void *cuda_stream);
+
+/* The same batch with host images (n_frames pointers to H*W*3 floats each), synchronous like vr_render. */
+VR_API vr_status vr_render_batch(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
+                                 const vr_volume *illumination, const float factors[3],
+                                 const float element_size_um[3], const uint64_t resolution[2],
+                                 size_t n_frames, const float *rotations, const float *props,
+                                 float opacity_threshold, const float color[3], float *const *out_images);
+
 /* ---- HenyeyGreenstein(n[,g]) mex  (src/C/mex/HenyeyGreenstein.cc:29-96) ---------------- */
 /* n^3 floats, index k = c*n*n + a*n + b (HenyeyGreenstein.cc:86); evaluated on the GPU. */
 VR_API vr_status vr_henyey_greenstein(uint32_t n, float g, float *out_lut);
@@ -169,9 +187,10 @@ typedef enum vr_option {
   VR_OPT_TILE_H = 7,
   VR_OPT_BRICK_LAYOUT = 8,      /* 1 = bricked resident layout (default), 0 = linear */
   VR_OPT_COUNT_SAMPLES = 9,     /* 1 (default) = maintain vr_stats sample counters */
-  VR_OPT_CLEAR_IMAGE = 10       /* 1 (default) = zero the whole output image first (volumeRender.cpp:271); 0 = only the
+  VR_OPT_CLEAR_IMAGE = 10,      /* 1 (default) = zero the whole output image first (volumeRender.cpp:271); 0 = only the
                                    pixels of owned tiles are written (every owned pixel is, misses as 0): required when
                                    several ranks render into ONE shared image */
+  VR_OPT_TILE_ORDER = 11        /* 1 (default) = hand tiles out centre-first (long rays first); 0 = raster order */
 } vr_option;
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);
@@ -199,6 +218,9 @@ VR_API vr_status vr_volume_gradient(vr_ctx *ctx, const vr_volume *in, int32_t ou
 VR_API vr_status vr_ipc_export(vr_ctx *ctx, void *d_ptr, unsigned char handle[VR_IPC_HANDLE_BYTES]);
 VR_API vr_status vr_ipc_open(vr_ctx *ctx, const unsigned char handle[VR_IPC_HANDLE_BYTES], void **d_ptr);
 VR_API vr_status vr_ipc_close(vr_ctx *ctx, void *d_ptr);
+/* Debug: [start,end] globaltimer ns of every resident warp of the last ray-march launch
+ * (2 x max_warps uint64, at most 8192 warps); only when $VR_WARP_TIMES was set at vr_create. */
+VR_API vr_status vr_debug_warp_times(vr_ctx *ctx, uint64_t *host_pairs, size_t max_warps);
 /* Device memory helpers for callers without a CUDA runtime binding (C harness, ctypes). */
 VR_API vr_status vr_device_alloc(vr_ctx *ctx, size_t bytes, void **d_ptr);
 VR_API vr_status vr_device_free(vr_ctx *ctx, void *d_ptr);

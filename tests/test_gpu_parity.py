@@ -203,6 +203,7 @@ def test_image_space_partition_is_bit_identical(brain64, lut):
             r.setOption(_abi.OPT_TILE_H, 32)
             r.setOption(_abi.OPT_PART_RANK, rank)
             r.setOption(_abi.OPT_PART_NRANKS, nranks)
+            r.setOption(_abi.OPT_TILE_ORDER, rank % 2)  # the hand-out order is invisible in the pixels
             part = r.render()
             assert not (np.logical_and(acc != 0, part != 0)).any()
             acc += part
@@ -237,3 +238,39 @@ def test_errors_are_returned_not_thrown_across_the_abi():
     object.__setattr__(r, "objectHandle", None)
     with pytest.raises(ValueError):
         api.HenyeyGreenstein(8, 1.5)
+
+
+def test_batch_launch_equals_single_frames(brain64, lut):
+    """vr_render_batch: stereo pair / movie frames in one launch are bit-identical to one launch each."""
+    gpu = vrt.example1_scene(api.VolumeRender, brain64, (128, 96), lights=1, lut=lut)
+    rots = []
+    singles = []
+    for _ in range(3):
+        gpu.rotate(0, 20, 0)
+        rots.append(gpu.RotationMatrix.copy())
+        singles.append(gpu.render())
+    n1 = gpu.stats()["samples_marched"]
+    batch = gpu.renderMovie(rots)
+    for a, b in zip(singles, batch):
+        assert np.array_equal(a, b)
+    assert gpu.stats()["kernel_launches"] == 1 and gpu.stats()["samples_marched"] > 2 * n1
+    # stereo: batch of the two eyes vs two p_render passes
+    for r in (gpu,):
+        r.CameraXOffset = 0.06
+        r.FocalLength = 4.5
+    img_b = gpu.render()
+    gpu.BatchStereo = False
+    assert np.array_equal(img_b, gpu.render())
+    # partitioned batch: ranks' partial batches add up
+    gpu.CameraXOffset = 0
+    acc = [np.zeros_like(singles[0]) for _ in rots]
+    for rank in range(2):
+        r = vrt.example1_scene(api.VolumeRender, brain64, (128, 96), lights=1, lut=lut)
+        r.FocalLength = 4.5
+        r.setOption(_abi.OPT_TILE_W, 32), r.setOption(_abi.OPT_TILE_H, 32)
+        r.setOption(_abi.OPT_PART_RANK, rank), r.setOption(_abi.OPT_PART_NRANKS, 2)
+        for k, part in enumerate(r.renderMovie(rots)):
+            acc[k] += part
+    gpu.FocalLength = 4.5
+    for a, b in zip(acc, gpu.renderMovie(rots)):
+        assert np.array_equal(a, b)

@@ -35,6 +35,7 @@ OPT_TILE_H = 7
 OPT_BRICK_LAYOUT = 8
 OPT_COUNT_SAMPLES = 9
 OPT_CLEAR_IMAGE = 10
+OPT_TILE_ORDER = 11
 IPC_HANDLE_BYTES = 64
 
 
@@ -92,6 +93,8 @@ def declare(lib):
         "vr_sync_volumes": ([vp, C.c_uint64] + [P(VrVolume)] * 6, C.c_int),
         "vr_render": (render_args + [vp], C.c_int),
         "vr_render_device": (render_args + [vp, vp], C.c_int),
+        "vr_render_batch": ([vp, P(VrLight), C.c_size_t, P(VrVolume), f3, f3, u64p, C.c_size_t, f3, f3, C.c_float, f3, P(vp)], C.c_int),
+        "vr_render_batch_device": ([vp, P(VrLight), C.c_size_t, P(VrVolume), f3, f3, u64p, C.c_size_t, f3, f3, C.c_float, f3, P(vp), vp], C.c_int),
         "vr_henyey_greenstein": ([C.c_uint32, C.c_float, vp], C.c_int),
         "vr_timestamp_ms": ([C.c_int], C.c_uint64),
         "vr_last_error": ([vp], C.c_char_p),
@@ -104,6 +107,7 @@ def declare(lib):
         "vr_get_device": ([vp, P(C.c_int)], C.c_int),
         "vr_synth_volume": ([vp, C.c_int, C.c_uint32, u64p, C.c_int32, vp], C.c_int),
         "vr_volume_gradient": ([vp, P(VrVolume), C.c_int32, vp, vp, vp], C.c_int),
+        "vr_debug_warp_times": ([vp, vp, C.c_size_t], C.c_int),
         "vr_ipc_export": ([vp, vp, C.c_char_p], C.c_int),
         "vr_ipc_open": ([vp, C.c_char_p, P(vp)], C.c_int),
         "vr_ipc_close": ([vp, vp], C.c_int),

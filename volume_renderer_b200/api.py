@@ -239,6 +239,20 @@ class _CudaBackend:
         return out
 
     # extensions with no mex counterpart (include/vr_abi.h, "extensions")
+    def render_batch(self, h, lights, lut, factors, es, res, rots, props_list, thr, color):
+        """Frames that differ only in camera, in one launch (vr_render_batch)."""
+        H, W = int(res[0]), int(res[1])
+        n = len(rots)
+        outs = [np.zeros((H, W, 3), dtype=np.float32, order="F") for _ in range(n)]
+        args, keep = _render_args(lights, lut, factors, es, res, rots[0], props_list[0], thr, color)
+        R = np.concatenate([np.asfortranarray(np.asarray(r, dtype=np.float32)).reshape(-1, order="F") for r in rots]).astype(np.float32)
+        Pp = np.concatenate([np.asarray(p, dtype=np.float32).reshape(3) for p in props_list]).astype(np.float32)
+        ptrs = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+        f32p = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+        _abi.check(_abi.lib().vr_render_batch(h, args[0], args[1], args[2], args[3], args[4], args[5], n, f32p(R), f32p(Pp),
+                                              args[8], args[9], ptrs), h)
+        return outs
+
     def stats(self, h):
         s = _abi.VrStats()
         _abi.check(_abi.lib().vr_get_stats(h, C.byref(s)), h)
@@ -316,6 +330,7 @@ class VolumeRender:
         self.RotationMatrix = np.eye(3)
         self.ImageResolution = [0, 0]
         self.TimeLastMemSync = 0
+        self.BatchStereo = True  # extension: render the stereo pair as one batch launch
         self._vols.update({k: False for k in self._volume_props})
         self._vols["VolumeReflection"] = Volume(1)  # VolumeRender.m:131
         self._backend = self._backend_cls()
@@ -419,8 +434,12 @@ class VolumeRender:
             return self.p_render(np.float32(self.CameraXOffset), flipped)
         base, delta = self.stereo_delta()
         resolution = [flipped[0], flipped[1] + delta]
-        rightImage = self.p_render(base, resolution)
-        leftImage = self.p_render(-base, resolution)
+        if hasattr(self._backend, "render_batch") and self.BatchStereo:
+            # both eyes in one launch (same pixels as two p_render passes; one work queue)
+            rightImage, leftImage = self.p_render_batch([base, -base], resolution)
+        else:
+            rightImage = self.p_render(base, resolution)
+            leftImage = self.p_render(-base, resolution)
         # imcrop(left, [delta+1 0 W' H]) keeps columns delta+1..W'; imcrop(right, [0 0 W'-delta H]) keeps 1..W'-delta
         leftImage = leftImage[:, delta:, :]
         rightImage = rightImage[:, : rightImage.shape[1] - delta, :]
@@ -458,6 +477,34 @@ class VolumeRender:
         lut = self.VolumeIllumination if self.VolumeIllumination is not False else None
         return self._backend.render(self.objectHandle, lights, lut, factors, self.ElementSizeUm, resolution,
                                     matrix, props, self.OpacityThreshold, self.Color)
+
+    def _check_volumes(self):
+        if self.VolumeIllumination is False:
+            import warnings
+
+            warnings.warn("VolumeIllumination is unset. Thus no lightning will be applied!")
+        if self.VolumeEmission is False or self.VolumeAbsorption is False or self.VolumeReflection is False:
+            raise RuntimeError("Not all volumes are properly set!")
+
+    def p_render_batch(self, offsets, resolution, rotations=None):
+        """Extension: p_render for several cameras at once - `offsets` are CameraXOffsets, `rotations`
+        (optional) RotationMatrix values per frame.  Same marshalling as p_render per frame."""
+        self._check_volumes()
+        self.syncVolumes()
+        factors = [self.FactorEmission, self.FactorReflection, self.FactorAbsorption]
+        rotations = rotations if rotations is not None else [self.RotationMatrix] * len(offsets)
+        rots = [np.flipud(np.asarray(R)) for R in rotations]
+        props = [[o, self.FocalLength, self.DistanceToObject] for o in offsets]
+        lights = self.LightSources if self.LightSources is not False else None
+        lut = self.VolumeIllumination if self.VolumeIllumination is not False else None
+        return self._backend.render_batch(self.objectHandle, lights, lut, factors, self.ElementSizeUm, resolution, rots, props,
+                                          self.OpacityThreshold, self.Color)
+
+    def renderMovie(self, rotations):
+        """Extension: the frames of a rotation movie (examples/example2.m:59-66) in one launch;
+        `rotations` is a list of RotationMatrix values.  Mono cameras only."""
+        flipped = [int(self.ImageResolution[1]), int(self.ImageResolution[0])]
+        return self.p_render_batch([np.float32(self.CameraXOffset)] * len(rotations), flipped, rotations)
 
     @staticmethod
     def normalizeSequence(sequence):

@@ -10,6 +10,7 @@
 // There is no CPU path in here: without a B200 every call fails with VR_ERR_NO_DEVICE.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -19,6 +20,7 @@
 #include <mutex>
 #include <set>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/vr_abi.h"
@@ -103,6 +105,12 @@ struct vr_ctx {
   void *d_stage = nullptr;
   size_t stage_cap = 0;
   unsigned int *d_counter = nullptr;      // work counter + padding
+  uint32_t *d_tile_order = nullptr;       // owned tiles, heaviest first
+  Camera *d_cams = nullptr;               // cameras of a batch
+  size_t cams_cap = 0;
+  unsigned long long *d_warp_times = nullptr;  // debug buffer ($VR_WARP_TIMES=1): 2 x 8192 entries
+  size_t tile_order_cap = 0;
+  std::vector<uint32_t> h_tile_order;
   unsigned long long *d_stats = nullptr;  // 3 counters
   unsigned long long *h_stats = nullptr;  // pinned
   // options
@@ -444,9 +452,12 @@ vr_status collect(vr_ctx *c) {
 // 'render' minus the read-back: marshal like render.cpp:142-245, set up like vr::initRender
 // (volumeRender.cpp:112-156) and vr::render (:264-277), launch on the context's stream.
 vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
-                        const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
-                        const float props[3], float thr, const float color[3], float *d_out, cudaStream_t stream) {
-  if (!factors || !es || !res || !R || !props || !color) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
+                        const float factors[3], const float es[3], const uint64_t res[2], size_t n_frames, const float *R,
+                        const float *props, float thr, const float color[3], float *const *d_outs, cudaStream_t stream) {
+  if (!factors || !es || !res || !R || !props || !color || !d_outs || n_frames == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
+  if (n_frames > 4096) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: at most 4096 frames per batch");
+  for (size_t f = 0; f < n_frames; ++f)
+    if (!d_outs[f]) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: null output");
   c->stats.bytes_uploaded = 0;
   if (lights && illumination) {  // render.cpp:145-191; a logical placeholder keeps the previous set
     c->host[S_LIGHT] = make_volume(illumination);
@@ -469,7 +480,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
 
   KernelParams P;
   memset(&P, 0, sizeof P);
-  P.out = d_out;
+  P.cam.out = d_outs[0];
   setup_frame(P, factors, es, W, H, R, props, thr, color, E.w, E.h, E.d);
 
   // role -> texture through the redirect indices (kernel.cu:127-144)
@@ -554,15 +565,82 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   P.wt_x = P.tile_w / 8, P.wt_y = P.tile_h / 4;
   const uint64_t ntiles = (uint64_t)P.ntx * P.nty;
   const uint64_t owned = ntiles > (uint64_t)P.part_rank ? (ntiles - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0;
-  P.num_owned = (uint32_t)owned;
-  const uint64_t work = owned * P.wt_x * P.wt_y;
-  if (work > 0xfffffff0ull) return fail(c, VR_ERR_UNSUPPORTED, "too many work items");
+  const uint64_t entries = owned * n_frames;  // (frame, owned tile) pairs of the launch
+  P.num_owned = (uint32_t)entries;
+  const uint64_t work = entries * P.wt_x * P.wt_y;
+  if (work > 0xfffffff0ull || ntiles * n_frames > 0xfffffff0ull) return fail(c, VR_ERR_UNSUPPORTED, "too many work items");
   P.num_work = (uint32_t)work;
   P.work_counter = c->d_counter;
+  P.warp_times = c->d_warp_times;
+  P.tiles_total = (uint32_t)ntiles;
+  P.n_frames = (int)n_frames;
+  // cameras of a batch
+  std::vector<Camera> cams(n_frames);
+  for (size_t f = 0; f < n_frames; ++f) {
+    fill_camera(cams[f], R + 9 * f, props + 3 * f);
+    cams[f].out = d_outs[f];
+  }
+  P.cams = nullptr;
+  if (n_frames > 1) {
+    const size_t need = n_frames * sizeof(Camera);
+    if (c->cams_cap < need) {
+      if (c->d_cams) cudaFree(c->d_cams);
+      c->d_cams = nullptr, c->cams_cap = 0;
+      VR_CUDA(c, cudaMalloc(&c->d_cams, need));
+      c->cams_cap = need;
+    }
+    VR_CUDA(c, cudaMemcpyAsync(c->d_cams, cams.data(), need, cudaMemcpyHostToDevice, stream));  // pageable: staged before return
+    P.cams = c->d_cams;
+  }
+  // Hand the tiles out heaviest first.  One warp marches 32 rays from start to end, so a tile of
+  // long rays picked up late would run alone at the end of the kernel; rays through the middle
+  // of the volume are the long ones, so owned tiles are ordered by the distance of their centre
+  // from the projection of the box centre (longest-processing-time-first, by a geometric guess).
+  // In a batch all frames share the one queue: the light tiles of every frame fill the tail.
+  P.tile_order = nullptr;
+  const bool ordered = c->opt[VR_OPT_TILE_ORDER] != 0;
+  if ((ordered && entries > 1) || n_frames > 1) {
+    std::vector<std::pair<float, uint32_t>> key((size_t)entries);
+    for (size_t f = 0; f < n_frames; ++f) {
+      const Camera &C = cams[f];
+      const float *xv = C.m[0], *yv = C.m[1], *zv = C.m[2];
+      const float xl = sqrtf(xv[0] * xv[0] + xv[1] * xv[1] + xv[2] * xv[2]);
+      float o[3];  // camera origin (kernel.cu:399-410); the box centre is the world origin
+      for (int i = 0; i < 3; ++i) o[i] = C.m[3][0] * xv[i] - C.m[3][2] * zv[i];
+      const float a = -(o[0] * xv[0] + o[1] * xv[1] + o[2] * xv[2]) / (xl > 0 ? xl : 1.f);
+      const float b = -(o[0] * yv[0] + o[1] * yv[1] + o[2] * yv[2]);
+      const float cz = -(o[0] * zv[0] + o[1] * zv[1] + o[2] * zv[2]);
+      const float ratio = (float)P.H / (float)P.W;
+      float px = 0.5f * P.W, py = 0.5f * P.H;
+      if (cz > 1e-6f) {
+        px = (a / cz * C.m[3][1] + 1.f) * 0.5f * P.W;
+        py = (b / cz * C.m[3][1] + ratio) / (2.f * ratio) * P.H;
+      }
+      for (uint64_t j = 0; j < owned; ++j) {
+        const uint32_t tile = (uint32_t)(P.part_rank + j * P.part_nranks);
+        const float tx = ((tile % P.ntx) + 0.5f) * P.tile_w - px, ty = ((tile / P.ntx) + 0.5f) * P.tile_h - py;
+        const uint32_t entry = (uint32_t)(f * ntiles + tile);
+        key[f * owned + j] = std::make_pair(ordered ? tx * tx + ty * ty : (float)(f * owned + j), entry);
+      }
+    }
+    std::sort(key.begin(), key.end());
+    c->h_tile_order.resize((size_t)entries);
+    for (uint64_t j = 0; j < entries; ++j) c->h_tile_order[j] = key[j].second;
+    if (c->tile_order_cap < entries * 4) {
+      if (c->d_tile_order) cudaFree(c->d_tile_order);
+      c->d_tile_order = nullptr, c->tile_order_cap = 0;
+      VR_CUDA(c, cudaMalloc(&c->d_tile_order, entries * 4));
+      c->tile_order_cap = entries * 4;
+    }
+    // pageable source: the runtime stages it before returning, so the vector may be reused next frame
+    VR_CUDA(c, cudaMemcpyAsync(c->d_tile_order, c->h_tile_order.data(), entries * 4, cudaMemcpyHostToDevice, stream));
+    P.tile_order = c->d_tile_order;
+  }
   P.stats = c->d_stats;
 
   // cudaMemset of the image (volumeRender.cpp:271): pixels whose ray misses the box stay 0
-  if (c->opt[VR_OPT_CLEAR_IMAGE]) VR_CUDA(c, cudaMemsetAsync(d_out, 0, (size_t)W * H * 3 * sizeof(float), stream));
+  if (c->opt[VR_OPT_CLEAR_IMAGE])
+    for (size_t f = 0; f < n_frames; ++f) VR_CUDA(c, cudaMemsetAsync(d_outs[f], 0, (size_t)W * H * 3 * sizeof(float), stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_stats, 0, 3 * sizeof(unsigned long long), stream));
   VR_CUDA(c, cudaEventRecord(c->ev0, stream));
@@ -610,6 +688,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->opt[VR_OPT_BRICK_LAYOUT] = 1;
   c->opt[VR_OPT_COUNT_SAMPLES] = 1;
   c->opt[VR_OPT_CLEAR_IMAGE] = 1;
+  c->opt[VR_OPT_TILE_ORDER] = 1;
   cudaError_t ce = cudaSetDevice(device);
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   c->own_stream = ce == cudaSuccess;
@@ -618,6 +697,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu0);
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu1);
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_counter, 64);
+  if (ce == cudaSuccess && getenv("VR_WARP_TIMES")) ce = cudaMalloc(&c->d_warp_times, 2 * 8192 * sizeof(unsigned long long));
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_stats, 64);
   if (ce == cudaSuccess) ce = cudaMallocHost(&c->h_stats, 64);
   if (ce != cudaSuccess) {
@@ -650,6 +730,9 @@ vr_status vr_destroy(vr_ctx *c) {
   if (c->d_stage) cudaFree(c->d_stage);
   if (c->d_lights_more) cudaFree(c->d_lights_more);
   if (c->d_counter) cudaFree(c->d_counter);
+  if (c->d_tile_order) cudaFree(c->d_tile_order);
+  if (c->d_cams) cudaFree(c->d_cams);
+  if (c->d_warp_times) cudaFree(c->d_warp_times);
   if (c->d_stats) cudaFree(c->d_stats);
   if (c->h_stats) cudaFreeHost(c->h_stats);
   cudaEventDestroy(c->ev0), cudaEventDestroy(c->ev1), cudaEventDestroy(c->evu0), cudaEventDestroy(c->evu1);
@@ -742,7 +825,47 @@ vr_status vr_render_device(vr_ctx *c, const vr_light *lights, size_t n_lights, c
   VR_TRY(collect(c));
   cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
   if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
-  return render_common(c, lights, n_lights, illumination, factors, es, res, R, props, thr, color, d_out, s);
+  return render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &d_out, s);
+}
+
+vr_status vr_render_batch_device(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+                                 const float factors[3], const float es[3], const uint64_t res[2], size_t n_frames,
+                                 const float *rotations, const float *props, float thr, const float color[3],
+                                 float *const *d_out_images, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  return render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_out_images, s);
+}
+
+vr_status vr_render_batch(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+                          const float factors[3], const float es[3], const uint64_t res[2], size_t n_frames,
+                          const float *rotations, const float *props, float thr, const float color[3], float *const *out_images) {
+  VR_CHECK_HANDLE(c);
+  if (!out_images || !res || n_frames == 0 || n_frames > 4096) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  const size_t bytes = (size_t)res[0] * res[1] * 3 * sizeof(float);
+  if (bytes == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: bad resolution");
+  if (c->image_cap < bytes * n_frames) {
+    if (c->d_image) cudaFree(c->d_image);
+    c->d_image = nullptr, c->image_cap = 0;
+    VR_CUDA(c, cudaMalloc(&c->d_image, bytes * n_frames));
+    c->image_cap = bytes * n_frames;
+  }
+  std::vector<float *> d_outs(n_frames);
+  for (size_t f = 0; f < n_frames; ++f) d_outs[f] = c->d_image + f * (bytes / sizeof(float));
+  VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_outs.data(), c->stream));
+  for (size_t f = 0; f < n_frames; ++f) {
+    if (!out_images[f]) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: null output");
+    VR_CUDA(c, cudaMemcpyAsync(out_images[f], d_outs[f], bytes, cudaMemcpyDeviceToHost, c->stream));
+  }
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  VR_TRY(collect(c));
+  c->stats.bytes_resident = resident_bytes(c);
+  return VR_OK;
 }
 
 vr_status vr_render(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
@@ -760,7 +883,7 @@ vr_status vr_render(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr
     VR_CUDA(c, cudaMalloc(&c->d_image, bytes));
     c->image_cap = bytes;
   }
-  VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, R, props, thr, color, c->d_image, c->stream));
+  VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &c->d_image, c->stream));
   // cudaDeviceSynchronize + cudaMemcpy D2H (volumeRender.cpp:280-281)
   VR_CUDA(c, cudaMemcpyAsync(out, c->d_image, bytes, cudaMemcpyDeviceToHost, c->stream));
   VR_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -809,14 +932,14 @@ int vr_abi_version(void) { return VR_ABI_VERSION; }
 
 vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_CLEAR_IMAGE) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_TILE_ORDER) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
   c->opt[option] = value;
   return VR_OK;
 }
 vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_CLEAR_IMAGE || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_TILE_ORDER || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   *value = c->opt[option];
   return VR_OK;
 }
@@ -926,6 +1049,15 @@ vr_status vr_device_free(vr_ctx *c, void *d_ptr) {
   VR_CHECK_HANDLE(c);
   VR_TRY(set_device(c));
   VR_CUDA(c, cudaFree(d_ptr));
+  return VR_OK;
+}
+vr_status vr_debug_warp_times(vr_ctx *c, uint64_t *host_pairs, size_t max_warps) {
+  VR_CHECK_HANDLE(c);
+  if (!c->d_warp_times) return fail(c, VR_ERR_UNSUPPORTED, "set VR_WARP_TIMES=1 before vr_create");
+  VR_TRY(set_device(c));
+  if (max_warps > 8192) max_warps = 8192;
+  VR_CUDA(c, cudaMemcpyAsync(host_pairs, c->d_warp_times, max_warps * 16, cudaMemcpyDeviceToHost, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
   return VR_OK;
 }
 vr_status vr_device_download(vr_ctx *c, void *host_dst, const void *d_src, size_t bytes) {

@@ -214,20 +214,20 @@ VR_HD bool intersect_box(F3 o, F3 d, F3 bmin, F3 bmax, float &tnear, float &tfar
   return true;
 }
 
-VR_HD F3 ray_origin(const KernelParams &P) {
+VR_HD F3 ray_origin(const Camera &C) {
   // kernel.cu:399-410: origin = camXOffset * xVec + (-1 * objDist * zVec)
-  const F3 xV = ld3(P.m[0]), zV = ld3(P.m[2]);
-  return (P.m[3][0] * xV) + (-1.0f * P.m[3][2] * zV);
+  const F3 xV = ld3(C.m[0]), zV = ld3(C.m[2]);
+  return (C.m[3][0] * xV) + (-1.0f * C.m[3][2] * zV);
 }
 
 // Ray generation + box clip (kernel.cu:388-431).  Returns false when the ray misses the box
 // (the pixel is then never written and keeps the memset 0).
-VR_HD bool ray_init(const KernelParams &P, uint32_t x, uint32_t y, F3 origin, Ray &r) {
+VR_HD bool ray_init(const KernelParams &P, const Camera &C, uint32_t x, uint32_t y, F3 origin, Ray &r) {
   const float u = (x / (float)P.W) * 2.0f - 1.0f;
   const float ratio = P.H / (float)P.W;
   const float v = (y / (float)P.H) * 2.0f * ratio - 1.0f * ratio;
-  const F3 xV = ld3(P.m[0]), yV = ld3(P.m[1]), zV = ld3(P.m[2]);
-  const F3 dir = normalize3(u * normalize3(xV) + v * yV + P.m[3][1] * zV);
+  const F3 xV = ld3(C.m[0]), yV = ld3(C.m[1]), zV = ld3(C.m[2]);
+  const F3 dir = normalize3(u * normalize3(xV) + v * yV + C.m[3][1] * zV);
   float tnear = 0.0f, tfar = 0.0f;
   if (!intersect_box(origin, dir, ld3(P.boxmin), ld3(P.boxmax), tnear, tfar)) return false;
   if (tnear < 0.0f) tnear = 0.0f;
@@ -585,9 +585,9 @@ VR_HD bool skip_empty(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, F3 dq, 
 // scheduling.  Used by the host emulation (tests/host_emul) and by the single-lane debug kernel.
 template <int GRAD, int LAYOUT, typename E, int UNI>
 VR_HD bool march_pixel(const KernelParams &P, uint32_t x, uint32_t y, float rgb[3], uint32_t &marched, uint32_t &shaded) {
-  const F3 origin = ray_origin(P);
+  const F3 origin = ray_origin(P.cam);
   Ray r;
-  if (!ray_init(P, x, y, origin, r)) return false;
+  if (!ray_init(P, P.cam, x, y, origin, r)) return false;
   const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);
   F3 dq, inv_dq;

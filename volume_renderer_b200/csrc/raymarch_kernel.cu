@@ -29,27 +29,41 @@ static constexpr unsigned kFull = 0xffffffffu;
 template <int GRAD, int LAYOUT, typename E, int UNI>
 __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const __grid_constant__ KernelParams P) {
   const int lane = threadIdx.x & 31;
-  const F3 origin = ray_origin(P);
   const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);
   const uint32_t wt_per_tile = (uint32_t)(P.wt_x * P.wt_y);
   unsigned long long tot_marched = 0, tot_shaded = 0, tot_hits = 0;
+  unsigned long long t_start = 0;
+  if (P.warp_times) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
 
   for (;;) {
     uint32_t w = 0;
     if (lane == 0) w = atomicAdd(P.work_counter, 1u);
     w = __shfl_sync(kFull, w, 0);
     if (w >= P.num_work) break;
-    // work item -> pixel
+    // work item -> frame, tile, pixel.  `entry` = frame * tiles_total + tile.
     const uint32_t owned = w / wt_per_tile, sub = w - owned * wt_per_tile;
-    const uint32_t tile = (uint32_t)P.part_rank + owned * (uint32_t)P.part_nranks;
+    const uint32_t entry = P.tile_order ? VR_LDG(P.tile_order + owned) : (uint32_t)P.part_rank + owned * (uint32_t)P.part_nranks;
+    uint32_t tile = entry;
+    Camera cam = P.cam;
+    if (P.n_frames > 1) {  // batch: the camera of this item's frame (uniform per warp, L1/L2 resident)
+      const uint32_t frame = entry / P.tiles_total;
+      tile = entry - frame * P.tiles_total;
+      const Camera *cp = P.cams + frame;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) cam.m[i][j] = VR_LDG(&cp->m[i][j]);
+      cam.out = cp->out;
+    }
+    const F3 origin = ray_origin(cam);
     const uint32_t ty = tile / (uint32_t)P.ntx, tx = tile - ty * (uint32_t)P.ntx;
     const uint32_t sy = sub / (uint32_t)P.wt_x, sx = sub - sy * (uint32_t)P.wt_x;
     const uint32_t x = tx * P.tile_w + sx * 8 + (lane & 7);
     const uint32_t y = ty * P.tile_h + sy * 4 + (lane >> 3);
 
     Ray r;
-    bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, x, y, origin, r);
+    bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, cam, x, y, origin, r);
     bool active = hit;
     F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
     if (active && P.skip == 1) skip_setup(P, r, bscale, dq, inv_dq);
@@ -64,18 +78,24 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
     if (x < (uint32_t)P.W && y < (uint32_t)P.H) {
       // column-major planar H x W x 3 (kernel.cu:496-506); lanes of a warp cover 4 consecutive y.
       // A ray that misses the box leaves the reference's pixel at its memset 0 (volumeRender.cpp:271):
-      // the owner of the pixel writes that 0 itself, so the image needs no clear and P.out may be
+      // the owner of the pixel writes that 0 itself, so the image needs no clear and cam.out may be
       // another GPU's memory (image-space direct send: each rank stores its tiles into the root's image).
       const size_t size = (size_t)P.W * P.H, k = (size_t)x * P.H + y;
-      P.out[k] = hit ? r.sx : 0.0f;
-      P.out[k + size] = hit ? r.sy : 0.0f;
-      P.out[k + 2 * size] = hit ? r.sz : 0.0f;
+      cam.out[k] = hit ? r.sx : 0.0f;
+      cam.out[k + size] = hit ? r.sy : 0.0f;
+      cam.out[k + 2 * size] = hit ? r.sz : 0.0f;
     }
     if (hit) {
       tot_marched += r.n_marched;
       tot_shaded += r.n_shaded;
       tot_hits += 1;
     }
+  }
+  if (P.warp_times && lane == 0) {
+    unsigned long long t_end;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+    const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    P.warp_times[2 * wid] = t_start, P.warp_times[2 * wid + 1] = t_end;
   }
   if (P.count) {
     for (int o = 16; o > 0; o >>= 1) {

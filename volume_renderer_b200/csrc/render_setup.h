@@ -13,6 +13,12 @@
 
 namespace vrb {
 
+// rotation rows, axis-reversed (render.cpp:211-219), and the property row (render.cpp:220-221)
+inline void fill_camera(Camera &C, const float R[9], const float props[3]) {
+  for (int k = 0; k < 3; ++k) C.m[k][0] = R[3 * k + 2], C.m[k][1] = R[3 * k + 1], C.m[k][2] = R[3 * k + 0];
+  C.m[3][0] = props[0], C.m[3][1] = props[1], C.m[3][2] = props[2];
+}
+
 inline void setup_frame(KernelParams &P, const float factors[3], const float es[3], uint64_t W, uint64_t H,
                         const float R[9], const float props[3], float thr, const float color[3], uint64_t w,
                         uint64_t h, uint64_t d) {
@@ -27,9 +33,7 @@ inline void setup_frame(KernelParams &P, const float factors[3], const float es[
   const float dxy = sqrtf((float)(w * w + h * h)), dyz = sqrtf((float)(h * h + d * d)), dxz = sqrtf((float)(w * w + d * d));
   const float minDiagonal = fminf(dxy, fminf(dyz, dxz));  // named maxDiagonal in the reference, volumeRender.cpp:141
   P.tstep = 1.f / (2.2f * minDiagonal);                    // volumeRender.cpp:144-145
-  // rotation rows, axis-reversed (render.cpp:211-219)
-  for (int k = 0; k < 3; ++k) P.m[k][0] = R[3 * k + 2], P.m[k][1] = R[3 * k + 1], P.m[k][2] = R[3 * k + 0];
-  P.m[3][0] = props[0], P.m[3][1] = props[1], P.m[3][2] = props[2];  // render.cpp:220-221
+  fill_camera(P.cam, R, props);
   P.thr = thr;
   memcpy(P.color, color, sizeof P.color);
   P.gstep[0] = 1.f / w, P.gstep[1] = 1.f / h, P.gstep[2] = 1.f / d;  // volumeRender.cpp:273-275

@@ -44,9 +44,18 @@ struct TexDesc {
 
 enum { MAX_PARAM_LIGHTS = 8 };
 
+// One camera of a launch: what differs between the frames of a batch (a stereo pair, a rotation movie).
+struct Camera {
+  float m[4][3];  // rows 0..2 camera axes, row 3 = (camXOffset, focal, objDist)  (volumeRender.h:37-44)
+  float *out;     // W*H*3 floats, column-major planar: k = x*H + y (kernel.cu:496-506)
+};
+
 // Everything one ray-march launch needs; passed by value as a __grid_constant__ parameter.
 struct KernelParams {
-  float *out;  // W*H*3 floats, column-major planar: k = x*H + y (kernel.cu:496-506)
+  Camera cam;           // the frame of a single-frame launch
+  const Camera *cams;   // n_frames > 1: the cameras of the batch (device memory); work items of all
+  int n_frames;         // frames share ONE queue, so the long rays of one frame fill the tail of another
+  uint32_t tiles_total; // ntx * nty
   int W, H;
   // image-space partition (multi-GPU): the image is cut into tile_w x tile_h tiles, tile j is
   // rendered by the context with j % part_nranks == part_rank.
@@ -56,11 +65,14 @@ struct KernelParams {
   uint32_t num_owned;      // partition tiles owned by this rank
   uint32_t num_work;       // warp work items = num_owned * wt_x * wt_y
   unsigned int *work_counter;
+  // owned tiles in the order they are handed out (heaviest first, see context.cu: tile_order);
+  // entry j is a tile index ty * ntx + tx.  NULL = part_rank + j * part_nranks.
+  const uint32_t *tile_order;
+  unsigned long long *warp_times;  // debug: per resident warp [start, end] in globaltimer ns (NULL = off)
   unsigned long long *stats;  // [0] samples marched, [1] samples shaded, [2] rays hit
   // vr::RenderOptions (volumeRender.h:81-109)
   float fEm, fAb, fRe;
   float boxmin[3], boxmax[3];
-  float m[4][3];  // rows 0..2 camera axes, row 3 = (camXOffset, focal, objDist)
   float thr, tstep;
   float color[3];
   float gstep[3];  // (1/w, 1/h, 1/d) of the emission volume (volumeRender.cpp:273-275)

@@ -71,10 +71,12 @@ class SharedImage:
     `ptr` is the device pointer to pass as d_out_image of vr_render_device on this rank.
     """
 
-    def __init__(self, ctx, H, W, rank, world, root=0, group=None):
+    def __init__(self, ctx, H, W, rank, world, root=0, group=None, count=1):
         lib = _abi.lib()
         self.ctx, self.rank, self.root, self.world = ctx, rank, root, world
-        self.nbytes = int(H) * int(W) * 3 * 4
+        self.frame_bytes = int(H) * int(W) * 3 * 4
+        self.count = int(count)  # frames of a batch live back to back in the one allocation
+        self.nbytes = self.frame_bytes * self.count
         self._owned = rank == root
         p = C.c_void_p()
         handle = C.create_string_buffer(_abi.IPC_HANDLE_BYTES)
@@ -86,13 +88,15 @@ class SharedImage:
         if not self._owned:
             _abi.check(lib.vr_ipc_open(ctx, raw, C.byref(p)), ctx)
         self.ptr = p
+        self.ptrs = [C.c_void_p(p.value + i * self.frame_bytes) for i in range(self.count)]
         # several ranks write disjoint tiles of this one image: nobody may clear the whole of it
         _abi.check(lib.vr_set_option(ctx, _abi.OPT_CLEAR_IMAGE, 0 if world > 1 else 1), ctx)
 
-    def download(self, host_array):
-        """Root only: copy the finished frame to a host numpy array (H x W x 3, Fortran order)."""
+    def download(self, host_array, frames=None):
+        """Root only: copy the first `frames` finished frames (default all) to a host numpy array."""
         assert self._owned
-        _abi.check(_abi.lib().vr_device_download(self.ctx, host_array.ctypes.data, self.ptr, self.nbytes), self.ctx)
+        n = self.frame_bytes * (self.count if frames is None else int(frames))
+        _abi.check(_abi.lib().vr_device_download(self.ctx, host_array.ctypes.data, self.ptr, n), self.ctx)
         return host_array
 
     def close(self):
