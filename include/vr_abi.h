@@ -57,7 +57,9 @@ typedef enum vr_dtype {
 
 typedef enum vr_memspace {
   VR_MEM_HOST = 0,   /* pageable or pinned host memory (the MATLAB case) */
-  VR_MEM_DEVICE = 1  /* already resident on this context's device (C harness / pipelines) */
+  VR_MEM_DEVICE = 1, /* already resident on this context's device (C harness / pipelines) */
+  VR_MEM_DEVICE_REGION = 2 /* device buffer holding ONLY this context's region plus halo, clipped to the volume
+                              (vr_set_region); dims still describe the whole volume */
 } vr_memspace;
 
 /* One MATLAB `Volume` object as mxMake_volume reads it (volumeRender.cpp:307-342):
@@ -210,6 +212,42 @@ VR_API vr_status vr_synth_volume(vr_ctx *ctx, int kind, uint32_t seed, const uin
  * dims and dtype as `in`) live in `out_memspace`.  SURVEY 8(f) row 3: saves 3 volume uploads. */
 VR_API vr_status vr_volume_gradient(vr_ctx *ctx, const vr_volume *in, int32_t out_memspace, void *gx, void *gy,
                                     void *gz);
+/* ---- volume-space mode (sort-last), no reference counterpart -------------------------------
+ * For volumes that are sharded over GPUs (README.md:5 "huge data"; the reference renders volumes
+ * that do not fit together in separate passes and adds the images in MATLAB, example1.m:85).
+ * Each context owns the voxel box [lo, hi) of every volume it syncs after vr_set_region (plus
+ * `halo` >= 2 voxels of neighbours; 0 = 4) and marches, on the GLOBAL sample lattice, only the
+ * samples inside its box.  One frame = two launches per context with one exchange between them:
+ *   1. vr_render_opacity_device: per pixel the opacity this brick alone accumulates (H*W floats);
+ *      all-gather these planes (n_bricks x H*W floats, brick-major);
+ *   2. vr_render_partial_device: shades the owned samples starting from the opacity of the bricks
+ *      in front (so the reference's `sum.w > threshold` termination, volumeRender_kernel.cu:485,
+ *      acts exactly where it would in one pass) and writes this brick's ADDITIVE share of the image;
+ *   3. vr_compose_partials_device: sums the shares in brick order (pointers may be peer memory).
+ * brick_boxes = n_bricks x {lo x,y,z, hi x,y,z} in voxels.  vr_set_region(ctx, NULL, NULL, 0) ends
+ * the mode.  Volumes must share the emission volume's dims. */
+VR_API vr_status vr_set_region(vr_ctx *ctx, const uint64_t lo[3], const uint64_t hi[3], uint32_t halo);
+VR_API vr_status vr_render_opacity_device(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
+                                          const vr_volume *illumination, const float factors[3],
+                                          const float element_size_um[3], const uint64_t resolution[2],
+                                          const float rotation[9], const float props[3],
+                                          float opacity_threshold, const float color[3],
+                                          float *d_opacity, void *cuda_stream);
+VR_API vr_status vr_render_partial_device(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
+                                          const vr_volume *illumination, const float factors[3],
+                                          const float element_size_um[3], const uint64_t resolution[2],
+                                          const float rotation[9], const float props[3],
+                                          float opacity_threshold, const float color[3],
+                                          uint32_t n_bricks, uint32_t brick_index,
+                                          const uint64_t *brick_boxes, const float *d_opacity_all,
+                                          float *d_out_image, void *cuda_stream);
+VR_API vr_status vr_compose_partials_device(vr_ctx *ctx, uint32_t n, const float *const *d_partials,
+                                            uint64_t n_floats, float *d_out, void *cuda_stream);
+/* The voxel box [lo, hi) of vr_synth_volume's volume, dense, lo[0] fastest (a VR_MEM_DEVICE_REGION
+ * source when the box is the region plus halo clipped to the volume). */
+VR_API vr_status vr_synth_volume_region(vr_ctx *ctx, int kind, uint32_t seed, const uint64_t dims[3],
+                                        const uint64_t lo[3], const uint64_t hi[3], int32_t dtype, void *d_out);
+
 /* Sharing one device image between the per-GPU processes of the image-space mode (CUDA IPC over
  * NVLink peer access): the root exports the image it allocated with vr_device_alloc, every other
  * rank opens it and passes the mapped pointer as d_out_image of vr_render_device, so the ray-march

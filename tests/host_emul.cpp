@@ -6,6 +6,7 @@
  * product path: nothing under volume_renderer_b200/ builds or loads it.
  */
 #include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -104,15 +105,22 @@ void build(HostTex &T, const float *src, int w, int h, int d, bool with_occ) {
 template <int GRAD, int LAYOUT, int UNI>
 void run(const KernelParams &P, float *out, uint64_t *stats) {
   const size_t size = (size_t)P.W * P.H;
-  memset(out, 0, size * 3 * sizeof(float));
+  if (P.vs_mode == 1)
+    memset(P.vs_opacity_out, 0, size * sizeof(float));
+  else
+    memset(out, 0, size * 3 * sizeof(float));
   uint64_t marched = 0, shaded = 0, hits = 0;
 #pragma omp parallel for schedule(dynamic, 8) reduction(+ : marched, shaded, hits)
   for (int64_t x = 0; x < P.W; ++x)
     for (int y = 0; y < P.H; ++y) {
-      float rgb[3];
+      float rgb[4];
       uint32_t m = 0, s = 0;
       if (!march_pixel<GRAD, LAYOUT, ElemF32, UNI>(P, (uint32_t)x, (uint32_t)y, rgb, m, s)) continue;
       const size_t k = (size_t)x * P.H + y;
+      if (P.vs_mode == 1) {
+        P.vs_opacity_out[k] = rgb[3];
+        continue;
+      }
       out[k] = rgb[0], out[k + size] = rgb[1], out[k + 2 * size] = rgb[2];
       marched += m, shaded += s, hits += 1;
     }
@@ -123,7 +131,7 @@ template <int LAYOUT>
 int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr_volume *gy, const vr_volume *gz,
          const vr_volume *lut, const vr_light *lights, size_t n_lights, const float factors[3], const float es[3],
          const uint64_t res[2], const float R[9], const float props[3], float thr, const float color[3], int skip,
-         int frac_bits, int variant, float *out, uint64_t *stats) {
+         int frac_bits, int variant, int n_bricks, const uint64_t *boxes_vox, float *out, uint64_t *stats) {
   HostTex Em, Re, Gx, Gy, Gz, Lut;
   auto ptr = [](const vr_volume *v) { return v ? static_cast<const float *>(v->data) : nullptr; };
   auto dim = [](const vr_volume *v, int i) { return v ? (int)v->dims[i] : 0; };
@@ -162,10 +170,49 @@ int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr
     P.lights[i][0] = lights[i].position[2], P.lights[i][1] = lights[i].position[1], P.lights[i][2] = lights[i].position[0];
     memcpy(P.lights[i] + 3, lights[i].color, 12);
   }
-  if (P.gradient_method) {
-    if (P.uniform) run<1, LAYOUT, 1>(P, out, stats); else run<1, LAYOUT, 0>(P, out, stats);
-  } else {
-    if (P.uniform) run<0, LAYOUT, 1>(P, out, stats); else run<0, LAYOUT, 0>(P, out, stats);
+  auto go = [&](float *dst, uint64_t *st) {
+    if (P.gradient_method) {
+      if (P.uniform) run<1, LAYOUT, 1>(P, dst, st); else run<1, LAYOUT, 0>(P, dst, st);
+    } else {
+      if (P.uniform) run<0, LAYOUT, 1>(P, dst, st); else run<0, LAYOUT, 0>(P, dst, st);
+    }
+  };
+  if (n_bricks <= 0) {
+    go(out, stats);
+    return 0;
+  }
+  // volume-space mode on virtual shards (whole storage, region test only): opacity pass per brick,
+  // shading pass per brick, sum of the shares in brick order - what multigpu.VolumeSpace does on GPUs
+  const size_t plane = (size_t)P.W * P.H;
+  const int64_t dims[3] = {(int64_t)em->dims[0], (int64_t)em->dims[1], (int64_t)em->dims[2]};
+  std::vector<float> opac((size_t)n_bricks * plane, 0.f), boxes((size_t)n_bricks * 6), part(plane * 3);
+  for (int b = 0; b < n_bricks; ++b)
+    for (int i = 0; i < 3; ++i) {
+      const float ext = P.boxmax[i] - P.boxmin[i];
+      boxes[6 * b + i] = P.boxmin[i] + ext * ((float)boxes_vox[6 * b + i] / (float)dims[i]);
+      boxes[6 * b + 3 + i] = P.boxmin[i] + ext * ((float)boxes_vox[6 * b + 3 + i] / (float)dims[i]);
+    }
+  auto region = [&](int b) {
+    for (int i = 0; i < 3; ++i) {
+      const int64_t lo = (int64_t)boxes_vox[6 * b + i], hi = (int64_t)boxes_vox[6 * b + 3 + i];
+      P.reg_lo[i] = lo <= 0 ? -INFINITY : (float)lo / (float)dims[i];
+      P.reg_hi[i] = hi >= dims[i] ? INFINITY : (float)hi / (float)dims[i];
+    }
+    P.vs_index = b, P.vs_count = n_bricks;
+  };
+  for (int b = 0; b < n_bricks; ++b) {
+    region(b);
+    P.vs_mode = 1;
+    P.vs_opacity_out = opac.data() + (size_t)b * plane;
+    go(nullptr, nullptr);
+  }
+  memset(out, 0, plane * 3 * sizeof(float));
+  P.vs_opacity_all = opac.data(), P.vs_boxes = boxes.data();
+  for (int b = 0; b < n_bricks; ++b) {
+    region(b);
+    P.vs_mode = 2;
+    go(part.data(), nullptr);
+    for (size_t i = 0; i < plane * 3; ++i) out[i] += part[i];
   }
   return 0;
 }
@@ -176,11 +223,11 @@ extern "C" int emul_render(const vr_volume *em, const vr_volume *re, const vr_vo
                            const vr_volume *gz, const vr_volume *lut, const vr_light *lights, size_t n_lights,
                            const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
                            const float props[3], float thr, const float color[3], int layout, int skip, int frac_bits,
-                           int variant, float *out, uint64_t *stats) {
+                           int variant, int n_bricks, const uint64_t *boxes_vox, float *out, uint64_t *stats) {
   if (!em) return 1;
   if (layout == LAYOUT_BRICK)
-    return emul<LAYOUT_BRICK>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, out, stats);
-  return emul<LAYOUT_LINEAR>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, out, stats);
+    return emul<LAYOUT_BRICK>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, n_bricks, boxes_vox, out, stats);
+  return emul<LAYOUT_LINEAR>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, n_bricks, boxes_vox, out, stats);
 }
 
 // unit-test hooks for the small numeric helpers of raymarch_core.h

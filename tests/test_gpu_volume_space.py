@@ -1,0 +1,100 @@
+"""Volume-space (sort-last) mode on the GPU with virtual shards: every brick is its own context on
+cuda:0 holding only its voxel box plus halo; opacity pass, shading pass, composite.  Compared with
+the same library's single-pass render (bit-identical storage contents, different association of the
+opacity product) and with the oracle."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import vrt
+from volume_renderer_b200 import _abi, api, multigpu
+
+pytestmark = pytest.mark.gpu
+RES = (160, 128)
+
+
+def _scene(vol, lut, grad, bricks=None, b=None, halo=0):
+    r = api.VolumeRender()
+    if bricks is not None:
+        r.setRegion(bricks[b][0], bricks[b][1], halo)  # before the volumes are assigned / synced
+    r = vrt.example1_scene(lambda: r, vol, RES, lights=2, lut=lut)
+    r.FactorAbsorption = 30.0  # rays reach the 0.9 threshold inside the volume
+    if grad:
+        gx, gy, gz = api.Volume(vol).grad()
+        r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
+    return r
+
+
+@pytest.mark.parametrize("splits", [(1, 1, 2), (2, 2, 2), (3, 1, 2)])
+@pytest.mark.parametrize("grad", [0, 1])
+def test_bricks_on_one_gpu_match_single_pass(splits, grad):
+    vol = vrt.synth_brain((72, 64, 56))
+    lut = api.HenyeyGreenstein(64)
+    full = _scene(vol, lut, grad).render()
+    bricks = multigpu.brick_grid(vol.shape, splits)
+    rs = [_scene(vol, lut, grad, bricks, b) for b in range(len(bricks))]
+    img = multigpu.render_bricks_one_gpu(rs, bricks)
+    m = vrt.compare(img, full)
+    print(splits, grad, m)
+    assert m["max_abs_norm"] < 2e-5, m
+    # only the owned box (+ halo) is resident
+    whole = _scene(vol, lut, grad)
+    whole.render()
+    assert rs[0].stats()["bytes_resident"] < 0.75 * whole.stats()["bytes_resident"] or len(bricks) < 3
+    orc = vrt.example1_scene(vrt.OracleVolumeRender, vol, RES, lights=2, lut=lut)
+    orc.FactorAbsorption = 30.0
+    if grad:
+        gx, gy, gz = api.Volume(vol).grad()
+        orc.VolumeGradientX, orc.VolumeGradientY, orc.VolumeGradientZ = gx, gy, gz
+    assert vrt.compare(img, orc.render())["max_abs_norm"] <= vrt.TOL
+
+
+def test_region_buffer_generated_on_the_device():
+    """config 5 shape: each brick's voxels (+ halo) are generated straight into HBM and handed over
+    as a VR_MEM_DEVICE_REGION source - the whole volume never exists anywhere."""
+    dims = (64, 48, 80)
+    vol = vrt.synth_brain(dims)
+    lut = api.HenyeyGreenstein(64)
+    full = _scene(vol, lut, 0).render()
+    bricks = multigpu.brick_grid(dims, (2, 1, 2))
+    lib = _abi.lib()
+    rs, bufs = [], []
+    halo = 3
+    for b, (lo, hi) in enumerate(bricks):
+        r = api.VolumeRender()
+        r.setRegion(lo, hi, halo)
+        blo = [max(l - halo, 0) for l in lo]
+        bhi = [min(h + halo, d) for h, d in zip(hi, dims)]
+        n = int(np.prod([h - l for l, h in zip(blo, bhi)]))
+        ptr = C.c_void_p()
+        _abi.check(lib.vr_device_alloc(r.objectHandle, n * 4, C.byref(ptr)), r.objectHandle)
+        u3 = lambda v: (C.c_uint64 * 3)(*[int(x) for x in v])
+        _abi.check(lib.vr_synth_volume_region(r.objectHandle, 0, vrt.SEED, u3(dims), u3(blo), u3(bhi), _abi.DTYPE_F32, ptr), r.objectHandle)
+        dv = api.DeviceVolume(ptr.value, dims, _abi.DTYPE_F32, _abi.MEM_DEVICE_REGION)
+        r = vrt.example1_scene(lambda r=r: r, dv, RES, lights=2, lut=lut)
+        r.FactorAbsorption = 30.0
+        rs.append(r)
+        bufs.append((r, ptr))
+    img = multigpu.render_bricks_one_gpu(rs, bricks)
+    assert vrt.compare(img, full)["max_abs_norm"] < 2e-5
+    for r, ptr in bufs:
+        _abi.check(lib.vr_device_free(r.objectHandle, ptr), r.objectHandle)
+
+
+def test_region_contexts_refuse_plain_render_and_small_halos():
+    vol = vrt.synth_brain((32, 32, 32))
+    lut = api.HenyeyGreenstein(64)
+    bricks = multigpu.brick_grid(vol.shape, (1, 1, 2))
+    r = _scene(vol, lut, 0, bricks, 0)
+    with pytest.raises(_abi.VrError):
+        r.render()
+    r2 = api.VolumeRender()
+    r2.setRegion(*bricks[0], 2)
+    r2 = vrt.example1_scene(lambda: r2, vol, RES, lights=1, lut=lut)
+    r2.ElementSizeUm = [1.0, 0.2, 1.0]  # boxmax.y = 0.2: the on-the-fly gradient taps reach 4 voxels out
+    import torch
+
+    buf = torch.zeros(RES[0] * RES[1], device="cuda")
+    with pytest.raises(_abi.VrError):
+        r2.renderOpacity(buf.data_ptr())

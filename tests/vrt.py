@@ -186,12 +186,12 @@ def host_emul():
         P = C.POINTER
         f3, u64p = P(C.c_float), P(C.c_uint64)
         lib.emul_render.argtypes = [P(_abi.VrVolume)] * 6 + [P(_abi.VrLight), C.c_size_t, f3, f3, u64p, f3, f3, C.c_float, f3,
-                                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, u64p]
+                                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u64p, C.c_void_p, u64p]
         _emul = lib
     return _emul
 
 
-def emul_render(r, layout=1, skip=2, frac_bits=0, resolution=None, xoffset=0.0, variant=0):
+def emul_render(r, layout=1, skip=2, frac_bits=0, resolution=None, xoffset=0.0, variant=0, bricks=None):
     """Run a configured api.VolumeRender-like scene `r` (Em = Ab aliased) through the host
     emulation of the device code.  Returns (image HxWx3, stats[3])."""
     lib = host_emul()
@@ -212,8 +212,10 @@ def emul_render(r, layout=1, skip=2, frac_bits=0, resolution=None, xoffset=0.0, 
     H, W = res
     out = np.zeros((H, W, 3), dtype=np.float32, order="F")
     stats = (C.c_uint64 * 3)()
+    nb = len(bricks) if bricks else 0
+    bv = (C.c_uint64 * (6 * max(nb, 1)))(*[int(v) for box in (bricks or []) for v in (list(box[0]) + list(box[1]))])
     rc = lib.emul_render(vs(r.VolumeEmission), vs(r.VolumeReflection), vs(g[0]), vs(g[1]), vs(g[2]), args[2], args[0], args[1],
-                         *args[3:], layout, skip, frac_bits, variant, out.ctypes.data, stats)
+                         *args[3:], layout, skip, frac_bits, variant, nb, bv, out.ctypes.data, stats)
     assert rc == 0, rc
     return out, list(stats)
 

@@ -21,7 +21,7 @@ STATUS_NAMES = {
     6: "VR_ERR_UNSUPPORTED",
 }
 DTYPE_F32, DTYPE_BF16 = 0, 1
-MEM_HOST, MEM_DEVICE = 0, 1
+MEM_HOST, MEM_DEVICE, MEM_DEVICE_REGION = 0, 1, 2
 
 # vr_option
 OPT_FILTER_FRAC_BITS = 0
@@ -107,6 +107,11 @@ def declare(lib):
         "vr_get_device": ([vp, P(C.c_int)], C.c_int),
         "vr_synth_volume": ([vp, C.c_int, C.c_uint32, u64p, C.c_int32, vp], C.c_int),
         "vr_volume_gradient": ([vp, P(VrVolume), C.c_int32, vp, vp, vp], C.c_int),
+        "vr_set_region": ([vp, u64p, u64p, C.c_uint32], C.c_int),
+        "vr_render_opacity_device": (render_args + [vp, vp], C.c_int),
+        "vr_render_partial_device": (render_args + [C.c_uint32, C.c_uint32, u64p, vp, vp, vp], C.c_int),
+        "vr_compose_partials_device": ([vp, C.c_uint32, P(vp), C.c_uint64, vp, vp], C.c_int),
+        "vr_synth_volume_region": ([vp, C.c_int, C.c_uint32, u64p, u64p, u64p, C.c_int32, vp], C.c_int),
         "vr_debug_warp_times": ([vp, vp, C.c_size_t], C.c_int),
         "vr_ipc_export": ([vp, vp, C.c_char_p], C.c_int),
         "vr_ipc_open": ([vp, C.c_char_p, P(vp)], C.c_int),
@@ -151,9 +156,9 @@ def volume_struct(data, last_update, keepalive=None):
     """
     v = VrVolume()
     if isinstance(data, tuple):
-        ptr, dims, dtype = data
+        ptr, dims, dtype = data[:3]
         v.data = ptr
-        v.memspace = MEM_DEVICE
+        v.memspace = data[3] if len(data) > 3 else MEM_DEVICE
         v.dtype = dtype
     else:
         a = np.asarray(data)

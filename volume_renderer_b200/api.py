@@ -29,6 +29,7 @@ from . import _abi
 __all__ = [
     "VolumeRender",
     "Volume",
+    "DeviceVolume",
     "LightSource",
     "StereoRenderMode",
     "HenyeyGreenstein",
@@ -163,6 +164,24 @@ class Volume:
         a = np.asarray(self._data)
         mx, mn = a.max(), a.min()
         self.Data = (a - mn) * np.float32((newMax - newMin) / (mx - mn)) + np.float32(newMin)
+
+
+class DeviceVolume(Volume):
+    """Extension: a volume that already lives in device memory (whole: _abi.MEM_DEVICE, or only this
+    context's region plus halo: _abi.MEM_DEVICE_REGION).  `dims` are always the whole volume's."""
+
+    def __init__(self, ptr, dims, dtype=_abi.DTYPE_F32, memspace=_abi.MEM_DEVICE, keepalive=None):
+        self.TimeLastUpdate = 0
+        self._keep = keepalive
+        self._data = (int(ptr), tuple(int(d) for d in dims), int(dtype), int(memspace))
+        self._stamp()
+
+    @property
+    def Data(self):
+        return self._data
+
+    def size(self):
+        return self._data[1]
 
 
 class LightSource:
@@ -499,6 +518,42 @@ class VolumeRender:
         lut = self.VolumeIllumination if self.VolumeIllumination is not False else None
         return self._backend.render_batch(self.objectHandle, lights, lut, factors, self.ElementSizeUm, resolution, rots, props,
                                           self.OpacityThreshold, self.Color)
+
+    # --- volume-space (sort-last) extension: this object owns one voxel box of every volume -------
+    def setRegion(self, lo=None, hi=None, halo=0):
+        """vr_set_region: volumes synced afterwards keep only [lo, hi) (+ halo) resident."""
+        lib = _abi.lib()
+        if lo is None:
+            _abi.check(lib.vr_set_region(self.objectHandle, None, None, 0), self.objectHandle)
+            return
+        l3, h3 = (C.c_uint64 * 3)(*[int(v) for v in lo]), (C.c_uint64 * 3)(*[int(v) for v in hi])
+        _abi.check(lib.vr_set_region(self.objectHandle, l3, h3, int(halo)), self.objectHandle)
+
+    def _packed_mono_args(self):
+        """p_render's marshalling (VolumeRender.m:497-583) for a mono frame, for the device entry points."""
+        self._check_volumes()
+        self.syncVolumes()
+        factors = [self.FactorEmission, self.FactorReflection, self.FactorAbsorption]
+        props = [np.float32(self.CameraXOffset), self.FocalLength, self.DistanceToObject]
+        res = [int(self.ImageResolution[1]), int(self.ImageResolution[0])]
+        lights = self.LightSources if self.LightSources is not False else None
+        lut = self.VolumeIllumination if self.VolumeIllumination is not False else None
+        return _render_args(lights, lut, factors, self.ElementSizeUm, res, np.flipud(np.asarray(self.RotationMatrix)), props,
+                            self.OpacityThreshold, self.Color)
+
+    def renderOpacity(self, d_opacity, stream=None):
+        """Pass 1 of a sort-last frame: this brick's own opacity per pixel into device memory (H*W floats)."""
+        args, keep = self._packed_mono_args()
+        _abi.check(_abi.lib().vr_render_opacity_device(self.objectHandle, *args, C.c_void_p(d_opacity), C.c_void_p(stream or 0)), self.objectHandle)
+
+    def renderPartial(self, bricks, index, d_opacity_all, d_out, stream=None):
+        """Pass 2: this brick's additive share of the image (H*W*3 floats in device memory)."""
+        from . import multigpu
+
+        args, keep = self._packed_mono_args()
+        boxes = multigpu.boxes_array(bricks)
+        _abi.check(_abi.lib().vr_render_partial_device(self.objectHandle, *args, len(bricks), int(index), boxes.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                       C.c_void_p(d_opacity_all), C.c_void_p(d_out), C.c_void_p(stream or 0)), self.objectHandle)
 
     def renderMovie(self, rotations):
         """Extension: the frames of a rotation movie (examples/example2.m:59-66) in one launch;

@@ -70,7 +70,9 @@ struct Resident {
   uint8_t *dist = nullptr;  // distance grid (cells to the nearest non-empty cell)
   size_t dist_bytes = 0;
   int ocx = 0, ocy = 0, ocz = 0;
-  int w = 0, h = 0, d = 0;
+  int w = 0, h = 0, d = 0;        // global voxel dims
+  int ox = 0, oy = 0, oz = 0;     // global padded index -> local padded index
+  int lw = 0, lh = 0, ld = 0;     // local padded dims
   int dtype = VR_DTYPE_F32;
   int layout = LAYOUT_LINEAR;
   uint32_t sy = 0, sz = 0;
@@ -113,6 +115,12 @@ struct vr_ctx {
   std::vector<uint32_t> h_tile_order;
   unsigned long long *d_stats = nullptr;  // 3 counters
   unsigned long long *h_stats = nullptr;  // pinned
+  // volume-space mode: the voxel sub-box this context owns (region_on == false: everything)
+  bool region_on = false;
+  int64_t rlo[3] = {0, 0, 0}, rhi[3] = {0, 0, 0};
+  int halo = 2;
+  float *d_boxes = nullptr;  // world-space brick boxes of the last partial render
+  size_t boxes_cap = 0;
   // options
   int64_t opt[16];
   // bookkeeping
@@ -171,9 +179,8 @@ uint64_t resident_bytes(const vr_ctx *c) {
 }
 
 // storage geometry of a padded volume
-void geometry(int layout, uint64_t w, uint64_t h, uint64_t d, uint32_t *sy, uint32_t *sz, uint64_t *elems,
+void geometry(int layout, uint64_t pw, uint64_t ph, uint64_t pd, uint32_t *sy, uint32_t *sz, uint64_t *elems,
               uint64_t *layers, uint64_t *layer_elems) {
-  const uint64_t pw = w + 2, ph = h + 2, pd = d + 2;
   if (layout == LAYOUT_BRICK) {
     const uint64_t nbx = (pw + 7) / 8, nby = (ph + 7) / 8, nbz = (pd + 7) / 8;
     *sy = (uint32_t)(nbx * 512);
@@ -188,6 +195,8 @@ void geometry(int layout, uint64_t w, uint64_t h, uint64_t d, uint32_t *sy, uint
   }
   *elems = *layers * *layer_elems;
 }
+
+TexDesc describe(const Resident &r);
 
 vr_status ensure_stage(vr_ctx *c, size_t bytes) {
   if (c->stage_cap >= bytes) return VR_OK;
@@ -228,9 +237,24 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
     return VR_OK;
   }
   const int layout = slot == S_LIGHT ? LAYOUT_LINEAR : (c->opt[VR_OPT_BRICK_LAYOUT] ? LAYOUT_BRICK : LAYOUT_LINEAR);
+  // what becomes resident: the whole volume padded by one replicated voxel, or (volume-space mode)
+  // the owned voxel box [rlo, rhi) plus `halo` voxels of real neighbours (replicated at the volume's faces)
+  const bool region = c->region_on && slot != S_LIGHT;
+  const int64_t dims[3] = {(int64_t)v.w, (int64_t)v.h, (int64_t)v.d};
+  int64_t lo[3] = {0, 0, 0}, hi[3] = {dims[0], dims[1], dims[2]};
+  int halo = 1;
+  if (region) {
+    halo = c->halo;
+    for (int i = 0; i < 3; ++i) {
+      lo[i] = c->rlo[i], hi[i] = c->rhi[i];
+      if (lo[i] < 0 || hi[i] > dims[i] || lo[i] >= hi[i]) return fail(c, VR_ERR_INVALID_ARGUMENT, "region [%lld,%lld) does not fit axis %d of a %lld-voxel volume", (long long)lo[i], (long long)hi[i], i, (long long)dims[i]);
+    }
+  }
+  const int64_t g0[3] = {lo[0] - halo, lo[1] - halo, lo[2] - halo};  // global voxel of local padded index 0
+  const uint64_t pw = (uint64_t)(hi[0] - lo[0] + 2 * halo), ph = (uint64_t)(hi[1] - lo[1] + 2 * halo), pd = (uint64_t)(hi[2] - lo[2] + 2 * halo);
   uint64_t elems, layers, layer_elems;
   uint32_t sy, sz;
-  geometry(layout, v.w, v.h, v.d, &sy, &sz, &elems, &layers, &layer_elems);
+  geometry(layout, pw, ph, pd, &sy, &sz, &elems, &layers, &layer_elems);
   if (layer_elems > 0xffffffffull) return fail(c, VR_ERR_UNSUPPORTED, "volume slice too large for 32-bit in-layer offsets");
   const size_t es = elem_size(v.dtype);
   size_t free_b = 0, total_b = 0;
@@ -243,6 +267,8 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
   VR_CUDA(c, cudaMalloc(&r.storage, elems * es));
   r.storage_bytes = elems * es;
   r.w = (int)v.w, r.h = (int)v.h, r.d = (int)v.d;
+  r.ox = (int)(1 + g0[0]), r.oy = (int)(1 + g0[1]), r.oz = (int)(1 + g0[2]);
+  r.lw = (int)pw, r.lh = (int)ph, r.ld = (int)pd;
   r.dtype = v.dtype;
   r.layout = layout;
   r.sy = sy, r.sz = sz;
@@ -250,18 +276,32 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
   RepackArgs a;
   a.dst = r.storage;
   a.w = r.w, a.h = r.h, a.d = r.d;
+  a.lw = r.lw, a.lh = r.lh, a.ld = r.ld;
+  a.gx0 = (int)g0[0], a.gy0 = (int)g0[1], a.gz0 = (int)g0[2];
+  a.sx0 = 0, a.sy0 = 0, a.sw = r.w, a.sh = r.h;
   a.sy = sy, a.sz = sz;
   a.layout = layout;
   a.src_dtype = a.dst_dtype = v.dtype;
+  auto clampz = [&](int64_t z) { return z < 0 ? 0 : (z > dims[2] - 1 ? dims[2] - 1 : z); };
   const uint64_t zper = layout == LAYOUT_BRICK ? 8 : 1;  // padded Z planes per layer
   const size_t slice_bytes = (size_t)v.w * v.h * es;
-  if (v.memspace == VR_MEM_DEVICE) {
+  if (v.memspace == VR_MEM_DEVICE_REGION) {
+    // the caller's device buffer holds exactly the owned box plus halo, clipped to the volume
+    if (!region) return fail(c, VR_ERR_INVALID_ARGUMENT, "a region buffer needs vr_set_region first");
+    int64_t b0[3], b1[3];
+    for (int i = 0; i < 3; ++i) b0[i] = g0[i] < 0 ? 0 : g0[i], b1[i] = hi[i] + halo > dims[i] ? dims[i] : hi[i] + halo;
+    a.src = v.data;
+    a.sx0 = (int)b0[0], a.sy0 = (int)b0[1], a.sw = (int)(b1[0] - b0[0]), a.sh = (int)(b1[1] - b0[1]);
+    a.src_z0 = (int)b0[2];
+    a.o0 = 0, a.o1 = elems;
+    VR_CUDA(c, launch_repack(a, c->stream));
+  } else if (v.memspace == VR_MEM_DEVICE) {
     a.src = v.data;
     a.src_z0 = 0;
     a.o0 = 0, a.o1 = elems;
     VR_CUDA(c, launch_repack(a, c->stream));
   } else {
-    // slab = as many layers as fit a ~256 MiB staging buffer
+    // slab = as many layers as fit a ~256 MiB staging buffer; only the z slices the region needs cross PCIe
     const size_t budget = (size_t)256 << 20;
     uint64_t slab_layers = budget / (slice_bytes * zper);
     if (slab_layers < 1) slab_layers = 1;
@@ -269,10 +309,8 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
     VR_TRY(ensure_stage(c, (size_t)(slab_layers * zper + 1) * slice_bytes));
     for (uint64_t l0 = 0; l0 < layers; l0 += slab_layers) {
       const uint64_t l1 = l0 + slab_layers < layers ? l0 + slab_layers : layers;
-      // padded planes [l0*zper, l1*zper) hold voxel z = clamp(Z-1)
-      int64_t z0 = (int64_t)(l0 * zper) - 1, z1 = (int64_t)(l1 * zper) - 2;
-      z0 = z0 < 0 ? 0 : (z0 > (int64_t)v.d - 1 ? (int64_t)v.d - 1 : z0);
-      z1 = z1 < 0 ? 0 : (z1 > (int64_t)v.d - 1 ? (int64_t)v.d - 1 : z1);
+      // padded planes [l0*zper, l1*zper) hold global voxel z = clamp(Z + gz0)
+      const int64_t z0 = clampz((int64_t)(l0 * zper) + g0[2]), z1 = clampz((int64_t)(l1 * zper) - 1 + g0[2]);
       const size_t nbytes = (size_t)(z1 - z0 + 1) * slice_bytes;
       // the staging buffer is reused: the previous slab's repack must have consumed it (same stream)
       VR_CUDA(c, cudaMemcpyAsync(c->d_stage, static_cast<const char *>(v.data) + (size_t)z0 * slice_bytes, nbytes,
@@ -292,9 +330,9 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
     r.occ_bytes = (size_t)((ncell + 31) / 32) * 4;
     VR_CUDA(c, cudaMalloc(&r.occ, r.occ_bytes));
     VR_CUDA(c, cudaMemsetAsync(r.occ, 0, r.occ_bytes, c->stream));
-    TexDesc t{};
-    t.p = r.storage, t.w = r.w, t.h = r.h, t.d = r.d, t.sy = r.sy, t.sz = r.sz, t.kind = r.kind;
-    VR_CUDA(c, launch_occupancy(t, r.layout, r.dtype, r.occ, r.ocx, r.ocy, r.ocz, 2, c->stream));
+    const TexDesc t = describe(r);
+    const int reg[6] = {(int)lo[0], (int)lo[1], (int)lo[2], (int)hi[0], (int)hi[1], (int)hi[2]};
+    VR_CUDA(c, launch_occupancy(t, r.layout, r.dtype, r.occ, r.ocx, r.ocy, r.ocz, 2, reg, c->stream));
     r.dist_bytes = (size_t)ncell;
     VR_CUDA(c, cudaMalloc(&r.dist, r.dist_bytes));
     VR_TRY(ensure_stage(c, r.dist_bytes));  // scratch of the middle pass; stream order protects it
@@ -424,6 +462,8 @@ TexDesc describe(const Resident &r) {
   t.sy = r.sy, t.sz = r.sz;
   t.kind = r.kind;
   t.cval = r.cval;
+  t.ox = r.ox, t.oy = r.oy, t.oz = r.oz;
+  t.lw = r.lw, t.lh = r.lh, t.ld = r.ld;
   return t;
 }
 
@@ -449,11 +489,24 @@ vr_status collect(vr_ctx *c) {
   return VR_OK;
 }
 
+// volume-space passes of render_common (NULL = plain render)
+struct VsArgs {
+  int mode;                    // 1 opacity pass, 2 shading pass
+  int index, count;            // this brick, number of bricks
+  float *opacity_out;          // mode 1
+  const float *opacity_all;    // mode 2
+  const uint64_t *boxes_vox;   // mode 2: count x {lo x,y,z, hi x,y,z} in voxels
+};
+
 // 'render' minus the read-back: marshal like render.cpp:142-245, set up like vr::initRender
 // (volumeRender.cpp:112-156) and vr::render (:264-277), launch on the context's stream.
 vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
                         const float factors[3], const float es[3], const uint64_t res[2], size_t n_frames, const float *R,
-                        const float *props, float thr, const float color[3], float *const *d_outs, cudaStream_t stream) {
+                        const float *props, float thr, const float color[3], float *const *d_outs, cudaStream_t stream,
+                        const VsArgs *vs = nullptr) {
+  if (c->region_on != (vs != nullptr))
+    return fail(c, VR_ERR_INVALID_ARGUMENT, c->region_on ? "this context owns a region (vr_set_region): use vr_render_opacity_device / vr_render_partial_device"
+                                                         : "volume-space passes need vr_set_region first");
   if (!factors || !es || !res || !R || !props || !color || !d_outs || n_frames == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
   if (n_frames > 4096) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: at most 4096 frames per batch");
   for (size_t f = 0; f < n_frames; ++f)
@@ -529,9 +582,53 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   for (const TexDesc *t : vt) {
     if (t->kind != TEX_VOLUME) continue;
     if (!have_geo) P.geo = *t, P.geo.p = nullptr, have_geo = true;
-    if (t->w != P.geo.w || t->h != P.geo.h || t->d != P.geo.d || t->sy != P.geo.sy || t->sz != P.geo.sz) P.uniform = 0;
+    if (t->w != P.geo.w || t->h != P.geo.h || t->d != P.geo.d || t->sy != P.geo.sy || t->sz != P.geo.sz || t->ox != P.geo.ox ||
+        t->oy != P.geo.oy || t->oz != P.geo.oz)
+      P.uniform = 0;
   }
   if (c->opt[VR_OPT_KERNEL_VARIANT] == 1) P.uniform = 0;  // variant 1: per-texture addressing everywhere (A/B measurements)
+
+  // volume-space mode
+  P.vs_mode = 0;
+  if (vs) {
+    if (n_frames != 1) return fail(c, VR_ERR_UNSUPPORTED, "volume-space passes render one frame per launch");
+    const int64_t dims[3] = {(int64_t)E.w, (int64_t)E.h, (int64_t)E.d};
+    for (const TexDesc *t : vt)
+      if (t->kind == TEX_VOLUME && (t->w != dims[0] || t->h != dims[1] || t->d != dims[2]))
+        return fail(c, VR_ERR_UNSUPPORTED, "volume-space mode: every volume must have the emission volume's dims");
+    // taps of an owned sample reach 1.5 voxels (+ the on-the-fly gradient offset 1/(2*boxmax_i) voxels) beyond the region
+    float reach = 1.5f;
+    if (!P.gradient_method && !c->lights.empty())
+      for (int i = 0; i < 3; ++i) reach = fmaxf(reach, 1.5f + 1.0f / (2.0f * P.boxmax[i]));
+    if ((float)c->halo < reach) return fail(c, VR_ERR_INVALID_ARGUMENT, "region halo %d too small: this scene needs %d voxels", c->halo, (int)ceilf(reach));
+    P.vs_mode = vs->mode, P.vs_index = vs->index, P.vs_count = vs->count;
+    for (int i = 0; i < 3; ++i) {
+      P.reg_lo[i] = c->rlo[i] <= 0 ? -INFINITY : (float)c->rlo[i] / (float)dims[i];
+      P.reg_hi[i] = c->rhi[i] >= dims[i] ? INFINITY : (float)c->rhi[i] / (float)dims[i];
+    }
+    P.vs_opacity_out = vs->opacity_out, P.vs_opacity_all = vs->opacity_all;
+    if (vs->mode == 2) {
+      if (vs->count < 1 || vs->index < 0 || vs->index >= vs->count || !vs->boxes_vox || !vs->opacity_all) return fail(c, VR_ERR_INVALID_ARGUMENT, "partial render: bad brick arguments");
+      std::vector<float> boxes((size_t)vs->count * 6);
+      for (int b = 0; b < vs->count; ++b)
+        for (int i = 0; i < 3; ++i) {  // voxel planes -> world planes of the box [boxmin, boxmax]
+          const float ext = P.boxmax[i] - P.boxmin[i];
+          boxes[6 * b + i] = P.boxmin[i] + ext * ((float)vs->boxes_vox[6 * b + i] / (float)dims[i]);
+          boxes[6 * b + 3 + i] = P.boxmin[i] + ext * ((float)vs->boxes_vox[6 * b + 3 + i] / (float)dims[i]);
+        }
+      const size_t need = boxes.size() * sizeof(float);
+      if (c->boxes_cap < need) {
+        if (c->d_boxes) cudaFree(c->d_boxes);
+        c->d_boxes = nullptr, c->boxes_cap = 0;
+        VR_CUDA(c, cudaMalloc(&c->d_boxes, need));
+        c->boxes_cap = need;
+      }
+      VR_CUDA(c, cudaMemcpyAsync(c->d_boxes, boxes.data(), need, cudaMemcpyHostToDevice, stream));
+      P.vs_boxes = c->d_boxes;
+    } else if (!vs->opacity_out) {
+      return fail(c, VR_ERR_INVALID_ARGUMENT, "opacity pass: null output");
+    }
+  }
 
   // lights
   P.n_lights = (int)c->lights.size();
@@ -585,6 +682,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     const size_t need = n_frames * sizeof(Camera);
     if (c->cams_cap < need) {
       if (c->d_cams) cudaFree(c->d_cams);
+  if (c->d_boxes) cudaFree(c->d_boxes);
       c->d_cams = nullptr, c->cams_cap = 0;
       VR_CUDA(c, cudaMalloc(&c->d_cams, need));
       c->cams_cap = need;
@@ -732,6 +830,7 @@ vr_status vr_destroy(vr_ctx *c) {
   if (c->d_counter) cudaFree(c->d_counter);
   if (c->d_tile_order) cudaFree(c->d_tile_order);
   if (c->d_cams) cudaFree(c->d_cams);
+  if (c->d_boxes) cudaFree(c->d_boxes);
   if (c->d_warp_times) cudaFree(c->d_warp_times);
   if (c->d_stats) cudaFree(c->d_stats);
   if (c->h_stats) cudaFreeHost(c->h_stats);
@@ -838,6 +937,69 @@ vr_status vr_render_batch_device(vr_ctx *c, const vr_light *lights, size_t n_lig
   cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
   if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
   return render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_out_images, s);
+}
+
+vr_status vr_set_region(vr_ctx *c, const uint64_t lo[3], const uint64_t hi[3], uint32_t halo) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  if (!lo || !hi || (hi[0] == 0 && hi[1] == 0 && hi[2] == 0)) {
+    c->region_on = false;
+    return VR_OK;
+  }
+  for (int i = 0; i < 3; ++i) {
+    if (lo[i] >= hi[i] || hi[i] > 0x3fffffff) return fail(c, VR_ERR_INVALID_ARGUMENT, "set_region: empty or oversized box on axis %d", i);
+    c->rlo[i] = (int64_t)lo[i], c->rhi[i] = (int64_t)hi[i];
+  }
+  c->halo = halo ? (int)halo : 4;
+  if (c->halo < 2 || c->halo > 64) return fail(c, VR_ERR_INVALID_ARGUMENT, "set_region: halo must be in [2, 64]");
+  c->region_on = true;
+  return VR_OK;
+}
+
+vr_status vr_render_opacity_device(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+                                   const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
+                                   const float props[3], float thr, const float color[3], float *d_opacity, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  if (!d_opacity) return fail(c, VR_ERR_INVALID_ARGUMENT, "opacity pass: null output");
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  VsArgs vs{};
+  vs.mode = 1;
+  vs.opacity_out = d_opacity;
+  float *dummy = d_opacity;  // no image is written in this pass; any non-null pointer passes the argument check
+  const int64_t clear = c->opt[VR_OPT_CLEAR_IMAGE];
+  c->opt[VR_OPT_CLEAR_IMAGE] = 0;
+  const vr_status st = render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &dummy, s, &vs);
+  c->opt[VR_OPT_CLEAR_IMAGE] = clear;
+  return st;
+}
+
+vr_status vr_render_partial_device(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
+                                   const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
+                                   const float props[3], float thr, const float color[3], uint32_t n_bricks, uint32_t brick_index,
+                                   const uint64_t *brick_boxes, const float *d_opacity_all, float *d_out, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  if (!d_out) return fail(c, VR_ERR_INVALID_ARGUMENT, "partial render: null output");
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  VsArgs vs{};
+  vs.mode = 2, vs.index = (int)brick_index, vs.count = (int)n_bricks;
+  vs.opacity_all = d_opacity_all, vs.boxes_vox = brick_boxes;
+  return render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &d_out, s, &vs);
+}
+
+vr_status vr_compose_partials_device(vr_ctx *c, uint32_t n, const float *const *d_partials, uint64_t n_floats, float *d_out, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  if (!d_partials || !d_out || n == 0 || n > 64) return fail(c, VR_ERR_INVALID_ARGUMENT, "compose: bad arguments");
+  VR_TRY(set_device(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  VR_CUDA(c, launch_compose(d_partials, (int)n, n_floats, d_out, s));
+  return VR_OK;
 }
 
 vr_status vr_render_batch(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
@@ -972,6 +1134,18 @@ vr_status vr_synth_volume(vr_ctx *c, int kind, uint32_t seed, const uint64_t dim
   if (!dims || !d_out || kind < 0 || kind > 1 || (dtype != VR_DTYPE_F32 && dtype != VR_DTYPE_BF16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "synth: bad argument");
   VR_TRY(set_device(c));
   VR_CUDA(c, launch_synth(d_out, kind, seed, (int)dims[0], (int)dims[1], (int)dims[2], dtype, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
+vr_status vr_synth_volume_region(vr_ctx *c, int kind, uint32_t seed, const uint64_t dims[3], const uint64_t lo[3], const uint64_t hi[3],
+                                 int32_t dtype, void *d_out) {
+  VR_CHECK_HANDLE(c);
+  if (!dims || !lo || !hi || !d_out || kind < 0 || kind > 1 || (dtype != VR_DTYPE_F32 && dtype != VR_DTYPE_BF16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "synth: bad argument");
+  for (int i = 0; i < 3; ++i)
+    if (lo[i] >= hi[i] || hi[i] > dims[i]) return fail(c, VR_ERR_INVALID_ARGUMENT, "synth: bad box on axis %d", i);
+  VR_TRY(set_device(c));
+  const int d3[3] = {(int)dims[0], (int)dims[1], (int)dims[2]}, l3[3] = {(int)lo[0], (int)lo[1], (int)lo[2]}, h3[3] = {(int)hi[0], (int)hi[1], (int)hi[2]};
+  VR_CUDA(c, launch_synth_region(d_out, kind, seed, d3, l3, h3, dtype, c->stream));
   VR_CUDA(c, cudaStreamSynchronize(c->stream));
   return VR_OK;
 }

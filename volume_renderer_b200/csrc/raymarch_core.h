@@ -111,6 +111,7 @@ VR_HD float tex3d_volume(const TexDesc &t, float x, float y, float z, int frac_b
   axis_setup(x, t.fw, frac_bits, X, fx);
   axis_setup(y, t.fh, frac_bits, Y, fy);
   axis_setup(z, t.fd, frac_bits, Z, fz);
+  X -= t.ox, Y -= t.oy, Z -= t.oz;  // global padded index -> local storage (0 for a whole volume)
   typedef Addr<LAYOUT> A;
   const uint32_t x0 = A::x(X), x1 = A::x(X + 1);
   const uint32_t y0 = A::y(Y, t.sy), y1 = A::y(Y + 1, t.sy);
@@ -142,26 +143,29 @@ struct AxisTap {
   float f;          // weight of the high tap
 };
 template <int LAYOUT>
-VR_HD AxisTap axis_tap_x(float x, float fN, int fb) {
+VR_HD AxisTap axis_tap_x(float x, float fN, int off, int fb) {
   int X;
   AxisTap a;
   axis_setup(x, fN, fb, X, a.f);
+  X -= off;
   a.o0 = Addr<LAYOUT>::x(X), a.o1 = Addr<LAYOUT>::x(X + 1);
   return a;
 }
 template <int LAYOUT>
-VR_HD AxisTap axis_tap_y(float y, float fN, uint32_t sy, int fb) {
+VR_HD AxisTap axis_tap_y(float y, float fN, uint32_t sy, int off, int fb) {
   int Y;
   AxisTap a;
   axis_setup(y, fN, fb, Y, a.f);
+  Y -= off;
   a.o0 = Addr<LAYOUT>::y(Y, sy), a.o1 = Addr<LAYOUT>::y(Y + 1, sy);
   return a;
 }
 template <int LAYOUT>
-VR_HD AxisTap axis_tap_z(float z, float fN, uint32_t sz, int fb) {
+VR_HD AxisTap axis_tap_z(float z, float fN, uint32_t sz, int off, int fb) {
   int Z;
   AxisTap a;
   axis_setup(z, fN, fb, Z, a.f);
+  Z -= off;
   a.o0 = Addr<LAYOUT>::z(Z, sz), a.o1 = Addr<LAYOUT>::z(Z + 1, sz);
   return a;
 }
@@ -324,12 +328,17 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);  // kernel.cu:396
   const F3 ps = (r.pos - bmin) * bscale;                            // kernel.cu:437
   const int fb = P.frac_bits;
+  if (P.vs_mode && !(ps.x >= P.reg_lo[0] && ps.x < P.reg_hi[0] && ps.y >= P.reg_lo[1] && ps.y < P.reg_hi[1] && ps.z >= P.reg_lo[2] &&
+                     ps.z < P.reg_hi[2])) {
+    r.n_marched++;  // a sample of the global lattice that another brick owns
+    return;
+  }
   AxisTap ax, ay, az;
   float em_raw, ab_raw;
   if (UNI) {
-    ax = axis_tap_x<LAYOUT>(ps.x, P.geo.fw, fb);
-    ay = axis_tap_y<LAYOUT>(ps.y, P.geo.fh, P.geo.sy, fb);
-    az = axis_tap_z<LAYOUT>(ps.z, P.geo.fd, P.geo.sz, fb);
+    ax = axis_tap_x<LAYOUT>(ps.x, P.geo.fw, P.geo.ox, fb);
+    ay = axis_tap_y<LAYOUT>(ps.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
+    az = axis_tap_z<LAYOUT>(ps.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
     em_raw = taps_any<E>(P.em, ax, ay, az);
     ab_raw = P.ab_is_em ? em_raw : taps_any<E>(P.ab, ax, ay, az);
   } else {
@@ -340,6 +349,10 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const float absorption = P.fAb * ab_raw;
   const float alpha = 1 - VR_EXPF(-absorption * P.tstep);  // kernel.cu:455-456
   r.n_marched++;
+  if (P.vs_mode == 1) {  // transmittance pass: only sum.w of kernel.cu:482, no colour
+    r.sw = (1 - r.sw) * alpha + r.sw;
+    return;
+  }
   // alpha == 0 makes the premultiplied sample exactly (0,0,0,0) for finite inputs, so the
   // illumination (the expensive part) contributes nothing and is not evaluated.
   if (alpha == 0.0f) return;
@@ -356,14 +369,14 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
         // computeGradient: the six taps differ from the sample position in ONE coordinate each
         // ((pos.y + 0 - bmin.y) * bscale.y is ps.y bit for bit), so only that axis is set up anew.
         const F3 gs = ld3(P.gstep);
-        const AxisTap xp = axis_tap_x<LAYOUT>((r.pos.x + gs.x - bmin.x) * bscale.x, P.geo.fw, fb);
-        const AxisTap xm = axis_tap_x<LAYOUT>((r.pos.x - gs.x - bmin.x) * bscale.x, P.geo.fw, fb);
+        const AxisTap xp = axis_tap_x<LAYOUT>((r.pos.x + gs.x - bmin.x) * bscale.x, P.geo.fw, P.geo.ox, fb);
+        const AxisTap xm = axis_tap_x<LAYOUT>((r.pos.x - gs.x - bmin.x) * bscale.x, P.geo.fw, P.geo.ox, fb);
         g.x = taps_any<E>(P.em_direct, xp, ay, az) - taps_any<E>(P.em_direct, xm, ay, az);
-        const AxisTap yp = axis_tap_y<LAYOUT>((r.pos.y + gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, fb);
-        const AxisTap ym = axis_tap_y<LAYOUT>((r.pos.y - gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, fb);
+        const AxisTap yp = axis_tap_y<LAYOUT>((r.pos.y + gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
+        const AxisTap ym = axis_tap_y<LAYOUT>((r.pos.y - gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
         g.y = taps_any<E>(P.em_direct, ax, yp, az) - taps_any<E>(P.em_direct, ax, ym, az);
-        const AxisTap zp = axis_tap_z<LAYOUT>((r.pos.z + gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, fb);
-        const AxisTap zm = axis_tap_z<LAYOUT>((r.pos.z - gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, fb);
+        const AxisTap zp = axis_tap_z<LAYOUT>((r.pos.z + gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
+        const AxisTap zm = axis_tap_z<LAYOUT>((r.pos.z - gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
         g.z = taps_any<E>(P.em_direct, ax, ay, zp) - taps_any<E>(P.em_direct, ax, ay, zm);
         g = g * mk3(0.5f, 0.5f, 0.5f);
       } else {
@@ -401,6 +414,29 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   r.sy = k * shy + r.sy;
   r.sz = k * shz + r.sz;
   r.sw = k * alpha + r.sw;
+}
+
+// Volume-space shading pass: the opacity the ray has accumulated in the bricks it crosses BEFORE
+// this one, 1 - prod(1 - a_b'), from the gathered per-brick opacities.  Bricks are disjoint convex
+// boxes, so their intervals along a ray are ordered by entry distance.  Returns false when the ray
+// never enters this brick's box (no owned samples).
+VR_HD bool vs_opacity_in(const KernelParams &P, F3 origin, const Ray &r, size_t pixel, float &a_in) {
+  const float *mine = P.vs_boxes + 6 * P.vs_index;
+  float tn = 0.f, tf = 0.f;
+  // a little slack: ownership is decided per sample by the region test, the boxes only order bricks
+  const F3 e = mk3(1e-4f, 1e-4f, 1e-4f);
+  if (!intersect_box(origin, r.step, ld3(mine) - e, ld3(mine + 3) + e, tn, tf)) return false;
+  const size_t plane = (size_t)P.W * P.H;
+  float T = 1.0f;
+  for (int b = 0; b < P.vs_count; ++b) {
+    if (b == P.vs_index) continue;
+    const float *box = P.vs_boxes + 6 * b;
+    float bn = 0.f, bf = 0.f;
+    if (!intersect_box(origin, r.step, ld3(box), ld3(box + 3), bn, bf)) continue;
+    if (bn < tn || (bn == tn && b < P.vs_index)) T = T * (1.0f - VR_LDG(P.vs_opacity_all + (size_t)b * plane + pixel));
+  }
+  a_in = 1.0f - T;
+  return true;
 }
 
 // Loop tail (kernel.cu:485-492).  Returns false when the ray is finished.
@@ -584,7 +620,7 @@ VR_HD bool skip_empty(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, F3 dq, 
 // The whole march of one pixel, lane-serial: what the kernel does per lane, without the warp
 // scheduling.  Used by the host emulation (tests/host_emul) and by the single-lane debug kernel.
 template <int GRAD, int LAYOUT, typename E, int UNI>
-VR_HD bool march_pixel(const KernelParams &P, uint32_t x, uint32_t y, float rgb[3], uint32_t &marched, uint32_t &shaded) {
+VR_HD bool march_pixel(const KernelParams &P, uint32_t x, uint32_t y, float rgba[4], uint32_t &marched, uint32_t &shaded) {
   const F3 origin = ray_origin(P.cam);
   Ray r;
   if (!ray_init(P, P.cam, x, y, origin, r)) return false;
@@ -593,13 +629,19 @@ VR_HD bool march_pixel(const KernelParams &P, uint32_t x, uint32_t y, float rgb[
   F3 dq, inv_dq;
   skip_setup(P, r, bscale, dq, inv_dq);
   bool active = true;
+  if (P.vs_mode == 2) {
+    float a_in = 0.0f;
+    active = vs_opacity_in(P, origin, r, (size_t)x * P.H + y, a_in);
+    r.sw = a_in;
+    if (a_in > P.thr) active = false;
+  }
   while (active) {
     if (P.skip) active = skip_empty(P, r, bmin, bscale, dq, inv_dq);
     if (!active) break;
     shade_sample<GRAD, LAYOUT, E, UNI>(P, origin, r);
     active = ray_advance(P, r);
   }
-  rgb[0] = r.sx, rgb[1] = r.sy, rgb[2] = r.sz;
+  rgba[0] = r.sx, rgba[1] = r.sy, rgba[2] = r.sz, rgba[3] = r.sw;
   marched = r.n_marched, shaded = r.n_shaded;
   return true;
 }

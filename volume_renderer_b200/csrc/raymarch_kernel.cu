@@ -65,6 +65,12 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
     Ray r;
     bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, cam, x, y, origin, r);
     bool active = hit;
+    if (P.vs_mode == 2 && hit) {  // start from the opacity of the bricks in front; nothing to do behind the threshold
+      float a_in = 0.0f;
+      active = vs_opacity_in(P, origin, r, (size_t)x * P.H + y, a_in);
+      r.sw = a_in;
+      if (a_in > P.thr) active = false;
+    }
     F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
     if (active && P.skip == 1) skip_setup(P, r, bscale, dq, inv_dq);
 
@@ -81,9 +87,13 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
       // the owner of the pixel writes that 0 itself, so the image needs no clear and cam.out may be
       // another GPU's memory (image-space direct send: each rank stores its tiles into the root's image).
       const size_t size = (size_t)P.W * P.H, k = (size_t)x * P.H + y;
-      cam.out[k] = hit ? r.sx : 0.0f;
-      cam.out[k + size] = hit ? r.sy : 0.0f;
-      cam.out[k + 2 * size] = hit ? r.sz : 0.0f;
+      if (P.vs_mode == 1) {
+        P.vs_opacity_out[k] = hit ? r.sw : 0.0f;
+      } else {
+        cam.out[k] = hit ? r.sx : 0.0f;
+        cam.out[k + size] = hit ? r.sy : 0.0f;
+        cam.out[k + 2 * size] = hit ? r.sz : 0.0f;
+      }
     }
     if (hit) {
       tot_marched += r.n_marched;

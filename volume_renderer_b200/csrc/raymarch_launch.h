@@ -18,8 +18,12 @@ cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, int va
 struct RepackArgs {
   void *dst;           // padded (bricked) storage of the whole volume
   const void *src;     // staged source slices, MATLAB layout (dims[0] fastest)
-  int w, h, d;         // voxel dims
-  int src_z0;          // z index of the first staged slice
+  int w, h, d;         // GLOBAL voxel dims
+  int lw, lh, ld;      // local padded dims of dst (w+2, h+2, d+2 for a whole volume)
+  int gx0, gy0, gz0;   // dst padded index (X,Y,Z) holds global voxel clamp(X+gx0, 0, w-1)... (-1 for a whole volume)
+  int sx0, sy0;        // src covers global voxels [sx0, sx0+sw) x [sy0, sy0+sh) per slice
+  int sw, sh;
+  int src_z0;          // global z index of the first staged slice
   uint64_t o0, o1;     // destination element range [o0, o1) to produce
   uint32_t sy, sz;     // destination strides (see TexDesc)
   int layout;          // LAYOUT_*
@@ -30,8 +34,9 @@ cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream);
 
 // occupancy bit grid: bit set when any voxel of the 8^3 macro cell dilated by `dilate` voxels is
 // non-zero (read from the padded storage).
+// reg = {lo x,y,z, hi x,y,z} in voxels: cells that cannot hold an owned sample stay empty.
 cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *occ, int ocx, int ocy, int ocz,
-                             int dilate, cudaStream_t stream);
+                             int dilate, const int reg[6], cudaStream_t stream);
 
 // distance grid of an occupancy bit grid: dist[cell] = Chebyshev distance in cells to the nearest
 // set bit (0 on a set bit, capped at 255).  tmp: scratch of the same size.
@@ -42,6 +47,14 @@ cudaError_t launch_hg_lut(float *d_out, uint32_t n, float g, cudaStream_t stream
 
 // synthetic ViBE-Z-shaped volumes; kind 0 = brain, 1 = tubes
 cudaError_t launch_synth(void *d_out, int kind, uint32_t seed, int w, int h, int d, int dtype, cudaStream_t stream);
+
+// the voxel box [lo, hi) of the same synthetic volume, stored densely (lo[0] fastest)
+cudaError_t launch_synth_region(void *d_out, int kind, uint32_t seed, const int dims[3], const int lo[3], const int hi[3], int dtype,
+                                cudaStream_t stream);
+// sort-last compositing of the volume-space mode: out[i] = sum over bricks (in index order) of partial_b[i].
+// Every partial is already weighted by the transmittance of the bricks in front of it, so the "under"
+// operator over depth-ordered partials reduces to an order-free sum.  Partials may live on peer GPUs.
+cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_floats, float *d_out, cudaStream_t stream);
 
 // MATLAB gradient() of a MATLAB-layout volume (Volume.m:181-205): gx = d/d dim2, gy = d/d dim1, gz = d/d dim3
 cudaError_t launch_gradient(const void *d_in, int w, int h, int d, int dtype, void *gx, void *gy, void *gz, cudaStream_t stream);

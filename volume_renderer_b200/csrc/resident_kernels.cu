@@ -30,7 +30,7 @@ __device__ __forceinline__ void store_dst(void *p, size_t i, int dtype, float v)
 template <int LAYOUT>
 __global__ void __launch_bounds__(256) k_repack(const RepackArgs a) {
   const uint64_t n = a.o1 - a.o0;
-  const int pw = a.w + 2, ph = a.h + 2, pd = a.d + 2;
+  const int pw = a.lw, ph = a.lh, pd = a.ld;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
     const uint64_t o = a.o0 + i;
     int X, Y, Z;
@@ -51,10 +51,10 @@ __global__ void __launch_bounds__(256) k_repack(const RepackArgs a) {
     }
     float v = 0.0f;
     if (X < pw && Y < ph && Z < pd) {
-      const int sx = min(max(X - 1, 0), a.w - 1);
-      const int sy = min(max(Y - 1, 0), a.h - 1);
-      const int sz = min(max(Z - 1, 0), a.d - 1);
-      v = load_src(a.src, ((size_t)(sz - a.src_z0) * a.h + sy) * a.w + sx, a.src_dtype);
+      const int sx = min(max(X + a.gx0, 0), a.w - 1);
+      const int sy = min(max(Y + a.gy0, 0), a.h - 1);
+      const int sz = min(max(Z + a.gz0, 0), a.d - 1);
+      v = load_src(a.src, ((size_t)(sz - a.src_z0) * a.sh + (sy - a.sy0)) * a.sw + (sx - a.sx0), a.src_dtype);
     }
     store_dst(a.dst, o, a.dst_dtype, v);
   }
@@ -76,15 +76,23 @@ cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream) {
 // One warp per macro cell: scans padded voxels [8c+1-dilate, 8c+8+dilate] per axis (voxel index
 // v sits at padded index v+1; the replicated border only repeats edge voxels, so reading it is
 // harmless) and sets the cell's bit when any value is not exactly +-0.
+struct Reg6 {
+  int v[6];
+};
 template <int LAYOUT, typename E>
-__global__ void __launch_bounds__(256) k_occupancy(const TexDesc t, uint32_t *occ, int ocx, int ocy, int ocz, int dilate) {
+__global__ void __launch_bounds__(256) k_occupancy(const TexDesc t, uint32_t *occ, int ocx, int ocy, int ocz, int dilate, const Reg6 reg) {
   const int lane = threadIdx.x & 31;
   const uint64_t ncell = (uint64_t)ocx * ocy * ocz;
   const int span = 8 + 2 * dilate;
-  const int pw = t.w + 2, ph = t.h + 2, pd = t.d + 2;
+  const int pw = t.lw, ph = t.lh, pd = t.ld;
   for (uint64_t cell = (uint64_t)blockIdx.x * 8 + (threadIdx.x >> 5); cell < ncell; cell += (uint64_t)gridDim.x * 8) {
     const int cx = (int)(cell % ocx), cy = (int)((cell / ocx) % ocy), cz = (int)(cell / ((uint64_t)ocx * ocy));
-    const int x0 = cx * 8 + 1 - dilate, y0 = cy * 8 + 1 - dilate, z0 = cz * 8 + 1 - dilate;
+    // an owned sample has its low tap in [lo-1, hi-1]: a cell outside that range stays empty
+    if (cx * 8 + 7 < reg.v[0] - 1 || cx * 8 > reg.v[3] - 1 || cy * 8 + 7 < reg.v[1] - 1 || cy * 8 > reg.v[4] - 1 || cz * 8 + 7 < reg.v[2] - 1 ||
+        cz * 8 > reg.v[5] - 1)
+      continue;
+    // global padded index of the first scanned voxel, moved into the local storage
+    const int x0 = cx * 8 + 1 - dilate - t.ox, y0 = cy * 8 + 1 - dilate - t.oy, z0 = cz * 8 + 1 - dilate - t.oz;
     bool any = false;
     const int total = span * span * span;
     for (int i = lane; i < total && !any; i += 32) {
@@ -99,7 +107,9 @@ __global__ void __launch_bounds__(256) k_occupancy(const TexDesc t, uint32_t *oc
 }
 
 cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *occ, int ocx, int ocy, int ocz,
-                             int dilate, cudaStream_t stream) {
+                             int dilate, const int reg6[6], cudaStream_t stream) {
+  Reg6 reg;
+  for (int i = 0; i < 6; ++i) reg.v[i] = reg6[i];
   const uint64_t ncell = (uint64_t)ocx * ocy * ocz;
   uint64_t blocks = (ncell + 7) / 8;
   if (blocks > 148ull * 32) blocks = 148ull * 32;
@@ -107,14 +117,14 @@ cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *
   const unsigned g = (unsigned)blocks;
   if (layout == LAYOUT_BRICK) {
     if (dtype == 0)
-      k_occupancy<LAYOUT_BRICK, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+      k_occupancy<LAYOUT_BRICK, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate, reg);
     else
-      k_occupancy<LAYOUT_BRICK, ElemBF16><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+      k_occupancy<LAYOUT_BRICK, ElemBF16><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate, reg);
   } else {
     if (dtype == 0)
-      k_occupancy<LAYOUT_LINEAR, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+      k_occupancy<LAYOUT_LINEAR, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate, reg);
     else
-      k_occupancy<LAYOUT_LINEAR, ElemBF16><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate);
+      k_occupancy<LAYOUT_LINEAR, ElemBF16><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate, reg);
   }
   return cudaGetLastError();
 }
@@ -285,6 +295,57 @@ cudaError_t launch_synth(void *d_out, int kind, uint32_t seed, int w, int h, int
   if (blocks > 148ull * 64) blocks = 148ull * 64;
   if (blocks < 1) blocks = 1;
   k_synth<<<(unsigned)blocks, 256, 0, stream>>>(d_out, kind, seed, w, h, d, dtype);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) k_synth_region(void *out, int kind, uint32_t seed, int w, int h, int d, int x0, int y0, int z0, int bw, int bh,
+                                                      int bd, int dtype) {
+  const uint64_t total = (uint64_t)bw * bh * bd;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+    const int x = x0 + (int)(i % bw), y = y0 + (int)((i / bw) % bh), z = z0 + (int)(i / ((uint64_t)bw * bh));
+    const float v = kind == 0 ? synth_brain(x, y, z, w, h, d, seed) : synth_tubes(x, y, z, w, h, d, seed);
+    store_dst(out, i, dtype, v);
+  }
+}
+cudaError_t launch_synth_region(void *d_out, int kind, uint32_t seed, const int dims[3], const int lo[3], const int hi[3], int dtype,
+                                cudaStream_t stream) {
+  const uint64_t total = (uint64_t)(hi[0] - lo[0]) * (hi[1] - lo[1]) * (hi[2] - lo[2]);
+  uint64_t blocks = (total + 255) / 256;
+  if (blocks > 148ull * 64) blocks = 148ull * 64;
+  if (blocks < 1) blocks = 1;
+  k_synth_region<<<(unsigned)blocks, 256, 0, stream>>>(d_out, kind, seed, dims[0], dims[1], dims[2], lo[0], lo[1], lo[2], hi[0] - lo[0], hi[1] - lo[1],
+                                                       hi[2] - lo[2], dtype);
+  return cudaGetLastError();
+}
+
+// ---- sort-last compositing ------------------------------------------------------------------------
+struct PartialPtrs {
+  const float *p[64];
+};
+__global__ void __launch_bounds__(256) k_compose(const PartialPtrs in, int n, uint64_t n4, uint64_t n_floats, float *out) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (uint64_t)gridDim.x * blockDim.x) {
+    float4 acc = reinterpret_cast<const float4 *>(in.p[0])[i];  // 128-bit loads; peers' partials come over NVLink
+    for (int b = 1; b < n; ++b) {
+      const float4 v = reinterpret_cast<const float4 *>(in.p[b])[i];
+      acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+    }
+    reinterpret_cast<float4 *>(out)[i] = acc;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (uint64_t i = n4 * 4; i < n_floats; ++i) {
+      float a = in.p[0][i];
+      for (int b = 1; b < n; ++b) a += in.p[b][i];
+      out[i] = a;
+    }
+}
+cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_floats, float *d_out, cudaStream_t stream) {
+  PartialPtrs pp;
+  for (int i = 0; i < 64; ++i) pp.p[i] = i < n ? d_partials[i] : nullptr;
+  const uint64_t n4 = n_floats / 4;
+  uint64_t blocks = (n4 + 255) / 256;
+  if (blocks > 148ull * 8) blocks = 148ull * 8;
+  if (blocks < 1) blocks = 1;
+  k_compose<<<(unsigned)blocks, 256, 0, stream>>>(pp, n, n4, n_floats, d_out);
   return cudaGetLastError();
 }
 

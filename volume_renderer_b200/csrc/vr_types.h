@@ -33,6 +33,10 @@ enum { CELL_SHIFT = 3 };  // empty-space macro cell = 8^3 voxels
 //   linear : off = X + Y*sy + Z*sz                       (sy = w+2, sz = sy*(h+2))
 //   bricked: off = (X>>3)*512 + (X&7) + (Y>>3)*sy + (Y&7)*8 + (Z>>3)*sz + (Z&7)*64
 //            (sy = nbx*512, sz = nbx*nby*512; a brick is 8x8x8 voxels = 2 KiB of fp32)
+// A context that owns only a sub-box of the volume (volume-space mode) stores just that region plus
+// a halo: w, h, d stay the GLOBAL dims (they define the coordinate math), ox/oy/oz are subtracted
+// from the global padded tap index to get the index into the local storage (0 for a whole volume),
+// lw/lh/ld are the local padded dims.
 struct TexDesc {
   const void *p;
   int w, h, d;
@@ -40,6 +44,8 @@ struct TexDesc {
   uint32_t sy, sz;
   int kind;
   float cval;
+  int ox, oy, oz;
+  int lw, lh, ld;
 };
 
 enum { MAX_PARAM_LIGHTS = 8 };
@@ -88,6 +94,18 @@ struct KernelParams {
   int frac_bits;        // 0 = fp32 weights, 8 = 1.8 fixed point
   int skip;             // empty-space skipping: 0 off, 1 serial per cell, 2 closed-form jumps (default)
   int count;            // maintain stats
+  // volume-space mode (sort-last): this launch marches only the samples whose normalized position
+  // lies in [reg_lo, reg_hi) - the global sample lattice is kept, other samples count as empty.
+  //   vs_mode 0: off.  1: transmittance pass - per pixel the opacity a_b this brick alone would
+  //   accumulate (no shading), written to vs_opacity_out[pixel].  2: shading pass - sum.w starts at
+  //   the opacity of the bricks in front, 1 - prod(1 - a_b'), read from vs_opacity_all
+  //   [brick][pixel]; the output is this brick's additive share of the final image.
+  int vs_mode;
+  int vs_index, vs_count;          // this brick, number of bricks
+  float reg_lo[3], reg_hi[3];      // owned region in normalized texture coordinates
+  float *vs_opacity_out;           // mode 1
+  const float *vs_opacity_all;     // mode 2: vs_count planes of W*H floats (pixel k = x*H + y)
+  const float *vs_boxes;           // mode 2: vs_count x 6 floats, world-space brick boxes (lo xyz, hi xyz)
   // lights (volumeRender.h:50-55), position already axis-reversed
   int n_lights;
   float lights[MAX_PARAM_LIGHTS][6];

@@ -120,3 +120,128 @@ def frame_barrier(stream_tensor=None, group=None):
             dist.all_reduce(stream_tensor, group=group)
         else:
             dist.barrier(group=group)
+
+
+# ---- volume-space mode (sort-last) -------------------------------------------------------------
+def brick_grid(dims, splits):
+    """Cut a (w, h, d) volume into splits[0] x splits[1] x splits[2] voxel boxes.
+    Returns [(lo, hi), ...] with lo/hi 3-tuples, brick index = (bz * sy + by) * sx + bx."""
+    edges = [[(n * i) // s for i in range(s + 1)] for n, s in zip(dims, splits)]
+    out = []
+    for bz in range(splits[2]):
+        for by in range(splits[1]):
+            for bx in range(splits[0]):
+                out.append(((edges[0][bx], edges[1][by], edges[2][bz]), (edges[0][bx + 1], edges[1][by + 1], edges[2][bz + 1])))
+    return out
+
+
+def splits_for(n):
+    """Brick grid for n ranks: powers of two are split octant-wise (8 -> 2x2x2), anything else along z."""
+    s = [1, 1, 1]
+    axis = 2
+    while n > 1 and n % 2 == 0:
+        s[axis] *= 2
+        n //= 2
+        axis = (axis - 1) % 3
+    s[2] *= n
+    return tuple(s)
+
+
+def boxes_array(bricks):
+    import numpy as np
+
+    return np.array([list(lo) + list(hi) for lo, hi in bricks], dtype=np.uint64).reshape(-1)
+
+
+def compose(ctx, partial_ptrs, n_floats, d_out, stream=None):
+    """vr_compose_partials_device: out = sum of the bricks' shares, in brick order."""
+    arr = (C.c_void_p * len(partial_ptrs))(*[int(p) for p in partial_ptrs])
+    _abi.check(_abi.lib().vr_compose_partials_device(ctx, len(partial_ptrs), arr, int(n_floats), C.c_void_p(int(d_out)), C.c_void_p(stream or 0)), ctx)
+
+
+def render_bricks_one_gpu(renderers, bricks):
+    """A whole sort-last frame with every brick on THIS GPU (virtual shards; tests and single-GPU
+    runs of volumes cut into bricks).  `renderers[b]` is an api.VolumeRender that called
+    setRegion(*bricks[b]) before its volumes were assigned.  Returns the H x W x 3 image."""
+    import numpy as np
+    import torch
+
+    W, H = int(renderers[0].ImageResolution[0]), int(renderers[0].ImageResolution[1])
+    n = len(bricks)
+    opac = torch.zeros(n * H * W, dtype=torch.float32, device="cuda")
+    part = torch.zeros(n * H * W * 3, dtype=torch.float32, device="cuda")
+    out = torch.zeros(H * W * 3, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    for b, r in enumerate(renderers):
+        r.renderOpacity(opac.data_ptr() + 4 * b * H * W)
+    for r in renderers:
+        r.stats()  # synchronise: every brick's opacity plane is complete ("all-gather")
+    for b, r in enumerate(renderers):
+        r.renderPartial(bricks, b, opac.data_ptr(), part.data_ptr() + 4 * b * H * W * 3)
+    for r in renderers:
+        r.stats()
+    compose(renderers[0].objectHandle, [part.data_ptr() + 4 * b * H * W * 3 for b in range(n)], H * W * 3, out.data_ptr())
+    renderers[0].stats()
+    torch.cuda.synchronize()
+    return out.cpu().numpy().reshape((H, W, 3), order="F")
+
+
+class VolumeSpaceRank:
+    """One process = one GPU = one brick of a sort-last render (torch.distributed, NCCL or gloo-free:
+    the exchanges are an all-gather of opacity planes and a gather of the shares).
+
+        vs = VolumeSpaceRank(renderer, bricks, rank)     # renderer.setRegion(*bricks[rank]) already done
+        img = vs.render()                                # H x W x 3 numpy on rank 0, None elsewhere
+    """
+
+    def __init__(self, renderer, bricks, rank, group=None, exchange="p2p"):
+        import torch
+
+        self.r, self.bricks, self.rank, self.group = renderer, bricks, rank, group
+        self.n = len(bricks)
+        W, H = int(renderer.ImageResolution[0]), int(renderer.ImageResolution[1])
+        self.H, self.W = H, W
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.opac_mine = torch.zeros(H * W, dtype=torch.float32, device=dev)
+        self.opac_all = torch.zeros(self.n * H * W, dtype=torch.float32, device=dev)
+        self.out = torch.zeros(H * W * 3, dtype=torch.float32, device=dev) if rank == 0 else None
+        self.exchange = exchange if self.n > 1 else "local"
+        if self.exchange == "p2p":
+            # the n shares live back to back in rank 0's HBM; rank b's shading kernel stores slot b over NVLink
+            self.shared = SharedImage(renderer.objectHandle, H, W, rank, self.n, root=0, group=group, count=self.n)
+            renderer.setOption(_abi.OPT_CLEAR_IMAGE, 0)
+            self.token = torch.zeros(1, dtype=torch.float32, device=dev)
+        else:
+            self.shared = None
+            self.part = torch.zeros(H * W * 3, dtype=torch.float32, device=dev)
+
+    def render(self, download=True):
+        import torch
+        import torch.distributed as dist
+
+        stream = torch.cuda.current_stream().cuda_stream
+        self.r.renderOpacity(self.opac_mine.data_ptr(), stream)
+        if self.n > 1:
+            dist.all_gather_into_tensor(self.opac_all, self.opac_mine, group=self.group)
+        else:
+            self.opac_all.copy_(self.opac_mine)
+        if self.shared is not None:
+            self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.shared.ptrs[self.rank].value, stream)
+            frame_barrier(self.token, self.group)
+            if self.rank == 0:
+                compose(self.r.objectHandle, [p.value for p in self.shared.ptrs], self.H * self.W * 3, self.out.data_ptr(), stream)
+        else:
+            self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.part.data_ptr(), stream)
+            if self.n > 1:
+                dist.reduce(self.part, dst=0, op=dist.ReduceOp.SUM, group=self.group)  # the sum IS the composite
+            if self.rank == 0:
+                self.out.copy_(self.part)
+        if self.rank == 0 and download:
+            torch.cuda.synchronize()
+            return self.out.cpu().numpy().reshape((self.H, self.W, 3), order="F")
+        return None
+
+    def close(self):
+        if self.shared is not None:
+            self.shared.close()
+            self.shared = None
