@@ -53,6 +53,8 @@ def parse():
     p.add_argument("--tile", type=int, default=64)
     p.add_argument("--batch", type=int, default=8, help="frames per launch (one work queue per batch; clipped to --steps)")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
+    p.add_argument("--mode", default="image", choices=["image", "volume"],
+                   help="image = tiles over replicated volumes (the metric's config); volume = bricks sharded over the ranks, sort-last composite (config 5)")
     p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                    help="N > 1: p2p = every rank's kernel stores its tiles into rank 0's image over NVLink (default); nccl = SUM-reduce of partial images")
     return p.parse_args()
@@ -556,6 +558,135 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m):
             "sample": "frame 0, centred %dx%d pixel window of the %dx%d image, %s; %.1f s of CPU time, %d samples" % (2 * half, 2 * half, scene.W, scene.H, note, sec, nsm)}
 
 
+def run_volume(args):
+    """BASELINE configs[4]: a volume too big to replicate, bricks sharded over the ranks (one brick per
+    GPU, generated straight into its HBM), example1 camera, 1 light, on-the-fly gradient; per frame an
+    opacity pass, an all-gather of H*W floats per brick, a shading pass whose kernel stores the brick's
+    share into rank 0's HBM over NVLink, and the composite on rank 0."""
+    import torch
+    import torch.distributed as dist
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from volume_renderer_b200 import _abi, api, multigpu
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _abi.lib()
+    n = args.size
+    dims = (n, n, n)
+    bricks = multigpu.brick_grid(dims, multigpu.splits_for(world))
+    lo, hi = bricks[rank]
+    halo = 4
+    dt = _abi.DTYPE_F32 if args.dtype == "f32" else _abi.DTYPE_BF16
+    es = 4 if dt == _abi.DTYPE_F32 else 2
+    r = api.VolumeRender()
+    ctx = r.objectHandle
+    _abi.check(lib.vr_set_stream(ctx, C.c_void_p(torch.cuda.current_stream().cuda_stream)), ctx)  # torch's stream, also for timing events
+    if world > 1:
+        r.setRegion(lo, hi, halo)
+    blo = [max(l - halo, 0) for l in lo] if world > 1 else [0, 0, 0]
+    bhi = [min(h + halo, d) for h, d in zip(hi, dims)] if world > 1 else list(dims)
+    nvox = int(np.prod([h - l for l, h in zip(blo, bhi)]))
+    buf = C.c_void_p()
+    _abi.check(lib.vr_device_alloc(ctx, nvox * es, C.byref(buf)), ctx)
+    u3 = lambda v: (C.c_uint64 * 3)(*[int(x) for x in v])
+    t_gen = time.perf_counter()
+    _abi.check(lib.vr_synth_volume_region(ctx, 0, SEED, u3(dims), u3(blo), u3(bhi), dt, buf), ctx)
+    t_gen = time.perf_counter() - t_gen
+    E = api.DeviceVolume(buf.value, dims, dt, _abi.MEM_DEVICE_REGION if world > 1 else _abi.MEM_DEVICE)
+    lut = api.HenyeyGreenstein(64)
+    r.VolumeIllumination = api.Volume(lut)
+    r.LightSources = [api.LightSource([500, 1000, 550], [0, 1, 1])]
+    r.ElementSizeUm = [1, 1, 1]
+    r.FocalLength, r.DistanceToObject, r.OpacityThreshold = 3.0, 6.0, 0.9
+    r.ImageResolution = [args.image, args.image]
+    r.VolumeEmission = E
+    r.VolumeAbsorption = E
+    r.FactorEmission, r.FactorAbsorption, r.FactorReflection = 1.0, 0.6, 0.4
+    r.Color = [1, 1, 0]
+    R0 = rotation(125, 25, 0)
+    t_up = time.perf_counter()
+    r.syncVolumes()
+    torch.cuda.synchronize()
+    t_up = time.perf_counter() - t_up
+    _abi.check(lib.vr_device_free(ctx, buf), ctx)  # only the resident bricks stay
+    r.VolumeEmission.TimeLastUpdate = 1  # keep the (now dangling) source clean: nothing is re-read
+    r.VolumeAbsorption.TimeLastUpdate = 1
+    if world > 1:
+        vs = multigpu.VolumeSpaceRank(r, bricks, rank, exchange=args.exchange)
+        frame = lambda k: (setattr(r, "RotationMatrix", rotation(0, float(k), 0, R0)), vs.render(download=False))
+    else:
+        d_img = torch.zeros(args.image * args.image * 3, dtype=torch.float32, device=dev)
+
+        def frame(k):
+            r.RotationMatrix = rotation(0, float(k), 0, R0)
+            a, keep = r._packed_mono_args()
+            _abi.check(lib.vr_render_device(ctx, *a, C.c_void_p(d_img.data_ptr()), None), ctx)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for w in range(args.warmup):
+        frame(-1 - w)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    shaded = marched = 0
+    t0 = time.time()
+    barrier()
+    ev0.record()
+    for k in range(args.steps):
+        frame(k)
+        st = r.stats()  # counters of this rank's shading pass
+        shaded += st["samples_shaded"]
+        marched += st["samples_marched"]
+    ev1.record()
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    ms = ev0.elapsed_time(ev1)
+    tot = torch.tensor([ms, float(shaded), float(marched)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = tot.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        ms = float(mx[0])
+    res_b = r.stats()["bytes_resident"]
+    if rank == 0:
+        line = {
+            "metric": "Gsamples/s shaded (%d^2 image, %d^3 %s vol sharded over %d GPU(s))" % (args.image, n, args.dtype, world),
+            "value": float(tot[1]) / (ms * 1e-3) / 1e9, "unit": "Gsamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "frames_per_s": args.steps / (ms * 1e-3), "samples_shaded_per_frame": float(tot[1]) / args.steps,
+            "lattice_samples_visited_per_frame_all_ranks": float(tot[2]) / args.steps,
+            "config": {"workload": "huge-volume-shaped: %d^3 %s synthetic ViBE-Z-like E (Em=Ab), bricks %s (+%d voxel halo) one per GPU, 1 HG light, on-the-fly gradient, %dx%d mono, F=3 D=6 thr=0.9, +1deg/step"
+                       % (n, args.dtype, "x".join(str(x) for x in multigpu.splits_for(world)), halo, args.image, args.image),
+                       "multi_gpu": "volume-space sort-last: opacity pass, all-gather of H*W floats per brick (NCCL), shading pass storing shares into rank 0 over NVLink (%s), composite kernel" % args.exchange,
+                       "brick_generate_s": t_gen, "brick_upload_s": t_up, "bytes_resident_rank0": res_b},
+            "clocks": clocks, "gpu_launches": 2 * args.steps * world + args.steps,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank != 0:
+            vs.close()
+        dist.barrier()
+        if rank == 0:
+            vs.close()
+        dist.destroy_process_group()
+    return 0
+
+
 if __name__ == "__main__":
     a = parse()
-    sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))
+    if a.impl == "reference":
+        sys.exit(run_reference(a))
+    sys.exit(run_volume(a) if a.mode == "volume" else run_b200(a))

@@ -93,3 +93,59 @@ def test_two_processes_share_the_root_image_through_cuda_ipc(tmp_path):
     out = str(tmp_path / "shared.npy")
     mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
     assert np.array_equal(np.load(out), full)
+
+
+def _vs_worker(rank, world, port, out_path):
+    """One process per GPU: sort-last render of a volume cut into `world` bricks, both exchanges."""
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    vol = vrt.synth_brain((64, 56, 72))
+    lut = vrt.oracle_lut(64)
+    bricks = multigpu.brick_grid(vol.shape, multigpu.splits_for(world))
+    imgs = {}
+    for exchange in ("p2p", "nccl"):
+        r = api.VolumeRender()
+        r.setRegion(*bricks[rank])
+        r = vrt.example1_scene(lambda: r, vol, RES, lights=2, lut=lut)
+        r.FactorAbsorption = 30.0
+        vs = multigpu.VolumeSpaceRank(r, bricks, rank, exchange=exchange)
+        for _ in range(2):  # a second frame reuses every buffer
+            r.rotate(0, 10, 0)
+            img = vs.render()
+        if rank == 0:
+            imgs[exchange] = img
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank != 0:
+            vs.close()
+        dist.barrier()
+        if rank == 0:
+            vs.close()
+    if rank == 0:
+        whole = vrt.example1_scene(api.VolumeRender, vol, RES, lights=2, lut=lut)
+        whole.FactorAbsorption = 30.0
+        whole.rotate(0, 20, 0)
+        np.savez(out_path, full=whole.render(), **imgs)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_volume_space_one_brick_per_gpu(tmp_path):
+    import torch
+    import torch.multiprocessing as mp
+
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs (gpurun --gpus 2)")
+    out = str(tmp_path / "vs.npz")
+    mp.spawn(_vs_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    z = np.load(out)
+    for k in ("p2p", "nccl"):
+        m = vrt.compare(z[k], z["full"])
+        print(k, m)
+        assert m["max_abs_norm"] < 2e-5, (k, m)

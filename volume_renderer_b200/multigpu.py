@@ -202,6 +202,9 @@ class VolumeSpaceRank:
         W, H = int(renderer.ImageResolution[0]), int(renderer.ImageResolution[1])
         self.H, self.W = H, W
         dev = torch.device("cuda", torch.cuda.current_device())
+        # the context works on torch's current stream (handle 0 = the legacy default stream), where the
+        # collectives are enqueued too: passing 0 per call would mean "the context's own stream"
+        _abi.check(_abi.lib().vr_set_stream(renderer.objectHandle, C.c_void_p(torch.cuda.current_stream().cuda_stream)), renderer.objectHandle)
         self.opac_mine = torch.zeros(H * W, dtype=torch.float32, device=dev)
         self.opac_all = torch.zeros(self.n * H * W, dtype=torch.float32, device=dev)
         self.out = torch.zeros(H * W * 3, dtype=torch.float32, device=dev) if rank == 0 else None
@@ -219,7 +222,7 @@ class VolumeSpaceRank:
         import torch
         import torch.distributed as dist
 
-        stream = torch.cuda.current_stream().cuda_stream
+        stream = None  # = the context's stream = torch's current stream (set in __init__)
         self.r.renderOpacity(self.opac_mine.data_ptr(), stream)
         if self.n > 1:
             dist.all_gather_into_tensor(self.opac_all, self.opac_mine, group=self.group)
