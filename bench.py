@@ -243,6 +243,9 @@ def run_reference(args):
     vols = host_volumes_cpu(args)
     cpu = CpuRender(scene, args, vols)
     half = cpu.calibrated_half(10.0)
+    n0, s0, _ = cpu.render_window(0, half)
+    if s0 < 6.0 and half < scene.W // 2:
+        half = int(min(half * math.sqrt(10.0 / max(s0, 1e-3)), scene.W // 2))
     for w in range(args.warmup):
         cpu.render_window(w, 16)
     tot_n, tot_s, threads = 0, 0.0, 1
@@ -505,7 +508,10 @@ def run_b200(args):
     per_launch_marched = samples / n_launch
     achieved = per_launch_shaded * bps / (kavg_ms * 1e-3) / 1e9
     roofline = {
-        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v2_summary.md:
+        # 4.05 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
+        "traffic": (2.03e9 * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
         "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "peak_source": peak_src,
         "bytes_per_sample": bps, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
         "achieved_if_every_marched_sample_gathered": per_launch_marched * bps / (kavg_ms * 1e-3) / 1e9,
@@ -554,6 +560,9 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m):
     cpu = CpuRender(scene, args, vols)
     half = cpu.calibrated_half(args.cpu_seconds)
     nsm, sec, threads = cpu.render_window(0, half)
+    if sec < 0.6 * args.cpu_seconds and half < scene.W // 2:  # the small probe window over-estimates the cost per pixel: once more, rescaled
+        half = int(min(half * math.sqrt(args.cpu_seconds / max(sec, 1e-3)), scene.W // 2))
+        nsm, sec, threads = cpu.render_window(0, half)
     return {"value": nsm / sec / 1e9, "unit": "Gsamples/s", "cores": int(threads), "kind": "port",
             "sample": "frame 0, centred %dx%d pixel window of the %dx%d image, %s; %.1f s of CPU time, %d samples" % (2 * half, 2 * half, scene.W, scene.H, note, sec, nsm)}
 

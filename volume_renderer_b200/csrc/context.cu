@@ -67,6 +67,7 @@ struct Resident {
   size_t storage_bytes = 0;
   uint32_t *occ = nullptr;  // occupancy bit grid
   size_t occ_bytes = 0;
+  int reg[6] = {0, 0, 0, 0, 0, 0};  // owned voxel box (the whole volume unless vr_set_region)
   uint8_t *dist = nullptr;  // distance grid (cells to the nearest non-empty cell)
   size_t dist_bytes = 0;
   int ocx = 0, ocy = 0, ocz = 0;
@@ -324,20 +325,29 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
   }
   r.kind = TEX_VOLUME;
   r.src = v;
-  if (slot != S_LIGHT) {
-    r.ocx = (r.w + 7) / 8, r.ocy = (r.h + 7) / 8, r.ocz = (r.d + 7) / 8;
-    const uint64_t ncell = (uint64_t)r.ocx * r.ocy * r.ocz;
-    r.occ_bytes = (size_t)((ncell + 31) / 32) * 4;
-    VR_CUDA(c, cudaMalloc(&r.occ, r.occ_bytes));
-    VR_CUDA(c, cudaMemsetAsync(r.occ, 0, r.occ_bytes, c->stream));
-    const TexDesc t = describe(r);
-    const int reg[6] = {(int)lo[0], (int)lo[1], (int)lo[2], (int)hi[0], (int)hi[1], (int)hi[2]};
-    VR_CUDA(c, launch_occupancy(t, r.layout, r.dtype, r.occ, r.ocx, r.ocy, r.ocz, 2, reg, c->stream));
-    r.dist_bytes = (size_t)ncell;
-    VR_CUDA(c, cudaMalloc(&r.dist, r.dist_bytes));
-    VR_TRY(ensure_stage(c, r.dist_bytes));  // scratch of the middle pass; stream order protects it
-    VR_CUDA(c, launch_distance(r.occ, r.dist, static_cast<uint8_t *>(c->d_stage), r.ocx, r.ocy, r.ocz, c->stream));
-  }
+  for (int i = 0; i < 3; ++i) r.reg[i] = (int)lo[i], r.reg[3 + i] = (int)hi[i];
+  // the empty-space grids are built on first use as the absorption role (ensure_skip_grids)
+  return VR_OK;
+}
+
+// Occupancy bits + distance bytes of a resident volume, built the first time it serves as the
+// absorption role (only that texture decides which samples are empty): one streaming pass over
+// the bricks, a pass over the cells, three passes of the distance transform.
+vr_status ensure_skip_grids(vr_ctx *c, Resident &r, cudaStream_t stream) {
+  if (r.kind != TEX_VOLUME || (r.occ && r.dist)) return VR_OK;
+  r.ocx = (r.w + 7) / 8, r.ocy = (r.h + 7) / 8, r.ocz = (r.d + 7) / 8;
+  const uint64_t ncell = (uint64_t)r.ocx * r.ocy * r.ocz;
+  r.occ_bytes = (size_t)((ncell + 31) / 32) * 4;
+  VR_CUDA(c, cudaMalloc(&r.occ, r.occ_bytes));
+  VR_CUDA(c, cudaMemsetAsync(r.occ, 0, r.occ_bytes, stream));
+  const TexDesc t = describe(r);
+  VR_CUDA(c, launch_occupancy(t, r.layout, r.dtype, r.occ, r.ocx, r.ocy, r.ocz, 2, r.reg, stream));
+  r.dist_bytes = (size_t)ncell;
+  VR_CUDA(c, cudaMalloc(&r.dist, r.dist_bytes));
+  uint8_t *tmp = nullptr;
+  VR_CUDA(c, cudaMallocAsync(&tmp, r.dist_bytes, stream));
+  VR_CUDA(c, launch_distance(r.occ, r.dist, tmp, r.ocx, r.ocy, r.ocz, stream));
+  VR_CUDA(c, cudaFreeAsync(tmp, stream));
   return VR_OK;
 }
 
@@ -563,7 +573,8 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       return fail(c, VR_ERR_UNSUPPORTED, "volumes of one render must share dtype and layout (slot %d differs)", s);
   }
   if (dtype < 0) dtype = VR_DTYPE_F32, layout = LAYOUT_LINEAR;
-  const Resident &rab = c->tex[sAb];
+  Resident &rab = c->tex[sAb];
+  if (c->opt[VR_OPT_EMPTY_SPACE_SKIP]) VR_TRY(ensure_skip_grids(c, rab, stream));
   P.skip = (rab.kind == TEX_VOLUME && rab.occ && rab.dist) ? (int)c->opt[VR_OPT_EMPTY_SPACE_SKIP] : 0;
   P.occ = rab.occ, P.dist = rab.dist, P.ocx = rab.ocx, P.ocy = rab.ocy, P.ocz = rab.ocz;
   if (P.skip) {

@@ -106,6 +106,67 @@ __global__ void __launch_bounds__(256) k_occupancy(const TexDesc t, uint32_t *oc
   }
 }
 
+// Bricked storage, two streaming passes instead of one gather per cell:
+//  A. one warp per 8^3 storage brick (2 KiB fp32, read once, coalesced): a 64-bit mask with one bit
+//     per 2^3 sub-cell of the brick, set when any of its voxels is not +-0;
+//  B. one thread per macro cell: OR of the sub-cell bits that cover the cell dilated by `dilate`
+//     voxels (rounded outwards to sub-cells, i.e. at most one voxel more conservative).
+template <typename E>
+__global__ void __launch_bounds__(256) k_subcell_masks(const void *storage, uint64_t nbricks, unsigned long long *masks) {
+  const int lane = threadIdx.x & 31;
+  for (uint64_t b = (uint64_t)blockIdx.x * 8 + (threadIdx.x >> 5); b < nbricks; b += (uint64_t)gridDim.x * 8) {
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const uint32_t e = (uint32_t)lane + 32u * j;  // element of the brick: i = e&7, j = (e>>3)&7, k = e>>6
+      const float v = E::load(static_cast<const typename E::T *>(storage) + b * 512, e);
+      if (!(v == 0.0f)) {
+        const uint32_t bit = ((e & 7) >> 1) + 4u * (((e >> 3) & 7) >> 1) + 16u * (e >> 7);
+        if (bit < 32) lo |= 1u << bit; else hi |= 1u << (bit - 32);
+      }
+    }
+    lo = __reduce_or_sync(0xffffffffu, lo), hi = __reduce_or_sync(0xffffffffu, hi);
+    if (lane == 0) masks[b] = ((unsigned long long)hi << 32) | lo;
+  }
+}
+__global__ void __launch_bounds__(256) k_occupancy_from_masks(const TexDesc t, const unsigned long long *masks, uint32_t *occ, int ocx, int ocy,
+                                                             int ocz, int dilate, const Reg6 reg) {
+  const uint64_t ncell = (uint64_t)ocx * ocy * ocz;
+  const uint32_t nbx = t.sy >> 9, nby = t.sz / t.sy;  // bricks per row / per layer (TexDesc strides of the bricked layout)
+  for (uint64_t cell = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; cell < ncell; cell += (uint64_t)gridDim.x * blockDim.x) {
+    const int c[3] = {(int)(cell % ocx), (int)((cell / ocx) % ocy), (int)(cell / ((uint64_t)ocx * ocy))};
+    if (c[0] * 8 + 7 < reg.v[0] - 1 || c[0] * 8 > reg.v[3] - 1 || c[1] * 8 + 7 < reg.v[1] - 1 || c[1] * 8 > reg.v[4] - 1 || c[2] * 8 + 7 < reg.v[2] - 1 ||
+        c[2] * 8 > reg.v[5] - 1)
+      continue;
+    // sub-cell range of the dilated cell in local storage coordinates (voxel v sits at padded index v + 1 - o)
+    const int off[3] = {t.ox, t.oy, t.oz}, ldim[3] = {t.lw, t.lh, t.ld};
+    int s0[3], s1[3];
+    for (int a = 0; a < 3; ++a) {
+      const int x0 = min(max(c[a] * 8 + 1 - dilate - off[a], 0), ldim[a] - 1), x1 = min(max(c[a] * 8 + 8 + dilate - off[a], 0), ldim[a] - 1);
+      s0[a] = x0 >> 1, s1[a] = x1 >> 1;
+    }
+    bool any = false;
+    for (int bz = s0[2] >> 2; bz <= s1[2] >> 2 && !any; ++bz)
+      for (int by = s0[1] >> 2; by <= s1[1] >> 2 && !any; ++by)
+        for (int bx = s0[0] >> 2; bx <= s1[0] >> 2 && !any; ++bx) {
+          // sub-cells of this brick inside the range, per axis, as 4-bit masks
+          uint32_t m[3];
+          const int bb[3] = {bx, by, bz};
+          for (int a = 0; a < 3; ++a) {
+            const int lo = max(s0[a] - 4 * bb[a], 0), hi = min(s1[a] - 4 * bb[a], 3);
+            m[a] = ((1u << (hi + 1)) - 1u) & ~((1u << lo) - 1u);
+          }
+          unsigned long long want = 0;
+          for (int kz = 0; kz < 4; ++kz)
+            if (m[2] >> kz & 1u)
+              for (int ky = 0; ky < 4; ++ky)
+                if (m[1] >> ky & 1u) want |= (unsigned long long)m[0] << (4 * ky + 16 * kz);
+          any = (__ldg(masks + ((uint64_t)bz * nby + by) * nbx + bx) & want) != 0ull;
+        }
+    if (any) atomicOr(occ + (cell >> 5), 1u << (cell & 31));
+  }
+}
+
 cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *occ, int ocx, int ocy, int ocz,
                              int dilate, const int reg6[6], cudaStream_t stream) {
   Reg6 reg;
@@ -116,10 +177,22 @@ cudaError_t launch_occupancy(const TexDesc &t, int layout, int dtype, uint32_t *
   if (blocks < 1) blocks = 1;
   const unsigned g = (unsigned)blocks;
   if (layout == LAYOUT_BRICK) {
+    const uint64_t nbricks = (uint64_t)((t.lw + 7) / 8) * ((t.lh + 7) / 8) * ((t.ld + 7) / 8);
+    unsigned long long *masks = nullptr;
+    cudaError_t e = cudaMallocAsync(&masks, nbricks * 8, stream);
+    if (e != cudaSuccess) return e;
+    uint64_t ba = (nbricks + 7) / 8;
+    if (ba > 148ull * 64) ba = 148ull * 64;
     if (dtype == 0)
-      k_occupancy<LAYOUT_BRICK, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate, reg);
+      k_subcell_masks<ElemF32><<<(unsigned)ba, 256, 0, stream>>>(t.p, nbricks, masks);
     else
-      k_occupancy<LAYOUT_BRICK, ElemBF16><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate, reg);
+      k_subcell_masks<ElemBF16><<<(unsigned)ba, 256, 0, stream>>>(t.p, nbricks, masks);
+    uint64_t bb = (ncell + 255) / 256;
+    if (bb > 148ull * 32) bb = 148ull * 32;
+    k_occupancy_from_masks<<<(unsigned)bb, 256, 0, stream>>>(t, masks, occ, ocx, ocy, ocz, dilate, reg);
+    e = cudaGetLastError();
+    cudaFreeAsync(masks, stream);
+    return e;
   } else {
     if (dtype == 0)
       k_occupancy<LAYOUT_LINEAR, ElemF32><<<g, 256, 0, stream>>>(t, occ, ocx, ocy, ocz, dilate, reg);
