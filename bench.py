@@ -51,7 +51,7 @@ def parse():
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--skip", type=int, default=2)
     p.add_argument("--tile", type=int, default=64)
-    p.add_argument("--batch", type=int, default=8, help="frames per launch (one work queue per batch; clipped to --steps)")
+    p.add_argument("--batch", type=int, default=16, help="frames per launch (one work queue per batch; clipped to --steps)")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
                    help="image = tiles over replicated volumes (the metric's config); volume = bricks sharded over the ranks, sort-last composite (config 5)")

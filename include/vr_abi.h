@@ -192,7 +192,9 @@ typedef enum vr_option {
   VR_OPT_CLEAR_IMAGE = 10,      /* 1 (default) = zero the whole output image first (volumeRender.cpp:271); 0 = only the
                                    pixels of owned tiles are written (every owned pixel is, misses as 0): required when
                                    several ranks render into ONE shared image */
-  VR_OPT_TILE_ORDER = 11        /* 1 (default) = hand tiles out centre-first (long rays first); 0 = raster order */
+  VR_OPT_TILE_ORDER = 11        /* hand-out order of tiles: 1 (default) = most expensive first (measured on the previous launch,
+                                   else centre-first), one list over all frames of a batch; 2 = the same, frame after
+                                   frame; 0 = raster order */
 } vr_option;
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);

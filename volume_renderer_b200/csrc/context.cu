@@ -110,6 +110,12 @@ struct vr_ctx {
   unsigned int *d_counter = nullptr;      // work counter + padding
   uint32_t *d_tile_order = nullptr;       // owned tiles, heaviest first
   Camera *d_cams = nullptr;               // cameras of a batch
+  // measured cost per tile of the previous launch (device counters, pinned host copy, completion event)
+  unsigned int *d_tile_cost = nullptr, *h_tile_cost = nullptr;
+  size_t tile_cost_tiles = 0;     // capacity in tiles
+  uint64_t cost_sig = 0;          // geometry the host copy belongs to (W, H, tile size)
+  bool cost_valid = false;
+  cudaEvent_t ev_cost = nullptr;
   size_t cams_cap = 0;
   unsigned long long *d_warp_times = nullptr;  // debug buffer ($VR_WARP_TIMES=1): 2 x 8192 entries
   size_t tile_order_cap = 0;
@@ -693,7 +699,6 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     const size_t need = n_frames * sizeof(Camera);
     if (c->cams_cap < need) {
       if (c->d_cams) cudaFree(c->d_cams);
-  if (c->d_boxes) cudaFree(c->d_boxes);
       c->d_cams = nullptr, c->cams_cap = 0;
       VR_CUDA(c, cudaMalloc(&c->d_cams, need));
       c->cams_cap = need;
@@ -708,6 +713,9 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   // In a batch all frames share the one queue: the light tiles of every frame fill the tail.
   P.tile_order = nullptr;
   const bool ordered = c->opt[VR_OPT_TILE_ORDER] != 0;
+  const uint64_t sig = ((uint64_t)P.W << 40) ^ ((uint64_t)P.H << 20) ^ ((uint64_t)P.tile_w << 8) ^ (uint64_t)P.tile_h;
+  const bool use_cost = c->cost_valid && c->cost_sig == sig && c->tile_cost_tiles >= ntiles && cudaEventQuery(c->ev_cost) == cudaSuccess;
+  cudaGetLastError();  // cudaErrorNotReady of the query is not an error
   if ((ordered && entries > 1) || n_frames > 1) {
     std::vector<std::pair<float, uint32_t>> key((size_t)entries);
     for (size_t f = 0; f < n_frames; ++f) {
@@ -729,7 +737,13 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
         const uint32_t tile = (uint32_t)(P.part_rank + j * P.part_nranks);
         const float tx = ((tile % P.ntx) + 0.5f) * P.tile_w - px, ty = ((tile / P.ntx) + 0.5f) * P.tile_h - py;
         const uint32_t entry = (uint32_t)(f * ntiles + tile);
-        key[f * owned + j] = std::make_pair(ordered ? tx * tx + ty * ty : (float)(f * owned + j), entry);
+        float k = ordered ? tx * tx + ty * ty : (float)(f * owned + j);
+        // measured beats guessed: the previous launch's shaded samples per tile (a movie turns slowly), most expensive first
+        if (ordered && use_cost) k = -(float)c->h_tile_cost[tile] + 1e-9f * k;
+        // order 1: one heaviest-first list over all frames of the batch (measured best: 30.3 vs 31.3 ms per frame);
+        // order 2: frame after frame, each heaviest-first
+        if (c->opt[VR_OPT_TILE_ORDER] == 2) k = (float)f * 4.0e9f + fminf(fmaxf(k, -1.9e9f), 1.9e9f);
+        key[f * owned + j] = std::make_pair(k, entry);
       }
     }
     std::sort(key.begin(), key.end());
@@ -746,6 +760,20 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     P.tile_order = c->d_tile_order;
   }
   P.stats = c->d_stats;
+  P.tile_cost = nullptr;
+  if (ordered && !vs) {
+    if (c->tile_cost_tiles < ntiles) {
+      if (c->d_tile_cost) cudaFree(c->d_tile_cost);
+      if (c->h_tile_cost) cudaFreeHost(c->h_tile_cost);
+      c->d_tile_cost = c->h_tile_cost = nullptr, c->tile_cost_tiles = 0, c->cost_valid = false;
+      VR_CUDA(c, cudaMalloc(&c->d_tile_cost, ntiles * sizeof(unsigned int)));
+      VR_CUDA(c, cudaMallocHost(&c->h_tile_cost, ntiles * sizeof(unsigned int)));
+      c->tile_cost_tiles = ntiles;
+    }
+    // the host copy of the previous launch is final before it is overwritten: same stream, and use_cost saw its event
+    VR_CUDA(c, cudaMemsetAsync(c->d_tile_cost, 0, ntiles * sizeof(unsigned int), stream));
+    P.tile_cost = c->d_tile_cost;
+  }
 
   // cudaMemset of the image (volumeRender.cpp:271): pixels whose ray misses the box stay 0
   if (c->opt[VR_OPT_CLEAR_IMAGE])
@@ -755,6 +783,11 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   VR_CUDA(c, cudaEventRecord(c->ev0, stream));
   if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, (int)c->opt[VR_OPT_KERNEL_VARIANT], stream, c->sm_count));
   VR_CUDA(c, cudaEventRecord(c->ev1, stream));
+  if (P.tile_cost) {
+    VR_CUDA(c, cudaMemcpyAsync(c->h_tile_cost, c->d_tile_cost, ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+    VR_CUDA(c, cudaEventRecord(c->ev_cost, stream));
+    c->cost_valid = true, c->cost_sig = sig;
+  }
   if (P.count) {
     VR_CUDA(c, cudaMemcpyAsync(c->h_stats, c->d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
     c->stats_pending = true;
@@ -805,6 +838,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu0);
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu1);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&c->ev_cost, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_counter, 64);
   if (ce == cudaSuccess && getenv("VR_WARP_TIMES")) ce = cudaMalloc(&c->d_warp_times, 2 * 8192 * sizeof(unsigned long long));
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_stats, 64);
@@ -841,6 +875,9 @@ vr_status vr_destroy(vr_ctx *c) {
   if (c->d_counter) cudaFree(c->d_counter);
   if (c->d_tile_order) cudaFree(c->d_tile_order);
   if (c->d_cams) cudaFree(c->d_cams);
+  if (c->d_tile_cost) cudaFree(c->d_tile_cost);
+  if (c->h_tile_cost) cudaFreeHost(c->h_tile_cost);
+  if (c->ev_cost) cudaEventDestroy(c->ev_cost);
   if (c->d_boxes) cudaFree(c->d_boxes);
   if (c->d_warp_times) cudaFree(c->d_warp_times);
   if (c->d_stats) cudaFree(c->d_stats);

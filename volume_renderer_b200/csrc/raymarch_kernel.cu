@@ -95,6 +95,10 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
         cam.out[k + 2 * size] = hit ? r.sz : 0.0f;
       }
     }
+    if (P.tile_cost) {  // what this item cost: the next launch hands the expensive tiles out first
+      const unsigned cost = __reduce_add_sync(kFull, hit ? r.n_shaded : 0u);
+      if (lane == 0) atomicAdd(P.tile_cost + tile, cost + 1u);
+    }
     if (hit) {
       tot_marched += r.n_marched;
       tot_shaded += r.n_shaded;

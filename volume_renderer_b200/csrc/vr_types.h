@@ -74,6 +74,7 @@ struct KernelParams {
   // owned tiles in the order they are handed out (heaviest first, see context.cu: tile_order);
   // entry j is a tile index ty * ntx + tx.  NULL = part_rank + j * part_nranks.
   const uint32_t *tile_order;
+  unsigned int *tile_cost;         // per tile: shaded samples of the launch (feeds the next launch's hand-out order); NULL = off
   unsigned long long *warp_times;  // debug: per resident warp [start, end] in globaltimer ns (NULL = off)
   unsigned long long *stats;  // [0] samples marched, [1] samples shaded, [2] rays hit
   // vr::RenderOptions (volumeRender.h:81-109)
