@@ -192,9 +192,10 @@ typedef enum vr_option {
   VR_OPT_CLEAR_IMAGE = 10,      /* 1 (default) = zero the whole output image first (volumeRender.cpp:271); 0 = only the
                                    pixels of owned tiles are written (every owned pixel is, misses as 0): required when
                                    several ranks render into ONE shared image */
-  VR_OPT_TILE_ORDER = 11        /* hand-out order of tiles: 1 (default) = most expensive first (measured on the previous launch,
+  VR_OPT_TILE_ORDER = 11,       /* hand-out order of tiles: 1 (default) = most expensive first (measured on the previous launch,
                                    else centre-first), one list over all frames of a batch; 2 = the same, frame after
                                    frame; 0 = raster order */
+  VR_OPT_WARP_SHAPE = 12        /* s in [0,5]: one warp marches a (1<<s) x (32>>s) pixel footprint; default 3 = 8 x 4 */
 } vr_option;
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);

@@ -36,6 +36,7 @@ OPT_BRICK_LAYOUT = 8
 OPT_COUNT_SAMPLES = 9
 OPT_CLEAR_IMAGE = 10
 OPT_TILE_ORDER = 11
+OPT_WARP_SHAPE = 12
 IPC_HANDLE_BYTES = 64
 
 

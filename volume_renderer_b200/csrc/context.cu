@@ -674,9 +674,12 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   P.part_nranks = (int)c->opt[VR_OPT_PART_NRANKS];
   if (P.part_nranks < 1 || P.part_rank < 0 || P.part_rank >= P.part_nranks) return fail(c, VR_ERR_INVALID_ARGUMENT, "bad partition %d/%d", P.part_rank, P.part_nranks);
   P.tile_w = (int)c->opt[VR_OPT_TILE_W], P.tile_h = (int)c->opt[VR_OPT_TILE_H];
-  if (P.tile_w < 8 || P.tile_h < 4 || P.tile_w % 8 || P.tile_h % 4) return fail(c, VR_ERR_INVALID_ARGUMENT, "tile must be a multiple of 8x4");
+  P.wshift = (int)c->opt[VR_OPT_WARP_SHAPE];
+  if (P.wshift < 0 || P.wshift > 5) return fail(c, VR_ERR_INVALID_ARGUMENT, "warp shape must be in [0, 5]");
+  const int ww = 1 << P.wshift, wh = 32 >> P.wshift;
+  if (P.tile_w < ww || P.tile_h < wh || P.tile_w % ww || P.tile_h % wh) return fail(c, VR_ERR_INVALID_ARGUMENT, "tile must be a multiple of the %dx%d warp footprint", ww, wh);
   P.ntx = (P.W + P.tile_w - 1) / P.tile_w, P.nty = (P.H + P.tile_h - 1) / P.tile_h;
-  P.wt_x = P.tile_w / 8, P.wt_y = P.tile_h / 4;
+  P.wt_x = P.tile_w / ww, P.wt_y = P.tile_h / wh;
   const uint64_t ntiles = (uint64_t)P.ntx * P.nty;
   const uint64_t owned = ntiles > (uint64_t)P.part_rank ? (ntiles - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0;
   const uint64_t entries = owned * n_frames;  // (frame, owned tile) pairs of the launch
@@ -831,6 +834,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->opt[VR_OPT_COUNT_SAMPLES] = 1;
   c->opt[VR_OPT_CLEAR_IMAGE] = 1;
   c->opt[VR_OPT_TILE_ORDER] = 1;
+  c->opt[VR_OPT_WARP_SHAPE] = 3;
   cudaError_t ce = cudaSetDevice(device);
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   c->own_stream = ce == cudaSuccess;
@@ -1142,14 +1146,14 @@ int vr_abi_version(void) { return VR_ABI_VERSION; }
 
 vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_TILE_ORDER) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_WARP_SHAPE) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
   c->opt[option] = value;
   return VR_OK;
 }
 vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_TILE_ORDER || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_WARP_SHAPE || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   *value = c->opt[option];
   return VR_OK;
 }

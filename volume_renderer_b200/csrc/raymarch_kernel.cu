@@ -59,8 +59,8 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
     const F3 origin = ray_origin(cam);
     const uint32_t ty = tile / (uint32_t)P.ntx, tx = tile - ty * (uint32_t)P.ntx;
     const uint32_t sy = sub / (uint32_t)P.wt_x, sx = sub - sy * (uint32_t)P.wt_x;
-    const uint32_t x = tx * P.tile_w + sx * 8 + (lane & 7);
-    const uint32_t y = ty * P.tile_h + sy * 4 + (lane >> 3);
+    const uint32_t x = tx * P.tile_w + (sx << P.wshift) + (lane & ((1u << P.wshift) - 1u));
+    const uint32_t y = ty * P.tile_h + sy * (32u >> P.wshift) + (lane >> P.wshift);
 
     Ray r;
     bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, cam, x, y, origin, r);

@@ -67,7 +67,8 @@ struct KernelParams {
   // rendered by the context with j % part_nranks == part_rank.
   int part_rank, part_nranks;
   int tile_w, tile_h, ntx, nty;
-  int wt_x, wt_y;          // warp tiles (8x4 px) per partition tile
+  int wt_x, wt_y;          // warp tiles per partition tile
+  int wshift;              // a warp covers (1 << wshift) x (32 >> wshift) pixels (default 3: 8 x 4)
   uint32_t num_owned;      // partition tiles owned by this rank
   uint32_t num_work;       // warp work items = num_owned * wt_x * wt_y
   unsigned int *work_counter;
