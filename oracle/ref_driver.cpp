@@ -111,11 +111,13 @@ void ts_mexFunction(int nlhs, mxArray *plhs[], int nrhs, const mxArray *prhs[]);
 
 /* vr::render (volumeRender.cpp:233-300) references the CUDA launcher that lives in the .cu file,
  * which cannot be compiled (texture references).  It is never called from here. */
+#ifndef REF_WITH_CUDA_KERNEL /* the shimmed CUDA build (libref_cuda.so) links the reference's real launcher */
 namespace vr {
 void render_kernel(float *, const dim3 &, const dim3 &, const RenderOptions &, const float3 &, const float3 &) {
   throw std::runtime_error("render_kernel is not available in the CPU-only reference build");
 }
 } // namespace vr
+#endif
 
 static mxArray *scalar_double(double v) {
   mxArray *a = mxCreateNumericMatrix(1, 1, mxDOUBLE_CLASS, mxREAL);

@@ -375,3 +375,107 @@ def compare(img, ref):
 
 
 TOL = 1e-3  # BASELINE.json north_star: max abs error <= 1e-3 on [0,1]-normalised RGB
+
+
+# ---- the shimmed reference CUDA kernel (oracle/_ref/libref_cuda.so) -----------------------------------
+def ref_cuda():
+    """The reference's own d_render + upload code on texture objects (oracle/ref_cuda), or None."""
+    path = os.path.join(ORACLE_DIR, "_ref", "libref_cuda.so")
+    if not os.path.exists(path):
+        return None
+    lib = C.CDLL(path)
+    P = C.POINTER
+    f3, u64p = P(C.c_float), P(C.c_uint64)
+    lib.refcuda_sync_volumes.argtypes = [C.c_uint64] + [P(_abi.VrVolume)] * 6
+    lib.refcuda_render.argtypes = [P(_abi.VrLight), C.c_size_t, P(_abi.VrVolume), f3, f3, u64p, f3, f3, C.c_float, f3, C.c_void_p]
+    return lib
+
+
+class RefCudaBackend:
+    """The mex command protocol on top of the shimmed reference.  Its state is process-global (the
+    reference's texture references and d_idx* are), so use ONE renderer per process."""
+
+    def __init__(self):
+        self.lib = ref_cuda()
+        if self.lib is None:
+            raise RuntimeError("oracle/_ref/libref_cuda.so is not built (make -C oracle refcuda)")
+
+    def new(self):
+        return C.c_void_p(1)
+
+    def delete(self, h):
+        return 0
+
+    def mem_info(self, h):
+        return "shimmed reference\n"
+
+    def sync_volumes(self, h, T, em, re, ab, gx=None, gy=None, gz=None):
+        keep = []
+        vols = [_abi.volume_struct(v.Data, v.TimeLastUpdate, keep) if v is not None else None for v in (em, re, ab, gx, gy, gz)]
+        ptrs = [C.byref(v) if v is not None else None for v in vols]
+        rc = self.lib.refcuda_sync_volumes(int(T), *ptrs)
+        assert rc == 0, rc
+        self._keep = keep
+
+    def render(self, h, lights, lut, factors, es, res, rot, props, thr, color):
+        H, W = int(res[0]), int(res[1])
+        out = np.zeros((H, W, 3), dtype=np.float32, order="F")
+        args, keep = api._render_args(lights, lut, factors, es, res, rot, props, thr, color)
+        rc = self.lib.refcuda_render(*args, out.ctypes.data)
+        assert rc == 0, rc
+        return out
+
+
+class RefCudaVolumeRender(api.VolumeRender):
+    _backend_cls = RefCudaBackend
+
+
+def golden_scenes():
+    """name -> function(cls) building a configured renderer: the scenes whose images, rendered on a
+    B200 by the shimmed reference kernel, are committed under tests/golden/refcuda_*.npy."""
+    res = (96, 80)
+
+    def base(cls, vol, lights, **kw):
+        return example1_scene(cls, vol, res, lights=lights, lut=oracle_lut(64))
+
+    def s_example1(cls):
+        return base(cls, synth_brain((48, 48, 48)), 1)
+
+    def s_two_lights_dense(cls):
+        r = base(cls, synth_brain((48, 48, 48)), 2)
+        r.FactorAbsorption = 30.0  # rays terminate at the 0.9 threshold
+        return r
+
+    def s_gradient_volumes(cls):
+        r = base(cls, synth_brain((48, 48, 48)), 2)
+        gx, gy, gz = r.VolumeEmission.grad()
+        r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
+        r.FactorEmission, r.FactorAbsorption, r.FactorReflection = 0.1, 0.4, 0.1
+        r.Color = [1, 1, 1]
+        return r
+
+    def s_anisotropic(cls):
+        r = base(cls, synth_brain((56, 40, 28)), 1)
+        r.ElementSizeUm = [1.0, 0.8, 2.5]
+        return r
+
+    def s_distinct_roles(cls):
+        v = synth_brain((40, 40, 40))
+        r = base(cls, v, 1)
+        r.VolumeAbsorption = api.Volume(np.asfortranarray(np.sqrt(v)))
+        r.VolumeReflection = api.Volume(np.asfortranarray(v * v))
+        return r
+
+    def s_constant_volume_nan_normal(cls):
+        return base(cls, np.full((16, 16, 16), 0.5, dtype=np.float32, order="F"), 1)
+
+    def s_stereo_pass(cls):
+        r = base(cls, synth_brain((40, 40, 40)), 1)
+        r.CameraXOffset = 0.06
+        r.FocalLength = 4.5
+        r.StereoOutput = api.StereoRenderMode.LeftRightHorizontal
+        return r
+
+    return {"example1": s_example1, "two_lights_dense": s_two_lights_dense, "gradient_volumes": s_gradient_volumes,
+            "anisotropic": s_anisotropic, "distinct_roles": s_distinct_roles, "constant_volume_nan_normal": s_constant_volume_nan_normal,
+            "stereo_pass": s_stereo_pass}
