@@ -259,6 +259,18 @@ VR_API vr_status vr_synth_volume_region(vr_ctx *ctx, int kind, uint32_t seed, co
 VR_API vr_status vr_ipc_export(vr_ctx *ctx, void *d_ptr, unsigned char handle[VR_IPC_HANDLE_BYTES]);
 VR_API vr_status vr_ipc_open(vr_ctx *ctx, const unsigned char handle[VR_IPC_HANDLE_BYTES], void **d_ptr);
 VR_API vr_status vr_ipc_close(vr_ctx *ctx, void *d_ptr);
+/* ---- image epilogue on the device (done in MATLAB by the reference) -----------
+ * Stereo compose of VolumeRender.m:286-306: d_left / d_right are the two eyes rendered at
+ * res_wide = [H, W + delta]; mode 0 = RedCyan -> H x W x 3, mode 1 = LeftRightHorizontal -> H x 2W x 3.
+ * Sequence normalisation of VolumeRender.m:587-701 in place over n_images frames (global min / max,
+ * including the reference's `+ min` shift for negative minima).  Multi-channel combine
+ * (example3.m:239, plain addition) is vr_compose_partials_device. */
+VR_API vr_status vr_compose_stereo_device(vr_ctx *ctx, const float *d_left, const float *d_right,
+                                          const uint64_t res_wide[2], uint64_t delta, int mode,
+                                          float *d_out, void *cuda_stream);
+VR_API vr_status vr_normalize_sequence_device(vr_ctx *ctx, float *const *d_images, uint32_t n_images,
+                                              uint64_t n_floats_each, void *cuda_stream);
+VR_API vr_status vr_device_upload(vr_ctx *ctx, void *d_dst, const void *host_src, size_t bytes);
 /* Debug: [start,end] globaltimer ns of every resident warp of the last ray-march launch
  * (2 x max_warps uint64, at most 8192 warps); only when $VR_WARP_TIMES was set at vr_create. */
 VR_API vr_status vr_debug_warp_times(vr_ctx *ctx, uint64_t *host_pairs, size_t max_warps);

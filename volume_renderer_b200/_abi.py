@@ -113,6 +113,9 @@ def declare(lib):
         "vr_render_partial_device": (render_args + [C.c_uint32, C.c_uint32, u64p, vp, vp, vp], C.c_int),
         "vr_compose_partials_device": ([vp, C.c_uint32, P(vp), C.c_uint64, vp, vp], C.c_int),
         "vr_synth_volume_region": ([vp, C.c_int, C.c_uint32, u64p, u64p, u64p, C.c_int32, vp], C.c_int),
+        "vr_compose_stereo_device": ([vp, vp, vp, u64p, C.c_uint64, C.c_int, vp, vp], C.c_int),
+        "vr_normalize_sequence_device": ([vp, P(vp), C.c_uint32, C.c_uint64, vp], C.c_int),
+        "vr_device_upload": ([vp, vp, vp, C.c_size_t], C.c_int),
         "vr_debug_warp_times": ([vp, vp, C.c_size_t], C.c_int),
         "vr_ipc_export": ([vp, vp, C.c_char_p], C.c_int),
         "vr_ipc_open": ([vp, C.c_char_p, P(vp)], C.c_int),

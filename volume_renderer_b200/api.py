@@ -272,6 +272,33 @@ class _CudaBackend:
                                               args[8], args[9], ptrs), h)
         return outs
 
+    def render_stereo(self, h, lights, lut, factors, es, res_wide, rot, props_right, props_left, thr, color, delta, mode):
+        """Both eyes in one launch and the crop + compose of VolumeRender.m:286-306 on the device: only the
+        final image crosses PCIe."""
+        lib = _abi.lib()
+        H, Wp = int(res_wide[0]), int(res_wide[1])
+        Wo = (Wp - delta) * (1 if mode == 0 else 2)
+        nb = H * Wp * 3 * 4
+        bufs = [C.c_void_p() for _ in range(3)]
+        for b, size in zip(bufs, (nb, nb, H * Wo * 3 * 4)):
+            _abi.check(lib.vr_device_alloc(h, size, C.byref(b)), h)
+        try:
+            args, keep = _render_args(lights, lut, factors, es, res_wide, rot, props_right, thr, color)
+            R = np.tile(np.asfortranarray(np.asarray(rot, dtype=np.float32)).reshape(-1, order="F"), 2).astype(np.float32)
+            Pp = np.concatenate([np.asarray(props_right, dtype=np.float32), np.asarray(props_left, dtype=np.float32)]).astype(np.float32)
+            f32p = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+            outs = (C.c_void_p * 2)(bufs[0].value, bufs[1].value)  # right eye, left eye
+            _abi.check(lib.vr_render_batch_device(h, args[0], args[1], args[2], args[3], args[4], args[5], 2, f32p(R), f32p(Pp), args[8], args[9], outs, None), h)
+            rw = np.asarray(res_wide, dtype=np.uint64)
+            _abi.check(lib.vr_compose_stereo_device(h, bufs[1], bufs[0], rw.ctypes.data_as(C.POINTER(C.c_uint64)), int(delta), int(mode), bufs[2], None), h)
+            out = np.zeros((H, Wo, 3), dtype=np.float32, order="F")
+            _abi.check(lib.vr_device_download(h, out.ctypes.data, bufs[2], out.nbytes), h)
+            return out
+        finally:
+            for b in bufs:
+                if b:
+                    lib.vr_device_free(h, b)
+
     def stats(self, h):
         s = _abi.VrStats()
         _abi.check(_abi.lib().vr_get_stats(h, C.byref(s)), h)
@@ -349,7 +376,7 @@ class VolumeRender:
         self.RotationMatrix = np.eye(3)
         self.ImageResolution = [0, 0]
         self.TimeLastMemSync = 0
-        self.BatchStereo = True  # extension: render the stereo pair as one batch launch
+        self.BatchStereo = True  # extension: True = the stereo pair as one batch launch, "device" = also crop + compose on the GPU, False = two passes
         self._vols.update({k: False for k in self._volume_props})
         self._vols["VolumeReflection"] = Volume(1)  # VolumeRender.m:131
         self._backend = self._backend_cls()
@@ -453,6 +480,17 @@ class VolumeRender:
             return self.p_render(np.float32(self.CameraXOffset), flipped)
         base, delta = self.stereo_delta()
         resolution = [flipped[0], flipped[1] + delta]
+        if hasattr(self._backend, "render_stereo") and self.BatchStereo == "device":
+            # both eyes in one launch, crop + compose on the device (vr_compose_stereo_device)
+            self._check_volumes()
+            self.syncVolumes()
+            mode = 0 if self.StereoOutput == StereoRenderMode.RedCyan else 1
+            img = self._backend.render_stereo(self.objectHandle, self.LightSources if self.LightSources is not False else None,
+                                              self.VolumeIllumination if self.VolumeIllumination is not False else None,
+                                              [self.FactorEmission, self.FactorReflection, self.FactorAbsorption], self.ElementSizeUm, resolution,
+                                              np.flipud(np.asarray(self.RotationMatrix)), [base, self.FocalLength, self.DistanceToObject],
+                                              [-base, self.FocalLength, self.DistanceToObject], self.OpacityThreshold, self.Color, delta, mode)
+            return img.astype(np.float64) if mode == 0 else img
         if hasattr(self._backend, "render_batch") and self.BatchStereo:
             # both eyes in one launch (same pixels as two p_render passes; one work queue)
             rightImage, leftImage = self.p_render_batch([base, -base], resolution)

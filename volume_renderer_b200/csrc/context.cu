@@ -1264,6 +1264,30 @@ vr_status vr_ipc_close(vr_ctx *c, void *d_ptr) {
   VR_CUDA(c, cudaIpcCloseMemHandle(d_ptr));
   return VR_OK;
 }
+vr_status vr_compose_stereo_device(vr_ctx *c, const float *d_left, const float *d_right, const uint64_t res_wide[2], uint64_t delta, int mode,
+                                   float *d_out, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  if (!d_left || !d_right || !d_out || !res_wide || (mode != 0 && mode != 1) || delta >= res_wide[1]) return fail(c, VR_ERR_INVALID_ARGUMENT, "compose_stereo: bad arguments");
+  VR_TRY(set_device(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  VR_CUDA(c, launch_stereo(d_left, d_right, (int)res_wide[0], (int)res_wide[1], (int)delta, mode, d_out, s));
+  return VR_OK;
+}
+vr_status vr_normalize_sequence_device(vr_ctx *c, float *const *d_images, uint32_t n_images, uint64_t n_floats_each, void *cuda_stream) {
+  VR_CHECK_HANDLE(c);
+  if (!d_images || n_images == 0 || n_floats_each == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "normalize: bad arguments");
+  VR_TRY(set_device(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  VR_CUDA(c, launch_normalize(d_images, (int)n_images, (size_t)n_floats_each, reinterpret_cast<unsigned *>(c->d_counter + 8), s));
+  return VR_OK;
+}
+vr_status vr_device_upload(vr_ctx *c, void *d_dst, const void *host_src, size_t bytes) {
+  VR_CHECK_HANDLE(c);
+  VR_TRY(set_device(c));
+  VR_CUDA(c, cudaMemcpyAsync(d_dst, host_src, bytes, cudaMemcpyHostToDevice, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
 vr_status vr_device_alloc(vr_ctx *c, size_t bytes, void **d_ptr) {
   VR_CHECK_HANDLE(c);
   if (!d_ptr) return fail(c, VR_ERR_INVALID_ARGUMENT, "null pointer");

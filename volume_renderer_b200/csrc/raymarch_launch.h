@@ -56,6 +56,10 @@ cudaError_t launch_synth_region(void *d_out, int kind, uint32_t seed, const int 
 // operator over depth-ordered partials reduces to an order-free sum.  Partials may live on peer GPUs.
 cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_floats, float *d_out, cudaStream_t stream);
 
+// image epilogue: stereo crop + compose (mode 0 RedCyan, 1 LeftRightHorizontal) and sequence normalisation
+cudaError_t launch_stereo(const float *left, const float *right, int H, int Wp, int delta, int mode, float *out, cudaStream_t stream);
+cudaError_t launch_normalize(float *const *imgs, int n_imgs, size_t n_each, unsigned *d_mm, cudaStream_t stream);
+
 // MATLAB gradient() of a MATLAB-layout volume (Volume.m:181-205): gx = d/d dim2, gy = d/d dim1, gz = d/d dim3
 cudaError_t launch_gradient(const void *d_in, int w, int h, int d, int dtype, void *gx, void *gy, void *gz, cudaStream_t stream);
 

@@ -422,6 +422,69 @@ cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_flo
   return cudaGetLastError();
 }
 
+// ---- image epilogue (what the reference does in MATLAB after the mex returns) ---------------------------
+// Stereo compose (VolumeRender.m:286-306): both eyes were rendered delta columns wider; the left image
+// keeps columns delta.., the right one columns ..Wp-delta; RedCyan takes R from the left eye and G,B from
+// the right, LeftRightHorizontal puts the crops side by side.  Images are H x W x 3 column-major planar.
+__global__ void __launch_bounds__(256) k_stereo(const float *left, const float *right, int H, int Wp, int delta, int mode, float *out) {
+  const int Wc = Wp - delta, Wo = mode == 0 ? Wc : 2 * Wc;
+  const size_t plane_in = (size_t)H * Wp, plane_out = (size_t)H * Wo, total = plane_out * 3;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int ch = (int)(i / plane_out);
+    const size_t k = i - (size_t)ch * plane_out;
+    const int x = (int)(k / H), y = (int)(k - (size_t)x * H);
+    float v;
+    if (mode == 0) {
+      v = ch == 0 ? left[(size_t)ch * plane_in + (size_t)(x + delta) * H + y] : right[(size_t)ch * plane_in + (size_t)x * H + y];
+    } else {
+      v = x < Wc ? left[(size_t)ch * plane_in + (size_t)(x + delta) * H + y] : right[(size_t)ch * plane_in + (size_t)(x - Wc) * H + y];
+    }
+    out[i] = v;
+  }
+}
+cudaError_t launch_stereo(const float *left, const float *right, int H, int Wp, int delta, int mode, float *out, cudaStream_t stream) {
+  const size_t total = (size_t)H * (mode == 0 ? Wp - delta : 2 * (Wp - delta)) * 3;
+  size_t blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks < 1) blocks = 1;
+  k_stereo<<<(unsigned)blocks, 256, 0, stream>>>(left, right, H, Wp, delta, mode, out);
+  return cudaGetLastError();
+}
+
+// normalizeSequence / normalizeImage (VolumeRender.m:587-701): global min and max over all frames, then
+// (like the reference, including its `+ min` shift for negative minima) every value divided by the max.
+__device__ __forceinline__ unsigned ord(float f) {  // order-preserving float -> uint
+  const unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float unord(unsigned u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
+__global__ void __launch_bounds__(256) k_minmax(const float *img, size_t n, unsigned *mm) {
+  unsigned lo = 0xffffffffu, hi = 0u;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const unsigned o = ord(img[i]);
+    lo = min(lo, o), hi = max(hi, o);
+  }
+  lo = __reduce_min_sync(0xffffffffu, lo), hi = __reduce_max_sync(0xffffffffu, hi);
+  if ((threadIdx.x & 31) == 0) atomicMin(mm, lo), atomicMax(mm + 1, hi);
+}
+__global__ void __launch_bounds__(256) k_normalize(float *img, size_t n, const unsigned *mm) {
+  float mn = unord(mm[0]), mx = unord(mm[1]);
+  const float shift = mn < 0.0f ? mn : 0.0f;  // VolumeRender.m:676-683: r = r + minValue, max = max + abs(min)
+  if (mn < 0.0f) mx = mx + fabsf(mn);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) img[i] = (img[i] + shift) / mx;
+}
+cudaError_t launch_normalize(float *const *imgs, int n_imgs, size_t n_each, unsigned *d_mm, cudaStream_t stream) {
+  const unsigned init[2] = {0xffffffffu, 0u};
+  cudaError_t e = cudaMemcpyAsync(d_mm, init, sizeof init, cudaMemcpyHostToDevice, stream);
+  if (e != cudaSuccess) return e;
+  size_t blocks = (n_each + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  for (int i = 0; i < n_imgs; ++i) k_minmax<<<(unsigned)blocks, 256, 0, stream>>>(imgs[i], n_each, d_mm);
+  for (int i = 0; i < n_imgs; ++i) k_normalize<<<(unsigned)blocks, 256, 0, stream>>>(imgs[i], n_each, d_mm);
+  return cudaGetLastError();
+}
+
 // ---- MATLAB gradient() ---------------------------------------------------------------------------
 // Volume.grad (src/matlab/VolumeRender/Volume.m:181-205) calls MATLAB's gradient(Data): unit
 // spacing, central differences inside, one-sided at the ends, zero along a singleton axis; its
