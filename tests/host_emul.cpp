@@ -163,6 +163,7 @@ int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr
     if (t->w != P.geo.w || t->h != P.geo.h || t->d != P.geo.d || t->sy != P.geo.sy || t->sz != P.geo.sz) P.uniform = 0;
   }
   if (variant == 1) P.uniform = 0;
+  if (P.frac_bits) P.uniform = 0;
   P.count = 1;
   P.n_lights = lut ? (int)n_lights : 0;
   if (P.n_lights > MAX_PARAM_LIGHTS) return 2;

@@ -604,6 +604,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       P.uniform = 0;
   }
   if (c->opt[VR_OPT_KERNEL_VARIANT] == 1) P.uniform = 0;  // variant 1: per-texture addressing everywhere (A/B measurements)
+  if (P.frac_bits) P.uniform = 0;  // fixed-point weights (A/B option) are compiled into the per-texture kernels only
 
   // volume-space mode
   P.vs_mode = 0;
@@ -784,7 +785,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_stats, 0, 3 * sizeof(unsigned long long), stream));
   VR_CUDA(c, cudaEventRecord(c->ev0, stream));
-  if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, (int)c->opt[VR_OPT_KERNEL_VARIANT], stream, c->sm_count));
+  if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, stream, c->sm_count));
   VR_CUDA(c, cudaEventRecord(c->ev1, stream));
   if (P.tile_cost) {
     VR_CUDA(c, cudaMemcpyAsync(c->h_tile_cost, c->d_tile_cost, ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));

@@ -14,6 +14,7 @@
 
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "vr_types.h"
 
@@ -25,6 +26,10 @@
 #define VR_LDG(ptr) (*(ptr))
 #define VR_EXPF(x) exp2f((x) * 1.4426950408889634f)
 #define VR_RSQRT(x) (1.0f / sqrtf(x))
+#endif
+
+#ifndef VR_MAGIC_FLOOR
+#define VR_MAGIC_FLOOR 1
 #endif
 
 namespace vrb {
@@ -91,14 +96,51 @@ struct Addr<LAYOUT_BRICK> {
 // the edge voxel, as does x=0), it maps a NaN coordinate to 0 (fmaxf returns the non-NaN
 // operand - the texture unit's rule), and it bounds i to [-1, N-1] so that with the padded
 // storage no integer clamps are needed.  X0 = i+1 is the padded index of the low tap.
-VR_HD void axis_setup(float x, float fN, int frac_bits, int &X0, float &f) {
+// floor(xb) as a float and as an int for xb in [-0.5, 2^22).  On the device: one add rounded towards
+// -inf onto 1.5 * 2^23 leaves floor(xb) in the low mantissa bits (ulp there is 1), which replaces
+// FRND + F2I - both quarter-rate conversion-pipe instructions - by two FADDs and an integer
+// subtract; the values are those of floorf / (int).
+struct AxisCoord {
+  float xb;  // x*N - 0.5 of the clamped coordinate
+  float t;   // device: floor(xb) + 1.5 * 2^23; host: floor(xb)
+  VR_HD float fl() const {  // floor(xb)
+#if defined(__CUDA_ARCH__) && VR_MAGIC_FLOOR
+    return t - 12582912.0f;
+#else
+    return t;
+#endif
+  }
+  VR_HD int i() const {  // (int)floor(xb), in [-1, N-1]
+#if defined(__CUDA_ARCH__) && VR_MAGIC_FLOOR
+    return __float_as_int(t) - 0x4B400000;
+#else
+    return (int)t;
+#endif
+  }
+};
+VR_HD AxisCoord axis_coord(float x, float fN) {
+  AxisCoord a;
   x = fminf(fmaxf(x, 0.0f), 1.0f);
-  float xb = x * fN - 0.5f;
-  float fl = floorf(xb);
-  f = xb - fl;
-  if (frac_bits) f = floorf(f * 256.0f + 0.5f) * (1.0f / 256.0f);  // 1.8 fixed-point weights
-  X0 = (int)fl + 1;
+  a.xb = x * fN - 0.5f;
+#if defined(__CUDA_ARCH__) && VR_MAGIC_FLOOR
+  a.t = __fadd_rd(a.xb, 12582912.0f);
+#else
+  a.t = floorf(a.xb);
+#endif
+  return a;
 }
+// the macro cell of a sample (see cell_at)
+struct CellAt {
+  AxisCoord ax, ay, az;
+  int cx, cy, cz;
+  uint32_t cell;
+};
+VR_HD void axis_finish(const AxisCoord &a, int frac_bits, int &X0, float &f) {
+  f = a.xb - a.fl();
+  if (frac_bits) f = floorf(f * 256.0f + 0.5f) * (1.0f / 256.0f);  // 1.8 fixed-point weights
+  X0 = a.i() + 1;
+}
+VR_HD void axis_setup(float x, float fN, int frac_bits, int &X0, float &f) { axis_finish(axis_coord(x, fN), frac_bits, X0, f); }
 // one fused multiply-add per lerp, written explicitly so that the checker (oracle.cpp: lerp) and
 // this file round identically whatever the contraction flags are
 VR_HD float lerpf(float a, float b, float f) { return fmaf(f, b - a, a); }
@@ -169,13 +211,23 @@ VR_HD AxisTap axis_tap_z(float z, float fN, uint32_t sz, int off, int fb) {
   a.o0 = Addr<LAYOUT>::z(Z, sz), a.o1 = Addr<LAYOUT>::z(Z + 1, sz);
   return a;
 }
+template <int LAYOUT>
+VR_HD void axis_taps_from(const TexDesc &g, const AxisCoord &cx, const AxisCoord &cy, const AxisCoord &cz, int fb, AxisTap &ax, AxisTap &ay,
+                          AxisTap &az) {
+  int X, Y, Z;
+  axis_finish(cx, fb, X, ax.f), axis_finish(cy, fb, Y, ay.f), axis_finish(cz, fb, Z, az.f);
+  X -= g.ox, Y -= g.oy, Z -= g.oz;
+  ax.o0 = Addr<LAYOUT>::x(X), ax.o1 = Addr<LAYOUT>::x(X + 1);
+  ay.o0 = Addr<LAYOUT>::y(Y, g.sy), ay.o1 = Addr<LAYOUT>::y(Y + 1, g.sy);
+  az.o0 = Addr<LAYOUT>::z(Z, g.sz), az.o1 = Addr<LAYOUT>::z(Z + 1, g.sz);
+}
 template <typename E>
 VR_HD float taps_fetch(const void *p, const AxisTap &ax, const AxisTap &ay, const AxisTap &az) {
-  const uint32_t b00 = ay.o0 + az.o0, b10 = ay.o1 + az.o0, b01 = ay.o0 + az.o1, b11 = ay.o1 + az.o1;
-  const float c000 = E::load(p, b00 + ax.o0), c100 = E::load(p, b00 + ax.o1);
-  const float c010 = E::load(p, b10 + ax.o0), c110 = E::load(p, b10 + ax.o1);
-  const float c001 = E::load(p, b01 + ax.o0), c101 = E::load(p, b01 + ax.o1);
-  const float c011 = E::load(p, b11 + ax.o0), c111 = E::load(p, b11 + ax.o1);
+  // three-operand sums: one IADD3 per tap
+  const float c000 = E::load(p, ax.o0 + ay.o0 + az.o0), c100 = E::load(p, ax.o1 + ay.o0 + az.o0);
+  const float c010 = E::load(p, ax.o0 + ay.o1 + az.o0), c110 = E::load(p, ax.o1 + ay.o1 + az.o0);
+  const float c001 = E::load(p, ax.o0 + ay.o0 + az.o1), c101 = E::load(p, ax.o1 + ay.o0 + az.o1);
+  const float c011 = E::load(p, ax.o0 + ay.o1 + az.o1), c111 = E::load(p, ax.o1 + ay.o1 + az.o1);
   const float c00 = lerpf(c000, c100, ax.f), c10 = lerpf(c010, c110, ax.f);
   const float c01 = lerpf(c001, c101, ax.f), c11 = lerpf(c011, c111, ax.f);
   return lerpf(lerpf(c00, c10, ay.f), lerpf(c01, c11, ay.f), az.f);
@@ -295,8 +347,7 @@ VR_HD float div_pi(float x) {
 // none of them depends on the light (kernel.cu:329-344); they are evaluated once here - the same
 // operations on the same operands, so the values are those of the reference's loop.
 template <int LAYOUT>
-VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color) {
-  const int fb = P.frac_bits;
+VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color, int fb) {
   const F3 N = -1.0f * normalize3(g);
   const F3 lightIn = origin - pos;
   const float lenN = length3(N), lenIn = length3(lightIn);
@@ -305,8 +356,13 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
   const float lenInProj = length3(lightInProj);
   F3 illum = mk3(0.0f, 0.0f, 0.0f);
   for (int i = 0; i < P.n_lights; ++i) {
-    const float *L = i < MAX_PARAM_LIGHTS ? P.lights[i] : P.lights_more + 6 * (i - MAX_PARAM_LIGHTS);
-    const F3 lpos = mk3(L[0], L[1], L[2]), lcol = mk3(L[3], L[4], L[5]);
+    F3 lpos, lcol;
+    if (i < MAX_PARAM_LIGHTS) {  // kernel-parameter space: register-indexed constant loads (a pointer select would go generic)
+      lpos = mk3(P.lights[i][0], P.lights[i][1], P.lights[i][2]), lcol = mk3(P.lights[i][3], P.lights[i][4], P.lights[i][5]);
+    } else {
+      const float *L = P.lights_more + 6 * (i - MAX_PARAM_LIGHTS);
+      lpos = mk3(VR_LDG(L), VR_LDG(L + 1), VR_LDG(L + 2)), lcol = mk3(VR_LDG(L + 3), VR_LDG(L + 4), VR_LDG(L + 5));
+    }
     const F3 lightOut = lpos - pos;
     const float b = div_pi(vr_acosf(dot3(N, lightOut) / (lenN * length3(lightOut))));
     const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
@@ -321,13 +377,15 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
 // One full iteration of the loop kernel.cu:435-493 up to and including the "under" update.
 // GRAD: 0 = computeGradient (kernel.cu:212-253), 1 = lookupGradient (kernel.cu:266-276).
 // UNI : every volume texture of the launch shares one geometry -> shared tap sets.
+// Fixed-point weights (frac_bits, an A/B option) are only compiled into the UNI == 0 kernels; the
+// host selects those when the option is set.
 template <int GRAD, int LAYOUT, typename E, int UNI>
 VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const F3 bmin = ld3(P.boxmin), bmax = ld3(P.boxmax);
   const F3 ext = bmax - bmin;
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);  // kernel.cu:396
   const F3 ps = (r.pos - bmin) * bscale;                            // kernel.cu:437
-  const int fb = P.frac_bits;
+  const int fb = UNI ? 0 : P.frac_bits;
   if (P.vs_mode && !(ps.x >= P.reg_lo[0] && ps.x < P.reg_hi[0] && ps.y >= P.reg_lo[1] && ps.y < P.reg_hi[1] && ps.z >= P.reg_lo[2] &&
                      ps.z < P.reg_hi[2])) {
     r.n_marched++;  // a sample of the global lattice that another brick owns
@@ -336,9 +394,9 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   AxisTap ax, ay, az;
   float em_raw, ab_raw;
   if (UNI) {
-    ax = axis_tap_x<LAYOUT>(ps.x, P.geo.fw, P.geo.ox, fb);
-    ay = axis_tap_y<LAYOUT>(ps.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
-    az = axis_tap_z<LAYOUT>(ps.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
+    // (handing the skip phase's x*N - 0.5 and floors of this position over instead of computing
+    // them again costs more in live registers than it saves: measured +2.5 %)
+    axis_taps_from<LAYOUT>(P.geo, axis_coord(ps.x, P.geo.fw), axis_coord(ps.y, P.geo.fh), axis_coord(ps.z, P.geo.fd), fb, ax, ay, az);
     em_raw = taps_any<E>(P.em, ax, ay, az);
     ab_raw = P.ab_is_em ? em_raw : taps_any<E>(P.ab, ax, ay, az);
   } else {
@@ -368,17 +426,22 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
       if (GRAD == 0) {
         // computeGradient: the six taps differ from the sample position in ONE coordinate each
         // ((pos.y + 0 - bmin.y) * bscale.y is ps.y bit for bit), so only that axis is set up anew.
-        const F3 gs = ld3(P.gstep);
-        const AxisTap xp = axis_tap_x<LAYOUT>((r.pos.x + gs.x - bmin.x) * bscale.x, P.geo.fw, P.geo.ox, fb);
-        const AxisTap xm = axis_tap_x<LAYOUT>((r.pos.x - gs.x - bmin.x) * bscale.x, P.geo.fw, P.geo.ox, fb);
-        g.x = taps_any<E>(P.em_direct, xp, ay, az) - taps_any<E>(P.em_direct, xm, ay, az);
-        const AxisTap yp = axis_tap_y<LAYOUT>((r.pos.y + gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
-        const AxisTap ym = axis_tap_y<LAYOUT>((r.pos.y - gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
-        g.y = taps_any<E>(P.em_direct, ax, yp, az) - taps_any<E>(P.em_direct, ax, ym, az);
-        const AxisTap zp = axis_tap_z<LAYOUT>((r.pos.z + gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
-        const AxisTap zm = axis_tap_z<LAYOUT>((r.pos.z - gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
-        g.z = taps_any<E>(P.em_direct, ax, ay, zp) - taps_any<E>(P.em_direct, ax, ay, zm);
-        g = g * mk3(0.5f, 0.5f, 0.5f);
+        if (P.em_direct.kind == TEX_VOLUME) {
+          const void *p = P.em_direct.p;
+          const F3 gs = ld3(P.gstep);
+          const AxisTap xp = axis_tap_x<LAYOUT>((r.pos.x + gs.x - bmin.x) * bscale.x, P.geo.fw, P.geo.ox, fb);
+          const AxisTap xm = axis_tap_x<LAYOUT>((r.pos.x - gs.x - bmin.x) * bscale.x, P.geo.fw, P.geo.ox, fb);
+          g.x = taps_fetch<E>(p, xp, ay, az) - taps_fetch<E>(p, xm, ay, az);
+          const AxisTap yp = axis_tap_y<LAYOUT>((r.pos.y + gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
+          const AxisTap ym = axis_tap_y<LAYOUT>((r.pos.y - gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
+          g.y = taps_fetch<E>(p, ax, yp, az) - taps_fetch<E>(p, ax, ym, az);
+          const AxisTap zp = axis_tap_z<LAYOUT>((r.pos.z + gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
+          const AxisTap zm = axis_tap_z<LAYOUT>((r.pos.z - gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
+          g.z = taps_fetch<E>(p, ax, ay, zp) - taps_fetch<E>(p, ax, ay, zm);
+          g = g * mk3(0.5f, 0.5f, 0.5f);
+        } else {
+          g = mk3(0.0f, 0.0f, 0.0f);  // a constant or unbound tex_emission: equal fetches, (c - c) * 0.5 = 0
+        }
       } else {
         g = mk3(taps_any<E>(P.gx, ax, ay, az), taps_any<E>(P.gy, ax, ay, az), taps_any<E>(P.gz, ax, ay, az));
       }
@@ -405,7 +468,7 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
       // not depend on the light: fetched once
       re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
     }
-    illum = shade_lights<LAYOUT>(P, g, P.fRe * re_raw, r.pos, origin, color);
+    illum = shade_lights<LAYOUT>(P, g, P.fRe * re_raw, r.pos, origin, color, fb);
   }
   const F3 lit = colored + illum;
   const float shx = lit.x * alpha, shy = lit.y * alpha, shz = lit.z * alpha;  // kernel.cu:477-479
@@ -503,6 +566,8 @@ VR_HD bool one_binade(float v0, float v1, float v2) {
   return (e0 == e1 && e1 == e2 && ex != 0u && ex != 0xffu) || (v0 == v1 && v1 == v2);
 }
 // How many more additions of d keep v inside its binade (conservative; v normal, d a multiple of ulp(v)).
+// Jumping straight to the border matters: around 0 the binades are short and every ray through the
+// middle of the volume crosses dozens of them (halving the jump until it fits costs 15 %).
 VR_HD float binade_room(float v, float d) {
   if (d == 0.0f) return 1.0e9f;
   const float a = fabsf(v), lo = u2f(f2u(a) & 0x7f800000u);
@@ -512,18 +577,11 @@ VR_HD float binade_room(float v, float d) {
 }
 
 // the macro cell of the sample at r.pos and the lane's low-tap coordinates there
-struct CellAt {
-  float qx, qy, qz;
-  int cx, cy, cz;
-  uint32_t cell;
-};
 VR_HD CellAt cell_at(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale) {
   CellAt c;
   const F3 ps = (r.pos - bmin) * bscale;
-  c.qx = fminf(fmaxf(ps.x, 0.0f), 1.0f) * P.ab.fw - 0.5f;
-  c.qy = fminf(fmaxf(ps.y, 0.0f), 1.0f) * P.ab.fh - 0.5f;
-  c.qz = fminf(fmaxf(ps.z, 0.0f), 1.0f) * P.ab.fd - 0.5f;
-  int ix = (int)floorf(c.qx), iy = (int)floorf(c.qy), iz = (int)floorf(c.qz);
+  c.ax = axis_coord(ps.x, P.ab.fw), c.ay = axis_coord(ps.y, P.ab.fh), c.az = axis_coord(ps.z, P.ab.fd);
+  int ix = c.ax.i(), iy = c.ay.i(), iz = c.az.i();
   ix = ix < 0 ? 0 : ix, iy = iy < 0 ? 0 : iy, iz = iz < 0 ? 0 : iz;
   c.cx = ix >> CELL_SHIFT, c.cy = iy >> CELL_SHIFT, c.cz = iz >> CELL_SHIFT;
   c.cell = (uint32_t)((c.cz * P.ocy + c.cy) * P.ocx + c.cx);
@@ -535,7 +593,7 @@ VR_HD float steps_to_exit(const CellAt &c, int rad, F3 dq, F3 inv_dq) {
   const float bx = (float)((dq.x >= 0.0f ? c.cx + 1 + rad : c.cx - rad) << CELL_SHIFT);
   const float by = (float)((dq.y >= 0.0f ? c.cy + 1 + rad : c.cy - rad) << CELL_SHIFT);
   const float bz = (float)((dq.z >= 0.0f ? c.cz + 1 + rad : c.cz - rad) << CELL_SHIFT);
-  return fminf(fminf((bx - c.qx) * inv_dq.x, (by - c.qy) * inv_dq.y), (bz - c.qz) * inv_dq.z);
+  return fminf(fminf((bx - c.ax.xb) * inv_dq.x, (by - c.ay.xb) * inv_dq.y), (bz - c.az.xb) * inv_dq.z);
 }
 // one iteration of the reference's loop tail for an empty sample (kernel.cu:488-492)
 VR_HD bool step_empty(const KernelParams &P, Ray &r) {
@@ -559,6 +617,16 @@ VR_HD bool skip_empty_serial(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, 
   }
 }
 
+// the sample at r.pos lies in a cell of the distance grid that is empty (P.skip == 2)
+VR_HD bool on_empty_cell(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale) {
+  const CellAt c = cell_at(P, r, bmin, bscale);
+  return VR_LDG(P.dist + c.cell) != 0;
+}
+
+// (Letting a lane shade the rest of a non-empty cell without coming back to the grid - a "fuel"
+// counter - was tried: it saves the 38-instruction check per sample but lanes then reach the next
+// empty cell out of phase and run the jump below one by one: 27 -> 42 ms.  Checking every sample
+// keeps neighbouring rays in step.)
 VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale) {
   for (;;) {
     const CellAt c = cell_at(P, r, bmin, bscale);
@@ -581,9 +649,9 @@ VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale) {
     // increments it will really take
     const F3 ps = (r.pos - bmin) * bscale;
     CellAt now = c;
-    now.qx = fminf(fmaxf(ps.x, 0.0f), 1.0f) * P.ab.fw - 0.5f;
-    now.qy = fminf(fmaxf(ps.y, 0.0f), 1.0f) * P.ab.fh - 0.5f;
-    now.qz = fminf(fmaxf(ps.z, 0.0f), 1.0f) * P.ab.fd - 0.5f;
+    now.ax.xb = fminf(fmaxf(ps.x, 0.0f), 1.0f) * P.ab.fw - 0.5f;
+    now.ay.xb = fminf(fmaxf(ps.y, 0.0f), 1.0f) * P.ab.fh - 0.5f;
+    now.az.xb = fminf(fmaxf(ps.z, 0.0f), 1.0f) * P.ab.fd - 0.5f;
     const F3 dq = mk3(d.x * bscale.x * P.ab.fw, d.y * bscale.y * P.ab.fh, d.z * bscale.z * P.ab.fd);
     const float big = 3.0e38f;
     const F3 inv_dq = mk3(dq.x != 0.0f ? 1.0f / dq.x : big, dq.y != 0.0f ? 1.0f / dq.y : big, dq.z != 0.0f ? 1.0f / dq.z : big);

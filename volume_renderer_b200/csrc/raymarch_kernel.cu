@@ -10,24 +10,45 @@
 //    terminated (early ray termination or t > tfar);
 //  * volumes are padded (bricked) arrays read through the read-only path; no tensor cores, the
 //    path is gather + fp32 accumulate.
+//
+// This file is compiled twice (Makefile): -DVR_GRAD=1 -> raymarch_lookup.o (lookupGradient kernels),
+// -DVR_GRAD=0 -> raymarch_compute.o (computeGradient kernels).  Two modules keep ptxas' allocation
+// of one family independent of edits to the other and halve the build time.
 #include <cuda_runtime.h>
 
 #include "raymarch_core.h"
 #include "raymarch_launch.h"
 
+#ifndef VR_GRAD
+#error "compile with -DVR_GRAD=0 (computeGradient) or -DVR_GRAD=1 (lookupGradient)"
+#endif
+
 namespace vrb {
 
-#ifndef VR_BLOCK_THREADS
-#define VR_BLOCK_THREADS 256
+// Block shape and register budget per gradient method, measured on B200 (configs[1] / the same with
+// computeGradient; ms per 2048^2 frame): the kernel is bound by instruction issue AND by the latency
+// of its gathers, so resident warps are worth a few spilled registers.
+//   lookupGradient : 256x3 (80 regs) 28.9 | 128x7 (72) 27.2 | 256x4 (64, 72 B spilled) 26.8 | 128x5 (96) 30.8
+//   computeGradient: 256x3 (80 regs) 29.1 | 128x7 (72) 28.0 | 256x4 (64)               29.3 | 128x5 (96) 28.8
+// -DVR_BLOCK_THREADS / -DVR_MIN_BLOCKS override both (A/B builds).
+template <int GRAD>
+struct Tune {
+#if defined(VR_BLOCK_THREADS) && defined(VR_MIN_BLOCKS)
+  static constexpr int threads = VR_BLOCK_THREADS, min_blocks = VR_MIN_BLOCKS;
+#else
+  static constexpr int threads = GRAD ? 256 : 128, min_blocks = GRAD ? 4 : 7;
 #endif
-#ifndef VR_MIN_BLOCKS
-#define VR_MIN_BLOCKS 3
-#endif
-static constexpr int kBlockThreads = VR_BLOCK_THREADS;
+};
 static constexpr unsigned kFull = 0xffffffffu;
+#ifndef VR_JUMP_LANES
+#define VR_JUMP_LANES 24
+#endif
+#ifndef VR_JUMP_WAIT
+#define VR_JUMP_WAIT 64
+#endif
 
 template <int GRAD, int LAYOUT, typename E, int UNI>
-__global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const __grid_constant__ KernelParams P) {
+__global__ void __launch_bounds__(Tune<GRAD>::threads, Tune<GRAD>::min_blocks) k_raymarch(const __grid_constant__ KernelParams P) {
   const int lane = threadIdx.x & 31;
   const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);
@@ -74,9 +95,32 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
     F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
     if (active && P.skip == 1) skip_setup(P, r, bscale, dq, inv_dq);
 
+    int waited = 0;  // warp-uniform: iterations the oldest postponed jump has been waiting
     while (__any_sync(kFull, active)) {
-      if (active && P.skip) active = skip_empty(P, r, bmin, bscale, dq, inv_dq);
-      if (active) {
+      bool ready = active;  // shades a sample in this iteration
+      if (P.skip == 2) {
+        // The jump over empty space is ~290 instructions and is usually wanted by one or two lanes
+        // at a time; neighbouring rays reach the same empty cell within a few samples of each other.
+        // A lane that stands on an empty cell therefore sits out up to VR_JUMP_WAIT iterations (it
+        // costs the warp nothing: the others shade meanwhile) so that the lanes jump TOGETHER.
+        // Measured on configs[1] (ms/frame): no waiting 27.4 | 8 lanes or 4 iterations 26.8 | 16/8 26.6 |
+        // 16/16 26.3 | 24/64 26.0 | 24/256 26.4 | only when every live lane wants to 29.8.
+        const bool want = active && on_empty_cell(P, r, bmin, bscale);
+        const unsigned wm = __ballot_sync(kFull, want);
+        if (wm) {
+          const unsigned am = __ballot_sync(kFull, active);
+          if (__popc(wm) >= VR_JUMP_LANES || wm == am || waited >= VR_JUMP_WAIT) {
+            if (want) ready = active = skip_empty_jump(P, r, bmin, bscale);
+            waited = 0;
+          } else {
+            ++waited;
+            if (want) ready = false;
+          }
+        }
+      } else if (P.skip == 1) {
+        if (active) ready = active = skip_empty_serial(P, r, bmin, bscale, dq, inv_dq);
+      }
+      if (ready) {
         shade_sample<GRAD, LAYOUT, E, UNI>(P, origin, r);
         active = ray_advance(P, r);
       }
@@ -127,6 +171,7 @@ __global__ void __launch_bounds__(kBlockThreads, VR_MIN_BLOCKS) k_raymarch(const
 
 template <int GRAD, int LAYOUT, typename E, int UNI>
 static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
+  constexpr int kBlockThreads = Tune<GRAD>::threads;
   int per_sm = 0;
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E, UNI>, kBlockThreads, 0);
   if (e != cudaSuccess) return e;
@@ -142,12 +187,14 @@ static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm
 
 template <int LAYOUT, typename E>
 static cudaError_t launch_le(const KernelParams &P, cudaStream_t stream, int sm_count) {
-  if (P.gradient_method) return P.uniform ? launch_one<1, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<1, LAYOUT, E, 0>(P, stream, sm_count);
-  return P.uniform ? launch_one<0, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<0, LAYOUT, E, 0>(P, stream, sm_count);
+  return P.uniform ? launch_one<VR_GRAD, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<VR_GRAD, LAYOUT, E, 0>(P, stream, sm_count);
 }
 
-cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, int variant, cudaStream_t stream, int sm_count) {
-  (void)variant;
+#if VR_GRAD
+cudaError_t launch_raymarch_lookup(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
+#else
+cudaError_t launch_raymarch_compute(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
+#endif
   if (dtype == 0) return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemF32>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemF32>(P, stream, sm_count);
   return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemBF16>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemBF16>(P, stream, sm_count);
 }

@@ -11,8 +11,12 @@ namespace vrb {
 
 // raymarch_kernel.cu: the ray march.  layout / dtype describe the volume textures of the launch
 // (all volume slots of one launch share them; the LUT is always fp32 linear).
-cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, int variant, cudaStream_t stream,
-                            int sm_count);
+// One module per gradient method (volumeRender.h:141-144).
+cudaError_t launch_raymarch_lookup(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count);
+cudaError_t launch_raymarch_compute(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count);
+inline cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
+  return P.gradient_method ? launch_raymarch_lookup(P, layout, dtype, stream, sm_count) : launch_raymarch_compute(P, layout, dtype, stream, sm_count);
+}
 
 // resident_kernels.cu: everything that builds the resident representation of a volume.
 struct RepackArgs {
