@@ -53,6 +53,7 @@ def parse():
     p.add_argument("--tile", type=int, default=64)
     p.add_argument("--batch", type=int, default=16, help="frames per launch (one work queue per batch; clipped to --steps)")
     p.add_argument("--wshape", type=int, default=3, help="warp footprint (1<<s) x (32>>s) pixels")
+    p.add_argument("--interleave", type=int, default=1, help="1: Gx,Gy,Gz resident as one interleaved storage (default); 0: three volumes")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
                    help="image = tiles over replicated volumes (the metric's config); volume = bricks sharded over the ranks, sort-last composite (config 5)")
@@ -307,6 +308,7 @@ def run_b200(args):
     multigpu.configure_partition(ctx, rank, world, args.tile, args.tile)
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_TILE_ORDER, args.order), ctx)
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_WARP_SHAPE, args.wshape), ctx)
+    lib.vr_set_option(ctx, _abi.OPT_GRADIENT_INTERLEAVE, args.interleave)  # unchecked: older A/B builds lack the option
     scene = Scene(args)
     n = args.size
     dt = _abi.DTYPE_F32 if args.dtype == "f32" else _abi.DTYPE_BF16

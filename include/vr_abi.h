@@ -195,7 +195,10 @@ typedef enum vr_option {
   VR_OPT_TILE_ORDER = 11,       /* hand-out order of tiles: 1 (default) = most expensive first (measured on the previous launch,
                                    else centre-first), one list over all frames of a batch; 2 = the same, frame after
                                    frame; 0 = raster order */
-  VR_OPT_WARP_SHAPE = 12        /* s in [0,5]: one warp marches a (1<<s) x (32>>s) pixel footprint; default 3 = 8 x 4 */
+  VR_OPT_WARP_SHAPE = 12,       /* s in [0,5]: one warp marches a (1<<s) x (32>>s) pixel footprint; default 3 = 8 x 4 */
+  VR_OPT_GRADIENT_INTERLEAVE = 13 /* 1 (default): the three gradient volumes of lookupGradient are stored interleaved
+                                     (16-byte voxels Gx,Gy,Gz,-; one load per tap); 0: three separate volumes.  Takes
+                                     effect at the next upload of the gradient volumes; pixels are bit-identical */
 } vr_option;
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);

@@ -37,6 +37,7 @@ OPT_COUNT_SAMPLES = 9
 OPT_CLEAR_IMAGE = 10
 OPT_TILE_ORDER = 11
 OPT_WARP_SHAPE = 12
+OPT_GRADIENT_INTERLEAVE = 13
 IPC_HANDLE_BYTES = 64
 
 

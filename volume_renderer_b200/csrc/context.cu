@@ -80,6 +80,20 @@ struct Resident {
   int kind = TEX_UNBOUND;
   float cval = 0.0f;
   HostVol src;  // what was uploaded (identity: pointer, timestamp, bytes)
+  // a gradient volume that lives as component `ecomp` of the context's interleaved gradient storage
+  // (`storage` then points at vr_ctx::g4 and is not owned)
+  bool shared = false;
+  int estride = 1, ecomp = 0;
+};
+
+// geometry of the interleaved gradient storage: a gradient volume joins it when it matches
+struct G4Geo {
+  int w = 0, h = 0, d = 0, lw = 0, lh = 0, ld = 0, ox = 0, oy = 0, oz = 0, dtype = 0, layout = 0;
+  uint32_t sy = 0, sz = 0;
+  bool operator==(const G4Geo &o) const {
+    return w == o.w && h == o.h && d == o.d && lw == o.lw && lh == o.lh && ld == o.ld && ox == o.ox && oy == o.oy && oz == o.oz &&
+           dtype == o.dtype && layout == o.layout && sy == o.sy && sz == o.sz;
+  }
 };
 
 }  // namespace
@@ -99,6 +113,12 @@ struct vr_ctx {
   Resident tex[S_N];
   int idxEm = S_EM, idxAb = S_EM /* sic: kernel.cu:80 initialises d_idxAbsorption to emission */, idxRe = S_RE;
   int gradientMethod = 0;
+  // Gx, Gy, Gz interleaved as 4-element voxels (vr_types.h: TexDesc::estride): allocated by the first
+  // gradient volume uploaded, freed when the last one using it is released
+  void *g4 = nullptr;
+  size_t g4_bytes = 0;
+  int g4_users = 0;
+  G4Geo g4geo;
   std::vector<vr_light> lights;  // positions already axis-reversed (render.cpp:167)
   float *d_lights_more = nullptr;
   size_t lights_more_cap = 0;
@@ -171,17 +191,23 @@ bool live(const vr_ctx *c) {
   if (!live(c)) return fail(nullptr, VR_ERR_INVALID_HANDLE, "Handle not valid.")
 
 void release(vr_ctx *c, Resident &r) {
-  if (r.storage) cudaFree(r.storage);
+  if (r.shared) {
+    if (--c->g4_users == 0) {
+      cudaFree(c->g4);
+      c->g4 = nullptr, c->g4_bytes = 0;
+    }
+  } else if (r.storage) {
+    cudaFree(r.storage);
+  }
   if (r.occ) cudaFree(r.occ);
   if (r.dist) cudaFree(r.dist);
   r = Resident();
-  (void)c;
 }
 
 uint64_t resident_bytes(const vr_ctx *c) {
   uint64_t b = 0;
   for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes + c->tex[i].dist_bytes;
-  b += c->image_cap + c->stage_cap + c->lights_more_cap;
+  b += c->image_cap + c->stage_cap + c->lights_more_cap + c->g4_bytes;
   return b;
 }
 
@@ -271,14 +297,35 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
                 "insufficient free VRAM!\n\tTotal Memory (MB): \t%zu\n\tFree Memory (MB): \t%zu\n\tRequired memory (MB): \t%zu\n",
                 total_b >> 20, free_b >> 20, (size_t)(elems * es) >> 20);
   }
-  VR_CUDA(c, cudaMalloc(&r.storage, elems * es));
-  r.storage_bytes = elems * es;
   r.w = (int)v.w, r.h = (int)v.h, r.d = (int)v.d;
   r.ox = (int)(1 + g0[0]), r.oy = (int)(1 + g0[1]), r.oz = (int)(1 + g0[2]);
   r.lw = (int)pw, r.lh = (int)ph, r.ld = (int)pd;
   r.dtype = v.dtype;
   r.layout = layout;
   r.sy = sy, r.sz = sz;
+  if (slot >= S_DX && slot <= S_DZ && c->opt[VR_OPT_GRADIENT_INTERLEAVE] && elems <= 0xffffffffull) {
+    // lookupGradient reads the three gradient volumes at the same taps: they share one storage of
+    // 4-element voxels, this volume is component slot - S_DX of it
+    G4Geo geo;
+    geo.w = r.w, geo.h = r.h, geo.d = r.d, geo.lw = r.lw, geo.lh = r.lh, geo.ld = r.ld, geo.ox = r.ox, geo.oy = r.oy, geo.oz = r.oz;
+    geo.dtype = r.dtype, geo.layout = r.layout, geo.sy = sy, geo.sz = sz;
+    if (!c->g4 && free_b >= elems * es * 4) {
+      VR_CUDA(c, cudaMalloc(&c->g4, elems * es * 4));
+      VR_CUDA(c, cudaMemsetAsync(c->g4, 0, elems * es * 4, c->stream));
+      c->g4_bytes = elems * es * 4;
+      c->g4geo = geo;
+    }
+    if (c->g4 && c->g4geo == geo) {
+      r.storage = c->g4;
+      r.shared = true;
+      r.estride = 4, r.ecomp = slot - S_DX;
+      c->g4_users++;
+    }
+  }
+  if (!r.shared) {
+    VR_CUDA(c, cudaMalloc(&r.storage, elems * es));
+    r.storage_bytes = elems * es;
+  }
 
   RepackArgs a;
   a.dst = r.storage;
@@ -287,6 +334,7 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
   a.gx0 = (int)g0[0], a.gy0 = (int)g0[1], a.gz0 = (int)g0[2];
   a.sx0 = 0, a.sy0 = 0, a.sw = r.w, a.sh = r.h;
   a.sy = sy, a.sz = sz;
+  a.estride = r.estride, a.ecomp = r.ecomp;
   a.layout = layout;
   a.src_dtype = a.dst_dtype = v.dtype;
   auto clampz = [&](int64_t z) { return z < 0 ? 0 : (z > dims[2] - 1 ? dims[2] - 1 : z); };
@@ -365,11 +413,13 @@ vr_status syncVolume(vr_ctx *c, int slot, const HostVol &v) { return upload(c, s
 // 'sync_volumes' (syncVolume frees and re-creates whatever its flag says, kernel.cu:659-672 +
 // :522-541).  The data does not change between those calls unless the volume was stamped, so
 // the copy is elided when the slot already holds exactly this (pointer, timestamp, size).
-vr_status syncVolumeCached(vr_ctx *c, int slot, const HostVol &v) {
+bool slot_is_current(const vr_ctx *c, int slot, const HostVol &v) {
   const Resident &r = c->tex[slot];
-  if (c->arr[slot] && r.kind != TEX_UNBOUND && same(r.src, v) && r.src.w == v.w && r.src.h == v.h && r.src.d == v.d &&
-      r.src.dtype == v.dtype && v.last_update != 0)
-    return VR_OK;
+  return c->arr[slot] && r.kind != TEX_UNBOUND && same(r.src, v) && r.src.w == v.w && r.src.h == v.h && r.src.d == v.d &&
+         r.src.dtype == v.dtype && v.last_update != 0;
+}
+vr_status syncVolumeCached(vr_ctx *c, int slot, const HostVol &v) {
+  if (slot_is_current(c, slot, v)) return VR_OK;
   return upload(c, slot, v);
 }
 
@@ -442,6 +492,10 @@ vr_status mm_sync(vr_ctx *c) {
   VR_TRY(syncWithDevice(c));
   if (c->host[S_DX].last_update != 0 && c->host[S_DY].last_update != 0 && c->host[S_DZ].last_update != 0) {
     // setGradientTextures (kernel.cu:703-722)
+    if (!slot_is_current(c, S_DX, c->host[S_DX]) && !slot_is_current(c, S_DY, c->host[S_DY]) && !slot_is_current(c, S_DZ, c->host[S_DZ])) {
+      // all three are replaced: drop them together so that the interleaved storage is re-made for the new geometry
+      for (int s = S_DX; s <= S_DZ; ++s) release(c, c->tex[s]);
+    }
     VR_TRY(syncVolumeCached(c, S_DX, c->host[S_DX]));
     VR_TRY(syncVolumeCached(c, S_DY, c->host[S_DY]));
     VR_TRY(syncVolumeCached(c, S_DZ, c->host[S_DZ]));
@@ -480,6 +534,7 @@ TexDesc describe(const Resident &r) {
   t.cval = r.cval;
   t.ox = r.ox, t.oy = r.oy, t.oz = r.oz;
   t.lw = r.lw, t.lh = r.lh, t.ld = r.ld;
+  t.estride = r.estride, t.ecomp = r.ecomp;
   return t;
 }
 
@@ -603,7 +658,23 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
         t->oy != P.geo.oy || t->oz != P.geo.oz)
       P.uniform = 0;
   }
+  // the gradient trio is either three components of the interleaved storage or three plain volumes;
+  // a mix (geometries differed at upload time) goes through the per-texture path
+  const Resident &rx = c->tex[S_DX], &ry = c->tex[S_DY], &rz = c->tex[S_DZ];
+  P.grad4 = rx.kind == TEX_VOLUME && ry.kind == TEX_VOLUME && rz.kind == TEX_VOLUME && rx.shared && ry.shared && rz.shared;
+  if (!P.grad4 && (rx.shared || ry.shared || rz.shared)) P.uniform = 0;
   if (c->opt[VR_OPT_KERNEL_VARIANT] == 1) P.uniform = 0;  // variant 1: per-texture addressing everywhere (A/B measurements)
+  // a resident volume of more than 2^32 elements needs the kernels with 64-bit z terms
+  bool wide = false;
+  for (int s : used) {
+    const Resident &r = c->tex[s];
+    if (r.kind == TEX_VOLUME && (uint64_t)r.sz * (uint64_t)(r.layout == LAYOUT_BRICK ? (r.ld + 7) / 8 : r.ld) > 0xffffffffull) wide = true;
+  }
+  if (wide) {
+    if (!P.uniform || layout != LAYOUT_BRICK || P.frac_bits)
+      return fail(c, VR_ERR_UNSUPPORTED, "volumes of more than 2^32 resident elements need the bricked layout, one common geometry and fp32 weights");
+    P.uniform = 2;
+  }
   if (P.frac_bits) P.uniform = 0;  // fixed-point weights (A/B option) are compiled into the per-texture kernels only
 
   // volume-space mode
@@ -829,6 +900,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   memset(c->opt, 0, sizeof c->opt);
   c->opt[VR_OPT_EMPTY_SPACE_SKIP] = 2;
   c->opt[VR_OPT_PART_NRANKS] = 1;
+  c->opt[VR_OPT_GRADIENT_INTERLEAVE] = 1;
   c->opt[VR_OPT_TILE_W] = 64;
   c->opt[VR_OPT_TILE_H] = 64;
   c->opt[VR_OPT_BRICK_LAYOUT] = 1;
@@ -917,6 +989,7 @@ vr_status vr_mem_info(vr_ctx *c, char *buf, size_t cap, size_t *needed) {
   const char *names[S_N] = {"Emission", "Absorption", "Reflection", "dX", "dY", "dZ", "light"};
   for (int i = 0; i < S_N; ++i)
     add("\t\t%s (MB): %g ptr: %p resident (MB): %g\n", names[i], c->host[i].bytes / MB, c->tex[i].storage, c->tex[i].storage_bytes / MB);
+  if (c->g4) add("\t\tdX,dY,dZ interleaved (MB): %g ptr: %p users: %d\n", c->g4_bytes / MB, c->g4, c->g4_users);
   add("\t\trole -> texture: Em->%s Ab->%s Re->%s, gradient method: %s\n", names[c->idxEm], names[c->idxAb], names[c->idxRe],
       c->gradientMethod ? "lookup" : "compute");
   add("\n\t\tSimilarity of Volumes\n\t\t---------------------\n\t\t\tEm\tAb\tRe\n\t\tEm\t1\t\n\t\tAb\t%d\t1\n\t\tRe\t%d\t%d\t1\n\n",
@@ -1147,14 +1220,14 @@ int vr_abi_version(void) { return VR_ABI_VERSION; }
 
 vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_WARP_SHAPE) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_GRADIENT_INTERLEAVE) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
   c->opt[option] = value;
   return VR_OK;
 }
 vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_WARP_SHAPE || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_GRADIENT_INTERLEAVE || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   *value = c->opt[option];
   return VR_OK;
 }

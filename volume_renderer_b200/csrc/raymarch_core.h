@@ -59,6 +59,16 @@ VR_HD F3 ld3(const float *p) { return mk3(p[0], p[1], p[2]); }
 struct ElemF32 {
   typedef float T;
   static VR_HD float load(const void *p, uint32_t off) { return VR_LDG(static_cast<const float *>(p) + off); }
+  // voxel `off` of a 4-element interleaved storage: one 16-byte load
+  static VR_HD void load3(const void *p, uint32_t off, float &a, float &b, float &c) {
+#if defined(__CUDA_ARCH__)
+    const float4 v = __ldg(static_cast<const float4 *>(p) + off);
+    a = v.x, b = v.y, c = v.z;
+#else
+    const float *q = static_cast<const float *>(p) + 4 * (size_t)off;
+    a = q[0], b = q[1], c = q[2];
+#endif
+  }
 };
 struct ElemBF16 {
   typedef uint16_t T;
@@ -72,6 +82,14 @@ struct ElemBF16 {
     return f;
 #endif
   }
+  static VR_HD void load3(const void *p, uint32_t off, float &a, float &b, float &c) {  // one 8-byte load
+#if defined(__CUDA_ARCH__)
+    const uint2 v = __ldg(static_cast<const uint2 *>(p) + off);
+    a = __uint_as_float(v.x << 16), b = __uint_as_float(v.x & 0xffff0000u), c = __uint_as_float(v.y << 16);
+#else
+    a = load(p, 4 * off), b = load(p, 4 * off + 1), c = load(p, 4 * off + 2);
+#endif
+  }
 };
 
 // ---- addressing of the padded storage --------------------------------------------------
@@ -81,13 +99,13 @@ template <>
 struct Addr<LAYOUT_LINEAR> {
   static VR_HD uint32_t x(int X) { return (uint32_t)X; }
   static VR_HD uint32_t y(int Y, uint32_t sy) { return (uint32_t)Y * sy; }
-  static VR_HD uint32_t z(int Z, uint32_t sz) { return (uint32_t)Z * sz; }
+  static VR_HD size_t z(int Z, uint32_t sz) { return (size_t)(uint32_t)Z * sz; }  // the z term alone may pass 2^32 elements
 };
 template <>
 struct Addr<LAYOUT_BRICK> {
   static VR_HD uint32_t x(int X) { return (((uint32_t)X >> BRICK_SHIFT) << 9) + ((uint32_t)X & BRICK_MASK); }
   static VR_HD uint32_t y(int Y, uint32_t sy) { return ((uint32_t)Y >> BRICK_SHIFT) * sy + (((uint32_t)Y & BRICK_MASK) << 3); }
-  static VR_HD uint32_t z(int Z, uint32_t sz) { return ((uint32_t)Z >> BRICK_SHIFT) * sz + (((uint32_t)Z & BRICK_MASK) << 6); }
+  static VR_HD size_t z(int Z, uint32_t sz) { return (size_t)((uint32_t)Z >> BRICK_SHIFT) * sz + (((uint32_t)Z & BRICK_MASK) << 6); }
 };
 
 // One axis of a normalized-coordinate linear-filter fetch (CUDA Programming Guide, "Linear
@@ -155,14 +173,23 @@ VR_HD float tex3d_volume(const TexDesc &t, float x, float y, float z, int frac_b
   axis_setup(z, t.fd, frac_bits, Z, fz);
   X -= t.ox, Y -= t.oy, Z -= t.oz;  // global padded index -> local storage (0 for a whole volume)
   typedef Addr<LAYOUT> A;
+  typedef typename E::T T;
   const uint32_t x0 = A::x(X), x1 = A::x(X + 1);
   const uint32_t y0 = A::y(Y, t.sy), y1 = A::y(Y + 1, t.sy);
-  const uint32_t z0 = A::z(Z, t.sz), z1 = A::z(Z + 1, t.sz);
-  const uint32_t b00 = y0 + z0, b10 = y1 + z0, b01 = y0 + z1, b11 = y1 + z1;
-  const float c000 = E::load(t.p, b00 + x0), c100 = E::load(t.p, b00 + x1);
-  const float c010 = E::load(t.p, b10 + x0), c110 = E::load(t.p, b10 + x1);
-  const float c001 = E::load(t.p, b01 + x0), c101 = E::load(t.p, b01 + x1);
-  const float c011 = E::load(t.p, b11 + x0), c111 = E::load(t.p, b11 + x1);
+  // offsets inside one z layer fit 32 bits (checked at upload); the layer itself is a 64-bit term
+  const size_t z0 = A::z(Z, t.sz), z1 = A::z(Z + 1, t.sz);
+  const uint32_t o[4] = {y0 + x0, y0 + x1, y1 + x0, y1 + x1};
+  float c[8];
+  if (t.estride > 1) {  // a component of the interleaved gradient storage
+    const T *q = static_cast<const T *>(t.p) + t.ecomp;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c[i] = E::load(q + ((i < 4 ? z0 : z1) + o[i & 3]) * (size_t)t.estride, 0u);
+  } else {
+    const T *q0 = static_cast<const T *>(t.p) + z0, *q1 = static_cast<const T *>(t.p) + z1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c[i] = E::load(i < 4 ? q0 : q1, o[i & 3]);
+  }
+  const float c000 = c[0], c100 = c[1], c010 = c[2], c110 = c[3], c001 = c[4], c101 = c[5], c011 = c[6], c111 = c[7];
   const float c00 = lerpf(c000, c100, fx), c10 = lerpf(c010, c110, fx);
   const float c01 = lerpf(c001, c101, fx), c11 = lerpf(c011, c111, fx);
   return lerpf(lerpf(c00, c10, fy), lerpf(c01, c11, fy), fz);
@@ -181,8 +208,15 @@ VR_HD float tex3d_any(const TexDesc &t, float x, float y, float z, int frac_bits
 // weights of a sample position are computed ONCE and reused for every volume fetched there:
 // the arithmetic per fetch is exactly tex3d_volume's, only the common subexpressions are shared.
 struct AxisTap {
-  uint32_t o0, o1;  // storage offsets contributed by the two taps of this axis
+  uint32_t o0, o1;  // storage offsets contributed by the two taps of this axis (x, y: inside one z layer)
   float f;          // weight of the high tap
+};
+// The z term is the one that can pass 2^32 elements (a resident volume beyond 1625^3 voxels): ZT is
+// uint32_t in the regular kernels and size_t in the WIDE ones, which cost two more registers per lane.
+template <typename ZT>
+struct AxisTapZ {
+  ZT o0, o1;
+  float f;
 };
 template <int LAYOUT>
 VR_HD AxisTap axis_tap_x(float x, float fN, int off, int fb) {
@@ -202,40 +236,75 @@ VR_HD AxisTap axis_tap_y(float y, float fN, uint32_t sy, int off, int fb) {
   a.o0 = Addr<LAYOUT>::y(Y, sy), a.o1 = Addr<LAYOUT>::y(Y + 1, sy);
   return a;
 }
-template <int LAYOUT>
-VR_HD AxisTap axis_tap_z(float z, float fN, uint32_t sz, int off, int fb) {
+// UNI (template parameter of the kernels): 0 = per-texture addressing, 1 = shared tap sets,
+// 2 = shared tap sets with 64-bit z terms (a resident volume of more than 2^32 elements)
+template <int UNI>
+struct ZSel {
+  typedef uint32_t type;
+};
+template <>
+struct ZSel<2> {
+  typedef size_t type;
+};
+template <int LAYOUT, typename ZT>
+VR_HD AxisTapZ<ZT> axis_tap_z(float z, float fN, uint32_t sz, int off, int fb) {
   int Z;
-  AxisTap a;
+  AxisTapZ<ZT> a;
   axis_setup(z, fN, fb, Z, a.f);
   Z -= off;
-  a.o0 = Addr<LAYOUT>::z(Z, sz), a.o1 = Addr<LAYOUT>::z(Z + 1, sz);
+  a.o0 = (ZT)Addr<LAYOUT>::z(Z, sz), a.o1 = (ZT)Addr<LAYOUT>::z(Z + 1, sz);
   return a;
 }
-template <int LAYOUT>
+template <int LAYOUT, typename ZT>
 VR_HD void axis_taps_from(const TexDesc &g, const AxisCoord &cx, const AxisCoord &cy, const AxisCoord &cz, int fb, AxisTap &ax, AxisTap &ay,
-                          AxisTap &az) {
+                          AxisTapZ<ZT> &az) {
   int X, Y, Z;
   axis_finish(cx, fb, X, ax.f), axis_finish(cy, fb, Y, ay.f), axis_finish(cz, fb, Z, az.f);
   X -= g.ox, Y -= g.oy, Z -= g.oz;
   ax.o0 = Addr<LAYOUT>::x(X), ax.o1 = Addr<LAYOUT>::x(X + 1);
   ay.o0 = Addr<LAYOUT>::y(Y, g.sy), ay.o1 = Addr<LAYOUT>::y(Y + 1, g.sy);
-  az.o0 = Addr<LAYOUT>::z(Z, g.sz), az.o1 = Addr<LAYOUT>::z(Z + 1, g.sz);
+  az.o0 = (ZT)Addr<LAYOUT>::z(Z, g.sz), az.o1 = (ZT)Addr<LAYOUT>::z(Z + 1, g.sz);
 }
-template <typename E>
-VR_HD float taps_fetch(const void *p, const AxisTap &ax, const AxisTap &ay, const AxisTap &az) {
-  // three-operand sums: one IADD3 per tap
-  const float c000 = E::load(p, ax.o0 + ay.o0 + az.o0), c100 = E::load(p, ax.o1 + ay.o0 + az.o0);
-  const float c010 = E::load(p, ax.o0 + ay.o1 + az.o0), c110 = E::load(p, ax.o1 + ay.o1 + az.o0);
-  const float c001 = E::load(p, ax.o0 + ay.o0 + az.o1), c101 = E::load(p, ax.o1 + ay.o0 + az.o1);
-  const float c011 = E::load(p, ax.o0 + ay.o1 + az.o1), c111 = E::load(p, ax.o1 + ay.o1 + az.o1);
+template <typename E, typename ZT>
+VR_HD float taps_fetch(const void *p, const AxisTap &ax, const AxisTap &ay, const AxisTapZ<ZT> &az) {
+  typedef typename E::T T;
+  const T *p0 = static_cast<const T *>(p) + az.o0, *p1 = static_cast<const T *>(p) + az.o1;
+  const uint32_t o00 = ax.o0 + ay.o0, o10 = ax.o1 + ay.o0, o01 = ax.o0 + ay.o1, o11 = ax.o1 + ay.o1;  // shared by every fetch of a tap set
+  const float c000 = E::load(p0, o00), c100 = E::load(p0, o10);
+  const float c010 = E::load(p0, o01), c110 = E::load(p0, o11);
+  const float c001 = E::load(p1, o00), c101 = E::load(p1, o10);
+  const float c011 = E::load(p1, o01), c111 = E::load(p1, o11);
   const float c00 = lerpf(c000, c100, ax.f), c10 = lerpf(c010, c110, ax.f);
   const float c01 = lerpf(c001, c101, ax.f), c11 = lerpf(c011, c111, ax.f);
   return lerpf(lerpf(c00, c10, ay.f), lerpf(c01, c11, ay.f), az.f);
 }
+// Gx, Gy, Gz of the interleaved gradient storage through one tap set: eight 16-byte loads, then the
+// seven lerps of taps_fetch per channel (same operations on the same values as three taps_fetch).
+template <typename E, typename ZT>
+VR_HD F3 taps_fetch3(const void *p, const AxisTap &ax, const AxisTap &ay, const AxisTapZ<ZT> &az) {
+  typedef typename E::T T;
+  const T *p0 = static_cast<const T *>(p) + 4 * (size_t)az.o0, *p1 = static_cast<const T *>(p) + 4 * (size_t)az.o1;
+  const uint32_t o00 = ax.o0 + ay.o0, o10 = ax.o1 + ay.o0, o01 = ax.o0 + ay.o1, o11 = ax.o1 + ay.o1;
+  // row by row (two 16-byte loads, three x-lerps) to keep few values live: r[row] = x-interpolated (Gx, Gy, Gz)
+  F3 r[4];
+#pragma unroll
+  for (int row = 0; row < 4; ++row) {
+    const T *q = row < 2 ? p0 : p1;
+    const uint32_t lo = (row & 1) ? o01 : o00, hi = (row & 1) ? o11 : o10;
+    float a0, b0, c0, a1, b1, c1;
+    E::load3(q, lo, a0, b0, c0), E::load3(q, hi, a1, b1, c1);
+    r[row] = mk3(lerpf(a0, a1, ax.f), lerpf(b0, b1, ax.f), lerpf(c0, c1, ax.f));
+  }
+  F3 g;
+  g.x = lerpf(lerpf(r[0].x, r[1].x, ay.f), lerpf(r[2].x, r[3].x, ay.f), az.f);
+  g.y = lerpf(lerpf(r[0].y, r[1].y, ay.f), lerpf(r[2].y, r[3].y, ay.f), az.f);
+  g.z = lerpf(lerpf(r[0].z, r[1].z, ay.f), lerpf(r[2].z, r[3].z, ay.f), az.f);
+  return g;
+}
 // any slot through a shared tap set (the slot is a volume of the common geometry, a constant,
 // or unbound)
-template <typename E>
-VR_HD float taps_any(const TexDesc &t, const AxisTap &ax, const AxisTap &ay, const AxisTap &az) {
+template <typename E, typename ZT>
+VR_HD float taps_any(const TexDesc &t, const AxisTap &ax, const AxisTap &ay, const AxisTapZ<ZT> &az) {
   if (t.kind == TEX_VOLUME) return taps_fetch<E>(t.p, ax, ay, az);
   return t.kind == TEX_CONST ? t.cval : 0.0f;
 }
@@ -391,7 +460,9 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
     r.n_marched++;  // a sample of the global lattice that another brick owns
     return;
   }
-  AxisTap ax, ay, az;
+  typedef typename ZSel<UNI>::type ZT;
+  AxisTap ax, ay;
+  AxisTapZ<ZT> az;
   float em_raw, ab_raw;
   if (UNI) {
     // (handing the skip phase's x*N - 0.5 and floors of this position over instead of computing
@@ -435,15 +506,16 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
           const AxisTap yp = axis_tap_y<LAYOUT>((r.pos.y + gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
           const AxisTap ym = axis_tap_y<LAYOUT>((r.pos.y - gs.y - bmin.y) * bscale.y, P.geo.fh, P.geo.sy, P.geo.oy, fb);
           g.y = taps_fetch<E>(p, ax, yp, az) - taps_fetch<E>(p, ax, ym, az);
-          const AxisTap zp = axis_tap_z<LAYOUT>((r.pos.z + gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
-          const AxisTap zm = axis_tap_z<LAYOUT>((r.pos.z - gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
+          const AxisTapZ<ZT> zp = axis_tap_z<LAYOUT, ZT>((r.pos.z + gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
+          const AxisTapZ<ZT> zm = axis_tap_z<LAYOUT, ZT>((r.pos.z - gs.z - bmin.z) * bscale.z, P.geo.fd, P.geo.sz, P.geo.oz, fb);
           g.z = taps_fetch<E>(p, ax, ay, zp) - taps_fetch<E>(p, ax, ay, zm);
           g = g * mk3(0.5f, 0.5f, 0.5f);
         } else {
           g = mk3(0.0f, 0.0f, 0.0f);  // a constant or unbound tex_emission: equal fetches, (c - c) * 0.5 = 0
         }
       } else {
-        g = mk3(taps_any<E>(P.gx, ax, ay, az), taps_any<E>(P.gy, ax, ay, az), taps_any<E>(P.gz, ax, ay, az));
+        if (P.grad4) g = taps_fetch3<E>(P.gx.p, ax, ay, az);
+        else g = mk3(taps_any<E>(P.gx, ax, ay, az), taps_any<E>(P.gy, ax, ay, az), taps_any<E>(P.gz, ax, ay, az));
       }
       re_raw = P.re_is_em ? em_raw : taps_any<E>(P.re, ax, ay, az);
     } else {

@@ -25,18 +25,18 @@
 
 namespace vrb {
 
-// Block shape and register budget per gradient method, measured on B200 (configs[1] / the same with
-// computeGradient; ms per 2048^2 frame): the kernel is bound by instruction issue AND by the latency
-// of its gathers, so resident warps are worth a few spilled registers.
-//   lookupGradient : 256x3 (80 regs) 28.9 | 128x7 (72) 27.2 | 256x4 (64, 72 B spilled) 26.8 | 128x5 (96) 30.8
-//   computeGradient: 256x3 (80 regs) 29.1 | 128x7 (72) 28.0 | 256x4 (64)               29.3 | 128x5 (96) 28.8
+// Block shape and register budget, measured on B200 (configs[1] / the same with computeGradient; ms per
+// 2048^2 frame): the kernel is bound by instruction issue AND by the latency of its gathers, so
+// resident warps are worth a few spilled registers.
+//   lookupGradient, interleaved Gx,Gy,Gz: 256x3 (80 regs) 25.1 | 128x7 (72) 24.5 | 256x4 (64) 25.1
+//   computeGradient                     : 256x3 (80 regs) 27.8 | 128x7 (72) 27.5 | 256x4 (64) 29.3 | 128x5 (96) 28.8
 // -DVR_BLOCK_THREADS / -DVR_MIN_BLOCKS override both (A/B builds).
 template <int GRAD>
 struct Tune {
 #if defined(VR_BLOCK_THREADS) && defined(VR_MIN_BLOCKS)
   static constexpr int threads = VR_BLOCK_THREADS, min_blocks = VR_MIN_BLOCKS;
 #else
-  static constexpr int threads = GRAD ? 256 : 128, min_blocks = GRAD ? 4 : 7;
+  static constexpr int threads = 128, min_blocks = 7;
 #endif
 };
 static constexpr unsigned kFull = 0xffffffffu;
@@ -187,6 +187,10 @@ static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm
 
 template <int LAYOUT, typename E>
 static cudaError_t launch_le(const KernelParams &P, cudaStream_t stream, int sm_count) {
+  if (P.uniform == 2) {  // 64-bit z terms: bricked layout only (context.cu refuses the other combinations)
+    if (LAYOUT == LAYOUT_BRICK) return launch_one<VR_GRAD, LAYOUT_BRICK, E, 2>(P, stream, sm_count);
+    return cudaErrorInvalidValue;
+  }
   return P.uniform ? launch_one<VR_GRAD, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<VR_GRAD, LAYOUT, E, 0>(P, stream, sm_count);
 }
 

@@ -30,6 +30,7 @@ struct RepackArgs {
   int src_z0;          // global z index of the first staged slice
   uint64_t o0, o1;     // destination element range [o0, o1) to produce
   uint32_t sy, sz;     // destination strides (see TexDesc)
+  int estride, ecomp;  // destination element o is written to dst[o * estride + ecomp] (1, 0 unless interleaved)
   int layout;          // LAYOUT_*
   int src_dtype;       // vr_dtype of src
   int dst_dtype;       // vr_dtype of dst

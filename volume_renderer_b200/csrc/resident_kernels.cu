@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256) k_repack(const RepackArgs a) {
       const int sz = min(max(Z + a.gz0, 0), a.d - 1);
       v = load_src(a.src, ((size_t)(sz - a.src_z0) * a.sh + (sy - a.sy0)) * a.sw + (sx - a.sx0), a.src_dtype);
     }
-    store_dst(a.dst, o, a.dst_dtype, v);
+    store_dst(a.dst, o * (uint64_t)a.estride + (uint64_t)a.ecomp, a.dst_dtype, v);
   }
 }
 
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(256) k_occupancy(const TexDesc t, uint32_t *oc
       const int dx = i % span, dy = (i / span) % span, dz = i / (span * span);
       const int X = min(max(x0 + dx, 0), pw - 1), Y = min(max(y0 + dy, 0), ph - 1), Z = min(max(z0 + dz, 0), pd - 1);
       typedef Addr<LAYOUT> A;
-      const float v = E::load(t.p, A::x(X) + A::y(Y, t.sy) + A::z(Z, t.sz));
+      const float v = E::load(static_cast<const typename E::T *>(t.p) + A::z(Z, t.sz), A::x(X) + A::y(Y, t.sy));
       any = !(v == 0.0f);  // NaN counts as occupied
     }
     if (__any_sync(0xffffffffu, any) && lane == 0) atomicOr(occ + (cell >> 5), 1u << (cell & 31));

@@ -46,6 +46,10 @@ struct TexDesc {
   float cval;
   int ox, oy, oz;
   int lw, lh, ld;
+  // element (X,Y,Z) sits at p[off * estride + ecomp].  estride is 1 (0 reads as 1) except for the
+  // three gradient volumes, which share ONE storage of 4-element voxels (Gx, Gy, Gz, unused) so
+  // that lookupGradient costs one 16-byte load per tap instead of three 4-byte ones.
+  int estride, ecomp;
 };
 
 enum { MAX_PARAM_LIGHTS = 8 };
@@ -92,6 +96,7 @@ struct KernelParams {
   int uniform;   // all volume textures of the launch share one geometry -> shared tap sets
   int ab_is_em;  // absorption role resolves to the same texture as the emission role
   int re_is_em;  // reflection role resolves to the same texture as the emission role
+  int grad4;     // gx, gy, gz are components 0..2 of one interleaved storage (gx.p)
   int gradient_method;  // 0 compute, 1 lookup (volumeRender.h:141-144)
   int frac_bits;        // 0 = fp32 weights, 8 = 1.8 fixed point
   int skip;             // empty-space skipping: 0 off, 1 serial per cell, 2 closed-form jumps (default)
