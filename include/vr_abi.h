@@ -180,7 +180,9 @@ typedef enum vr_option {
   VR_OPT_FILTER_FRAC_BITS = 0,  /* 0 = fp32 trilinear weights (default); 8 = the texture unit's 1.8 fixed point */
   VR_OPT_EMPTY_SPACE_SKIP = 1,  /* exact empty-space skipping: 2 (default) = closed-form jumps over the distance grid,
                                    1 = serial recurrences cell by cell, 0 = march every sample; pixels are bit-identical */
-  VR_OPT_KERNEL_VARIANT = 2,    /* 0 (default) = shared tap sets when all volumes share a geometry; 1 = per-texture addressing */
+  VR_OPT_KERNEL_VARIANT = 2,    /* 0 (default) = shared tap sets when all volumes share a geometry; 1 = per-texture addressing;
+                                   3 = force the kernels with 64-bit z offsets (chosen automatically for a resident
+                                   volume of more than 2^32 elements).  Pixels are bit-identical */
   VR_OPT_ABSORPTION_ROLE_FIX = 3, /* 0 (default) = reference as written: absorption samples the emission texture
                                      (kernel.cu:80); 1 = sample the uploaded absorption volume */
   VR_OPT_PART_RANK = 4,         /* image-space partition: this context renders tiles t with t % nranks == rank */

@@ -93,6 +93,46 @@ def test_gradient_volumes_lookup(brain64, lut):
     _check(gpu, orc)
 
 
+def _with_gradients(r):
+    gx, gy, gz = r.VolumeEmission.grad()
+    r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
+    return r
+
+
+@pytest.mark.parametrize("brick", [1, 0])
+def test_interleaved_gradient_storage_is_invisible(brain64, lut, brick):
+    """lookupGradient reads Gx,Gy,Gz from one interleaved storage by default (one 16-byte load per tap);
+    three separate volumes (option off), the per-texture kernels and the 64-bit-offset kernels give the
+    same bits, and so does a re-upload of ONE gradient volume into the shared storage."""
+    def scene(opts={}):
+        r = vrt.example1_scene(api.VolumeRender, brain64, (128, 96), lights=2, lut=lut)
+        r.setOption(_abi.OPT_BRICK_LAYOUT, brick)
+        for k, v in opts.items():
+            r.setOption(k, v)
+        return _with_gradients(r)
+
+    inter = scene()
+    base = inter.render()
+    assert np.array_equal(scene({_abi.OPT_GRADIENT_INTERLEAVE: 0}).render(), base)
+    assert np.array_equal(scene({_abi.OPT_KERNEL_VARIANT: 1}).render(), base)
+    if brick:
+        assert np.array_equal(scene({_abi.OPT_KERNEL_VARIANT: 3}).render(), base)
+        assert np.array_equal(scene({_abi.OPT_KERNEL_VARIANT: 3, _abi.OPT_GRADIENT_INTERLEAVE: 0}).render(), base)
+    # one gradient volume changes: only that component of the shared storage is rewritten
+    gy2 = api.Volume(np.asarray(inter.VolumeGradientY.Data) * np.float32(0.5))
+    inter.VolumeGradientY = gy2
+    changed = inter.render()
+    assert not np.array_equal(changed, base)
+    ref = scene({_abi.OPT_GRADIENT_INTERLEAVE: 0})
+    ref.VolumeGradientY = api.Volume(np.asarray(ref.VolumeGradientY.Data) * np.float32(0.5))
+    assert np.array_equal(ref.render(), changed)
+    # a gradient volume of another size cannot join the shared storage: mixed storage still renders (per-texture path)
+    small = api.Volume(np.ascontiguousarray(np.asarray(inter.VolumeGradientZ.Data)[::2, ::2, ::2]))
+    inter.VolumeGradientZ = small
+    ref.VolumeGradientZ = api.Volume(np.asarray(small.Data).copy())
+    assert np.array_equal(inter.render(), ref.render())
+
+
 def test_distinct_absorption_and_reflection_volumes(brain64, lut):
     """example1.m:65-70 second pass: a distinct absorption volume is uploaded but, as written,
     the kernel keeps sampling emission; with the role fix it samples absorption."""
@@ -315,6 +355,53 @@ def test_full_size_properties_1024_cubed_2048_squared():
     nxt = r.render()
     movie = r.renderMovie([R0, r.RotationMatrix])
     assert np.array_equal(movie[0], base) and np.array_equal(movie[1], nxt)
+
+
+def test_resident_volume_beyond_2_to_32_elements():
+    """A 1664^3 fp32 volume (4.7 G resident elements, 18 GB) is addressed with 64-bit z terms: the image equals the
+    sum of the shares of the same volume cut into 8 bricks (each far below 2^32 elements; volume-space mode with all
+    bricks on this GPU, generated straight into HBM), which the regular kernels render."""
+    import torch
+
+    if torch.cuda.mem_get_info()[0] < 90e9:
+        pytest.skip("needs ~80 GB of free device memory")
+    from volume_renderer_b200 import multigpu
+
+    n, W, halo = 1664, 256, 4
+    dims = (n, n, n)
+    lut = api.HenyeyGreenstein(64)
+    lib = _abi.lib()
+    u3 = lambda v: (C.c_uint64 * 3)(*[int(x) for x in v])
+
+    def finish(r, vol):
+        r = vrt.example1_scene(lambda: r, vol, (W, W), lights=1, lut=lut)
+        r.FactorAbsorption = 30.0
+        return r
+
+    r = api.VolumeRender()
+    E = torch.empty(n ** 3, dtype=torch.float32, device="cuda")
+    _abi.check(lib.vr_synth_volume(r.objectHandle, 0, vrt.SEED, u3(dims), _abi.DTYPE_F32, C.c_void_p(E.data_ptr())), r.objectHandle)
+    whole_r = finish(r, api.DeviceVolume(E.data_ptr(), dims, _abi.DTYPE_F32, _abi.MEM_DEVICE, keepalive=E))
+    whole = whole_r.render()
+    assert whole_r.stats()["bytes_resident"] > 4 * 2 ** 32
+    del whole_r, r, E
+    torch.cuda.empty_cache()
+
+    bricks = multigpu.brick_grid(dims, (2, 2, 2))
+    rs, keep = [], []
+    for lo, hi in bricks:
+        r = api.VolumeRender()
+        r.setRegion(lo, hi, halo)
+        blo = [max(l - halo, 0) for l in lo]
+        bhi = [min(h + halo, d) for h, d in zip(hi, dims)]
+        buf = torch.empty(int(np.prod([h - l for l, h in zip(blo, bhi)])), dtype=torch.float32, device="cuda")
+        _abi.check(lib.vr_synth_volume_region(r.objectHandle, 0, vrt.SEED, u3(dims), u3(blo), u3(bhi), _abi.DTYPE_F32, C.c_void_p(buf.data_ptr())), r.objectHandle)
+        rs.append(finish(r, api.DeviceVolume(buf.data_ptr(), dims, _abi.DTYPE_F32, _abi.MEM_DEVICE_REGION, keepalive=buf)))
+        keep.append(buf)
+    parts = multigpu.render_bricks_one_gpu(rs, bricks)
+    m = vrt.compare(parts, whole)
+    print(m)
+    assert whole.max() > 0 and m["max_abs_norm"] < 2e-5, m
 
 
 def test_device_epilogue_stereo_compose_and_normalize_sequence(brain64, lut):

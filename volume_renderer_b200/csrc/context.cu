@@ -675,6 +675,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       return fail(c, VR_ERR_UNSUPPORTED, "volumes of more than 2^32 resident elements need the bricked layout, one common geometry and fp32 weights");
     P.uniform = 2;
   }
+  if (c->opt[VR_OPT_KERNEL_VARIANT] == 3 && P.uniform == 1 && layout == LAYOUT_BRICK) P.uniform = 2;  // variant 3: force the 64-bit kernels (tests)
   if (P.frac_bits) P.uniform = 0;  // fixed-point weights (A/B option) are compiled into the per-texture kernels only
 
   // volume-space mode
