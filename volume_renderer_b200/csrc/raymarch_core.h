@@ -31,6 +31,9 @@
 #ifndef VR_MAGIC_FLOOR
 #define VR_MAGIC_FLOOR 1
 #endif
+#ifndef VR_LUT_ADJACENT
+#define VR_LUT_ADJACENT 1
+#endif
 
 namespace vrb {
 
@@ -186,8 +189,15 @@ VR_HD float tex3d_volume(const TexDesc &t, float x, float y, float z, int frac_b
     for (int i = 0; i < 8; ++i) c[i] = E::load(q + ((i < 4 ? z0 : z1) + o[i & 3]) * (size_t)t.estride, 0u);
   } else {
     const T *q0 = static_cast<const T *>(t.p) + z0, *q1 = static_cast<const T *>(t.p) + z1;
+    if (LAYOUT == LAYOUT_LINEAR && VR_LUT_ADJACENT) {
+      // the high x tap is the next element: four addresses, the +1 rides in the load's immediate offset
+      // (measured: -2.4 % in the lookupGradient kernels, +2.5 % in the computeGradient ones - see raymarch_kernel.cu)
+      c[0] = E::load(q0 + o[0], 0u), c[1] = E::load(q0 + o[0], 1u), c[2] = E::load(q0 + o[2], 0u), c[3] = E::load(q0 + o[2], 1u);
+      c[4] = E::load(q1 + o[0], 0u), c[5] = E::load(q1 + o[0], 1u), c[6] = E::load(q1 + o[2], 0u), c[7] = E::load(q1 + o[2], 1u);
+    } else {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) c[i] = E::load(i < 4 ? q0 : q1, o[i & 3]);
+      for (int i = 0; i < 8; ++i) c[i] = E::load(i < 4 ? q0 : q1, o[i & 3]);
+    }
   }
   const float c000 = c[0], c100 = c[1], c010 = c[2], c110 = c[3], c001 = c[4], c101 = c[5], c011 = c[6], c111 = c[7];
   const float c00 = lerpf(c000, c100, fx), c10 = lerpf(c010, c110, fx);

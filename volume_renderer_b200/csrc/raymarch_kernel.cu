@@ -16,6 +16,10 @@
 // of one family independent of edits to the other and halve the build time.
 #include <cuda_runtime.h>
 
+#ifndef VR_LUT_ADJACENT
+#define VR_LUT_ADJACENT VR_GRAD /* which form of the LUT fetch each family runs faster with (A/B on B200) */
+#endif
+
 #include "raymarch_core.h"
 #include "raymarch_launch.h"
 
