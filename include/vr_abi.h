@@ -235,6 +235,14 @@ VR_API vr_status vr_volume_gradient(vr_ctx *ctx, const vr_volume *in, int32_t ou
  * brick_boxes = n_bricks x {lo x,y,z, hi x,y,z} in voxels.  vr_set_region(ctx, NULL, NULL, 0) ends
  * the mode.  Volumes must share the emission volume's dims. */
 VR_API vr_status vr_set_region(vr_ctx *ctx, const uint64_t lo[3], const uint64_t hi[3], uint32_t halo);
+
+/* Partial update (extension): rewrites the voxel box [lo, hi) of the RESIDENT volume that `role`
+ * reads (0 emission, 1 absorption, 2 reflection, 3..5 gradient x, y, z) from `volume`, which must have the dims and
+ * dtype of the resident one and hold the new contents at least inside the box (the rest of it is not read).  Only the
+ * z slices of the box cross PCIe.  examples/example3.m:135-161 rewrites a masked half of the volume every frame; the
+ * reference re-uploads all of it (volumeRender_kernel.cu:659-672).  The slot takes `volume`'s identity (pointer,
+ * timestamp), so a following vr_sync_volumes with a time_last_mem_sync at or after that timestamp moves nothing. */
+VR_API vr_status vr_update_box(vr_ctx *ctx, int role, const vr_volume *volume, const uint64_t lo[3], const uint64_t hi[3]);
 VR_API vr_status vr_render_opacity_device(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
                                           const vr_volume *illumination, const float factors[3],
                                           const float element_size_um[3], const uint64_t resolution[2],

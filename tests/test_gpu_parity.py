@@ -357,6 +357,47 @@ def test_full_size_properties_1024_cubed_2048_squared():
     assert np.array_equal(movie[0], base) and np.array_equal(movie[1], nxt)
 
 
+@pytest.mark.parametrize("brick", [1, 0])
+def test_partial_update_equals_full_upload(lut, brick):
+    """vr_update_box (the example3.m:135-161 pattern): rewriting a voxel box of a resident volume
+    gives the bits of a full re-upload - bricks, padding replicas at the faces, the empty-space grids and a component of
+    the interleaved gradient storage included - while only the box's slices cross PCIe."""
+    dims = (72, 56, 48)
+    vol = vrt.synth_brain(dims)
+
+    def scene(data):
+        r = vrt.example1_scene(api.VolumeRender, np.array(data, order="F"), (128, 96), lights=2, lut=lut)
+        r.setOption(_abi.OPT_BRICK_LAYOUT, brick)
+        return _with_gradients(r)
+
+    r = scene(vol)
+    r.render()
+    rng = np.random.default_rng(5)
+    boxes = [((0, 0, 0), (72, 56, 24)),      # the half-space of example3
+             ((10, 7, 30), (50, 41, 48)),    # touches the high z face
+             ((0, 20, 5), (9, 21, 6)),       # a sliver at the low x face
+             ((71, 55, 47), (72, 56, 48))]   # the last voxel
+    cur = np.array(vol, order="F")
+    for lo, hi in boxes:
+        sl = tuple(slice(a, b) for a, b in zip(lo, hi))
+        # new contents: faded, and a block that was empty becomes non-empty (the skip grids must follow)
+        cur[sl] = cur[sl] * np.float32(0.5) + (rng.random(cur[sl].shape, dtype=np.float32) * np.float32(0.2)).astype(np.float32)
+        r.VolumeEmission.Data[sl] = cur[sl]  # in place: no stamp, nothing is marked dirty
+        r.updateVolumeBox("emission", lo, hi)
+        st = r.stats()
+        assert st["bytes_uploaded"] <= (hi[2] - lo[2]) * dims[0] * dims[1] * 4
+        img = r.render()
+        assert r.stats()["uploads"] == 0  # the render's own sync moved nothing
+        ref = scene(cur)
+        # the reference scene computes its gradient volumes from the NEW data; ours must be told about them
+        for k, name in enumerate(("VolumeGradientX", "VolumeGradientY", "VolumeGradientZ")):
+            g_new = np.asarray(getattr(ref, name).Data)
+            getattr(r, name).Data[...] = g_new
+            r.updateVolumeBox(("gradientx", "gradienty", "gradientz")[k], (0, 0, 0), dims)
+        img = r.render()
+        assert np.array_equal(img, ref.render()), (lo, hi)
+
+
 def test_resident_volume_beyond_2_to_32_elements():
     """A 1664^3 fp32 volume (4.7 G resident elements, 18 GB) is addressed with 64-bit z terms: the image equals the
     sum of the shares of the same volume cut into 8 bricks (each far below 2^32 elements; volume-space mode with all

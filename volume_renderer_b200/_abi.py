@@ -110,6 +110,7 @@ def declare(lib):
         "vr_synth_volume": ([vp, C.c_int, C.c_uint32, u64p, C.c_int32, vp], C.c_int),
         "vr_volume_gradient": ([vp, P(VrVolume), C.c_int32, vp, vp, vp], C.c_int),
         "vr_set_region": ([vp, u64p, u64p, C.c_uint32], C.c_int),
+        "vr_update_box": ([vp, C.c_int, P(VrVolume), u64p, u64p], C.c_int),
         "vr_render_opacity_device": (render_args + [vp, vp], C.c_int),
         "vr_render_partial_device": (render_args + [C.c_uint32, C.c_uint32, u64p, vp, vp, vp], C.c_int),
         "vr_compose_partials_device": ([vp, C.c_uint32, P(vp), C.c_uint64, vp, vp], C.c_int),

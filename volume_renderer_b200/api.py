@@ -442,6 +442,26 @@ class VolumeRender:
                                        self.VolumeReflection, self.VolumeAbsorption)
         self.TimeLastMemSync = timestamp()
 
+    ROLES = {"emission": 0, "absorption": 1, "reflection": 2, "gradientx": 3, "gradienty": 4, "gradientz": 5}
+
+    def updateVolumeBox(self, role, lo, hi):
+        """Extension (vr_update_box): the voxel box [lo, hi) of the volume that `role`
+        ("emission", "absorption", "reflection", "gradientx|y|z") refers to has been rewritten in place on the host
+        (the example3.m:135-161 pattern) - move only that box to the GPU instead of the whole volume.  The volume
+        object is re-stamped and counts as synced afterwards."""
+        attr = {0: "VolumeEmission", 1: "VolumeAbsorption", 2: "VolumeReflection", 3: "VolumeGradientX", 4: "VolumeGradientY",
+                5: "VolumeGradientZ"}[self.ROLES[role.lower()]]
+        vol = getattr(self, attr)
+        if getattr(self, "TimeLastMemSync", 0) == 0:
+            self.syncVolumes()  # nothing resident yet: the first upload is a whole one
+            return
+        vol._stamp()
+        keep = []
+        v = _abi.volume_struct(vol.Data, vol.TimeLastUpdate, keep)
+        l3, h3 = (C.c_uint64 * 3)(*[int(x) for x in lo]), (C.c_uint64 * 3)(*[int(x) for x in hi])
+        _abi.check(_abi.lib().vr_update_box(self.objectHandle, self.ROLES[role.lower()], C.byref(v), l3, h3), self.objectHandle)
+        self.TimeLastMemSync = timestamp()
+
     def memInfo(self):
         """VolumeRender.m:221-228 (prints like mexPrintf, and returns the text)"""
         s = self._backend.mem_info(self.objectHandle)

@@ -20,6 +20,7 @@
 #include <mutex>
 #include <set>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -62,6 +63,8 @@ HostVol make_volume(const vr_volume *v) {
 }
 
 // One texture slot = what a bound texture reference + its cudaArray was (kernel.cu:90-120).
+enum { kStageBufs = 3 };
+
 struct Resident {
   void *storage = nullptr;  // padded (bricked) voxels
   size_t storage_bytes = 0;
@@ -125,7 +128,9 @@ struct vr_ctx {
   // persistent buffers
   float *d_image = nullptr;
   size_t image_cap = 0;
-  void *d_stage = nullptr;
+  void *d_stage[kStageBufs] = {nullptr, nullptr, nullptr};  // device side of the upload staging
+  void *h_stage[kStageBufs] = {nullptr, nullptr, nullptr};  // pinned host side
+  cudaEvent_t ev_stage[kStageBufs] = {nullptr, nullptr, nullptr};
   size_t stage_cap = 0;
   unsigned int *d_counter = nullptr;      // work counter + padding
   uint32_t *d_tile_order = nullptr;       // owned tiles, heaviest first
@@ -207,7 +212,7 @@ void release(vr_ctx *c, Resident &r) {
 uint64_t resident_bytes(const vr_ctx *c) {
   uint64_t b = 0;
   for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes + c->tex[i].dist_bytes;
-  b += c->image_cap + c->stage_cap + c->lights_more_cap + c->g4_bytes;
+  b += c->image_cap + kStageBufs * c->stage_cap + c->lights_more_cap + c->g4_bytes;
   return b;
 }
 
@@ -231,13 +236,125 @@ void geometry(int layout, uint64_t pw, uint64_t ph, uint64_t pd, uint32_t *sy, u
 
 TexDesc describe(const Resident &r);
 
+
+// memcpy with a few threads: one core copies ~10 GB/s, the PCIe 5 link takes 50
+void parallel_copy(void *dst, const void *src, size_t bytes) {
+  unsigned nt = std::thread::hardware_concurrency();
+  nt = nt > 8 ? 8 : (nt < 1 ? 1 : nt);
+  if (bytes < ((size_t)8 << 20) || nt == 1) {
+    memcpy(dst, src, bytes);
+    return;
+  }
+  const size_t per = ((bytes / nt) + 4095) & ~(size_t)4095;
+  std::vector<std::thread> th;
+  for (unsigned i = 0; i < nt; ++i) {
+    const size_t o = (size_t)i * per;
+    if (o >= bytes) break;
+    const size_t n = o + per < bytes ? per : bytes - o;
+    th.emplace_back([=] { memcpy(static_cast<char *>(dst) + o, static_cast<const char *>(src) + o, n); });
+  }
+  for (auto &t : th) t.join();
+}
+
+// staging of host sources: kStageBufs buffers in pinned host memory and as many on the device, so
+// that the CPU copy of slab k+1 (pageable -> pinned), the DMA of slab k and its repack overlap
 vr_status ensure_stage(vr_ctx *c, size_t bytes) {
   if (c->stage_cap >= bytes) return VR_OK;
-  if (c->d_stage) cudaFree(c->d_stage);
-  c->d_stage = nullptr;
+  for (int i = 0; i < kStageBufs; ++i) {
+    if (c->d_stage[i]) cudaFree(c->d_stage[i]);
+    if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
+    c->d_stage[i] = c->h_stage[i] = nullptr;
+  }
   c->stage_cap = 0;
-  VR_CUDA(c, cudaMalloc(&c->d_stage, bytes));
+  for (int i = 0; i < kStageBufs; ++i) {
+    VR_CUDA(c, cudaMalloc(&c->d_stage[i], bytes));
+    VR_CUDA(c, cudaMallocHost(&c->h_stage[i], bytes));
+  }
   c->stage_cap = bytes;
+  return VR_OK;
+}
+
+// Writes the voxels of `v` that lie in the voxel box `box` = {lo xyz, hi xyz} into the resident
+// storage of `r` (whose geometry is already set): the whole volume at upload time, a sub-box for
+// vr_update_box.  Host sources are streamed in slabs of whole destination layers (H2D of the source
+// slices a slab needs, then a repack kernel that writes the padded, bricked storage); only the z
+// slices inside the box cross PCIe.
+vr_status fill_resident(vr_ctx *c, Resident &r, const HostVol &v, const int box[6]) {
+  const int64_t dims[3] = {r.w, r.h, r.d};
+  const int64_t g0[3] = {r.ox - 1, r.oy - 1, r.oz - 1};  // global voxel of local padded index 0
+  const size_t es = elem_size(v.dtype);
+  uint64_t elems, layers, layer_elems;
+  uint32_t sy, sz;
+  geometry(r.layout, (uint64_t)r.lw, (uint64_t)r.lh, (uint64_t)r.ld, &sy, &sz, &elems, &layers, &layer_elems);
+  RepackArgs a;
+  a.dst = r.storage;
+  a.w = r.w, a.h = r.h, a.d = r.d;
+  a.lw = r.lw, a.lh = r.lh, a.ld = r.ld;
+  a.gx0 = (int)g0[0], a.gy0 = (int)g0[1], a.gz0 = (int)g0[2];
+  a.sx0 = 0, a.sy0 = 0, a.sw = r.w, a.sh = r.h;
+  a.sy = sy, a.sz = sz;
+  a.estride = r.estride, a.ecomp = r.ecomp;
+  a.layout = r.layout;
+  a.src_dtype = a.dst_dtype = v.dtype;
+  for (int i = 0; i < 6; ++i) a.box[i] = box[i];
+  const uint64_t zper = r.layout == LAYOUT_BRICK ? 8 : 1;  // padded Z planes per layer
+  // local padded planes that hold a voxel of the box (the planes below / above the volume replicate its faces)
+  const int64_t Zlo = box[2] <= 0 ? 0 : std::max<int64_t>(box[2] - g0[2], 0);
+  const int64_t Zhi = box[5] >= dims[2] ? (int64_t)r.ld : std::min<int64_t>(box[5] - g0[2], r.ld);
+  if (Zhi <= Zlo) return VR_OK;
+  const uint64_t lay0 = (uint64_t)Zlo / zper, lay1 = ((uint64_t)Zhi + zper - 1) / zper;
+  const size_t slice_bytes = (size_t)v.w * v.h * es;
+  if (v.memspace == VR_MEM_DEVICE_REGION) {
+    // the caller's device buffer holds exactly the resident box (owned region plus halo, clipped to the volume)
+    int64_t b0[3], b1[3];
+    const int64_t lext[3] = {r.lw, r.lh, r.ld};
+    for (int i = 0; i < 3; ++i) b0[i] = g0[i] < 0 ? 0 : g0[i], b1[i] = g0[i] + lext[i] > dims[i] ? dims[i] : g0[i] + lext[i];
+    a.src = v.data;
+    a.sx0 = (int)b0[0], a.sy0 = (int)b0[1], a.sw = (int)(b1[0] - b0[0]), a.sh = (int)(b1[1] - b0[1]);
+    a.src_z0 = (int)b0[2];
+    a.o0 = lay0 * layer_elems, a.o1 = lay1 * layer_elems;
+    VR_CUDA(c, launch_repack(a, c->stream));
+  } else if (v.memspace == VR_MEM_DEVICE) {
+    a.src = v.data;
+    a.src_z0 = 0;
+    a.o0 = lay0 * layer_elems, a.o1 = lay1 * layer_elems;
+    VR_CUDA(c, launch_repack(a, c->stream));
+  } else {
+    // slabs of ~64 MiB of source slices through kStageBufs staging buffers
+    const size_t budget = (size_t)64 << 20;
+    uint64_t slab_layers = budget / (slice_bytes * zper);
+    if (slab_layers < 1) slab_layers = 1;
+    if (slab_layers > lay1 - lay0) slab_layers = lay1 - lay0;
+    VR_TRY(ensure_stage(c, (size_t)(slab_layers * zper + 1) * slice_bytes));
+    cudaPointerAttributes attr;
+    const bool pinned = cudaPointerGetAttributes(&attr, v.data) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();  // an unregistered host pointer is reported as an error by older drivers
+    auto clampz = [&](int64_t z) { return z < box[2] ? (int64_t)box[2] : (z > box[5] - 1 ? (int64_t)box[5] - 1 : z); };
+    int k = 0;
+    for (uint64_t l0 = lay0; l0 < lay1; l0 += slab_layers, ++k) {
+      const uint64_t l1 = l0 + slab_layers < lay1 ? l0 + slab_layers : lay1;
+      // padded planes [l0*zper, l1*zper) hold global voxel z = clamp(Z + gz0); only slices inside the box are read
+      const int64_t z0 = clampz((int64_t)(l0 * zper) + g0[2]), z1 = clampz((int64_t)(l1 * zper) - 1 + g0[2]);
+      const size_t nbytes = (size_t)(z1 - z0 + 1) * slice_bytes;
+      const int bi = k % kStageBufs;
+      if (k >= kStageBufs) VR_CUDA(c, cudaEventSynchronize(c->ev_stage[bi]));  // its previous slab has been repacked
+      const char *src = static_cast<const char *>(v.data) + (size_t)z0 * slice_bytes;
+      if (!pinned) {
+        parallel_copy(c->h_stage[bi], src, nbytes);
+        src = static_cast<const char *>(c->h_stage[bi]);
+      }
+      VR_CUDA(c, cudaMemcpyAsync(c->d_stage[bi], src, nbytes, cudaMemcpyHostToDevice, c->stream));
+      a.src = c->d_stage[bi];
+      a.src_z0 = (int)z0;
+      a.o0 = l0 * layer_elems, a.o1 = l1 * layer_elems;
+      VR_CUDA(c, launch_repack(a, c->stream));
+      VR_CUDA(c, cudaEventRecord(c->ev_stage[bi], c->stream));
+      c->stats.bytes_uploaded += nbytes;
+    }
+    // the caller's memory is borrowed for the duration of the call only (MATLAB owns it): a pinned
+    // source is read by the DMA engine itself, so wait for the last copies
+    if (pinned) VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
   return VR_OK;
 }
 
@@ -327,56 +444,9 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
     r.storage_bytes = elems * es;
   }
 
-  RepackArgs a;
-  a.dst = r.storage;
-  a.w = r.w, a.h = r.h, a.d = r.d;
-  a.lw = r.lw, a.lh = r.lh, a.ld = r.ld;
-  a.gx0 = (int)g0[0], a.gy0 = (int)g0[1], a.gz0 = (int)g0[2];
-  a.sx0 = 0, a.sy0 = 0, a.sw = r.w, a.sh = r.h;
-  a.sy = sy, a.sz = sz;
-  a.estride = r.estride, a.ecomp = r.ecomp;
-  a.layout = layout;
-  a.src_dtype = a.dst_dtype = v.dtype;
-  auto clampz = [&](int64_t z) { return z < 0 ? 0 : (z > dims[2] - 1 ? dims[2] - 1 : z); };
-  const uint64_t zper = layout == LAYOUT_BRICK ? 8 : 1;  // padded Z planes per layer
-  const size_t slice_bytes = (size_t)v.w * v.h * es;
-  if (v.memspace == VR_MEM_DEVICE_REGION) {
-    // the caller's device buffer holds exactly the owned box plus halo, clipped to the volume
-    if (!region) return fail(c, VR_ERR_INVALID_ARGUMENT, "a region buffer needs vr_set_region first");
-    int64_t b0[3], b1[3];
-    for (int i = 0; i < 3; ++i) b0[i] = g0[i] < 0 ? 0 : g0[i], b1[i] = hi[i] + halo > dims[i] ? dims[i] : hi[i] + halo;
-    a.src = v.data;
-    a.sx0 = (int)b0[0], a.sy0 = (int)b0[1], a.sw = (int)(b1[0] - b0[0]), a.sh = (int)(b1[1] - b0[1]);
-    a.src_z0 = (int)b0[2];
-    a.o0 = 0, a.o1 = elems;
-    VR_CUDA(c, launch_repack(a, c->stream));
-  } else if (v.memspace == VR_MEM_DEVICE) {
-    a.src = v.data;
-    a.src_z0 = 0;
-    a.o0 = 0, a.o1 = elems;
-    VR_CUDA(c, launch_repack(a, c->stream));
-  } else {
-    // slab = as many layers as fit a ~256 MiB staging buffer; only the z slices the region needs cross PCIe
-    const size_t budget = (size_t)256 << 20;
-    uint64_t slab_layers = budget / (slice_bytes * zper);
-    if (slab_layers < 1) slab_layers = 1;
-    if (slab_layers > layers) slab_layers = layers;
-    VR_TRY(ensure_stage(c, (size_t)(slab_layers * zper + 1) * slice_bytes));
-    for (uint64_t l0 = 0; l0 < layers; l0 += slab_layers) {
-      const uint64_t l1 = l0 + slab_layers < layers ? l0 + slab_layers : layers;
-      // padded planes [l0*zper, l1*zper) hold global voxel z = clamp(Z + gz0)
-      const int64_t z0 = clampz((int64_t)(l0 * zper) + g0[2]), z1 = clampz((int64_t)(l1 * zper) - 1 + g0[2]);
-      const size_t nbytes = (size_t)(z1 - z0 + 1) * slice_bytes;
-      // the staging buffer is reused: the previous slab's repack must have consumed it (same stream)
-      VR_CUDA(c, cudaMemcpyAsync(c->d_stage, static_cast<const char *>(v.data) + (size_t)z0 * slice_bytes, nbytes,
-                                 cudaMemcpyHostToDevice, c->stream));
-      a.src = c->d_stage;
-      a.src_z0 = (int)z0;
-      a.o0 = l0 * layer_elems, a.o1 = l1 * layer_elems;
-      VR_CUDA(c, launch_repack(a, c->stream));
-      c->stats.bytes_uploaded += nbytes;
-    }
-  }
+  if (v.memspace == VR_MEM_DEVICE_REGION && !region) return fail(c, VR_ERR_INVALID_ARGUMENT, "a region buffer needs vr_set_region first");
+  const int full[6] = {0, 0, 0, r.w, r.h, r.d};
+  VR_TRY(fill_resident(c, r, v, full));
   r.kind = TEX_VOLUME;
   r.src = v;
   for (int i = 0; i < 3; ++i) r.reg[i] = (int)lo[i], r.reg[3 + i] = (int)hi[i];
@@ -916,6 +986,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu0);
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu1);
+  for (int i = 0; i < kStageBufs && ce == cudaSuccess; ++i) ce = cudaEventCreateWithFlags(&c->ev_stage[i], cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&c->ev_cost, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_counter, 64);
   if (ce == cudaSuccess && getenv("VR_WARP_TIMES")) ce = cudaMalloc(&c->d_warp_times, 2 * 8192 * sizeof(unsigned long long));
@@ -948,7 +1019,11 @@ vr_status vr_destroy(vr_ctx *c) {
   cudaStreamSynchronize(c->stream);
   for (int i = 0; i < S_N; ++i) release(c, c->tex[i]);
   if (c->d_image) cudaFree(c->d_image);
-  if (c->d_stage) cudaFree(c->d_stage);
+  for (int i = 0; i < kStageBufs; ++i) {
+    if (c->d_stage[i]) cudaFree(c->d_stage[i]);
+    if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
+    if (c->ev_stage[i]) cudaEventDestroy(c->ev_stage[i]);
+  }
   if (c->d_lights_more) cudaFree(c->d_lights_more);
   if (c->d_counter) cudaFree(c->d_counter);
   if (c->d_tile_order) cudaFree(c->d_tile_order);
@@ -1081,6 +1156,49 @@ vr_status vr_set_region(vr_ctx *c, const uint64_t lo[3], const uint64_t hi[3], u
   c->halo = halo ? (int)halo : 4;
   if (c->halo < 2 || c->halo > 64) return fail(c, VR_ERR_INVALID_ARGUMENT, "set_region: halo must be in [2, 64]");
   c->region_on = true;
+  return VR_OK;
+}
+
+// Partial update of a resident volume (example3.m:135-161 rewrites a masked half of
+// the volume every frame and the reference uploads all of it again, kernel.cu:659-672).
+vr_status vr_update_box(vr_ctx *c, int role, const vr_volume *vol, const uint64_t lo[3], const uint64_t hi[3]) {
+  VR_CHECK_HANDLE(c);
+  if (!vol || !lo || !hi) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: null argument");
+  if (role < 0 || role > S_DZ) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: role %d (0 emission, 1 absorption, 2 reflection, 3..5 gradient x,y,z)", role);
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  // the texture the role reads (roles that alias it see the update too)
+  const int slot = role == S_EM ? c->idxEm : role == S_AB ? c->idxAb : role == S_RE ? c->idxRe : role;
+  Resident &r = c->tex[slot];
+  const HostVol v = make_volume(vol);
+  if (r.kind != TEX_VOLUME) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: the role has no resident volume (sync it first)");
+  if ((int)v.w != r.w || (int)v.h != r.h || (int)v.d != r.d || v.dtype != r.dtype)
+    return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: the volume must have the dims and dtype of the resident one (%d x %d x %d)", r.w, r.h, r.d);
+  if (v.memspace == VR_MEM_DEVICE_REGION && !c->region_on) return fail(c, VR_ERR_INVALID_ARGUMENT, "a region buffer needs vr_set_region first");
+  int box[6];
+  const int dims[3] = {r.w, r.h, r.d};
+  for (int i = 0; i < 3; ++i) {
+    if (lo[i] >= hi[i] || hi[i] > (uint64_t)dims[i]) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: box [%llu,%llu) does not fit axis %d (%d voxels)", (unsigned long long)lo[i], (unsigned long long)hi[i], i, dims[i]);
+    box[i] = (int)lo[i], box[3 + i] = (int)hi[i];
+  }
+  c->stats.bytes_uploaded = 0;
+  VR_CUDA(c, cudaEventRecord(c->evu0, c->stream));
+  VR_TRY(fill_resident(c, r, v, box));
+  // what the slot now holds: the caller's volume at its new timestamp (the next sync must not upload it again)
+  r.src = v;
+  const HostVol before = c->host[role];
+  for (int s = 0; s <= S_DZ; ++s)
+    if (s == role || (s <= S_RE && role <= S_RE && same(c->host[s], before))) c->host[s] = v;  // aliased roles stay aliased
+  // the empty-space grids describe the old contents: rebuilt on the next render that needs them
+  if (r.occ) cudaFree(r.occ);
+  if (r.dist) cudaFree(r.dist);
+  r.occ = nullptr, r.dist = nullptr, r.occ_bytes = r.dist_bytes = 0;
+  VR_CUDA(c, cudaEventRecord(c->evu1, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, c->evu0, c->evu1);
+  c->stats.upload_ms = ms;
+  c->stats.uploads = 1;
   return VR_OK;
 }
 

@@ -31,6 +31,8 @@ struct RepackArgs {
   uint64_t o0, o1;     // destination element range [o0, o1) to produce
   uint32_t sy, sz;     // destination strides (see TexDesc)
   int estride, ecomp;  // destination element o is written to dst[o * estride + ecomp] (1, 0 unless interleaved)
+  int box[6];          // only elements whose (clamped) source voxel lies in [box[0..2], box[3..5]) are written;
+                       // {0,0,0,w,h,d} = all (partial update of a resident volume, vr_update_box)
   int layout;          // LAYOUT_*
   int src_dtype;       // vr_dtype of src
   int dst_dtype;       // vr_dtype of dst
