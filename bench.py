@@ -53,6 +53,7 @@ def parse():
     p.add_argument("--tile", type=int, default=64)
     p.add_argument("--batch", type=int, default=16, help="frames per launch (one work queue per batch; clipped to --steps)")
     p.add_argument("--wshape", type=int, default=3, help="warp footprint (1<<s) x (32>>s) pixels")
+    p.add_argument("--no-upload-probe", action="store_true", help="skip the host->resident upload measurement")
     p.add_argument("--interleave", type=int, default=1, help="1: Gx,Gy,Gz resident as one interleaved storage (default); 0: three volumes")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
@@ -513,9 +514,9 @@ def run_b200(args):
     achieved = per_launch_shaded * bps / (kavg_ms * 1e-3) / 1e9
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v2_summary.md:
-        # 4.05 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
-        "traffic": (2.03e9 * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v4_summary.md:
+        # 4.90 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
+        "traffic": (2.45e9 * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
         "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "peak_source": peak_src,
         "bytes_per_sample": bps, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
         "achieved_if_every_marched_sample_gathered": per_launch_marched * bps / (kavg_ms * 1e-3) / 1e9,
@@ -532,6 +533,13 @@ def run_b200(args):
         "gpu_launches": launches_all, "clocks": clocks, "roofline": roofline,
     }
 
+    # ---- upload path: a dirty volume from host memory into resident bricks ----
+    if world == 1 and not args.no_upload_probe:
+        try:
+            line["upload"] = upload_probe(args)
+        except Exception as ex:
+            line["upload"] = {"failed": repr(ex)}
+
     # ---- cpu_baseline: the oracle on host copies of the same volumes, bounded sample ----
     if world == 1 and not args.no_cpu_baseline:
         try:
@@ -546,6 +554,52 @@ def run_b200(args):
     print(json.dumps(line), flush=True)
     finish()
     return 0
+
+
+def upload_probe(args):
+    """vr_sync_volumes of one dirty N^3 fp32 volume from pageable and from pinned host memory, and vr_update_box of half of
+    it (the example3.m:135-161 pattern), in a context of its own; wall clock around the call, best of 2 after a warm-up."""
+    import torch
+
+    from volume_renderer_b200 import _abi
+
+    n = min(args.size, 1024)
+    if mem_available_gib() < 3 * 4.0 * n ** 3 / 2 ** 30 + 8:
+        return {"skipped": "host memory"}
+    lib = _abi.lib()
+    ctx = C.c_void_p()
+    _abi.check(lib.vr_create(C.byref(ctx)))
+    one = np.ones(1, dtype=np.float32)
+    out = {"volume": "%d^3 fp32" % n, "gib": n ** 3 * 4 / 2 ** 30}
+
+    def sync(ptr, stamp, T):
+        E = _abi.volume_struct((ptr, (n, n, n), _abi.DTYPE_F32, _abi.MEM_HOST), stamp)
+        R = _abi.volume_struct((one.ctypes.data, (1, 1, 1), _abi.DTYPE_F32, _abi.MEM_HOST), 1)
+        t0 = time.perf_counter()
+        _abi.check(lib.vr_sync_volumes(ctx, C.c_uint64(T), C.byref(E), C.byref(R), C.byref(E), None, None, None), ctx)
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0
+
+    pageable = np.full(n ** 3, 0.25, dtype=np.float32)
+    pinned = torch.full((n ** 3,), 0.25, dtype=torch.float32).pin_memory()
+    for name, ptr in (("pageable", pageable.ctypes.data), ("pinned", pinned.data_ptr())):
+        stamp, T, ts = 10, 0, []
+        for _ in range(3):
+            ts.append(sync(ptr, stamp, T))
+            T, stamp = stamp, stamp + 10  # the next stamp is newer than the last sync: dirty again
+        out[name + "_GBps"] = n ** 3 * 4 / min(ts[1:]) / 1e9
+    lo, hi = (C.c_uint64 * 3)(0, 0, 0), (C.c_uint64 * 3)(n, n, n // 2)
+    E = _abi.volume_struct((pageable.ctypes.data, (n, n, n), _abi.DTYPE_F32, _abi.MEM_HOST), 1000)
+    ts = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        _abi.check(lib.vr_update_box(ctx, 0, C.byref(E), lo, hi), ctx)
+        torch.cuda.synchronize()
+        ts.append(time.perf_counter() - t0)
+    out["half_volume_update_ms"] = min(ts[1:]) * 1e3
+    out["whole_volume_pageable_ms"] = n ** 3 * 4 / out["pageable_GBps"] / 1e6
+    _abi.check(lib.vr_destroy(ctx))
+    return out
 
 
 def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m):

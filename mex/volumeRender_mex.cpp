@@ -99,6 +99,17 @@ extern "C" void mexFunction(int nlhs, mxArray *plhs[], int nrhs, const mxArray *
     if (s != VR_OK) fail(ctx, "sync_volumes failed");
     return;
   }
+  if (!strcmp("update_box", cmd)) {  // extension, no reference counterpart: volumeRender('update_box', h, role, volume, lo, hi)
+    if (nrhs != 6) mexErrMsgTxt("insufficient parameter!");
+    if (mxGetClassID(prhs[4]) != mxUINT64_CLASS || mxGetClassID(prhs[5]) != mxUINT64_CLASS || mxGetNumberOfElements(prhs[4]) < 3 ||
+        mxGetNumberOfElements(prhs[5]) < 3)
+      mexErrMsgTxt("update_box: lo and hi must be uint64[3] (zero-based, hi exclusive)");
+    const vr_volume v = make_volume(prhs[3]);
+    const vr_status s = vr_update_box(ctx, (int)mxGetScalar(prhs[2]), &v, static_cast<const uint64_t *>(mxGetData(prhs[4])),
+                                      static_cast<const uint64_t *>(mxGetData(prhs[5])));
+    if (s != VR_OK) fail(ctx, "update_box failed");
+    return;
+  }
   if (!strcmp("render", cmd)) {  // render.cpp:134-277
     if (nrhs < 11) mexErrMsgTxt("insufficient parameter!");  // render.cpp:136-140
     // lights + illumination: skipped when either is a logical placeholder (render.cpp:145-146)
