@@ -54,6 +54,7 @@ def parse():
     p.add_argument("--batch", type=int, default=16, help="frames per launch (one work queue per batch; clipped to --steps)")
     p.add_argument("--wshape", type=int, default=3, help="warp footprint (1<<s) x (32>>s) pixels")
     p.add_argument("--no-upload-probe", action="store_true", help="skip the host->resident upload measurement")
+    p.add_argument("--no-gather-probe", action="store_true", help="skip the gather-ceiling microbenchmark (roofline.gather)")
     p.add_argument("--interleave", type=int, default=1, help="1: Gx,Gy,Gz resident as one interleaved storage (default); 0: three volumes")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
@@ -476,6 +477,33 @@ def run_b200(args):
         dist.all_reduce(e, op=dist.ReduceOp.SUM)
         te = float(emx[0])
     e2e_value = float(e[1]) / te / 1e9
+    # the mex 'render' command itself (render.cpp:134-277): ONE frame per call into PAGEABLE host memory (an mxArray),
+    # sync_volumes before every frame as VolumeRender.m:565-581 does
+    single = None
+    if world == 1:
+        pageable = np.zeros(npx, dtype=np.float32)
+        n1 = min(args.steps, 8)
+
+        def one(step):
+            _abi.check(lib.vr_sync_volumes(ctx, stamp_sync, C.byref(vE), C.byref(vR), C.byref(vA), *[C.byref(x) if x is not None else None for x in g]), ctx)
+            _abi.check(lib.vr_render(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
+                                     f32p(scene.rot(step).reshape(-1, order="F").astype(np.float32)), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color),
+                                     pageable.ctypes.data_as(C.POINTER(C.c_float))), ctx)
+
+        one(-1)
+        s_samples, s_kernel = 0, 0.0
+        per_frame = []
+        ts = time.perf_counter()
+        for k in range(n1):
+            tk = time.perf_counter()
+            one(k)
+            per_frame.append(1e3 * (time.perf_counter() - tk))
+            st = stats()
+            s_samples += st.samples_marched
+            s_kernel += st.kernel_ms
+        ts = time.perf_counter() - ts
+        single = {"ms_per_frame": 1e3 * ts / n1, "value": s_samples / ts / 1e9, "unit": "Gsamples/s", "frames": n1, "kernel_ms_per_frame": s_kernel / n1, "ms_each": [round(x, 2) for x in per_frame],
+                  "note": "vr_sync_volumes + vr_render, one frame per call, output into pageable host memory (the MATLAB mex path)"}
     h2d = 9 * 4 + 3 * 4 * 4 + 8 * 2 + nl * 24 + 6 * 40  # rotation, factors/es/props/color, resolution, lights, volume descriptors
     d2h = scene.W * scene.H * 3 * 4
 
@@ -532,6 +560,15 @@ def run_b200(args):
                 "note": "vr_sync_volumes + vr_render through the C ABI with host parameter/output buffers; volumes persistent (uploaded once, %0.2f s)" % t_up},
         "gpu_launches": launches_all, "clocks": clocks, "roofline": roofline,
     }
+    if single is not None:
+        line["e2e"]["single_frame"] = single
+
+    # ---- gather ceilings of this box with the march's access pattern (BW_gather, measured live) ----
+    if world == 1 and not args.no_gather_probe:
+        try:
+            roofline["gather"] = gather_probe(lib, ctx, args, len(scene.lights), shaded / (float(np.sum(kernel_ms)) * 1e-3))
+        except Exception as ex:
+            roofline["gather"] = {"failed": repr(ex)}
 
     # ---- upload path: a dirty volume from host memory into resident bricks ----
     if world == 1 and not args.no_upload_probe:
@@ -554,6 +591,41 @@ def run_b200(args):
     print(json.dumps(line), flush=True)
     finish()
     return 0
+
+
+def gather_probe(lib, ctx, args, n_lights, shaded_per_s):
+    """vr_probe_gather (csrc/probe_kernels.cu): trilinear fetches per second of kernels that ONLY gather, with the march's
+    access pattern (8x4 bundles of parallel rays 0.7 voxels apart, 0.45-voxel steps), served from L1 / L2 / HBM-sized
+    footprints; loads as the march issues them (8 x 4 B, 8 x 16 B) and the texture unit's filtered fetch (the reference's
+    path) for comparison.  From those the time a shaded sample's fetches alone would take, i.e. the gather-only ceiling
+    in shaded samples per second, and the march's fraction of it."""
+    from volume_renderer_b200 import _abi
+
+    def probe(kind, log2_edge):
+        f, ms = C.c_double(), C.c_double()
+        _abi.check(lib.vr_probe_gather(ctx, kind, log2_edge, C.byref(f), C.byref(ms)), ctx)
+        return f.value
+
+    out = {"pattern": "8x4 bundles of parallel rays 0.7 voxel apart, 0.45-voxel steps, one trilinear fetch (8 taps) per step, 2048 threads/SM",
+           "unit": "G trilinear fetches/s"}
+    for name, kind, e in (("ldg4_L1_32^3", 0, 5), ("ldg4_L2_256^3", 0, 8), ("ldg4_HBM_1024^3", 0, 10), ("ldg16_L2_128^3", 1, 7), ("ldg16_HBM_512^3", 1, 9),
+                          ("tex_f32_L1_32^3", 2, 5), ("tex_f32_L2_256^3", 2, 8), ("tex_f32_HBM_1024^3", 2, 10), ("tex_f32x4_L2_128^3", 3, 7), ("tex_f32x4_HBM_512^3", 3, 9)):
+        out[name] = probe(kind, e) / 1e9
+    # fetches of one shaded sample (DESIGN 4.1): gradient volumes -> emission + reflection (8 x 4 B each), one interleaved
+    # gradient fetch (8 x 16 B), L LUT fetches (8 x 4 B, 1.1 MiB table: L1/L2); on the fly -> emission + reflection + 6 more + L LUT
+    if args.gradient == "lookup":
+        t = 2.0 / out["ldg4_HBM_1024^3"] + 1.0 / out["ldg16_HBM_512^3"] + n_lights / out["ldg4_L1_32^3"]
+        t_l2 = 2.0 / out["ldg4_L2_256^3"] + 1.0 / out["ldg16_L2_128^3"] + n_lights / out["ldg4_L1_32^3"]
+    else:
+        t = 8.0 / out["ldg4_HBM_1024^3"] + n_lights / out["ldg4_L1_32^3"]
+        t_l2 = 8.0 / out["ldg4_L2_256^3"] + n_lights / out["ldg4_L1_32^3"]
+    out["ceiling_gsamples_shaded_per_s"] = 1.0 / t  # volumes at their real size (HBM-sized footprints), LUT from L1
+    out["ceiling_l2_resident_gsamples_shaded_per_s"] = 1.0 / t_l2
+    out["achieved_gsamples_shaded_per_s"] = shaded_per_s / 1e9  # inside the kernel (kernel time, not step time)
+    out["frac"] = out["achieved_gsamples_shaded_per_s"] * t
+    out["note"] = ("ceiling = a kernel that issues ONLY the loads of a shaded sample (no shading arithmetic, no empty-space test); "
+                   "the march adds ~800 instructions of illumination per sample, so issue slots bind before the load path does")
+    return out
 
 
 def upload_probe(args):

@@ -194,9 +194,9 @@ typedef enum vr_option {
   VR_OPT_CLEAR_IMAGE = 10,      /* 1 (default) = zero the whole output image first (volumeRender.cpp:271); 0 = only the
                                    pixels of owned tiles are written (every owned pixel is, misses as 0): required when
                                    several ranks render into ONE shared image */
-  VR_OPT_TILE_ORDER = 11,       /* hand-out order of tiles: 1 (default) = most expensive first (measured on the previous launch,
-                                   else centre-first), one list over all frames of a batch; 2 = the same, frame after
-                                   frame; 0 = raster order */
+  VR_OPT_TILE_ORDER = 11,       /* hand-out order of tiles: 1 (default) = the tiles with the longest rays first (measured on
+                                   the previous launch, else centre-first), one list over all frames of a batch; 2 = the
+                                   same, frame after frame; 3 = by the tile's total of shaded samples (A/B); 0 = raster order */
   VR_OPT_WARP_SHAPE = 12,       /* s in [0,5]: one warp marches a (1<<s) x (32>>s) pixel footprint; default 3 = 8 x 4 */
   VR_OPT_GRADIENT_INTERLEAVE = 13 /* 1 (default): the three gradient volumes of lookupGradient are stored interleaved
                                      (16-byte voxels Gx,Gy,Gz,-; one load per tap); 0: three separate volumes.  Takes
@@ -291,6 +291,12 @@ VR_API vr_status vr_debug_warp_times(vr_ctx *ctx, uint64_t *host_pairs, size_t m
 VR_API vr_status vr_device_alloc(vr_ctx *ctx, size_t bytes, void **d_ptr);
 VR_API vr_status vr_device_free(vr_ctx *ctx, void *d_ptr);
 VR_API vr_status vr_device_download(vr_ctx *ctx, void *host_dst, const void *d_src, size_t bytes);
+/* Measurement only: the gather ceilings of this device with the march's access pattern (8x4 bundles of
+ * parallel rays, one trilinear fetch = 8 taps per step; SURVEY 8(d) "BW_gather from a committed
+ * microbenchmark").  kind 0 = eight 4-byte loads per fetch, 1 = eight 16-byte loads, 2 = one tex3D<float>
+ * with hardware linear filtering (the reference's fetch, volumeRender_kernel.cu:544-548), 3 = tex3D<float4>.
+ * Footprint (2^log2_edge)^3 voxels: 5 -> L1, 8 -> L2, 10 -> HBM.  Returns trilinear fetches per second. */
+VR_API vr_status vr_probe_gather(vr_ctx *ctx, int kind, int log2_edge, double *fetches_per_s, double *ms);
 
 #ifdef __cplusplus
 }

@@ -477,3 +477,30 @@ def test_device_epilogue_stereo_compose_and_normalize_sequence(brain64, lut):
             _abi.check(lib.vr_device_download(h, got.ctypes.data, p, got.nbytes), h)
             assert np.allclose(got, want.astype(np.float32), rtol=0, atol=1e-7), np.abs(got - want).max()
             _abi.check(lib.vr_device_free(h, p), h)
+
+
+def test_download_into_pageable_pinned_and_from_device_is_the_same_image(brain64, lut):
+    """vr_render into pageable host memory (MATLAB's mxArray), into pinned memory, and vr_render_device +
+    vr_device_download: the same bytes (odd image size, > 4 MiB)."""
+    import torch
+
+    gpu = vrt.example1_scene(api.VolumeRender, brain64, (1031, 777), lights=2, lut=lut)
+    pageable = gpu.render()
+    assert pageable.nbytes > (4 << 20)
+    lib, h = _abi.lib(), gpu.objectHandle
+    H, W = pageable.shape[:2]
+    pinned = torch.zeros(H * W * 3, dtype=torch.float32).pin_memory()
+    args, keep = api._render_args(gpu.LightSources, gpu.VolumeIllumination, [gpu.FactorEmission, gpu.FactorReflection, gpu.FactorAbsorption],
+                                  gpu.ElementSizeUm, [H, W], np.flipud(np.asarray(gpu.RotationMatrix)),
+                                  [0.0, gpu.FocalLength, gpu.DistanceToObject], gpu.OpacityThreshold, gpu.Color)
+    _abi.check(lib.vr_render(h, *args, C.c_void_p(pinned.data_ptr())), h)
+    assert np.array_equal(pinned.numpy(), pageable.reshape(-1, order="F"))
+    d = C.c_void_p()
+    _abi.check(lib.vr_device_alloc(h, pageable.nbytes, C.byref(d)), h)
+    try:
+        _abi.check(lib.vr_render_device(h, *args, d, None), h)
+        back = np.zeros_like(pageable)
+        _abi.check(lib.vr_device_download(h, back.ctypes.data, d, back.nbytes), h)
+    finally:
+        lib.vr_device_free(h, d)
+    assert np.array_equal(back, pageable)

@@ -125,6 +125,7 @@ def declare(lib):
         "vr_device_alloc": ([vp, C.c_size_t, P(vp)], C.c_int),
         "vr_device_free": ([vp, vp], C.c_int),
         "vr_device_download": ([vp, vp, vp, C.c_size_t], C.c_int),
+        "vr_probe_gather": ([vp, C.c_int, C.c_int, P(C.c_double), P(C.c_double)], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, name)

@@ -256,6 +256,18 @@ void parallel_copy(void *dst, const void *src, size_t bytes) {
   for (auto &t : th) t.join();
 }
 
+// A rendered frame into the caller's host memory (volumeRender.cpp:280-281 + the copy loop of render.cpp:267-269).
+// MATLAB's mxArray is pageable; the driver stages such a copy itself at ~16 GB/s (3.1 ms for a 2048^2 frame, measured).
+// A pinned mirror filled in eight DMA pieces with four host threads moving piece k while piece k+1 is on the wire was
+// tried: 2.1 ms at best, but every few frames the copy threads were descheduled on the bench box and a frame took
+// 40-77 ms instead of 29 (gpurun_out r4).  A steady 3 ms beats a fragile 2: the plain copy stays.  Returns with the
+// stream drained.
+vr_status download_frame(vr_ctx *c, void *out, const void *d_src, size_t bytes) {
+  VR_CUDA(c, cudaMemcpyAsync(out, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
+
 // staging of host sources: kStageBufs buffers in pinned host memory and as many on the device, so
 // that the CPU copy of slab k+1 (pageable -> pinned), the DMA of slab k and its repack overlap
 vr_status ensure_stage(vr_ctx *c, size_t bytes) {
@@ -885,9 +897,11 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
         const uint32_t entry = (uint32_t)(f * ntiles + tile);
         float k = ordered ? tx * tx + ty * ty : (float)(f * owned + j);
         // measured beats guessed: the previous launch's shaded samples per tile (a movie turns slowly), most expensive first
-        if (ordered && use_cost) k = -(float)c->h_tile_cost[tile] + 1e-9f * k;
+        // key: the longest ray of the tile (= the duration of its longest item), then the tile's total
+        if (ordered && use_cost) k = -((float)c->h_tile_cost[ntiles + tile] * 1024.0f + fminf((float)c->h_tile_cost[tile] * (1.0f / 4096.0f), 1023.0f));
         // order 1: one heaviest-first list over all frames of the batch (measured best: 30.3 vs 31.3 ms per frame);
         // order 2: frame after frame, each heaviest-first
+        if (ordered && use_cost && c->opt[VR_OPT_TILE_ORDER] == 3) k = -(float)c->h_tile_cost[tile];  // A/B: by the tile's total
         if (c->opt[VR_OPT_TILE_ORDER] == 2) k = (float)f * 4.0e9f + fminf(fmaxf(k, -1.9e9f), 1.9e9f);
         key[f * owned + j] = std::make_pair(k, entry);
       }
@@ -912,12 +926,12 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       if (c->d_tile_cost) cudaFree(c->d_tile_cost);
       if (c->h_tile_cost) cudaFreeHost(c->h_tile_cost);
       c->d_tile_cost = c->h_tile_cost = nullptr, c->tile_cost_tiles = 0, c->cost_valid = false;
-      VR_CUDA(c, cudaMalloc(&c->d_tile_cost, ntiles * sizeof(unsigned int)));
-      VR_CUDA(c, cudaMallocHost(&c->h_tile_cost, ntiles * sizeof(unsigned int)));
+      VR_CUDA(c, cudaMalloc(&c->d_tile_cost, 2 * ntiles * sizeof(unsigned int)));  // [sum of shaded samples | longest ray] per tile
+      VR_CUDA(c, cudaMallocHost(&c->h_tile_cost, 2 * ntiles * sizeof(unsigned int)));
       c->tile_cost_tiles = ntiles;
     }
     // the host copy of the previous launch is final before it is overwritten: same stream, and use_cost saw its event
-    VR_CUDA(c, cudaMemsetAsync(c->d_tile_cost, 0, ntiles * sizeof(unsigned int), stream));
+    VR_CUDA(c, cudaMemsetAsync(c->d_tile_cost, 0, 2 * ntiles * sizeof(unsigned int), stream));
     P.tile_cost = c->d_tile_cost;
   }
 
@@ -930,7 +944,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, stream, c->sm_count));
   VR_CUDA(c, cudaEventRecord(c->ev1, stream));
   if (P.tile_cost) {
-    VR_CUDA(c, cudaMemcpyAsync(c->h_tile_cost, c->d_tile_cost, ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+    VR_CUDA(c, cudaMemcpyAsync(c->h_tile_cost, c->d_tile_cost, 2 * ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
     VR_CUDA(c, cudaEventRecord(c->ev_cost, stream));
     c->cost_valid = true, c->cost_sig = sig;
   }
@@ -1265,11 +1279,9 @@ vr_status vr_render_batch(vr_ctx *c, const vr_light *lights, size_t n_lights, co
   std::vector<float *> d_outs(n_frames);
   for (size_t f = 0; f < n_frames; ++f) d_outs[f] = c->d_image + f * (bytes / sizeof(float));
   VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_outs.data(), c->stream));
-  for (size_t f = 0; f < n_frames; ++f) {
+  for (size_t f = 0; f < n_frames; ++f)
     if (!out_images[f]) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: null output");
-    VR_CUDA(c, cudaMemcpyAsync(out_images[f], d_outs[f], bytes, cudaMemcpyDeviceToHost, c->stream));
-  }
-  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (size_t f = 0; f < n_frames; ++f) VR_TRY(download_frame(c, out_images[f], d_outs[f], bytes));
   VR_TRY(collect(c));
   c->stats.bytes_resident = resident_bytes(c);
   return VR_OK;
@@ -1292,8 +1304,7 @@ vr_status vr_render(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr
   }
   VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &c->d_image, c->stream));
   // cudaDeviceSynchronize + cudaMemcpy D2H (volumeRender.cpp:280-281)
-  VR_CUDA(c, cudaMemcpyAsync(out, c->d_image, bytes, cudaMemcpyDeviceToHost, c->stream));
-  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  VR_TRY(download_frame(c, out, c->d_image, bytes));
   VR_TRY(collect(c));
   c->stats.bytes_resident = resident_bytes(c);
   return VR_OK;
@@ -1481,6 +1492,13 @@ vr_status vr_device_upload(vr_ctx *c, void *d_dst, const void *host_src, size_t 
   VR_CUDA(c, cudaStreamSynchronize(c->stream));
   return VR_OK;
 }
+vr_status vr_probe_gather(vr_ctx *c, int kind, int log2_edge, double *fetches_per_s, double *ms) {
+  VR_CHECK_HANDLE(c);
+  if (!fetches_per_s || !ms || kind < 0 || kind > 3 || log2_edge < 4 || log2_edge > 10) return fail(c, VR_ERR_INVALID_ARGUMENT, "probe_gather: bad arguments");
+  VR_TRY(set_device(c));
+  VR_CUDA(c, launch_probe_gather(kind, log2_edge, c->sm_count, c->stream, fetches_per_s, ms));
+  return VR_OK;
+}
 vr_status vr_device_alloc(vr_ctx *c, size_t bytes, void **d_ptr) {
   VR_CHECK_HANDLE(c);
   if (!d_ptr) return fail(c, VR_ERR_INVALID_ARGUMENT, "null pointer");
@@ -1506,9 +1524,8 @@ vr_status vr_debug_warp_times(vr_ctx *c, uint64_t *host_pairs, size_t max_warps)
 vr_status vr_device_download(vr_ctx *c, void *host_dst, const void *d_src, size_t bytes) {
   VR_CHECK_HANDLE(c);
   VR_TRY(set_device(c));
-  VR_CUDA(c, cudaMemcpyAsync(host_dst, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
-  VR_CUDA(c, cudaStreamSynchronize(c->stream));
-  return VR_OK;
+  if (!host_dst || !d_src) return fail(c, VR_ERR_INVALID_ARGUMENT, "null pointer");
+  return download_frame(c, host_dst, d_src, bytes);
 }
 
 }  // extern "C"
