@@ -542,9 +542,9 @@ def run_b200(args):
     achieved = per_launch_shaded * bps / (kavg_ms * 1e-3) / 1e9
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v4_summary.md:
-        # 4.90 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
-        "traffic": (2.45e9 * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v5_summary.md:
+        # 5.19 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
+        "traffic": (2.6e9 * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
         "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "peak_source": peak_src,
         "bytes_per_sample": bps, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
         "achieved_if_every_marched_sample_gathered": per_launch_marched * bps / (kavg_ms * 1e-3) / 1e9,
@@ -610,7 +610,11 @@ def gather_probe(lib, ctx, args, n_lights, shaded_per_s):
            "unit": "G trilinear fetches/s"}
     for name, kind, e in (("ldg4_L1_32^3", 0, 5), ("ldg4_L2_256^3", 0, 8), ("ldg4_HBM_1024^3", 0, 10), ("ldg16_L2_128^3", 1, 7), ("ldg16_HBM_512^3", 1, 9),
                           ("tex_f32_L1_32^3", 2, 5), ("tex_f32_L2_256^3", 2, 8), ("tex_f32_HBM_1024^3", 2, 10), ("tex_f32x4_L2_128^3", 3, 7), ("tex_f32x4_HBM_512^3", 3, 9)):
-        out[name] = probe(kind, e) / 1e9
+        try:
+            out[name] = probe(kind, e) / 1e9
+        except Exception as ex:  # e.g. gather from layered arrays refused by the driver: the other probes still count
+            out[name] = None
+            out.setdefault("failed", {})[name] = repr(ex)[:200]
     # fetches of one shaded sample: gradient volumes -> emission + reflection (8 x 4 B each), one interleaved
     # gradient fetch (8 x 16 B), L LUT fetches (8 x 4 B, 1.1 MiB table: L1/L2); on the fly -> emission + reflection + 6 more + L LUT
     if args.gradient == "lookup":
