@@ -56,6 +56,8 @@ def parse():
     p.add_argument("--no-upload-probe", action="store_true", help="skip the host->resident upload measurement")
     p.add_argument("--no-gather-probe", action="store_true", help="skip the gather-ceiling microbenchmark (roofline.gather)")
     p.add_argument("--interleave", type=int, default=1, help="1: Gx,Gy,Gz resident as one interleaved storage (default); 0: three volumes")
+    p.add_argument("--texture-unit", type=int, default=0, help="1: VR_OPT_TEXTURE_UNIT (hardware-filtered fetches on cudaArray copies, fp32 only); default 0")
+    p.add_argument("--no-texture-leg", action="store_true", help="skip the extra texture-unit measurement of the default run")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
                    help="image = tiles over replicated volumes (the metric's config); volume = bricks sharded over the ranks, sort-last composite (config 5)")
@@ -281,6 +283,7 @@ def workload_config(args, scene, size=None):
         "multi_gpu": "image-space tiles %dx%d round-robin over replicated volumes; %s" % (
             args.tile, args.tile, "kernels store their tiles straight into rank 0's image over NVLink (CUDA IPC), one barrier per frame" if args.exchange == "p2p" else "NCCL sum-reduce of partial images to rank 0"),
         "frames_per_launch": max(1, min(args.batch, args.steps)),
+        "fetch": "texture unit (hardware linear filter, 1.8 fixed-point weights)" if getattr(args, "texture_unit", 0) else "loads + fp32 lerps",
         "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames",
     }
 
@@ -311,6 +314,8 @@ def run_b200(args):
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_TILE_ORDER, args.order), ctx)
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_WARP_SHAPE, args.wshape), ctx)
     lib.vr_set_option(ctx, _abi.OPT_GRADIENT_INTERLEAVE, args.interleave)  # unchecked: older A/B builds lack the option
+    if args.texture_unit:
+        _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, 1), ctx)
     scene = Scene(args)
     n = args.size
     dt = _abi.DTYPE_F32 if args.dtype == "f32" else _abi.DTYPE_BF16
@@ -562,6 +567,34 @@ def run_b200(args):
     }
     if single is not None:
         line["e2e"]["single_frame"] = single
+
+    # ---- the same frames with every fetch through the texture unit (VR_OPT_TEXTURE_UNIT, opt-in: hardware filter) ----
+    if world == 1 and not args.texture_unit and args.dtype == "f32" and not args.no_texture_leg:
+        try:
+            _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, 1), ctx)
+            frame_device(-B, B)  # builds the cudaArray copies, warm-up
+            torch.cuda.synchronize()
+            t_s = t_k = 0.0
+            t_shaded = 0
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for k in range(0, args.steps, B):
+                frame_device(k, min(B, args.steps - k))
+                st = stats()
+                t_shaded += st.samples_shaded
+                t_k += st.kernel_ms
+            e1.record(stream)
+            torch.cuda.synchronize()
+            t_s = e0.elapsed_time(e1)
+            line["texture_unit"] = {
+                "ms_per_step": t_s / args.steps, "value": samples_all / (t_s * 1e-3) / 1e9, "unit": "Gsamples/s", "kernel_ms_per_frame": t_k / args.steps,
+                "gsamples_shaded_per_s": t_shaded / (t_s * 1e-3) / 1e9,
+                "note": "opt-in VR_OPT_TEXTURE_UNIT = 1: the reference's own fetch (tex3D, hardware linear filter, 1.8 fixed-point weights) on cudaArray copies of the "
+                        "resident volumes; same frames, device-resident timing like `value`.  Not the default: the parity bar is stated on the fp32-weight render math "
+                        "(tests/test_golden_refcuda.py holds both modes to the reference kernel's own images)"}
+            _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, 0), ctx)
+        except Exception as ex:
+            line["texture_unit"] = {"failed": repr(ex)[:300]}
 
     # ---- gather ceilings of this box with the march's access pattern (BW_gather, measured live) ----
     if world == 1 and not args.no_gather_probe:

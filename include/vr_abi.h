@@ -198,9 +198,14 @@ typedef enum vr_option {
                                    the previous launch, else centre-first), one list over all frames of a batch; 2 = the
                                    same, frame after frame; 3 = by the tile's total of shaded samples (A/B); 0 = raster order */
   VR_OPT_WARP_SHAPE = 12,       /* s in [0,5]: one warp marches a (1<<s) x (32>>s) pixel footprint; default 3 = 8 x 4 */
-  VR_OPT_GRADIENT_INTERLEAVE = 13 /* 1 (default): the three gradient volumes of lookupGradient are stored interleaved
+  VR_OPT_GRADIENT_INTERLEAVE = 13, /* 1 (default): the three gradient volumes of lookupGradient are stored interleaved
                                      (16-byte voxels Gx,Gy,Gz,-; one load per tap); 0: three separate volumes.  Takes
                                      effect at the next upload of the gradient volumes; pixels are bit-identical */
+  VR_OPT_TEXTURE_UNIT = 14      /* 0 (default): trilinear fetches are loads + fp32 lerps (the render math the parity bar is
+                                   stated on).  1: every fetch goes through the texture unit on cudaArray copies of the
+                                   volumes, configured as the reference configures its textures (volumeRender_kernel.cu:
+                                   544-548) - the reference's own hardware filtering with 1.8 fixed-point weights; fp32
+                                   whole-volume contexts only (VR_ERR_UNSUPPORTED otherwise), twice the volume memory */
 } vr_option;
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);

@@ -67,6 +67,22 @@ def test_product_against_the_reference_kernel_on_b200(name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(vrt.golden_scenes()))
+def test_texture_unit_mode_against_the_reference_kernel_on_b200(name):
+    """VR_OPT_TEXTURE_UNIT: every fetch through the texture unit, configured like the reference's textures - the same
+    hardware filter the golden images were rendered with.  Held to the same envelope; the deviation that remains is
+    nvcc's FMA contraction and rsqrtf/__expf in the reference's arithmetic, not the filter."""
+    from volume_renderer_b200 import _abi, api
+
+    gold = np.load(os.path.join(GOLD, "refcuda_%s.npy" % name))
+    r = vrt.golden_scenes()[name](api.VolumeRender)
+    r.setOption(_abi.OPT_TEXTURE_UNIT, 1)
+    e = envelope(r.render(), gold)
+    print(name, e)
+    check_envelope(e, name)
+
+
+@pytest.mark.gpu
 def test_shimmed_reference_still_reproduces_its_golden():
     """When oracle/_ref/libref_cuda.so travelled to the box: the reference kernel, run again in a fresh
     process, reproduces the committed image (same GPU generation, same toolchain)."""

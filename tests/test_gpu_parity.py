@@ -504,3 +504,42 @@ def test_download_into_pageable_pinned_and_from_device_is_the_same_image(brain64
     finally:
         lib.vr_device_free(h, d)
     assert np.array_equal(back, pageable)
+
+
+def test_texture_unit_mode(brain64, lut):
+    """VR_OPT_TEXTURE_UNIT = 1: the reference's own fetch (hardware linear filter, 1.8 fixed-point weights) on cudaArray
+    copies of the resident volumes.  Against the oracle with the same 8-bit weights the image agrees to the hardware
+    envelope (tests/test_golden_refcuda.py), the sample lattice is the same, a dirty volume reaches the array, and the
+    mode refuses what it cannot do."""
+    from test_golden_refcuda import envelope
+
+    for grad in (False, True):
+        gpu, orc = _pair(brain64, (160, 128), 2, lut)
+        if grad:
+            gx, gy, gz = api.Volume(brain64).grad()
+            for r in (gpu, orc):
+                r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
+        gpu.setOption(_abi.OPT_TEXTURE_UNIT, 1)
+        orc._backend.lib.orc_set_option(orc.objectHandle, vrt.ORC_OPT_FILTER_FRAC_BITS, 8)
+        img, ref = gpu.render(), orc.render()
+        e = envelope(img, ref)
+        print("texture unit vs oracle(8-bit weights), gradient volumes:", grad, e)
+        assert np.isfinite(img).all()
+        assert e["psnr_db"] >= 68.0 and e["frac_within_1e-3"] >= 0.97 and e["max"] <= 3e-2 and e["median"] <= 5e-4, e
+        a, b = gpu.stats()["samples_marched"], orc._backend.stats(orc.objectHandle).samples_marched
+        assert abs(a - b) <= 1e-3 * b + 2, (a, b)
+    # a dirty volume is re-uploaded AND reaches the array: same image as a fresh context
+    gpu = vrt.example1_scene(api.VolumeRender, brain64, (96, 96), lights=1, lut=lut)
+    gpu.setOption(_abi.OPT_TEXTURE_UNIT, 1)
+    first = gpu.render()
+    other = np.asfortranarray(brain64[::-1, :, :] * 0.5)
+    gpu.VolumeEmission = api.Volume(other)
+    gpu.VolumeAbsorption = gpu.VolumeEmission
+    second = gpu.render()
+    fresh = vrt.example1_scene(api.VolumeRender, other, (96, 96), lights=1, lut=lut)
+    fresh.setOption(_abi.OPT_TEXTURE_UNIT, 1)
+    assert np.array_equal(second, fresh.render()) and not np.array_equal(first, second)
+    # switching the mode off again gives the load path's image bit for bit
+    gpu.setOption(_abi.OPT_TEXTURE_UNIT, 0)
+    plain = vrt.example1_scene(api.VolumeRender, other, (96, 96), lights=1, lut=lut)
+    assert np.array_equal(gpu.render(), plain.render())

@@ -38,6 +38,7 @@ OPT_CLEAR_IMAGE = 10
 OPT_TILE_ORDER = 11
 OPT_WARP_SHAPE = 12
 OPT_GRADIENT_INTERLEAVE = 13
+OPT_TEXTURE_UNIT = 14
 IPC_HANDLE_BYTES = 64
 
 

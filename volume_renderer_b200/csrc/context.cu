@@ -87,6 +87,12 @@ struct Resident {
   // (`storage` then points at vr_ctx::g4 and is not owned)
   bool shared = false;
   int estride = 1, ecomp = 0;
+  // texture-unit mode (VR_OPT_TEXTURE_UNIT): the same voxels as a w x h x d cudaArray behind a texture object configured
+  // like the reference's (kernel.cu:544-548); built lazily from `storage`, dropped whenever `storage` is rewritten
+  cudaArray_t array = nullptr;
+  cudaTextureObject_t texobj = 0;
+  size_t array_bytes = 0;
+  bool array_valid = false;
 };
 
 // geometry of the interleaved gradient storage: a gradient volume joins it when it matches
@@ -206,12 +212,14 @@ void release(vr_ctx *c, Resident &r) {
   }
   if (r.occ) cudaFree(r.occ);
   if (r.dist) cudaFree(r.dist);
+  if (r.texobj) cudaDestroyTextureObject(r.texobj);
+  if (r.array) cudaFreeArray(r.array);
   r = Resident();
 }
 
 uint64_t resident_bytes(const vr_ctx *c) {
   uint64_t b = 0;
-  for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes + c->tex[i].dist_bytes;
+  for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes + c->tex[i].dist_bytes + c->tex[i].array_bytes;
   b += c->image_cap + kStageBufs * c->stage_cap + c->lights_more_cap + c->g4_bytes;
   return b;
 }
@@ -292,6 +300,7 @@ vr_status ensure_stage(vr_ctx *c, size_t bytes) {
 // slices a slab needs, then a repack kernel that writes the padded, bricked storage); only the z
 // slices inside the box cross PCIe.
 vr_status fill_resident(vr_ctx *c, Resident &r, const HostVol &v, const int box[6]) {
+  r.array_valid = false;  // the texture-unit copy (if any) is refilled from the storage before the next launch that uses it
   const int64_t dims[3] = {r.w, r.h, r.d};
   const int64_t g0[3] = {r.ox - 1, r.oy - 1, r.oz - 1};  // global voxel of local padded index 0
   const size_t es = elem_size(v.dtype);
@@ -487,6 +496,43 @@ vr_status ensure_skip_grids(vr_ctx *c, Resident &r, cudaStream_t stream) {
   return VR_OK;
 }
 
+// Texture-unit mode: the volume as a cudaArray behind a texture object with the reference's settings
+// (createTextureFromVolume, kernel.cu:522-554: normalized coordinates, linear filter, clamp, element type), filled from
+// the resident padded storage - one path whatever the source was (host, device, partial update, interleaved component).
+vr_status ensure_array(vr_ctx *c, Resident &r, cudaStream_t stream) {
+  if (r.kind != TEX_VOLUME || r.array_valid) return VR_OK;
+  if (r.dtype != VR_DTYPE_F32) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode needs fp32 volumes (the filter has no bf16 element type)");
+  if (r.ox || r.oy || r.oz || r.lw != r.w + 2 || r.lh != r.h + 2 || r.ld != r.d + 2)
+    return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode needs whole volumes (no vr_set_region)");
+  if (r.w > 16384 || r.h > 16384 || r.d > 16384) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode: a 3D array holds at most 16384 voxels per axis");
+  if (!r.array) {
+    const cudaChannelFormatDesc cd = cudaCreateChannelDesc<float>();
+    VR_CUDA(c, cudaMalloc3DArray(&r.array, &cd, make_cudaExtent((size_t)r.w, (size_t)r.h, (size_t)r.d), cudaArraySurfaceLoadStore));
+    r.array_bytes = (size_t)r.w * r.h * r.d * sizeof(float);
+    cudaResourceDesc rd = {};
+    rd.resType = cudaResourceTypeArray;
+    rd.res.array.array = r.array;
+    cudaTextureDesc td = {};
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;  // kernel.cu:546-548
+    td.filterMode = cudaFilterModeLinear;                                                // kernel.cu:545
+    td.readMode = cudaReadModeElementType;
+    td.normalizedCoords = 1;                                                             // kernel.cu:544
+    VR_CUDA(c, cudaCreateTextureObject(&r.texobj, &rd, &td, nullptr));
+  }
+  cudaResourceDesc rd = {};
+  rd.resType = cudaResourceTypeArray;
+  rd.res.array.array = r.array;
+  cudaSurfaceObject_t surf = 0;
+  VR_CUDA(c, cudaCreateSurfaceObject(&surf, &rd));
+  const cudaError_t e = launch_fill_array(describe(r), r.layout, (unsigned long long)surf, stream);
+  // the kernel has the handle by value; destroying the object after the launch is ordered behind it by the stream sync
+  if (e == cudaSuccess) cudaStreamSynchronize(stream);
+  cudaDestroySurfaceObject(surf);
+  VR_CUDA(c, e);
+  r.array_valid = true;
+  return VR_OK;
+}
+
 // syncVolume (kernel.cu:659-672): whatever the flag says, the old array is released and the
 // volume is uploaded again.
 vr_status syncVolume(vr_ctx *c, int slot, const HostVol &v) { return upload(c, slot, v); }
@@ -617,6 +663,7 @@ TexDesc describe(const Resident &r) {
   t.ox = r.ox, t.oy = r.oy, t.oz = r.oz;
   t.lw = r.lw, t.lh = r.lh, t.ld = r.ld;
   t.estride = r.estride, t.ecomp = r.ecomp;
+  t.tex = r.array_valid ? (unsigned long long)r.texobj : 0ull;
   return t;
 }
 
@@ -692,6 +739,12 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   // role -> texture through the redirect indices (kernel.cu:127-144)
   int sEm = c->idxEm, sAb = c->idxAb, sRe = c->idxRe;
   if (c->opt[VR_OPT_ABSORPTION_ROLE_FIX] && c->tex[S_AB].kind != TEX_UNBOUND) sAb = S_AB;
+  const bool texhw = c->opt[VR_OPT_TEXTURE_UNIT] != 0;
+  if (texhw) {
+    if (vs) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode is not available for volume-space passes");
+    const int need[] = {sEm, sAb, sRe, S_EM, S_DX, S_DY, S_DZ, S_LIGHT};
+    for (int sl : need) VR_TRY(ensure_array(c, c->tex[sl], stream));
+  }
   P.em = describe(c->tex[sEm]);
   P.ab = describe(c->tex[sAb]);
   P.re = describe(c->tex[sRe]);
@@ -759,6 +812,12 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   }
   if (c->opt[VR_OPT_KERNEL_VARIANT] == 3 && P.uniform == 1 && layout == LAYOUT_BRICK) P.uniform = 2;  // variant 3: force the 64-bit kernels (tests)
   if (P.frac_bits) P.uniform = 0;  // fixed-point weights (A/B option) are compiled into the per-texture kernels only
+  if (texhw) {
+    if (wide) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode: volume too large");
+    if (dtype != VR_DTYPE_F32) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode needs fp32 volumes");
+    P.uniform = 0, P.frac_bits = 0;  // the hardware filters (1.8 fixed-point weights by construction)
+    layout = LAYOUT_TEXHW;
+  }
 
   // volume-space mode
   P.vs_mode = 0;
@@ -1350,14 +1409,14 @@ int vr_abi_version(void) { return VR_ABI_VERSION; }
 
 vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_GRADIENT_INTERLEAVE) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_TEXTURE_UNIT) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
   c->opt[option] = value;
   return VR_OK;
 }
 vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_GRADIENT_INTERLEAVE || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option > VR_OPT_TEXTURE_UNIT || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   *value = c->opt[option];
   return VR_OK;
 }

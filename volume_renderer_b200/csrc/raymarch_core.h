@@ -108,6 +108,8 @@ struct Addr<LAYOUT_LINEAR> {
   static VR_HD size_t z(int Z, uint32_t sz) { return (size_t)(uint32_t)Z * sz; }  // the z term alone may pass 2^32 elements
 };
 template <>
+struct Addr<LAYOUT_TEXHW> : Addr<LAYOUT_LINEAR> {};  // never addressed (texture-unit launches), only instantiated
+template <>
 struct Addr<LAYOUT_BRICK> {
   static VR_HD uint32_t x(int X) { return (((uint32_t)X >> BRICK_SHIFT) << 9) + ((uint32_t)X & BRICK_MASK); }
   static VR_HD uint32_t y(int Y, uint32_t sy) { return ((uint32_t)Y >> BRICK_SHIFT) * sy + (((uint32_t)Y & BRICK_MASK) << 3); }
@@ -211,8 +213,17 @@ VR_HD float tex3d_volume(const TexDesc &t, float x, float y, float z, int frac_b
 // is exact with a + f*(b-a) lerps), anything else is fetched.
 template <int LAYOUT, typename E>
 VR_HD float tex3d_any(const TexDesc &t, float x, float y, float z, int frac_bits) {
-  if (t.kind == TEX_VOLUME) return tex3d_volume<LAYOUT, E>(t, x, y, z, frac_bits);
-  return t.kind == TEX_CONST ? t.cval : 0.0f;
+  if (LAYOUT == LAYOUT_TEXHW) {
+#if defined(__CUDA_ARCH__)
+    // the reference's own fetch (kernel.cu:439-447 on textures configured at :544-548): normalized coordinates,
+    // clamp-to-edge, hardware linear filter with 1.8 fixed-point weights; a NaN coordinate reads as 0 in hardware
+    if (t.kind == TEX_VOLUME) return tex3D<float>((cudaTextureObject_t)t.tex, x, y, z);
+#endif
+    return t.kind == TEX_CONST ? t.cval : 0.0f;
+  } else {
+    if (t.kind == TEX_VOLUME) return tex3d_volume<LAYOUT == LAYOUT_TEXHW ? LAYOUT_LINEAR : LAYOUT, E>(t, x, y, z, frac_bits);
+    return t.kind == TEX_CONST ? t.cval : 0.0f;
+  }
 }
 
 // ---- shared tap sets ---------------------------------------------------------------------
@@ -452,7 +463,7 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
     const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
     const float c = div_pi(vr_acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))));
     // the LUT is always fp32 in the linear padded layout
-    const float light = tex3d_any<LAYOUT_LINEAR, ElemF32>(P.lut, a, b, c, fb);
+    const float light = tex3d_any<LAYOUT == LAYOUT_TEXHW ? LAYOUT_TEXHW : LAYOUT_LINEAR, ElemF32>(P.lut, a, b, c, fb);
     illum = illum + reflection * light * lcol * color;  // kernel.cu:349
   }
   return illum;

@@ -215,6 +215,8 @@ cudaError_t launch_raymarch_lookup(const KernelParams &P, int layout, int dtype,
 #else
 cudaError_t launch_raymarch_compute(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
 #endif
+  // texture-unit launches: fp32 arrays, per-texture fetches (there are no tap sets to share)
+  if (layout == LAYOUT_TEXHW) return dtype == 0 && P.uniform == 0 ? launch_one<VR_GRAD, LAYOUT_TEXHW, ElemF32, 0>(P, stream, sm_count) : cudaErrorInvalidValue;
   if (dtype == 0) return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemF32>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemF32>(P, stream, sm_count);
   return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemBF16>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemBF16>(P, stream, sm_count);
 }

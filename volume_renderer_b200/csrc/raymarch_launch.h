@@ -70,6 +70,10 @@ cudaError_t launch_normalize(float *const *imgs, int n_imgs, size_t n_each, unsi
 // MATLAB gradient() of a MATLAB-layout volume (Volume.m:181-205): gx = d/d dim2, gy = d/d dim1, gz = d/d dim3
 cudaError_t launch_gradient(const void *d_in, int w, int h, int d, int dtype, void *gx, void *gy, void *gz, cudaStream_t stream);
 
+// texture-unit mode (VR_OPT_TEXTURE_UNIT): copies the voxels of a whole resident fp32 volume (padded storage, any layout,
+// interleaved component or not) into a w x h x d cudaArray through a surface object
+cudaError_t launch_fill_array(const TexDesc &t, int layout, unsigned long long surface, cudaStream_t stream);
+
 // probe_kernels.cu: gather ceilings of the box with the march's access pattern; kind 0 = 8 x 4-byte
 // loads per fetch, 1 = 8 x 16-byte loads, 2 = tex3D<float> linear, 3 = tex3D<float4> linear; footprint (2^log2_edge)^3 voxels
 cudaError_t launch_probe_gather(int kind, int log2_edge, int sm_count, cudaStream_t stream, double *fetches_per_s, double *ms);

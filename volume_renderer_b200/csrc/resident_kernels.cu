@@ -75,6 +75,33 @@ cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
+// ---- texture-unit mode: padded storage -> cudaArray ---------------------------------------------
+// One thread per voxel, x fastest: a warp reads one or two brick rows and writes 128 contiguous bytes of the array's
+// row (the array's own tiling is the driver's business).  HBM bound: 4 bytes read + 4 written per voxel.
+template <int LAYOUT>
+__global__ void __launch_bounds__(256) k_fill_array(const TexDesc t, cudaSurfaceObject_t surf) {
+  const uint64_t n = (uint64_t)t.w * t.h * t.d;
+  const int es = t.estride > 1 ? t.estride : 1;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % (uint64_t)t.w), y = (int)((i / (uint64_t)t.w) % (uint64_t)t.h), z = (int)(i / ((uint64_t)t.w * t.h));
+    typedef Addr<LAYOUT> A;
+    const size_t off = A::z(z + 1 - t.oz, t.sz) + A::y(y + 1 - t.oy, t.sy) + A::x(x + 1 - t.ox);  // voxel v sits at padded index v + 1
+    const float v = __ldg(static_cast<const float *>(t.p) + off * (size_t)es + (size_t)t.ecomp);
+    surf3Dwrite(v, surf, x * (int)sizeof(float), y, z);
+  }
+}
+cudaError_t launch_fill_array(const TexDesc &t, int layout, unsigned long long surface, cudaStream_t stream) {
+  const uint64_t n = (uint64_t)t.w * t.h * t.d;
+  if (n == 0) return cudaSuccess;
+  uint64_t blocks = (n + 255) / 256;
+  if (blocks > 148ull * 64) blocks = 148ull * 64;
+  if (layout == LAYOUT_BRICK)
+    k_fill_array<LAYOUT_BRICK><<<(unsigned)blocks, 256, 0, stream>>>(t, (cudaSurfaceObject_t)surface);
+  else
+    k_fill_array<LAYOUT_LINEAR><<<(unsigned)blocks, 256, 0, stream>>>(t, (cudaSurfaceObject_t)surface);
+  return cudaGetLastError();
+}
+
 // ---- occupancy ------------------------------------------------------------------------------
 // One warp per macro cell: scans padded voxels [8c+1-dilate, 8c+8+dilate] per axis (voxel index
 // v sits at padded index v+1; the replicated border only repeats edge voxels, so reading it is

@@ -22,7 +22,9 @@ enum TexKind {
   TEX_VOLUME = 2
 };
 
-enum Layout { LAYOUT_LINEAR = 0, LAYOUT_BRICK = 1 };
+// LAYOUT_TEXHW: the launch fetches through the texture unit (TexDesc::tex, hardware linear filtering as the reference
+// configures it, kernel.cu:544-548); the padded storage then only feeds the empty-space grids
+enum Layout { LAYOUT_LINEAR = 0, LAYOUT_BRICK = 1, LAYOUT_TEXHW = 2 };
 enum { BRICK = 8, BRICK_SHIFT = 3, BRICK_MASK = 7, BRICK_ELEMS = 512 };
 enum { CELL_SHIFT = 3 };  // empty-space macro cell = 8^3 voxels
 
@@ -50,6 +52,7 @@ struct TexDesc {
   // three gradient volumes, which share ONE storage of 4-element voxels (Gx, Gy, Gz, unused) so
   // that lookupGradient costs one 16-byte load per tap instead of three 4-byte ones.
   int estride, ecomp;
+  unsigned long long tex;  // cudaTextureObject_t of the volume's cudaArray (VR_OPT_TEXTURE_UNIT), else 0
 };
 
 enum { MAX_PARAM_LIGHTS = 8 };
