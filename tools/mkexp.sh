@@ -11,5 +11,5 @@ cp $root/include/*.h $tmp/include/
 make -C $tmp/volume_renderer_b200/csrc clean > /dev/null
 make -C $tmp/volume_renderer_b200/csrc -j4 EXTRA="$flags" > $tmp/build.log 2>&1 || (tail -20 $tmp/build.log; false)
 cp $tmp/volume_renderer_b200/csrc/libvr_b200.so $root/exp_libs/libvr_$name.so
-grep -h "k_raymarch.*Li1ELi1ENS_7ElemF32ELi1E" -A2 $tmp/volume_renderer_b200/csrc/raymarch_lookup.ptxas.log | grep -h "spill\|Used" | head -2
+grep -h "k_raymarch.*Li1ELi2ENS_7ElemF32ELi0E" -A2 $tmp/volume_renderer_b200/csrc/raymarch_lookup.ptxas.log | grep -h "spill\|Used" | head -2
 rm -rf $tmp

@@ -39,13 +39,26 @@ namespace vrb {
 //   lookupGradient, interleaved Gx,Gy,Gz: 256x3 (80 regs) 25.1 | 128x7 (72) 24.5 | 256x4 (64) 25.1
 //   computeGradient                     : 256x3 (80 regs) 27.8 | 128x7 (72) 27.5 | 256x4 (64) 29.3 | 128x5 (96) 28.8
 // -DVR_BLOCK_THREADS / -DVR_MIN_BLOCKS override both (A/B builds).
-template <int GRAD>
+template <int GRAD, int LAYOUT>
 struct Tune {
 #if defined(VR_BLOCK_THREADS) && defined(VR_MIN_BLOCKS)
   static constexpr int threads = VR_BLOCK_THREADS, min_blocks = VR_MIN_BLOCKS;
 #else
   static constexpr int threads = 128, min_blocks = 7;
 #endif
+};
+// texture-unit kernels: no tap arithmetic to keep live, the fetch latency is longer -> more resident warps.
+// Measured (ms per frame, configs[1] / computeGradient with 1 light): 128x6 17.6 / 17.0 | 128x7 16.3 / 16.0 |
+// 128x8 (64 registers) 15.9 / 15.2 | 256x4 15.9 / 15.2 | 128x10 (48) 16.8 / 17.2 | 128x12 (40) 17.7 / 17.6
+#ifndef VR_TEX_THREADS
+#define VR_TEX_THREADS 128
+#endif
+#ifndef VR_TEX_MIN_BLOCKS
+#define VR_TEX_MIN_BLOCKS 8
+#endif
+template <int GRAD>
+struct Tune<GRAD, LAYOUT_TEXHW> {
+  static constexpr int threads = VR_TEX_THREADS, min_blocks = VR_TEX_MIN_BLOCKS;
 };
 static constexpr unsigned kFull = 0xffffffffu;
 #ifndef VR_JUMP_LANES
@@ -56,7 +69,7 @@ static constexpr unsigned kFull = 0xffffffffu;
 #endif
 
 template <int GRAD, int LAYOUT, typename E, int UNI>
-__global__ void __launch_bounds__(Tune<GRAD>::threads, Tune<GRAD>::min_blocks) k_raymarch(const __grid_constant__ KernelParams P) {
+__global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT>::min_blocks) k_raymarch(const __grid_constant__ KernelParams P) {
   const int lane = threadIdx.x & 31;
   const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);
@@ -187,7 +200,7 @@ __global__ void __launch_bounds__(Tune<GRAD>::threads, Tune<GRAD>::min_blocks) k
 
 template <int GRAD, int LAYOUT, typename E, int UNI>
 static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
-  constexpr int kBlockThreads = Tune<GRAD>::threads;
+  constexpr int kBlockThreads = Tune<GRAD, LAYOUT>::threads;
   int per_sm = 0;
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E, UNI>, kBlockThreads, 0);
   if (e != cudaSuccess) return e;
