@@ -110,6 +110,11 @@ extern "C" void mexFunction(int nlhs, mxArray *plhs[], int nrhs, const mxArray *
     if (s != VR_OK) fail(ctx, "update_box failed");
     return;
   }
+  if (!strcmp("set_option", cmd)) {  // extension, no reference counterpart: volumeRender('set_option', h, option, value)  (vr_option, include/vr_abi.h)
+    if (nrhs != 4) mexErrMsgTxt("insufficient parameter!");
+    if (vr_set_option(ctx, (int)mxGetScalar(prhs[2]), (int64_t)mxGetScalar(prhs[3])) != VR_OK) fail(ctx, "set_option failed");
+    return;
+  }
   if (!strcmp("render", cmd)) {  // render.cpp:134-277
     if (nrhs < 11) mexErrMsgTxt("insufficient parameter!");  // render.cpp:136-140
     // lights + illumination: skipped when either is a logical placeholder (render.cpp:145-146)

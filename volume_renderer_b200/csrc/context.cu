@@ -1052,6 +1052,8 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->opt[VR_OPT_CLEAR_IMAGE] = 1;
   c->opt[VR_OPT_TILE_ORDER] = 1;
   c->opt[VR_OPT_WARP_SHAPE] = 3;
+  // opt-in without touching the MATLAB classes: VR_TEXTURE_UNIT=1 in the environment of the MATLAB process
+  if (const char *tu = getenv("VR_TEXTURE_UNIT")) c->opt[VR_OPT_TEXTURE_UNIT] = atoi(tu) != 0;
   cudaError_t ce = cudaSetDevice(device);
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   c->own_stream = ce == cudaSuccess;
