@@ -35,7 +35,7 @@ void orc_destroy(orc_ctx *ctx);
 
 /* options (same numbering as vr_option where they overlap) */
 enum {
-  ORC_OPT_FILTER_FRAC_BITS = 0,    /* 0 = fp32 weights, 8 = texture-unit 1.8 fixed point */
+  ORC_OPT_FILTER_FRAC_BITS = 0,    /* 0 = fp32 weights, 8 = documented 1.8 fixed-point weights, 9 = the filter as measured on the B200 texture unit */
   ORC_OPT_ABSORPTION_ROLE_FIX = 3, /* 0 = reference as written */
   ORC_OPT_BORROW_HOST_DATA = 100,  /* 1 = "upload" keeps a pointer instead of a copy (big baselines) */
   ORC_OPT_THREADS = 101,           /* OpenMP threads, 0 = all */

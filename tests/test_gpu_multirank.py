@@ -128,6 +128,7 @@ def _vs_worker(rank, world, port, out_path):
             vs.close()
     if rank == 0:
         whole = vrt.example1_scene(api.VolumeRender, vol, RES, lights=2, lut=lut)
+        whole.setOption(_abi.OPT_TEXTURE_UNIT, 0)  # region contexts fetch with loads: compare like with like
         whole.FactorAbsorption = 30.0
         whole.rotate(0, 20, 0)
         np.savez(out_path, full=whole.render(), **imgs)

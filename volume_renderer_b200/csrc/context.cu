@@ -154,6 +154,7 @@ struct vr_ctx {
   unsigned long long *d_stats = nullptr;  // 3 counters
   unsigned long long *h_stats = nullptr;  // pinned
   // volume-space mode: the voxel sub-box this context owns (region_on == false: everything)
+  bool texhw_failed = false;  // VR_OPT_TEXTURE_UNIT = 2: the array copies did not fit; retried after the next upload
   bool region_on = false;
   int64_t rlo[3] = {0, 0, 0}, rhi[3] = {0, 0, 0};
   int halo = 2;
@@ -301,6 +302,7 @@ vr_status ensure_stage(vr_ctx *c, size_t bytes) {
 // slices inside the box cross PCIe.
 vr_status fill_resident(vr_ctx *c, Resident &r, const HostVol &v, const int box[6]) {
   r.array_valid = false;  // the texture-unit copy (if any) is refilled from the storage before the next launch that uses it
+  c->texhw_failed = false;
   const int64_t dims[3] = {r.w, r.h, r.d};
   const int64_t g0[3] = {r.ox - 1, r.oy - 1, r.oz - 1};  // global voxel of local padded index 0
   const size_t es = elem_size(v.dtype);
@@ -499,6 +501,16 @@ vr_status ensure_skip_grids(vr_ctx *c, Resident &r, cudaStream_t stream) {
 // Texture-unit mode: the volume as a cudaArray behind a texture object with the reference's settings
 // (createTextureFromVolume, kernel.cu:522-554: normalized coordinates, linear filter, clamp, element type), filled from
 // the resident padded storage - one path whatever the source was (host, device, partial update, interleaved component).
+bool array_eligible(const Resident &r) {
+  if (r.kind != TEX_VOLUME) return true;  // constants and unbound slots need no array
+  return r.dtype == VR_DTYPE_F32 && !r.ox && !r.oy && !r.oz && r.lw == r.w + 2 && r.lh == r.h + 2 && r.ld == r.d + 2 && r.w <= 16384 &&
+         r.h <= 16384 && r.d <= 16384;
+}
+void drop_array(Resident &r) {
+  if (r.texobj) cudaDestroyTextureObject(r.texobj);
+  if (r.array) cudaFreeArray(r.array);
+  r.texobj = 0, r.array = nullptr, r.array_bytes = 0, r.array_valid = false;
+}
 vr_status ensure_array(vr_ctx *c, Resident &r, cudaStream_t stream) {
   if (r.kind != TEX_VOLUME || r.array_valid) return VR_OK;
   if (r.dtype != VR_DTYPE_F32) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode needs fp32 volumes (the filter has no bf16 element type)");
@@ -739,11 +751,27 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   // role -> texture through the redirect indices (kernel.cu:127-144)
   int sEm = c->idxEm, sAb = c->idxAb, sRe = c->idxRe;
   if (c->opt[VR_OPT_ABSORPTION_ROLE_FIX] && c->tex[S_AB].kind != TEX_UNBOUND) sAb = S_AB;
-  const bool texhw = c->opt[VR_OPT_TEXTURE_UNIT] != 0;
-  if (texhw) {
-    if (vs) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode is not available for volume-space passes");
+  // VR_OPT_TEXTURE_UNIT: 0 = loads + fp32 lerps, 1 = texture unit or an error, 2 (default) = texture unit where this
+  // context can (fp32 whole volumes that fit twice), else loads
+  const int64_t tu = c->opt[VR_OPT_TEXTURE_UNIT];
+  bool texhw = false;
+  if (tu == 1 && vs) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode is not available for volume-space passes");
+  if (tu && !vs && !(tu == 2 && c->texhw_failed)) {
     const int need[] = {sEm, sAb, sRe, S_EM, S_DX, S_DY, S_DZ, S_LIGHT};
-    for (int sl : need) VR_TRY(ensure_array(c, c->tex[sl], stream));
+    bool eligible = true;
+    for (int sl : need) eligible = eligible && array_eligible(c->tex[sl]);
+    if (eligible || tu == 1) {  // tu == 1: ensure_array reports what is in the way
+      texhw = true;
+      for (int sl : need) {
+        const vr_status st = ensure_array(c, c->tex[sl], stream);
+        if (st == VR_OK) continue;
+        if (tu == 1) return st;
+        cudaGetLastError();  // auto: no room for the second copy -> loads, until the volumes change
+        c->texhw_failed = true, texhw = false;
+        for (int s2 : need) drop_array(c->tex[s2]);
+        break;
+      }
+    }
   }
   P.em = describe(c->tex[sEm]);
   P.ab = describe(c->tex[sAb]);
@@ -813,8 +841,6 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   if (c->opt[VR_OPT_KERNEL_VARIANT] == 3 && P.uniform == 1 && layout == LAYOUT_BRICK) P.uniform = 2;  // variant 3: force the 64-bit kernels (tests)
   if (P.frac_bits) P.uniform = 0;  // fixed-point weights (A/B option) are compiled into the per-texture kernels only
   if (texhw) {
-    if (wide) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode: volume too large");
-    if (dtype != VR_DTYPE_F32) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode needs fp32 volumes");
     P.uniform = 0, P.frac_bits = 0;  // the hardware filters (1.8 fixed-point weights by construction)
     layout = LAYOUT_TEXHW;
   }
@@ -1053,7 +1079,9 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->opt[VR_OPT_TILE_ORDER] = 1;
   c->opt[VR_OPT_WARP_SHAPE] = 3;
   // opt-in without touching the MATLAB classes: VR_TEXTURE_UNIT=1 in the environment of the MATLAB process
-  if (const char *tu = getenv("VR_TEXTURE_UNIT")) c->opt[VR_OPT_TEXTURE_UNIT] = atoi(tu) != 0;
+  c->opt[VR_OPT_TEXTURE_UNIT] = 2;
+  // without touching the MATLAB classes: VR_TEXTURE_UNIT=0 (loads + fp32 lerps) / 1 / 2 in the environment of the MATLAB process
+  if (const char *tu = getenv("VR_TEXTURE_UNIT")) c->opt[VR_OPT_TEXTURE_UNIT] = atoi(tu) < 0 ? 0 : (atoi(tu) > 2 ? 2 : atoi(tu));
   cudaError_t ce = cudaSetDevice(device);
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   c->own_stream = ce == cudaSuccess;
