@@ -56,8 +56,8 @@ def parse():
     p.add_argument("--no-upload-probe", action="store_true", help="skip the host->resident upload measurement")
     p.add_argument("--no-gather-probe", action="store_true", help="skip the gather-ceiling microbenchmark (roofline.gather)")
     p.add_argument("--interleave", type=int, default=1, help="1: Gx,Gy,Gz resident as one interleaved storage (default); 0: three volumes")
-    p.add_argument("--texture-unit", type=int, default=0, help="1: VR_OPT_TEXTURE_UNIT (hardware-filtered fetches on cudaArray copies, fp32 only); default 0")
-    p.add_argument("--no-texture-leg", action="store_true", help="skip the extra texture-unit measurement of the default run")
+    p.add_argument("--texture-unit", type=int, default=2, help="VR_OPT_TEXTURE_UNIT: 2 (default) texture unit where the context can, 1 required, 0 loads + fp32 lerps")
+    p.add_argument("--no-load-leg", action="store_true", help="skip the extra load-path measurement of the default run")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
                    help="image = tiles over replicated volumes (the metric's config); volume = bricks sharded over the ranks, sort-last composite (config 5)")
@@ -283,7 +283,7 @@ def workload_config(args, scene, size=None):
         "multi_gpu": "image-space tiles %dx%d round-robin over replicated volumes; %s" % (
             args.tile, args.tile, "kernels store their tiles straight into rank 0's image over NVLink (CUDA IPC), one barrier per frame" if args.exchange == "p2p" else "NCCL sum-reduce of partial images to rank 0"),
         "frames_per_launch": max(1, min(args.batch, args.steps)),
-        "fetch": "texture unit (hardware linear filter, 1.8 fixed-point weights)" if getattr(args, "texture_unit", 0) else "loads + fp32 lerps",
+        "fetch": "texture unit (tex3D, hardware linear filter as the reference configures it) where the context can, else loads" if getattr(args, "texture_unit", 2) and args.dtype == "f32" else "loads + fp32 lerps",
         "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames",
     }
 
@@ -314,8 +314,7 @@ def run_b200(args):
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_TILE_ORDER, args.order), ctx)
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_WARP_SHAPE, args.wshape), ctx)
     lib.vr_set_option(ctx, _abi.OPT_GRADIENT_INTERLEAVE, args.interleave)  # unchecked: older A/B builds lack the option
-    if args.texture_unit:
-        _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, 1), ctx)
+    lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, args.texture_unit)  # unchecked: older A/B builds lack the option
     scene = Scene(args)
     n = args.size
     dt = _abi.DTYPE_F32 if args.dtype == "f32" else _abi.DTYPE_BF16
@@ -507,7 +506,9 @@ def run_b200(args):
             s_samples += st.samples_marched
             s_kernel += st.kernel_ms
         ts = time.perf_counter() - ts
-        single = {"ms_per_frame": 1e3 * ts / n1, "value": s_samples / ts / 1e9, "unit": "Gsamples/s", "frames": n1, "kernel_ms_per_frame": s_kernel / n1, "ms_each": [round(x, 2) for x in per_frame],
+        med = float(np.median(per_frame))
+        single = {"ms_per_frame": med, "ms_per_frame_mean": 1e3 * ts / n1, "value": (s_samples / n1) / (med * 1e-3) / 1e9, "unit": "Gsamples/s", "frames": n1,
+                  "kernel_ms_per_frame": s_kernel / n1, "ms_each": [round(x, 2) for x in per_frame],
                   "note": "vr_sync_volumes + vr_render, one frame per call, output into pageable host memory (the MATLAB mex path)"}
     h2d = 9 * 4 + 3 * 4 * 4 + 8 * 2 + nl * 24 + 6 * 40  # rotation, factors/es/props/color, resolution, lights, volume descriptors
     d2h = scene.W * scene.H * 3 * 4
@@ -549,11 +550,12 @@ def run_b200(args):
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v5_summary.md:
         # 5.19 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
-        "traffic": (2.6e9 * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
+        # (texture-unit kernels: profiles/r01_v5_tex_summary.md, 3.67 GB for a 2-frame launch)
+        "traffic": ((1.83e9 if args.texture_unit else 2.6e9) * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
         "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "peak_source": peak_src,
         "bytes_per_sample": bps, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
         "achieved_if_every_marched_sample_gathered": per_launch_marched * bps / (kavg_ms * 1e-3) / 1e9,
-        "note": "algorithmic GATHER bytes (SURVEY 8(d)) of the samples that were actually shaded; the gather is served by L1/L2, so the HBM peak is a reference line, not a ceiling",
+        "note": "algorithmic GATHER bytes (SURVEY 8(d)) of the samples that were actually shaded; the gather is served by L1/L2 (through the texture unit by default), so the HBM peak is a reference line, not a ceiling - see `gather`",
     }
     line = {
         "metric": "Gsamples/s (%d^2 image, %d^3 vol)" % (args.image, args.size), "value": value, "unit": "Gsamples/s", "n_gpus": world,
@@ -568,14 +570,13 @@ def run_b200(args):
     if single is not None:
         line["e2e"]["single_frame"] = single
 
-    # ---- the same frames with every fetch through the texture unit (VR_OPT_TEXTURE_UNIT, opt-in: hardware filter) ----
-    if world == 1 and not args.texture_unit and args.dtype == "f32" and not args.no_texture_leg:
+    # ---- the same frames on the load path (VR_OPT_TEXTURE_UNIT = 0: loads + fp32 lerps, the documented-formula mode) ----
+    if world == 1 and args.texture_unit != 0 and not args.no_load_leg:
         try:
-            _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, 1), ctx)
-            frame_device(-B, B)  # builds the cudaArray copies, warm-up
+            _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, 0), ctx)
+            frame_device(-B, B)  # warm-up
             torch.cuda.synchronize()
-            t_s = t_k = 0.0
-            t_shaded = 0
+            t_k, t_shaded = 0.0, 0
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
             for k in range(0, args.steps, B):
@@ -586,15 +587,14 @@ def run_b200(args):
             e1.record(stream)
             torch.cuda.synchronize()
             t_s = e0.elapsed_time(e1)
-            line["texture_unit"] = {
+            line["load_path"] = {
                 "ms_per_step": t_s / args.steps, "value": samples_all / (t_s * 1e-3) / 1e9, "unit": "Gsamples/s", "kernel_ms_per_frame": t_k / args.steps,
                 "gsamples_shaded_per_s": t_shaded / (t_s * 1e-3) / 1e9,
-                "note": "opt-in VR_OPT_TEXTURE_UNIT = 1: the reference's own fetch (tex3D, hardware linear filter, 1.8 fixed-point weights) on cudaArray copies of the "
-                        "resident volumes; same frames, device-resident timing like `value`.  Not the default: the parity bar is stated on the fp32-weight render math "
-                        "(tests/test_golden_refcuda.py holds both modes to the reference kernel's own images)"}
-            _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, 0), ctx)
+                "note": "VR_OPT_TEXTURE_UNIT = 0: every fetch as eight loads + fp32 lerps (the documented filter formula with fp32 weights, bit-level "
+                        "with the CPU oracle's default); same frames, device-resident timing like `value`"}
+            _abi.check(lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, args.texture_unit), ctx)
         except Exception as ex:
-            line["texture_unit"] = {"failed": repr(ex)[:300]}
+            line["load_path"] = {"failed": repr(ex)[:300]}
 
     # ---- gather ceilings of this box with the march's access pattern (BW_gather, measured live) ----
     if world == 1 and not args.no_gather_probe:
@@ -650,18 +650,28 @@ def gather_probe(lib, ctx, args, n_lights, shaded_per_s):
             out.setdefault("failed", {})[name] = repr(ex)[:200]
     # fetches of one shaded sample: gradient volumes -> emission + reflection (8 x 4 B each), one interleaved
     # gradient fetch (8 x 16 B), L LUT fetches (8 x 4 B, 1.1 MiB table: L1/L2); on the fly -> emission + reflection + 6 more + L LUT
-    if args.gradient == "lookup":
+    # emission, reflection (+ Gx, Gy, Gz) stream through the volume; the six central-difference fetches of computeGradient
+    # re-read the texels of the emission fetch (within half a voxel): L1-sized rate
+    nvol, nnear = (5.0, 0.0) if args.gradient == "lookup" else (2.0, 6.0)
+    if args.texture_unit and args.dtype == "f32":
+        # the launch fetched through the texture unit: one filtered fetch per volume and per light (LUT: 1 MiB, L2-sized)
+        out["fetch"] = "texture unit"
+        t = nvol / out["tex_f32_HBM_1024^3"] + nnear / out["tex_f32_L1_32^3"] + n_lights / out["tex_f32_L2_256^3"]
+        t_l2 = nvol / out["tex_f32_L2_256^3"] + nnear / out["tex_f32_L1_32^3"] + n_lights / out["tex_f32_L2_256^3"]
+    elif args.gradient == "lookup":
+        out["fetch"] = "loads"
         t = 2.0 / out["ldg4_HBM_1024^3"] + 1.0 / out["ldg16_HBM_512^3"] + n_lights / out["ldg4_L1_32^3"]
         t_l2 = 2.0 / out["ldg4_L2_256^3"] + 1.0 / out["ldg16_L2_128^3"] + n_lights / out["ldg4_L1_32^3"]
     else:
-        t = 8.0 / out["ldg4_HBM_1024^3"] + n_lights / out["ldg4_L1_32^3"]
-        t_l2 = 8.0 / out["ldg4_L2_256^3"] + n_lights / out["ldg4_L1_32^3"]
+        out["fetch"] = "loads"
+        t = 2.0 / out["ldg4_HBM_1024^3"] + (6.0 + n_lights) / out["ldg4_L1_32^3"]
+        t_l2 = 2.0 / out["ldg4_L2_256^3"] + (6.0 + n_lights) / out["ldg4_L1_32^3"]
     out["ceiling_gsamples_shaded_per_s"] = 1.0 / t  # volumes at their real size (HBM-sized footprints), LUT from L1
     out["ceiling_l2_resident_gsamples_shaded_per_s"] = 1.0 / t_l2
     out["achieved_gsamples_shaded_per_s"] = shaded_per_s / 1e9  # inside the kernel (kernel time, not step time)
     out["frac"] = out["achieved_gsamples_shaded_per_s"] * t
-    out["note"] = ("ceiling = a kernel that issues ONLY the loads of a shaded sample (no shading arithmetic, no empty-space test); "
-                   "the march adds ~800 instructions of illumination per sample, so issue slots bind before the load path does")
+    out["note"] = ("ceiling = a kernel that issues ONLY the fetches of a shaded sample (no shading arithmetic, no empty-space test); "
+                   "the march adds ~600-800 instructions of illumination per sample, so issue slots bind before the fetch path does")
     return out
 
 

@@ -201,11 +201,11 @@ typedef enum vr_option {
   VR_OPT_GRADIENT_INTERLEAVE = 13, /* 1 (default): the three gradient volumes of lookupGradient are stored interleaved
                                      (16-byte voxels Gx,Gy,Gz,-; one load per tap); 0: three separate volumes.  Takes
                                      effect at the next upload of the gradient volumes; pixels are bit-identical */
-  VR_OPT_TEXTURE_UNIT = 14      /* 0 (default): trilinear fetches are loads + fp32 lerps (the render math the parity bar is
-                                   stated on).  1: every fetch goes through the texture unit on cudaArray copies of the
-                                   volumes, configured as the reference configures its textures (volumeRender_kernel.cu:
-                                   544-548) - the reference's own hardware filtering with 1.8 fixed-point weights; fp32
-                                   whole-volume contexts only (VR_ERR_UNSUPPORTED otherwise), twice the volume memory */
+  VR_OPT_TEXTURE_UNIT = 14      /* how a trilinear fetch is done.  2 (default): through the texture unit on cudaArray copies of
+                                   the volumes, configured as the reference configures its textures (volumeRender_kernel.cu:
+                                   544-548) - the reference's own hardware filtering - where this context can (fp32 whole
+                                   volumes that fit twice), else as 0.  1: texture unit or VR_ERR_UNSUPPORTED.  0: eight loads +
+                                   fp32 lerps, the documented filter formula with fp32 weights (or VR_OPT_FILTER_FRAC_BITS) */
 } vr_option;
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);
