@@ -185,17 +185,7 @@ def test_stereo_red_cyan_and_side_by_side(lut):
             r.CameraXOffset = 0.06
             r.FocalLength = 4.5
             r.StereoOutput = mode
-        if _MODE == "texture":
-            # the off-axis scene has a few pixels on the illumination's NaN discontinuity; the measured filter
-            # model reproduces 99.9 % of the hardware's fetches, the rest are one weight step off - enough to flip such a
-            # sample.  Everything but those pixels is held to the bar.
-            img, ref = gpu.render(), orc.render()
-            m = vrt.compare(img, ref)
-            d = np.abs(np.asarray(img, np.float64) - ref).max(axis=2) / ref.max()
-            print(m, "pixels beyond the bar:", int((d > vrt.TOL).sum()))
-            assert (d <= vrt.TOL).mean() >= 0.9995 and m["max_abs_norm"] <= 1e-2 and m["psnr_db"] >= 90.0, m
-        else:
-            _check(gpu, orc)
+        _check(gpu, orc)
 
 
 def test_filter_frac_bits_8(brain64, lut):
