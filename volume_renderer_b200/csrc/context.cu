@@ -1169,6 +1169,12 @@ vr_status vr_mem_info(vr_ctx *c, char *buf, size_t cap, size_t *needed) {
   for (int i = 0; i < S_N; ++i)
     add("\t\t%s (MB): %g ptr: %p resident (MB): %g\n", names[i], c->host[i].bytes / MB, c->tex[i].storage, c->tex[i].storage_bytes / MB);
   if (c->g4) add("\t\tdX,dY,dZ interleaved (MB): %g ptr: %p users: %d\n", c->g4_bytes / MB, c->g4, c->g4_users);
+  {
+    double arrays = 0;
+    for (int i = 0; i < S_N; ++i) arrays += (double)c->tex[i].array_bytes;
+    add("\t\tfetch: %s; texture-unit copies (MB): %g\n",
+        c->opt[VR_OPT_TEXTURE_UNIT] == 0 ? "loads + fp32 lerps" : (c->texhw_failed ? "loads (no room for the texture copies)" : "texture unit where possible"), arrays / MB);
+  }
   add("\t\trole -> texture: Em->%s Ab->%s Re->%s, gradient method: %s\n", names[c->idxEm], names[c->idxAb], names[c->idxRe],
       c->gradientMethod ? "lookup" : "compute");
   add("\n\t\tSimilarity of Volumes\n\t\t---------------------\n\t\t\tEm\tAb\tRe\n\t\tEm\t1\t\n\t\tAb\t%d\t1\n\t\tRe\t%d\t%d\t1\n\n",
