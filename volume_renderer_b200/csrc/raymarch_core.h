@@ -37,12 +37,6 @@
 #ifndef VR_EARLY_RE
 #define VR_EARLY_RE 0
 #endif
-#ifndef VR_TEX_EARLY
-#define VR_TEX_EARLY 0
-#endif
-#ifndef VR_TEX_LIGHT_PAIR
-#define VR_TEX_LIGHT_PAIR 0
-#endif
 
 namespace vrb {
 
@@ -456,37 +450,7 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
   F3 illum = mk3(0.0f, 0.0f, 0.0f);
   // (measured on B200, all slower under the 72-register budget: the loop unrolled by two +3.5 %; the angles of two lights
   // first and their sixteen LUT loads together +2.2 %; see also the notes in shade_sample)
-  int i = 0;
-#if VR_TEX_LIGHT_PAIR
-  // Texture-unit launches: lights two by two - both pairs of angles first, then the two LUT fetches back to back (one
-  // exposed fetch latency for two lights), accumulation in light order: the same operations on the same values.
-  if (LAYOUT == LAYOUT_TEXHW) {
-    for (; i + 1 < P.n_lights; i += 2) {
-      float bb[2], cc[2];
-      F3 lc[2];
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        F3 lpos;
-        const int k = i + j;
-        if (k < MAX_PARAM_LIGHTS) {
-          lpos = mk3(P.lights[k][0], P.lights[k][1], P.lights[k][2]), lc[j] = mk3(P.lights[k][3], P.lights[k][4], P.lights[k][5]);
-        } else {
-          const float *L = P.lights_more + 6 * (k - MAX_PARAM_LIGHTS);
-          lpos = mk3(VR_LDG(L), VR_LDG(L + 1), VR_LDG(L + 2)), lc[j] = mk3(VR_LDG(L + 3), VR_LDG(L + 4), VR_LDG(L + 5));
-        }
-        const F3 lightOut = lpos - pos;
-        bb[j] = div_pi(vr_acosf(dot3(N, lightOut) / (lenN * length3(lightOut))));
-        const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
-        cc[j] = div_pi(vr_acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))));
-      }
-      const float l0 = tex3d_any<LAYOUT_TEXHW, ElemF32>(P.lut, a, bb[0], cc[0], fb);
-      const float l1 = tex3d_any<LAYOUT_TEXHW, ElemF32>(P.lut, a, bb[1], cc[1], fb);
-      illum = illum + reflection * l0 * lc[0] * color;  // kernel.cu:349
-      illum = illum + reflection * l1 * lc[1] * color;
-    }
-  }
-#endif
-  for (; i < P.n_lights; ++i) {
+  for (int i = 0; i < P.n_lights; ++i) {
     F3 lpos, lcol;
     if (i < MAX_PARAM_LIGHTS) {  // kernel-parameter space: register-indexed constant loads (a pointer select would go generic)
       lpos = mk3(P.lights[i][0], P.lights[i][1], P.lights[i][2]), lcol = mk3(P.lights[i][3], P.lights[i][4], P.lights[i][5]);
@@ -545,19 +509,9 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   if (UNI && P.n_lights > 0 && !P.re_is_em) re_early = taps_any<E>(P.re, ax, ay, az);
 #endif
   // (the gradient taps issued here as well: 23.5 -> 25.1 ms, eight 16-byte loads in flight spill; the emission and
-  // reflection loads all issued before the first lerp: +1.1 %)
-#if VR_TEX_EARLY
-  // Texture-unit launches: a fetch is one instruction and one result register, and the unit's latency is long, so the
-  // reflection and gradient fetches of a lit sample are issued here, next to the emission fetch, before the alpha test.
-  float te_re = 0.0f;
-  F3 te_g = mk3(0.0f, 0.0f, 0.0f);
-  if (LAYOUT == LAYOUT_TEXHW && P.n_lights > 0) {
-    if (!P.re_is_em) te_re = tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
-    if (GRAD == 1)
-      te_g = mk3(tex3d_any<LAYOUT, E>(P.gx, ps.x, ps.y, ps.z, fb), tex3d_any<LAYOUT, E>(P.gy, ps.x, ps.y, ps.z, fb),
-                 tex3d_any<LAYOUT, E>(P.gz, ps.x, ps.y, ps.z, fb));
-  }
-#endif
+  // reflection loads all issued before the first lerp: +1.1 %.  Texture-unit launches: reflection + gradient fetches issued
+  // here 15.9 -> 16.3 ms, the LUT fetches of two lights back to back 16.1, both 17.1 - the kernel is issue bound, the
+  // speculative work of the unlit samples costs more than the latency it hides)
   const float emission = P.fEm * em_raw;  // kernel.cu:444-447
   const float absorption = P.fAb * ab_raw;
   const float alpha = 1 - VR_EXPF(-absorption * P.tstep);  // kernel.cu:455-456
@@ -621,20 +575,12 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
         g.z = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
         g = g * mk3(0.5f, 0.5f, 0.5f);
       } else {
-#if VR_TEX_EARLY
-        if (LAYOUT == LAYOUT_TEXHW) g = te_g;
-        else
-#endif
-          g = mk3(tex3d_any<LAYOUT, E>(P.gx, ps.x, ps.y, ps.z, fb), tex3d_any<LAYOUT, E>(P.gy, ps.x, ps.y, ps.z, fb),
-                  tex3d_any<LAYOUT, E>(P.gz, ps.x, ps.y, ps.z, fb));
+        g = mk3(tex3d_any<LAYOUT, E>(P.gx, ps.x, ps.y, ps.z, fb), tex3d_any<LAYOUT, E>(P.gy, ps.x, ps.y, ps.z, fb),
+                tex3d_any<LAYOUT, E>(P.gz, ps.x, ps.y, ps.z, fb));
       }
       // the reflection fetch sits inside the reference's light loop (kernel.cu:342-344) but does
       // not depend on the light: fetched once
-#if VR_TEX_EARLY
-      if (LAYOUT == LAYOUT_TEXHW) re_raw = P.re_is_em ? em_raw : te_re;
-      else
-#endif
-        re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
+      re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
     }
     illum = shade_lights<LAYOUT>(P, g, P.fRe * re_raw, r.pos, origin, color, fb);
   }
