@@ -260,7 +260,8 @@ def run_reference(args):
         tot_n += n
         tot_s += sec
     value = tot_n / tot_s / 1e9
-    sample = "centred %dx%d pixel window of each %dx%d frame over the %d^3 volume, %d frames" % (2 * half, 2 * half, scene.W, scene.H, args.size, args.steps)
+    sample = "centred %dx%d pixel window of each %dx%d frame over the %d^3 volume, %d frames; software tex3D by the documented filter formula (the model of the hardware filter is 30 %% slower on a CPU)" % (
+        2 * half, 2 * half, scene.W, scene.H, args.size, args.steps)
     line = {
         "impl": "reference", "metric": "Gsamples/s (%d^2 image, %d^3 vol)" % (args.image, size_used), "value": value, "unit": "Gsamples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / args.steps,
@@ -746,7 +747,7 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m):
         half = int(min(half * math.sqrt(args.cpu_seconds / max(sec, 1e-3)), scene.W // 2))
         nsm, sec, threads = cpu.render_window(0, half)
     out = {"value": nsm / sec / 1e9, "unit": "Gsamples/s", "cores": int(threads), "kind": "port",
-           "sample": "frame 0, centred %dx%d pixel window of the %dx%d image, %s; %.1f s of CPU time, %d samples" % (2 * half, 2 * half, scene.W, scene.H, note, sec, nsm)}
+           "sample": "frame 0, centred %dx%d pixel window of the %dx%d image, %s; %.1f s of CPU time, %d samples; software tex3D by the documented filter formula (the model of the hardware filter is 30 %% slower on a CPU)" % (2 * half, 2 * half, scene.W, scene.H, note, sec, nsm)}
     # north_star: "a baseline from the reference's CUDA kernel rebuilt standalone via nvcc is added where it builds" -
     # oracle/_ref/libref_cuda.so = the reference's own d_render + upload code on texture objects (oracle/ref_cuda)
     try:
