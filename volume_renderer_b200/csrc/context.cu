@@ -843,6 +843,8 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   if (texhw) {
     P.uniform = 0, P.frac_bits = 0;  // the hardware filters (1.8 fixed-point weights by construction)
     layout = LAYOUT_TEXHW;
+    P.tex_fast = (P.gx.kind == TEX_VOLUME && P.gy.kind == TEX_VOLUME && P.gz.kind == TEX_VOLUME ? 1 : 0) | (P.re.kind == TEX_VOLUME ? 2 : 0) |
+                 (P.em_direct.kind == TEX_VOLUME ? 4 : 0) | (P.em.kind == TEX_VOLUME ? 8 : 0) | (P.lut.kind == TEX_VOLUME ? 16 : 0);
   }
 
   // volume-space mode

@@ -37,6 +37,9 @@
 #ifndef VR_EARLY_RE
 #define VR_EARLY_RE 0
 #endif
+#ifndef VR_TEX_FAST
+#define VR_TEX_FAST 1
+#endif
 
 namespace vrb {
 
@@ -224,6 +227,16 @@ VR_HD float tex3d_any(const TexDesc &t, float x, float y, float z, int frac_bits
     if (t.kind == TEX_VOLUME) return tex3d_volume<LAYOUT == LAYOUT_TEXHW ? LAYOUT_LINEAR : LAYOUT, E>(t, x, y, z, frac_bits);
     return t.kind == TEX_CONST ? t.cval : 0.0f;
   }
+}
+
+// the texture-unit fetch itself, for slots the host has verified to be volumes (KernelParams::tex_fast)
+VR_HD float tex_raw(const TexDesc &t, float x, float y, float z) {
+#if defined(__CUDA_ARCH__)
+  return tex3D<float>((cudaTextureObject_t)t.tex, x, y, z);
+#else
+  (void)t, (void)x, (void)y, (void)z;
+  return 0.0f;
+#endif
 }
 
 // ---- shared tap sets ---------------------------------------------------------------------
@@ -463,7 +476,9 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
     const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
     const float c = div_pi(vr_acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))));
     // the LUT is always fp32 in the linear padded layout
-    const float light = tex3d_any<LAYOUT == LAYOUT_TEXHW ? LAYOUT_TEXHW : LAYOUT_LINEAR, ElemF32>(P.lut, a, b, c, fb);
+    float light;
+    if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 16)) light = tex_raw(P.lut, a, b, c);
+    else light = tex3d_any<LAYOUT == LAYOUT_TEXHW ? LAYOUT_TEXHW : LAYOUT_LINEAR, ElemF32>(P.lut, a, b, c, fb);
     illum = illum + reflection * light * lcol * color;  // kernel.cu:349
   }
   return illum;
@@ -496,6 +511,9 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
     axis_taps_from<LAYOUT>(P.geo, axis_coord(ps.x, P.geo.fw), axis_coord(ps.y, P.geo.fh), axis_coord(ps.z, P.geo.fd), fb, ax, ay, az);
     em_raw = taps_any<E>(P.em, ax, ay, az);
     ab_raw = P.ab_is_em ? em_raw : taps_any<E>(P.ab, ax, ay, az);
+  } else if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 8)) {
+    em_raw = tex_raw(P.em, ps.x, ps.y, ps.z);
+    ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, ps.x, ps.y, ps.z, fb);
   } else {
     em_raw = tex3d_any<LAYOUT, E>(P.em, ps.x, ps.y, ps.z, fb);
     ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, ps.x, ps.y, ps.z, fb);
@@ -561,7 +579,20 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
       re_raw = P.re_is_em ? em_raw : taps_any<E>(P.re, ax, ay, az);
 #endif
     } else {
-      if (GRAD == 0) {
+      if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && GRAD == 1 && (P.tex_fast & 1)) {
+        // straight-line: the three fetches (and the reflection fetch below) share the coordinate registers of ps
+        g = mk3(tex_raw(P.gx, ps.x, ps.y, ps.z), tex_raw(P.gy, ps.x, ps.y, ps.z), tex_raw(P.gz, ps.x, ps.y, ps.z));
+      } else if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && GRAD == 0 && (P.tex_fast & 4)) {
+        const F3 gs = ld3(P.gstep);
+        // the offset taps differ from ps in ONE coordinate each ((pos.y + 0 - bmin.y) * bscale.y is ps.y bit for bit)
+        const float xp = (r.pos.x + gs.x - bmin.x) * bscale.x, xm = (r.pos.x - gs.x - bmin.x) * bscale.x;
+        const float yp = (r.pos.y + gs.y - bmin.y) * bscale.y, ym = (r.pos.y - gs.y - bmin.y) * bscale.y;
+        const float zp = (r.pos.z + gs.z - bmin.z) * bscale.z, zm = (r.pos.z - gs.z - bmin.z) * bscale.z;
+        g.x = tex_raw(P.em_direct, xp, ps.y, ps.z) - tex_raw(P.em_direct, xm, ps.y, ps.z);
+        g.y = tex_raw(P.em_direct, ps.x, yp, ps.z) - tex_raw(P.em_direct, ps.x, ym, ps.z);
+        g.z = tex_raw(P.em_direct, ps.x, ps.y, zp) - tex_raw(P.em_direct, ps.x, ps.y, zm);
+        g = g * mk3(0.5f, 0.5f, 0.5f);
+      } else if (GRAD == 0) {
         const F3 gs = ld3(P.gstep);
         F3 s1, s2;
         s1 = (r.pos + mk3(gs.x, 0, 0) - bmin) * bscale;
@@ -580,7 +611,8 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
       }
       // the reflection fetch sits inside the reference's light loop (kernel.cu:342-344) but does
       // not depend on the light: fetched once
-      re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
+      if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 2)) re_raw = P.re_is_em ? em_raw : tex_raw(P.re, ps.x, ps.y, ps.z);
+      else re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
     }
     illum = shade_lights<LAYOUT>(P, g, P.fRe * re_raw, r.pos, origin, color, fb);
   }

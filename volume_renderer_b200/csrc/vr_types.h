@@ -100,6 +100,8 @@ struct KernelParams {
   int ab_is_em;  // absorption role resolves to the same texture as the emission role
   int re_is_em;  // reflection role resolves to the same texture as the emission role
   int grad4;     // gx, gy, gz are components 0..2 of one interleaved storage (gx.p)
+  int tex_fast;  // texture-unit launches: bit 0 = gx, gy, gz are all volumes, bit 1 = re is a volume, bit 2 = em_direct is a
+                 // volume, bit 3 = em, bit 4 = the LUT -> straight-line fetches that share one set of coordinate registers (no per-slot kind tests)
   int gradient_method;  // 0 compute, 1 lookup (volumeRender.h:141-144)
   int frac_bits;        // 0 = fp32 weights, 8 = 1.8 fixed point
   int skip;             // empty-space skipping: 0 off, 1 serial per cell, 2 closed-form jumps (default)
