@@ -37,6 +37,9 @@
 #ifndef VR_EARLY_RE
 #define VR_EARLY_RE 0
 #endif
+#ifndef VR_SPLIT_LIGHT_LOOP
+#define VR_SPLIT_LIGHT_LOOP 1
+#endif
 #ifndef VR_TEX_FAST
 #define VR_TEX_FAST 1
 #endif
@@ -484,6 +487,50 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
   return illum;
 }
 
+// The same loop for the texture-unit kernels, as TWO loops instead of a select per light: in one loop the compiler predicates
+// both ways of reading a light and issues the six (switched-off) global loads of the overflow list for every light that sits
+// in the kernel parameters.  Measured: texture-unit kernels 15.25 -> 15.15 ms; the load kernels lose 1.5 % with it
+// (23.76 -> 24.12), so they keep the loop above.
+VR_HD F3 shade_lights_split(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color, int fb) {
+  const F3 N = -1.0f * normalize3(g);
+  const F3 lightIn = origin - pos;
+  const float lenN = length3(N), lenIn = length3(lightIn);
+  const float a = div_pi(vr_acosf(dot3(N, lightIn) / (lenN * lenIn)));  // angle(N, lightIn)/pi
+  const F3 lightInProj = lightIn - (dot3(lightIn, N) * N);
+  const float lenInProj = length3(lightInProj);
+  F3 illum = mk3(0.0f, 0.0f, 0.0f);
+  auto one_light = [&](const F3 lpos, const F3 lcol) {
+    const F3 lightOut = lpos - pos;
+    const float b = div_pi(vr_acosf(dot3(N, lightOut) / (lenN * length3(lightOut))));
+    const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
+    const float c = div_pi(vr_acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))));
+    const float light = (P.tex_fast & 16) ? tex_raw(P.lut, a, b, c) : tex3d_any<LAYOUT_TEXHW, ElemF32>(P.lut, a, b, c, fb);
+    illum = illum + reflection * light * lcol * color;  // kernel.cu:349
+  };
+  const int n_param = P.n_lights < MAX_PARAM_LIGHTS ? P.n_lights : MAX_PARAM_LIGHTS;
+  for (int i = 0; i < n_param; ++i)  // kernel-parameter space: register-indexed constant loads
+    one_light(mk3(P.lights[i][0], P.lights[i][1], P.lights[i][2]), mk3(P.lights[i][3], P.lights[i][4], P.lights[i][5]));
+  for (int i = MAX_PARAM_LIGHTS; i < P.n_lights; ++i) {
+    const float *L = P.lights_more + 6 * (i - MAX_PARAM_LIGHTS);
+    one_light(mk3(VR_LDG(L), VR_LDG(L + 1), VR_LDG(L + 2)), mk3(VR_LDG(L + 3), VR_LDG(L + 4), VR_LDG(L + 5)));
+  }
+  return illum;
+}
+template <int LAYOUT>
+struct Lights {
+  static VR_HD F3 shade(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color, int fb) {
+    return shade_lights<LAYOUT>(P, g, reflection, pos, origin, color, fb);
+  }
+};
+#if VR_SPLIT_LIGHT_LOOP
+template <>
+struct Lights<LAYOUT_TEXHW> {
+  static VR_HD F3 shade(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color, int fb) {
+    return shade_lights_split(P, g, reflection, pos, origin, color, fb);
+  }
+};
+#endif
+
 // One full iteration of the loop kernel.cu:435-493 up to and including the "under" update.
 // GRAD: 0 = computeGradient (kernel.cu:212-253), 1 = lookupGradient (kernel.cu:266-276).
 // UNI : every volume texture of the launch shares one geometry -> shared tap sets.
@@ -614,7 +661,7 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
       if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 2)) re_raw = P.re_is_em ? em_raw : tex_raw(P.re, ps.x, ps.y, ps.z);
       else re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
     }
-    illum = shade_lights<LAYOUT>(P, g, P.fRe * re_raw, r.pos, origin, color, fb);
+    illum = Lights<LAYOUT>::shade(P, g, P.fRe * re_raw, r.pos, origin, color, fb);
   }
   const F3 lit = colored + illum;
   const float shx = lit.x * alpha, shy = lit.y * alpha, shz = lit.z * alpha;  // kernel.cu:477-479
