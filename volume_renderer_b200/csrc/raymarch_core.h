@@ -576,7 +576,8 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   // (the gradient taps issued here as well: 23.5 -> 25.1 ms, eight 16-byte loads in flight spill; the emission and
   // reflection loads all issued before the first lerp: +1.1 %.  Texture-unit launches: reflection + gradient fetches issued
   // here 15.9 -> 16.3 ms, the LUT fetches of two lights back to back 16.1, both 17.1 - the kernel is issue bound, the
-  // speculative work of the unlit samples costs more than the latency it hides)
+  // speculative work of the unlit samples costs more than the latency it hides.  The emission fetch of pos + step issued one
+  // sample ahead, behind this sample's shading: 15.13 -> 15.26 ms, one more live register and 16 more bytes of spills)
   const float emission = P.fEm * em_raw;  // kernel.cu:444-447
   const float absorption = P.fAb * ab_raw;
   const float alpha = 1 - VR_EXPF(-absorption * P.tstep);  // kernel.cu:455-456
