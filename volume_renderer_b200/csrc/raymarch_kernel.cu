@@ -50,6 +50,8 @@ struct Tune {
 // texture-unit kernels: no tap arithmetic to keep live, the fetch latency is longer -> more resident warps.
 // Measured (ms per frame, configs[1] / computeGradient with 1 light): 128x6 17.6 / 17.0 | 128x7 16.3 / 16.0 |
 // 128x8 (64 registers) 15.9 / 15.2 | 256x4 15.9 / 15.2 | 128x10 (48) 16.8 / 17.2 | 128x12 (40) 17.7 / 17.6
+// On the final kernel (straight-line fetches): 128x8 15.14 / 14.44 | 128x9 (56 registers, 88 bytes of spills) 15.39 / 14.94.
+// The jump thresholds below on the same kernel: 24 lanes / 64 iterations 15.14 | 16 / 32 15.29 | 28 / 128 15.18.
 #ifndef VR_TEX_THREADS
 #define VR_TEX_THREADS 128
 #endif
