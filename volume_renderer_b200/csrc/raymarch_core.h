@@ -40,6 +40,9 @@
 #ifndef VR_SPLIT_LIGHT_LOOP
 #define VR_SPLIT_LIGHT_LOOP 1
 #endif
+#ifndef VR_TEX_NO_VS
+#define VR_TEX_NO_VS 1
+#endif
 #ifndef VR_TEX_FAST
 #define VR_TEX_FAST 1
 #endif
@@ -543,7 +546,9 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);  // kernel.cu:396
   const F3 ps = (r.pos - bmin) * bscale;                            // kernel.cu:437
   const int fb = UNI ? 0 : P.frac_bits;
-  if (P.vs_mode && !(ps.x >= P.reg_lo[0] && ps.x < P.reg_hi[0] && ps.y >= P.reg_lo[1] && ps.y < P.reg_hi[1] && ps.z >= P.reg_lo[2] &&
+  // texture-unit launches are never volume-space passes (render_common): their kernels carry no region test
+  const int vs_mode = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW) ? 0 : P.vs_mode;
+  if (vs_mode && !(ps.x >= P.reg_lo[0] && ps.x < P.reg_hi[0] && ps.y >= P.reg_lo[1] && ps.y < P.reg_hi[1] && ps.z >= P.reg_lo[2] &&
                      ps.z < P.reg_hi[2])) {
     r.n_marched++;  // a sample of the global lattice that another brick owns
     return;
@@ -582,7 +587,7 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const float absorption = P.fAb * ab_raw;
   const float alpha = 1 - VR_EXPF(-absorption * P.tstep);  // kernel.cu:455-456
   r.n_marched++;
-  if (P.vs_mode == 1) {  // transmittance pass: only sum.w of kernel.cu:482, no colour
+  if (vs_mode == 1) {  // transmittance pass: only sum.w of kernel.cu:482, no colour
     r.sw = (1 - r.sw) * alpha + r.sw;
     return;
   }

@@ -109,7 +109,8 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     Ray r;
     bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, cam, x, y, origin, r);
     bool active = hit;
-    if (P.vs_mode == 2 && hit) {  // start from the opacity of the bricks in front; nothing to do behind the threshold
+    const int vs_mode = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW) ? 0 : P.vs_mode;
+    if (vs_mode == 2 && hit) {  // start from the opacity of the bricks in front; nothing to do behind the threshold
       float a_in = 0.0f;
       active = vs_opacity_in(P, origin, r, (size_t)x * P.H + y, a_in);
       r.sw = a_in;
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
       // the owner of the pixel writes that 0 itself, so the image needs no clear and cam.out may be
       // another GPU's memory (image-space direct send: each rank stores its tiles into the root's image).
       const size_t size = (size_t)P.W * P.H, k = (size_t)x * P.H + y;
-      if (P.vs_mode == 1) {
+      if (vs_mode == 1) {
         P.vs_opacity_out[k] = hit ? r.sw : 0.0f;
       } else {
         cam.out[k] = hit ? r.sx : 0.0f;
