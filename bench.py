@@ -551,8 +551,8 @@ def run_b200(args):
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v5_summary.md:
         # 5.19 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
-        # (texture-unit kernels: profiles/r01_v5_tex_summary.md, 3.67 GB for a 2-frame launch)
-        "traffic": ((1.83e9 if args.texture_unit else 2.6e9) * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
+        # (texture-unit kernels: profiles/r01_v7_tex_summary.md, 3.35 GB for a 2-frame launch)
+        "traffic": ((1.67e9 if args.texture_unit else 2.6e9) * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
         "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "peak_source": peak_src,
         "bytes_per_sample": bps, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
         "achieved_if_every_marched_sample_gathered": per_launch_marched * bps / (kavg_ms * 1e-3) / 1e9,
