@@ -31,8 +31,13 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 SEED = 0x5EED01BE
-B_GATHER_LOOKUP_L2 = 256  # gradient volumes, (6 + L) * 32 B per sample at L = 2
-B_GATHER_COMPUTE_L1 = 320  # on-the-fly gradient, (9 + L) * 32 B per sample at L = 1
+# DRAM traffic of k_raymarch per frame from this round's ncu --set full captures (dram__bytes_read.sum + dram__bytes_write.sum),
+# keyed by (volume edge, image edge, gradient method, dtype, texture unit on/off).  Not measured live: bench.py scales it to
+# the frames of its own launches and names the profile it came from.
+DRAM_PROFILE = {
+    (1024, 2048, "lookup", "f32", 1): {"bytes_per_frame": 1.67e9, "profile": "profiles/r01_v7_tex_summary.md"},
+    (1024, 2048, "lookup", "f32", 0): {"bytes_per_frame": 2.6e9, "profile": "profiles/r01_v5_summary.md"},
+}
 
 
 def parse():
@@ -154,6 +159,21 @@ def oracle_lib():
     return vrt, ctypes
 
 
+def host_cores():
+    """Cores this process may run on (torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU legs ask for all of them explicitly)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def frames_per_launch(steps, batch):
+    """Equal batches: 20 steps with --batch 16 are 10 + 10 frames, not 16 + 4 (a short last batch is nearly all tail)."""
+    steps, batch = max(1, steps), max(1, batch)
+    launches = -(-steps // batch)
+    return -(-steps // launches)
+
+
 def mem_available_gib():
     try:
         for line in open("/proc/meminfo"):
@@ -168,16 +188,19 @@ class CpuRender:
     """The reference's per-ray render math (oracle/oracle.cpp, OpenMP over 16x16 tiles, all host
     cores) on host copies of the workload's volumes."""
 
-    def __init__(self, scene, args, vols):
+    def __init__(self, scene, args, vols, fast=True, filter_bits=0):
         vrt, _ = oracle_lib()
         self.vrt = vrt
         self.scene = scene
         from volume_renderer_b200 import _abi, api
 
         self.abi, self.api = _abi, api
-        self.lib = vrt.oracle(fast=True)
+        self.lib = vrt.oracle(fast=fast)
         self.h = C.c_void_p(self.lib.orc_create())
         self.lib.orc_set_option(self.h, vrt.ORC_OPT_BORROW_HOST_DATA, 1)
+        self.lib.orc_set_option(self.h, vrt.ORC_OPT_THREADS, host_cores())  # all host cores, whatever OMP_NUM_THREADS says
+        if filter_bits:
+            self.lib.orc_set_option(self.h, vrt.ORC_OPT_FILTER_FRAC_BITS, filter_bits)
         self.keep = []
         self.vols = vols
         vs = {k: (_abi.volume_struct(v, 1, self.keep) if v is not None else None) for k, v in vols.items()}
@@ -192,10 +215,11 @@ class CpuRender:
             self.lights[i].color[:] = c
         self.out = np.zeros((scene.H, scene.W, 3), dtype=np.float32, order="F")
 
-    def render_window(self, step, half):
+    def render_window(self, step, half, centre=None):
         s = self.scene
-        cx, cy = s.W // 2, s.H // 2
+        cx, cy = centre if centre is not None else (s.W // 2, s.H // 2)
         win = (C.c_uint64 * 4)(max(cx - half, 0), min(cx + half, s.W), max(cy - half, 0), min(cy + half, s.H))
+        self.window = [int(v) for v in win]
         rot = s.rot(step)
         n = len(s.lights)
         rc = self.lib.orc_render(self.h, self.lights if n else None, n, C.byref(self.lutv) if n else None, f32p(s.factors), f32p(s.es),
@@ -247,7 +271,7 @@ def run_reference(args):
     if mem_available_gib() < need * 1.5 + 4:
         args.size = 512
     vols = host_volumes_cpu(args)
-    cpu = CpuRender(scene, args, vols)
+    cpu = CpuRender(scene, args, vols)  # asks the oracle for host_cores() threads (torchrun exports OMP_NUM_THREADS=1)
     half = cpu.calibrated_half(10.0)
     n0, s0, _ = cpu.render_window(0, half)
     if s0 < 6.0 and half < scene.W // 2:
@@ -283,7 +307,7 @@ def workload_config(args, scene, size=None):
         "volume": [size] * 3, "image": [scene.W, scene.H], "gradient": args.gradient, "lights": len(scene.lights),
         "multi_gpu": "image-space tiles %dx%d round-robin over replicated volumes; %s" % (
             args.tile, args.tile, "kernels store their tiles straight into rank 0's image over NVLink (CUDA IPC), one barrier per frame" if args.exchange == "p2p" else "NCCL sum-reduce of partial images to rank 0"),
-        "frames_per_launch": max(1, min(args.batch, args.steps)),
+        "frames_per_launch": frames_per_launch(args.steps, args.batch),
         "fetch": "texture unit (tex3D, hardware linear filter as the reference configures it) where the context can, else loads" if getattr(args, "texture_unit", 2) and args.dtype == "f32" else "loads + fp32 lerps",
         "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames",
     }
@@ -367,7 +391,7 @@ def run_b200(args):
     for i, (p, c) in enumerate(scene.lights):
         lights[i].position[:] = p
         lights[i].color[:] = c
-    B = max(1, min(args.batch, args.steps))
+    B = frames_per_launch(args.steps, args.batch)
     npx = scene.W * scene.H * 3
     h_img = torch.zeros(B * npx, dtype=torch.float32).pin_memory()
     resp = scene.res.ctypes.data_as(C.POINTER(C.c_uint64))
@@ -535,28 +559,39 @@ def run_b200(args):
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s"
-    bps = B_GATHER_LOOKUP_L2 if args.gradient == "lookup" else B_GATHER_COMPUTE_L1
-    if args.gradient == "lookup":
-        bps = (6 + len(scene.lights)) * 32
-    else:
-        bps = (9 + len(scene.lights)) * 32
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    hbm_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (B200_PROFILING.md)"
+    # ---- roofline of the dominant kernel, k_raymarch ----
+    # The path is an on-chip GATHER: its unit of memory work is one trilinear fetch = 8 taps x 4 B = 32
+    # algorithmic bytes; a shaded sample issues FETCHES of them.  achieved = fetches of this run's launches x 32 B
+    # / kernel time (CUDA events around each launch, on the launching stream); peak = the same 32 B x the fetch rate of a
+    # kernel that ONLY fetches with the march's access pattern out of an L2-sized footprint, measured live below
+    # (vr_probe_gather) - the ceiling whose L1 / L2 hit rates match the march's (profiles/r02_probe_hit_rates.md).
+    nl_ = len(scene.lights)
+    fetches_per_sample = (5 + nl_) if args.gradient == "lookup" else (2 + 6 + nl_)  # em, re (+ gx, gy, gz | 6 central-difference taps) + one LUT fetch per light
     n_launch = max(len(kernel_ms), 1)
-    kavg_ms = float(np.sum(kernel_ms)) / n_launch
+    ksum_ms = float(np.sum(kernel_ms))
+    kavg_ms = ksum_ms / n_launch
+    frames_per_launch_avg = args.steps / float(n_launch)
     per_launch_shaded = shaded / n_launch  # rank 0's launches (a launch = a batch of frames)
     per_launch_marched = samples / n_launch
-    achieved = per_launch_shaded * bps / (kavg_ms * 1e-3) / 1e9
+    fetch_rate = shaded * fetches_per_sample / (ksum_ms * 1e-3)  # trilinear fetches per second inside the kernel
+    achieved = fetch_rate * 32.0 / 1e9
+    # DRAM traffic of the kernel: not measurable live (needs ncu); taken from this round's committed capture of the same
+    # kernel and scene, per frame, scaled to the frames of one launch of THIS run
+    prof = DRAM_PROFILE.get((args.size, args.image, args.gradient, args.dtype, 1 if args.texture_unit else 0))
+    traffic = prof["bytes_per_frame"] * frames_per_launch_avg if prof else None
     roofline = {
-        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel (profiles/r01_v5_summary.md:
-        # 5.19 GB for a 2-frame launch), scaled to the frames of this run's launches; not measured live
-        # (texture-unit kernels: profiles/r01_v7_tex_summary.md, 3.35 GB for a 2-frame launch)
-        "traffic": ((1.67e9 if args.texture_unit else 2.6e9) * max(1, min(args.batch, args.steps))) if (args.size == 1024 and args.image == 2048 and args.gradient == "lookup" and args.dtype == "f32") else None,
-        "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "peak_source": peak_src,
-        "bytes_per_sample": bps, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
-        "achieved_if_every_marched_sample_gathered": per_launch_marched * bps / (kavg_ms * 1e-3) / 1e9,
-        "note": "algorithmic GATHER bytes (SURVEY 8(d)) of the samples that were actually shaded; the gather is served by L1/L2 (through the texture unit by default), so the HBM peak is a reference line, not a ceiling - see `gather`",
+        "bound": "gather", "achieved": achieved, "peak": None, "unit": "GB/s", "frac": None, "traffic": traffic,
+        "traffic_source": ("%s (%.3g B per frame x %.1f frames per launch of this run; dram__bytes_read.sum + dram__bytes_write.sum of an ncu --set full capture, not live)"
+                           % (prof["profile"], prof["bytes_per_frame"], frames_per_launch_avg)) if prof else None,
+        "kernel": "k_raymarch", "kernel_ms_avg": kavg_ms, "launches": n_launch, "frames_per_launch": frames_per_launch_avg,
+        "algorithmic_bytes_per_fetch": 32, "fetches_per_shaded_sample": fetches_per_sample,
+        "fetches_per_s": fetch_rate, "samples_shaded_per_launch": per_launch_shaded, "samples_marched_per_launch": per_launch_marched,
+        "hbm": {"achieved": (traffic / (kavg_ms * 1e-3) / 1e9) if traffic else None, "peak": hbm_peak, "unit": "GB/s", "peak_source": hbm_src,
+                "frac": (traffic / (kavg_ms * 1e-3) / 1e9 / hbm_peak) if traffic else None,
+                "note": "DRAM bytes of the kernel (profile) / kernel time: the march touches each resident voxel of the frustum about once per frame and serves the rest from L1/L2 - HBM is not the bound"},
+        "note": "bound = on-chip gather through the texture unit; achieved / peak in algorithmic bytes (32 B per trilinear fetch); peak filled from the live gather probe",
     }
     line = {
         "metric": "Gsamples/s (%d^2 image, %d^3 vol)" % (args.image, args.size), "value": value, "unit": "Gsamples/s", "n_gpus": world,
@@ -600,7 +635,13 @@ def run_b200(args):
     # ---- gather ceilings of this box with the march's access pattern (BW_gather, measured live) ----
     if world == 1 and not args.no_gather_probe:
         try:
-            roofline["gather"] = gather_probe(lib, ctx, args, len(scene.lights), shaded / (float(np.sum(kernel_ms)) * 1e-3))
+            gp = gather_probe(lib, ctx, args, len(scene.lights), shaded / (float(np.sum(kernel_ms)) * 1e-3))
+            roofline["gather"] = gp
+            # peak: the fetch-only kernel with the march's mix of fetches, footprints L2-resident (the march's own L2 hit rate is 97 %)
+            roofline["peak"] = gp["ceiling_l2_resident_gsamples_shaded_per_s"] * fetches_per_sample * 32.0
+            roofline["frac"] = roofline["achieved"] / roofline["peak"]
+            roofline["peak_source"] = "live vr_probe_gather: fetch-only kernels, march access pattern, L2-resident footprints (see roofline.gather; hit rates in profiles/r02_probe_hit_rates.md)"
+            roofline["frac_vs_hbm_sized_footprint_ceiling"] = gp["frac"]
         except Exception as ex:
             roofline["gather"] = {"failed": repr(ex)}
 
@@ -614,7 +655,11 @@ def run_b200(args):
     # ---- cpu_baseline: the oracle on host copies of the same volumes, bounded sample ----
     if world == 1 and not args.no_cpu_baseline:
         try:
-            line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m)
+            one(0)  # frame 0 of the movie through the mex path, for the full-size parity figure
+            frame0 = pageable.reshape((scene.H, scene.W, 3), order="F").copy()
+            line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m, frame0, stats().fetch_mode)
+            if "parity" in line["cpu_baseline"]:
+                line["parity"] = line["cpu_baseline"].pop("parity")
             rcb = line["cpu_baseline"].get("reference_cuda", {})
             if "ms_per_frame" in rcb:  # same frames, same lattice: samples per frame from this run's counters
                 rcb["value"] = line["samples_per_frame"] / (rcb["ms_per_frame"] * 1e-3) / 1e9
@@ -722,7 +767,7 @@ def upload_probe(args):
     return out
 
 
-def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m):
+def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mode=1):
     import torch
 
     need = (5 if G is not None else 2) * 4.0 * n ** 3 / 2 ** 30
@@ -748,6 +793,29 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m):
         nsm, sec, threads = cpu.render_window(0, half)
     out = {"value": nsm / sec / 1e9, "unit": "Gsamples/s", "cores": int(threads), "kind": "port",
            "sample": "frame 0, centred %dx%d pixel window of the %dx%d image, %s; %.1f s of CPU time, %d samples; software tex3D by the documented filter formula (the model of the hardware filter is 30 %% slower on a CPU)" % (2 * half, 2 * half, scene.W, scene.H, note, sec, nsm)}
+    # ---- full-size parity: the checker build of the oracle (strict IEEE), filtering the way the product fetched, on a
+    # window of the very frame the GPU rendered (same volumes, same camera); north_star's bar is 1e-3 of the image maximum
+    if gpu_frame0 is not None and not note.startswith("512^3 twin"):
+        try:
+            chk = CpuRender(scene, args, vols, fast=False, filter_bits=9 if fetch_mode == 1 else 0)
+            # centred on the volume's silhouette where rays are long and shaded: cost ~ the timing window's per-pixel cost
+            ph = max(16, min(half, int(half * math.sqrt(8.0 / max(sec, 1e-3)))))
+            t0 = time.perf_counter()
+            chk.render_window(0, ph)
+            x0, x1, y0, y1 = chk.window
+            ref_w = chk.out[y0:y1, x0:x1, :].astype(np.float64)
+            gpu_w = gpu_frame0[y0:y1, x0:x1, :].astype(np.float64)
+            peak = float(chk.out.max()) or 1.0
+            d = np.abs(gpu_w - ref_w)
+            mse = float(np.mean((d / peak) ** 2))
+            out["parity"] = {"max_abs_norm": float(d.max() / peak), "psnr_db": (float("inf") if mse == 0 else 10.0 * math.log10(1.0 / mse)),
+                             "frac_within_1e-3": float((d.max(axis=2) / peak <= 1e-3).mean()), "window": [x0, x1, y0, y1], "pixels": int((x1 - x0) * (y1 - y0)),
+                             "normalised_by": "maximum of the oracle window (%.6g)" % peak, "tolerance": 1e-3,
+                             "checker": "oracle/liboracle.so (strict IEEE build), %s, frame 0 of this run's movie, %s" % (
+                                 "texture filter as measured on the B200 texture unit (ORC_OPT_FILTER_FRAC_BITS = 9)" if fetch_mode == 1 else "fp32 filter weights (documented formula)", note),
+                             "seconds": time.perf_counter() - t0}
+        except Exception as ex:
+            out["parity"] = {"failed": repr(ex)[:300]}
     # north_star: "a baseline from the reference's CUDA kernel rebuilt standalone via nvcc is added where it builds" -
     # oracle/_ref/libref_cuda.so = the reference's own d_render + upload code on texture objects (oracle/ref_cuda)
     try:
@@ -773,7 +841,7 @@ def reference_cuda_baseline(cpu, scene, vols):
     n = len(scene.lights)
     out = np.zeros((scene.H, scene.W, 3), dtype=np.float32, order="F")
     times = []
-    for k in range(3):
+    for k in range(9):  # one warm-up + 8 timed frames, median
         rot = scene.rot(k)
         t = time.perf_counter()
         assert rc.refcuda_render(cpu.lights if n else None, n, C.byref(cpu.lutv) if n else None, f32p(scene.factors), f32p(scene.es),
@@ -782,7 +850,8 @@ def reference_cuda_baseline(cpu, scene, vols):
         times.append(time.perf_counter() - t)
     # the lattice of frame 0 is the one the oracle counted per pixel above; count it for the full frame with the same rule
     return {"kind": "shimmed reference: the reference's d_render/upload code on texture objects, nvcc sm_100a, unmodified launch shape (16x16 blocks)",
-            "ms_per_frame": 1e3 * min(times[1:]), "frames": len(times) - 1, "first_frame_ms": 1e3 * times[0]}
+            "ms_per_frame": 1e3 * float(np.median(times[1:])), "ms_per_frame_min": 1e3 * min(times[1:]), "ms_per_frame_max": 1e3 * max(times[1:]),
+            "frames": len(times) - 1, "first_frame_ms": 1e3 * times[0], "statistic": "median of %d frames (camera +1 degree each) after one warm-up frame" % (len(times) - 1)}
 
 
 def run_volume(args):
@@ -932,5 +1001,6 @@ if __name__ == "__main__":
     os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
+        os.environ["OMP_NUM_THREADS"] = str(host_cores())  # before libgomp loads: torchrun hands its workers OMP_NUM_THREADS=1
         sys.exit(run_reference(a))
     sys.exit(run_volume(a) if a.mode == "volume" else run_b200(a))

@@ -90,6 +90,8 @@ typedef struct vr_stats {
   uint64_t bytes_uploaded;   /* host->device bytes moved by the last vr_sync_volumes / vr_render */
   uint32_t kernel_launches;  /* kernels launched by the last vr_render */
   uint32_t uploads;          /* volume uploads done by the last vr_sync_volumes */
+  uint32_t fetch_mode;       /* how the last render fetched: 0 = loads + fp32 lerps, 1 = texture unit (VR_OPT_TEXTURE_UNIT) */
+  uint32_t arithmetic;       /* arithmetic flavour of the last render's kernel (VR_OPT_ARITHMETIC) */
 } vr_stats;
 
 /* ---- 'new'  (render.cpp:58-65) -------------------------------------------------------- */
@@ -179,7 +181,12 @@ VR_API int vr_abi_version(void);
 typedef enum vr_option {
   VR_OPT_FILTER_FRAC_BITS = 0,  /* 0 = fp32 trilinear weights (default); 8 = the texture unit's 1.8 fixed point */
   VR_OPT_EMPTY_SPACE_SKIP = 1,  /* exact empty-space skipping: 2 (default) = closed-form jumps over the distance grid,
-                                   1 = serial recurrences cell by cell, 0 = march every sample; pixels are bit-identical */
+                                   1 = serial recurrences cell by cell, 0 = march every sample; pixels are bit-identical.
+                                   PRECONDITION of the bit-identity: voxels and factors are finite.  A sample whose
+                                   absorption fetch is 0 is not shaded (alpha = 0 makes its premultiplied contribution
+                                   exactly 0 for finite inputs); the reference would carry a NaN/Inf emission or reflection
+                                   voxel at such a sample into the pixel.  A negative OpacityThreshold (the reference then
+                                   stops after its first sample) switches skipping off for that render. */
   VR_OPT_KERNEL_VARIANT = 2,    /* 0 (default) = shared tap sets when all volumes share a geometry; 1 = per-texture addressing;
                                    3 = force the kernels with 64-bit z offsets (chosen automatically for a resident
                                    volume of more than 2^32 elements).  Pixels are bit-identical */

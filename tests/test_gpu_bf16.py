@@ -1,0 +1,168 @@
+"""bf16 volume storage (north_star "bf16/fp32 bricks", BASELINE configs[4]) on the GPU.
+
+The reference is fp32 only (src/C/vr/volumeRender.h:26), so the checker of a bf16 volume is the oracle fed the
+bf16-ROUNDED fp32 volume: storage is bf16, arithmetic stays fp32, and bf16 -> fp32 is exact.  Two bars per scene:
+  * against the oracle: vrt.TOL (1e-3 of the image maximum, BASELINE.json north_star);
+  * against this library rendering the SAME rounded values from fp32 storage: bit for bit - the bf16 kernels
+    (ElemBF16::load / load3, k_subcell_masks<ElemBF16>, the bf16 repack) must change nothing but the bytes in HBM.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import vrt
+from volume_renderer_b200 import _abi, api, multigpu
+
+pytestmark = pytest.mark.gpu
+RES = (144, 112)
+
+
+def bf16_bits(a):
+    """fp32 ndarray -> uint16 bf16 bit patterns, round to nearest even (what __float2bfloat16_rn does for finite values)."""
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    r = (u + 0x7FFF + ((u >> 16) & 1)) >> 16
+    return r.astype(np.uint16).reshape(a.shape)
+
+
+def bf16_to_f32(bits):
+    return (bits.astype(np.uint32) << 16).view(np.float32).reshape(bits.shape)
+
+
+def host_bf16_volume(values_f32):
+    """(a host volume of bf16 storage for the product, the same values as an fp32 array for the checker)."""
+    bits = np.asfortranarray(bf16_bits(np.asfortranarray(values_f32)))
+    rounded = np.asfortranarray(bf16_to_f32(bits))
+    dims = tuple(bits.shape) + (1,) * (3 - bits.ndim)
+    return api.DeviceVolume(bits.ctypes.data, dims, _abi.DTYPE_BF16, _abi.MEM_HOST, keepalive=bits), rounded
+
+
+@pytest.fixture(scope="module")
+def lut():
+    return api.HenyeyGreenstein(64)
+
+
+def _scene(cls, vol, lut, lights, grads=None, second_pass=False):
+    r = vrt.example1_scene(cls, vol, RES, lights=lights, lut=lut)
+    if grads is not None:
+        r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = grads
+    if second_pass:  # example1_grad.m:79-82
+        r.FactorEmission, r.FactorAbsorption, r.FactorReflection = 0.1, 0.4, 0.1
+        r.Color = [1, 1, 1]
+    return r
+
+
+def _oracle_for(gpu, orc):
+    """The checker filters the way the product's last render fetched (vr_stats.fetch_mode)."""
+    if gpu.stats()["fetch_mode"] == 1:
+        orc._backend.lib.orc_set_option(orc.objectHandle, vrt.ORC_OPT_FILTER_FRAC_BITS, 9)
+
+
+@pytest.mark.parametrize("texture_unit", [0, 2])
+@pytest.mark.parametrize("brick", [1, 0])
+@pytest.mark.parametrize("grad", [0, 1])
+def test_bf16_storage_against_the_oracle_and_against_fp32_storage(lut, brick, grad, texture_unit):
+    vol = vrt.synth_brain((72, 56, 48))
+    v16, v32 = host_bf16_volume(vol)
+    grads16 = grads32 = None
+    if grad:
+        g = [np.asarray(x.Data) for x in api.Volume(v32).grad()]
+        pairs = [host_bf16_volume(x) for x in g]
+        grads16 = [p[0] for p in pairs]
+        grads32 = [api.Volume(p[1]) for p in pairs]
+
+    def product(vol_obj, grads, opts=()):
+        r = _scene(api.VolumeRender, vol_obj, lut, 2, grads, second_pass=bool(grad))
+        r.setOption(_abi.OPT_BRICK_LAYOUT, brick)
+        r.setOption(_abi.OPT_TEXTURE_UNIT, texture_unit)
+        for k, v in opts:
+            r.setOption(k, v)
+        return r
+
+    gpu = product(v16, grads16)
+    img = gpu.render()
+    assert np.isfinite(img).all() and img.max() > 0
+    orc = _scene(vrt.OracleVolumeRender, api.Volume(v32), lut, 2, [api.Volume(np.asarray(x.Data)) for x in grads32] if grad else None, second_pass=bool(grad))
+    _oracle_for(gpu, orc)
+    m = vrt.compare(img, orc.render())
+    print("bf16 storage vs oracle(bf16-rounded volume): brick", brick, "grad", grad, "texture_unit", texture_unit, "fetch_mode", gpu.stats()["fetch_mode"], m)
+    assert m["max_abs_norm"] <= vrt.TOL, m
+    a, b = gpu.stats()["samples_marched"], orc._backend.stats(orc.objectHandle).samples_marched
+    assert abs(a - b) <= 1e-3 * b + 2, (a, b)
+    # the same values from fp32 storage, same options: identical bits
+    same_values = product(api.Volume(v32), grads32)
+    assert np.array_equal(same_values.render(), img)
+    assert same_values.stats()["samples_shaded"] == gpu.stats()["samples_shaded"]
+    # storage variants of the bf16 path are invisible: skipping modes, separate gradient volumes (load vs load3), per-texture kernels
+    for opts in ([(_abi.OPT_EMPTY_SPACE_SKIP, 0)], [(_abi.OPT_EMPTY_SPACE_SKIP, 1)], [(_abi.OPT_GRADIENT_INTERLEAVE, 0)], [(_abi.OPT_KERNEL_VARIANT, 1)]):
+        assert np.array_equal(product(v16, grads16, opts).render(), img), opts
+    # bf16 halves the resident voxel bytes on the load path
+    if texture_unit == 0 and not grad:
+        assert gpu.stats()["bytes_resident"] < 0.6 * same_values.stats()["bytes_resident"]
+
+
+def test_bf16_device_source_and_synth_twin(lut):
+    """vr_synth_volume(bf16) = the fp32 generator rounded to nearest even; a VR_MEM_DEVICE bf16 volume renders like the
+    same bits uploaded from the host."""
+    lib = _abi.lib()
+    dims = (40, 48, 56)
+    r = api.VolumeRender()
+    h = r.objectHandle
+    ptr = C.c_void_p()
+    n = int(np.prod(dims))
+    _abi.check(lib.vr_device_alloc(h, n * 2, C.byref(ptr)), h)
+    _abi.check(lib.vr_synth_volume(h, 0, vrt.SEED, (C.c_uint64 * 3)(*dims), _abi.DTYPE_BF16, ptr), h)
+    got = np.zeros(dims, dtype=np.uint16, order="F")
+    _abi.check(lib.vr_device_download(h, got.ctypes.data, ptr, got.nbytes), h)
+    want = bf16_bits(vrt.synth_brain(dims))
+    assert np.array_equal(got, want)
+    dev = _scene(lambda: r, api.DeviceVolume(ptr.value, dims, _abi.DTYPE_BF16, _abi.MEM_DEVICE), lut, 1)
+    host = _scene(api.VolumeRender, host_bf16_volume(vrt.synth_brain(dims))[0], lut, 1)
+    assert np.array_equal(dev.render(), host.render())
+    _abi.check(lib.vr_device_free(h, ptr), h)
+
+
+def test_bf16_two_bricks_volume_space(lut):
+    """vr_set_region with bf16 storage: two bricks of a bf16 volume on this GPU, composited, against the oracle and against
+    the single-pass bf16 render (2e-5: association of the opacity product, as for fp32)."""
+    vol = vrt.synth_brain((64, 56, 72))
+    v16, v32 = host_bf16_volume(vol)
+    bricks = multigpu.brick_grid(vol.shape, (1, 1, 2))
+
+    def scene(region=None):
+        r = api.VolumeRender()
+        if region is not None:
+            r.setRegion(region[0], region[1], 4)
+        r = _scene(lambda: r, v16, lut, 2)
+        r.FactorAbsorption = 30.0  # rays reach the threshold inside the volume: the opacity hand-over matters
+        return r
+
+    full_r = scene()
+    full = full_r.render()
+    img = multigpu.render_bricks_one_gpu([scene(b) for b in bricks], bricks)
+    m = vrt.compare(img, full)
+    print("bf16 bricks vs bf16 single pass", m)
+    assert m["max_abs_norm"] < 1e-4, m
+    orc = _scene(vrt.OracleVolumeRender, api.Volume(v32), lut, 2)
+    orc.FactorAbsorption = 30.0
+    _oracle_for(full_r, orc)
+    mo = vrt.compare(img, orc.render())
+    print("bf16 bricks vs oracle", mo)
+    assert mo["max_abs_norm"] <= vrt.TOL, mo
+
+
+def test_bf16_partial_update(lut):
+    """vr_update_box on a resident bf16 volume equals a full re-upload of the new contents."""
+    vol = vrt.synth_brain((48, 40, 56))
+    bits = np.asfortranarray(bf16_bits(vol))
+    v16 = api.DeviceVolume(bits.ctypes.data, vol.shape, _abi.DTYPE_BF16, _abi.MEM_HOST, keepalive=bits)
+    r = _scene(api.VolumeRender, v16, lut, 1)
+    r.render()
+    new = np.asfortranarray(bf16_bits(vol * np.float32(0.5)))
+    bits[:, :, :28] = new[:, :, :28]
+    r.updateVolumeBox("emission", (0, 0, 0), (48, 40, 28))
+    assert r.stats()["bytes_uploaded"] <= 28 * 48 * 40 * 2
+    img = r.render()
+    assert r.stats()["uploads"] == 0
+    fresh = _scene(api.VolumeRender, api.DeviceVolume(bits.ctypes.data, vol.shape, _abi.DTYPE_BF16, _abi.MEM_HOST, keepalive=bits), lut, 1)
+    assert np.array_equal(img, fresh.render())

@@ -67,6 +67,8 @@ class VrStats(C.Structure):
         ("bytes_uploaded", C.c_uint64),
         ("kernel_launches", C.c_uint32),
         ("uploads", C.c_uint32),
+        ("fetch_mode", C.c_uint32),
+        ("arithmetic", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -114,6 +114,7 @@ struct vr_ctx {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evu0 = nullptr, evu1 = nullptr;
+  cudaEvent_t ev_order = nullptr;  // orders a caller's stream behind work enqueued on the context's stream
   // mm::MManager state (mmanager.hxx:25-100)
   uint64_t timeLastMemSync = 0;
   HostVol host[S_N];
@@ -360,7 +361,10 @@ vr_status fill_resident(vr_ctx *c, Resident &r, const HostVol &v, const int box[
       const int64_t z0 = clampz((int64_t)(l0 * zper) + g0[2]), z1 = clampz((int64_t)(l1 * zper) - 1 + g0[2]);
       const size_t nbytes = (size_t)(z1 - z0 + 1) * slice_bytes;
       const int bi = k % kStageBufs;
-      if (k >= kStageBufs) VR_CUDA(c, cudaEventSynchronize(c->ev_stage[bi]));  // its previous slab has been repacked
+      // the DMA that last read this pinned buffer - a slab of this call or of the PREVIOUS upload (k restarts at 0 on
+      // every call and nothing else orders the CPU copy behind that DMA) - must have finished before the CPU rewrites
+      // it; on a never-recorded event this returns at once
+      VR_CUDA(c, cudaEventSynchronize(c->ev_stage[bi]));
       const char *src = static_cast<const char *>(v.data) + (size_t)z0 * slice_bytes;
       if (!pinned) {
         parallel_copy(c->h_stage[bi], src, nbytes);
@@ -735,7 +739,13 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     }
     // setIlluminationTexture (kernel.cu:682-689) tests `last_update > timeLastMemSync` but
     // syncVolume re-uploads regardless of its flag; the LUT is tiny, the data is what matters.
+    const uint32_t uploads_before = c->stats.uploads;
     VR_TRY(syncVolumeCached(c, S_LIGHT, c->host[S_LIGHT]));
+    if (c->stats.uploads != uploads_before && stream != c->stream) {
+      // the upload ran on the context's stream; a render on a caller's stream must not start before it has landed
+      VR_CUDA(c, cudaEventRecord(c->ev_order, c->stream));
+      VR_CUDA(c, cudaStreamWaitEvent(stream, c->ev_order, 0));
+    }
   }
   const HostVol &E = c->host[S_EM];
   if (E.w == 0 || E.h == 0 || E.d == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: no emission volume synced");
@@ -809,6 +819,9 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     const float dim[3] = {P.ab.fw, P.ab.fh, P.ab.fd};
     for (int i = 0; i < 3; ++i) mv = fmaxf(mv, P.tstep * dim[i] / (P.boxmax[i] - P.boxmin[i]));
     if (!(mv <= 0.45f)) P.skip = 0;
+    // Skipped samples never run the `sum.w > threshold` test (kernel.cu:485): with a NEGATIVE threshold the reference
+    // stops after its first sample wherever that is, so every sample is marched then.  (Non-finite voxels: see vr_abi.h.)
+    if (!(P.thr >= 0.0f)) P.skip = 0;
   }
   // shared tap sets: every volume texture of the launch has the geometry of the first one
   P.uniform = 1;
@@ -1041,6 +1054,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   }
   c->timing_pending = true;
   c->stats.kernel_launches = P.num_work > 0 ? 1 : 0;
+  c->stats.fetch_mode = texhw ? 1u : 0u;
   return VR_OK;
 }
 
@@ -1093,6 +1107,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu1);
   for (int i = 0; i < kStageBufs && ce == cudaSuccess; ++i) ce = cudaEventCreateWithFlags(&c->ev_stage[i], cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&c->ev_cost, cudaEventDisableTiming);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&c->ev_order, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_counter, 64);
   if (ce == cudaSuccess && getenv("VR_WARP_TIMES")) ce = cudaMalloc(&c->d_warp_times, 2 * 8192 * sizeof(unsigned long long));
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_stats, 64);
@@ -1136,6 +1151,7 @@ vr_status vr_destroy(vr_ctx *c) {
   if (c->d_tile_cost) cudaFree(c->d_tile_cost);
   if (c->h_tile_cost) cudaFreeHost(c->h_tile_cost);
   if (c->ev_cost) cudaEventDestroy(c->ev_cost);
+  if (c->ev_order) cudaEventDestroy(c->ev_order);
   if (c->d_boxes) cudaFree(c->d_boxes);
   if (c->d_warp_times) cudaFree(c->d_warp_times);
   if (c->d_stats) cudaFree(c->d_stats);
@@ -1278,8 +1294,15 @@ vr_status vr_update_box(vr_ctx *c, int role, const vr_volume *vol, const uint64_
   if (role < 0 || role > S_DZ) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: role %d (0 emission, 1 absorption, 2 reflection, 3..5 gradient x,y,z)", role);
   VR_TRY(set_device(c));
   VR_TRY(collect(c));
-  // the texture the role reads (roles that alias it see the update too)
-  const int slot = role == S_EM ? c->idxEm : role == S_AB ? c->idxAb : role == S_RE ? c->idxRe : role;
+  // The slot that HOLDS this host volume: the role's own texture when one was uploaded for it (a distinct absorption
+  // volume sits in tex[S_AB] although, as written, d_idxAbsorption keeps pointing at emission, kernel.cu:80), else the
+  // texture the role was aliased to by referenceTexture (kernel.cu:631-648; roles that alias it see the update too).
+  int slot = role;
+  if (role <= S_RE) {
+    const int idx = role == S_EM ? c->idxEm : role == S_AB ? c->idxAb : c->idxRe;
+    const bool own = c->arr[role] && c->tex[role].kind != TEX_UNBOUND && same(c->tex[role].src, c->host[role]);
+    if (!own && idx != role && same(c->host[role], c->host[idx])) slot = idx;
+  }
   Resident &r = c->tex[slot];
   const HostVol v = make_volume(vol);
   if (r.kind != TEX_VOLUME) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: the role has no resident volume (sync it first)");
