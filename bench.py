@@ -62,6 +62,7 @@ def parse():
     p.add_argument("--no-gather-probe", action="store_true", help="skip the gather-ceiling microbenchmark (roofline.gather)")
     p.add_argument("--interleave", type=int, default=1, help="1: Gx,Gy,Gz resident as one interleaved storage (default); 0: three volumes")
     p.add_argument("--texture-unit", type=int, default=2, help="VR_OPT_TEXTURE_UNIT: 2 (default) texture unit where the context can, 1 required, 0 loads + fp32 lerps")
+    p.add_argument("--arith", type=int, default=-1, help="VR_OPT_ARITHMETIC: 0 exact, 1 reference, 2 fast; -1 = the library's default")
     p.add_argument("--no-load-leg", action="store_true", help="skip the extra load-path measurement of the default run")
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
@@ -340,6 +341,8 @@ def run_b200(args):
     _abi.check(lib.vr_set_option(ctx, _abi.OPT_WARP_SHAPE, args.wshape), ctx)
     lib.vr_set_option(ctx, _abi.OPT_GRADIENT_INTERLEAVE, args.interleave)  # unchecked: older A/B builds lack the option
     lib.vr_set_option(ctx, _abi.OPT_TEXTURE_UNIT, args.texture_unit)  # unchecked: older A/B builds lack the option
+    if args.arith >= 0:
+        _abi.check(lib.vr_set_option(ctx, _abi.OPT_ARITHMETIC, args.arith), ctx)
     scene = Scene(args)
     n = args.size
     dt = _abi.DTYPE_F32 if args.dtype == "f32" else _abi.DTYPE_BF16

@@ -39,6 +39,8 @@ OPT_TILE_ORDER = 11
 OPT_WARP_SHAPE = 12
 OPT_GRADIENT_INTERLEAVE = 13
 OPT_TEXTURE_UNIT = 14
+OPT_ARITHMETIC = 15
+ARITH_EXACT, ARITH_REFERENCE, ARITH_FAST = 0, 1, 2
 IPC_HANDLE_BYTES = 64
 
 

@@ -162,7 +162,7 @@ struct vr_ctx {
   float *d_boxes = nullptr;  // world-space brick boxes of the last partial render
   size_t boxes_cap = 0;
   // options
-  int64_t opt[16];
+  int64_t opt[32];
   // bookkeeping
   vr_stats stats{};
   bool stats_pending = false;
@@ -822,6 +822,13 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     // Skipped samples never run the `sum.w > threshold` test (kernel.cu:485): with a NEGATIVE threshold the reference
     // stops after its first sample wherever that is, so every sample is marched then.  (Non-finite voxels: see vr_abi.h.)
     if (!(P.thr >= 0.0f)) P.skip = 0;
+    for (int i = 0; i < 3; ++i) {  // on_empty_cell: cell of the low tap = floor(((pos - bmin) * bscale * N - 0.5) / 8)
+      const double bscale = 1.0 / ((double)P.boxmax[i] - (double)P.boxmin[i]);
+      const int oc = i == 0 ? P.ocx : (i == 1 ? P.ocy : P.ocz);
+      P.cellA[i] = (float)(bscale * dim[i] / 8.0);
+      P.cellB[i] = (float)((-(double)P.boxmin[i] * bscale * dim[i] - 0.5) / 8.0);
+      P.cellMax[i] = (float)oc - 0.5f;
+    }
   }
   // shared tap sets: every volume texture of the launch has the geometry of the first one
   P.uniform = 1;
@@ -1041,7 +1048,9 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_stats, 0, 3 * sizeof(unsigned long long), stream));
   VR_CUDA(c, cudaEventRecord(c->ev0, stream));
-  if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, stream, c->sm_count));
+  const int arith = (int)c->opt[VR_OPT_ARITHMETIC];
+  if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, stream, c->sm_count, arith));
+  c->stats.arithmetic = (uint32_t)arith;
   VR_CUDA(c, cudaEventRecord(c->ev1, stream));
   if (P.tile_cost) {
     VR_CUDA(c, cudaMemcpyAsync(c->h_tile_cost, c->d_tile_cost, 2 * ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
@@ -1098,6 +1107,8 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->opt[VR_OPT_TEXTURE_UNIT] = 2;
   // without touching the MATLAB classes: VR_TEXTURE_UNIT=0 (loads + fp32 lerps) / 1 / 2 in the environment of the MATLAB process
   if (const char *tu = getenv("VR_TEXTURE_UNIT")) c->opt[VR_OPT_TEXTURE_UNIT] = atoi(tu) < 0 ? 0 : (atoi(tu) > 2 ? 2 : atoi(tu));
+  c->opt[VR_OPT_ARITHMETIC] = VR_DEFAULT_ARITHMETIC;
+  if (const char *ar = getenv("VR_ARITHMETIC")) c->opt[VR_OPT_ARITHMETIC] = atoi(ar) < 0 ? 0 : (atoi(ar) > 2 ? 2 : atoi(ar));
   cudaError_t ce = cudaSetDevice(device);
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   c->own_stream = ce == cudaSuccess;
@@ -1470,14 +1481,15 @@ int vr_abi_version(void) { return VR_ABI_VERSION; }
 
 vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_TEXTURE_UNIT) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option >= VR_OPT_COUNT_) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
+  if (option == VR_OPT_ARITHMETIC && (value < 0 || value > 2)) return fail(c, VR_ERR_INVALID_ARGUMENT, "arithmetic flavour must be 0 (exact), 1 (reference) or 2 (fast)");
   c->opt[option] = value;
   return VR_OK;
 }
 vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
   VR_CHECK_HANDLE(c);
-  if (option < 0 || option > VR_OPT_TEXTURE_UNIT || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
+  if (option < 0 || option >= VR_OPT_COUNT_ || !value) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   *value = c->opt[option];
   return VR_OK;
 }

@@ -18,10 +18,26 @@
 
 #include "vr_types.h"
 
+// Arithmetic flavour of the march (one set of kernels per flavour, selected per context by VR_OPT_ARITHMETIC):
+//   0  "exact": every operation individually rounded (the file is compiled with -fmad=false), IEEE sqrt and divide - bit-equal
+//      to the CPU checker, which is what makes the bit-level tests possible;
+//   1  "reference": what nvcc makes of the reference's own source - FMA contraction on, normalize() by rsqrtf
+//      (helper_math.h:1325-1328), IEEE sqrtf / divide in angle() (kernel.cu:284-287);
+//   2  "fast": flavour 1 with the cosine of angle() as dot * rsqrt(|a|^2 |b|^2) (one MUFU instead of two IEEE square roots and
+//      an IEEE divide) and x / pi as a multiplication.  The angles only address a 64^3 table through 8-bit filter weights.
+#ifndef VR_ARITH
+#define VR_ARITH 0
+#endif
 #if defined(__CUDA_ARCH__)
 #define VR_LDG(ptr) __ldg(ptr)
 #define VR_EXPF(x) __expf(x) /* the reference's intrinsic, kernel.cu:456 */
+#if VR_ARITH == 2
+#define VR_RSQRT(x) vrb::rsqrt_ftz(x) /* MUFU.RSQ alone: no scaling of subnormal arguments (a squared length below 1e-38 reads as 0) */
+#elif VR_ARITH == 1
+#define VR_RSQRT(x) rsqrtf(x) /* helper_math.h:1325-1328 */
+#else
 #define VR_RSQRT(x) (1.0f / sqrtf(x)) /* IEEE divide + sqrt: the normal must not depend on MUFU.RSQ's last bits */
+#endif
 #else
 #define VR_LDG(ptr) (*(ptr))
 #define VR_EXPF(x) exp2f((x) * 1.4426950408889634f)
@@ -46,8 +62,19 @@
 #ifndef VR_TEX_FAST
 #define VR_TEX_FAST 1
 #endif
+#ifndef VR_FAST_CELL
+#define VR_FAST_CELL 1
+#endif
 
 namespace vrb {
+
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ float rsqrt_ftz(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+#endif
 
 struct F3 {
   float x, y, z;
@@ -448,9 +475,24 @@ VR_HD float vr_acosf(float x) {
 // for NaN - checked exhaustively (tests/test_host_logic.py::test_div_pi_is_exact); the angles fed
 // to it are 0, NaN or >= 3e-4.
 VR_HD float div_pi(float x) {
+#if VR_ARITH == 2 && defined(__CUDA_ARCH__)
+  return x * (1.0f / VR_PI_F);
+#endif
   const float rcp = 1.0f / VR_PI_F;
   const float q0 = x * rcp;
   return fmaf(fmaf(-q0, VR_PI_F, x), rcp, q0);
+}
+
+// angle(a, b) / pi (kernel.cu:284-287, :331-339) from dot(a, b) and the two SQUARED lengths.  Flavours 0 and 1: the reference's
+// own operations, dot / (sqrt(|a|^2) * sqrt(|b|^2)) with IEEE square roots and divide (the square roots of a vector that
+// several angles share are common subexpressions).  Flavour 2: dot * rsqrt(|a|^2 |b|^2).  NaN whenever the reference's is
+// (a zero vector, an argument beyond [-1, 1]): acos_poly takes the square root of a negative number.
+VR_HD float angle_over_pi(float d, float la2, float lb2) {
+#if VR_ARITH == 2 && defined(__CUDA_ARCH__)
+  return div_pi(vr_acosf(d * rsqrt_ftz(la2 * lb2)));
+#else
+  return div_pi(vr_acosf(d / (sqrtf(la2) * sqrtf(lb2))));
+#endif
 }
 
 // shade (kernel.cu:308-353) given the gradient and the reflection sample: N = -normalize(g),
@@ -462,10 +504,10 @@ template <int LAYOUT>
 VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color, int fb) {
   const F3 N = -1.0f * normalize3(g);
   const F3 lightIn = origin - pos;
-  const float lenN = length3(N), lenIn = length3(lightIn);
-  const float a = div_pi(vr_acosf(dot3(N, lightIn) / (lenN * lenIn)));  // angle(N, lightIn)/pi
+  const float nn = dot3(N, N), ii = dot3(lightIn, lightIn);
+  const float a = angle_over_pi(dot3(N, lightIn), nn, ii);  // angle(N, lightIn)/pi
   const F3 lightInProj = lightIn - (dot3(lightIn, N) * N);
-  const float lenInProj = length3(lightInProj);
+  const float pp = dot3(lightInProj, lightInProj);
   F3 illum = mk3(0.0f, 0.0f, 0.0f);
   // (measured on B200, all slower under the 72-register budget: the loop unrolled by two +3.5 %; the angles of two lights
   // first and their sixteen LUT loads together +2.2 %; see also the notes in shade_sample)
@@ -478,9 +520,9 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
       lpos = mk3(VR_LDG(L), VR_LDG(L + 1), VR_LDG(L + 2)), lcol = mk3(VR_LDG(L + 3), VR_LDG(L + 4), VR_LDG(L + 5));
     }
     const F3 lightOut = lpos - pos;
-    const float b = div_pi(vr_acosf(dot3(N, lightOut) / (lenN * length3(lightOut))));
+    const float b = angle_over_pi(dot3(N, lightOut), nn, dot3(lightOut, lightOut));
     const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
-    const float c = div_pi(vr_acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))));
+    const float c = angle_over_pi(dot3(lightInProj, lightOutProj), pp, dot3(lightOutProj, lightOutProj));
     // the LUT is always fp32 in the linear padded layout
     float light;
     if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 16)) light = tex_raw(P.lut, a, b, c);
@@ -497,16 +539,16 @@ VR_HD F3 shade_lights(const KernelParams &P, F3 g, float reflection, F3 pos, F3 
 VR_HD F3 shade_lights_split(const KernelParams &P, F3 g, float reflection, F3 pos, F3 origin, F3 color, int fb) {
   const F3 N = -1.0f * normalize3(g);
   const F3 lightIn = origin - pos;
-  const float lenN = length3(N), lenIn = length3(lightIn);
-  const float a = div_pi(vr_acosf(dot3(N, lightIn) / (lenN * lenIn)));  // angle(N, lightIn)/pi
+  const float nn = dot3(N, N), ii = dot3(lightIn, lightIn);
+  const float a = angle_over_pi(dot3(N, lightIn), nn, ii);  // angle(N, lightIn)/pi
   const F3 lightInProj = lightIn - (dot3(lightIn, N) * N);
-  const float lenInProj = length3(lightInProj);
+  const float pp = dot3(lightInProj, lightInProj);
   F3 illum = mk3(0.0f, 0.0f, 0.0f);
   auto one_light = [&](const F3 lpos, const F3 lcol) {
     const F3 lightOut = lpos - pos;
-    const float b = div_pi(vr_acosf(dot3(N, lightOut) / (lenN * length3(lightOut))));
+    const float b = angle_over_pi(dot3(N, lightOut), nn, dot3(lightOut, lightOut));
     const F3 lightOutProj = lightOut - (dot3(lightOut, N) * N);
-    const float c = div_pi(vr_acosf(dot3(lightInProj, lightOutProj) / (lenInProj * length3(lightOutProj))));
+    const float c = angle_over_pi(dot3(lightInProj, lightOutProj), pp, dot3(lightOutProj, lightOutProj));
     const float light = (P.tex_fast & 16) ? tex_raw(P.lut, a, b, c) : tex3d_any<LAYOUT_TEXHW, ElemF32>(P.lut, a, b, c, fb);
     illum = illum + reflection * light * lcol * color;  // kernel.cu:349
   };
@@ -817,9 +859,26 @@ VR_HD bool skip_empty_serial(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, 
 }
 
 // the sample at r.pos lies in a cell of the distance grid that is empty (P.skip == 2)
+// On the device the cell comes from the world position with one multiply-add, two clamps and a magic-number floor per axis
+// (19 instructions with the load instead of 35): the result may differ from cell_at's by one cell when the low tap sits
+// within ~1e-4 voxels of a cell border, and either answer is safe there - a cell counts as empty only when every voxel of
+// the cell DILATED BY TWO VOXELS is zero, while the taps of such a sample reach at most one voxel beyond the cell.  A lane
+// that is told "empty" where the exact cell is not simply finds dist == 0 in skip_empty_jump and shades its (zero) sample;
+// pixels and sample counts are those of the exact test.
 VR_HD bool on_empty_cell(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale) {
+#if defined(__CUDA_ARCH__) && VR_FAST_CELL
+  (void)bmin, (void)bscale;
+  const float vx = fminf(fmaxf(fmaf(r.pos.x, P.cellA[0], P.cellB[0]), 0.0f), P.cellMax[0]);
+  const float vy = fminf(fmaxf(fmaf(r.pos.y, P.cellA[1], P.cellB[1]), 0.0f), P.cellMax[1]);
+  const float vz = fminf(fmaxf(fmaf(r.pos.z, P.cellA[2], P.cellB[2]), 0.0f), P.cellMax[2]);
+  const int cx = __float_as_int(__fadd_rd(vx, 12582912.0f)) - 0x4B400000;
+  const int cy = __float_as_int(__fadd_rd(vy, 12582912.0f)) - 0x4B400000;
+  const int cz = __float_as_int(__fadd_rd(vz, 12582912.0f)) - 0x4B400000;
+  return VR_LDG(P.dist + (uint32_t)((cz * P.ocy + cy) * P.ocx + cx)) != 0;
+#else
   const CellAt c = cell_at(P, r, bmin, bscale);
   return VR_LDG(P.dist + c.cell) != 0;
+#endif
 }
 
 // (The same test through the texture unit - the distance grid as a point-sampled 3D texture of bytes, one fetch at

@@ -11,9 +11,10 @@
 //  * volumes are padded (bricked) arrays read through the read-only path; no tensor cores, the
 //    path is gather + fp32 accumulate.
 //
-// This file is compiled twice (Makefile): -DVR_GRAD=1 -> raymarch_lookup.o (lookupGradient kernels),
-// -DVR_GRAD=0 -> raymarch_compute.o (computeGradient kernels).  Two modules keep ptxas' allocation
-// of one family independent of edits to the other and halve the build time.
+// This file is compiled once per gradient method and arithmetic flavour (Makefile): -DVR_GRAD=1 -> raymarch_lookup_a*.o
+// (lookupGradient kernels), -DVR_GRAD=0 -> raymarch_compute_a*.o (computeGradient kernels); -DVR_ARITH=0/1/2 with
+// -fmad=false for flavour 0 (raymarch_core.h).  Separate modules keep ptxas' allocation of one family independent of
+// edits to the other and the build parallel.
 #include <cuda_runtime.h>
 
 #ifndef VR_LUT_ADJACENT
@@ -22,6 +23,10 @@
 
 #ifndef VR_EARLY_RE
 #define VR_EARLY_RE VR_GRAD /* reflection taps issued with the emission taps: faster for lookupGradient only (A/B on B200) */
+#endif
+
+#ifndef VR_ARITH
+#define VR_ARITH 0
 #endif
 
 #include "raymarch_core.h"
@@ -70,7 +75,8 @@ static constexpr unsigned kFull = 0xffffffffu;
 #define VR_JUMP_WAIT 64
 #endif
 
-template <int GRAD, int LAYOUT, typename E, int UNI>
+// ARITH (= VR_ARITH of this translation unit, raymarch_core.h) only keeps the kernels of the arithmetic flavours apart by name
+template <int GRAD, int LAYOUT, typename E, int UNI, int ARITH>
 __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT>::min_blocks) k_raymarch(const __grid_constant__ KernelParams P) {
   const int lane = threadIdx.x & 31;
   const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
@@ -205,7 +211,7 @@ template <int GRAD, int LAYOUT, typename E, int UNI>
 static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
   constexpr int kBlockThreads = Tune<GRAD, LAYOUT>::threads;
   int per_sm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E, UNI>, kBlockThreads, 0);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E, UNI, VR_ARITH>, kBlockThreads, 0);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   // persistent grid: a whole number of waves, never more warps than work items
@@ -213,7 +219,7 @@ static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm
   const long long need = ((long long)P.num_work + (kBlockThreads / 32) - 1) / (kBlockThreads / 32);
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
-  k_raymarch<GRAD, LAYOUT, E, UNI><<<(unsigned)blocks, kBlockThreads, 0, stream>>>(P);
+  k_raymarch<GRAD, LAYOUT, E, UNI, VR_ARITH><<<(unsigned)blocks, kBlockThreads, 0, stream>>>(P);
   return cudaGetLastError();
 }
 
@@ -226,10 +232,12 @@ static cudaError_t launch_le(const KernelParams &P, cudaStream_t stream, int sm_
   return P.uniform ? launch_one<VR_GRAD, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<VR_GRAD, LAYOUT, E, 0>(P, stream, sm_count);
 }
 
+#define VR_CAT3_(a, b, c) a##b##c
+#define VR_CAT3(a, b, c) VR_CAT3_(a, b, c)
 #if VR_GRAD
-cudaError_t launch_raymarch_lookup(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
+cudaError_t VR_CAT3(launch_raymarch_lookup, _a, VR_ARITH)(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
 #else
-cudaError_t launch_raymarch_compute(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
+cudaError_t VR_CAT3(launch_raymarch_compute, _a, VR_ARITH)(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
 #endif
   // texture-unit launches: fp32 arrays, per-texture fetches (there are no tap sets to share)
   if (layout == LAYOUT_TEXHW) return dtype == 0 && P.uniform == 0 ? launch_one<VR_GRAD, LAYOUT_TEXHW, ElemF32, 0>(P, stream, sm_count) : cudaErrorInvalidValue;

@@ -12,10 +12,20 @@ namespace vrb {
 // raymarch_kernel.cu: the ray march.  layout / dtype describe the volume textures of the launch
 // (all volume slots of one launch share them; the LUT is always fp32 linear).
 // One module per gradient method (volumeRender.h:141-144).
-cudaError_t launch_raymarch_lookup(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count);
-cudaError_t launch_raymarch_compute(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count);
-inline cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
-  return P.gradient_method ? launch_raymarch_lookup(P, layout, dtype, stream, sm_count) : launch_raymarch_compute(P, layout, dtype, stream, sm_count);
+// ... and per arithmetic flavour (raymarch_core.h: VR_ARITH; 0 exact, 1 reference, 2 fast).
+#define VR_DECLARE_LAUNCH(a)                                                                                                  \
+  cudaError_t launch_raymarch_lookup_a##a(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count); \
+  cudaError_t launch_raymarch_compute_a##a(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count);
+VR_DECLARE_LAUNCH(0)
+VR_DECLARE_LAUNCH(1)
+VR_DECLARE_LAUNCH(2)
+#undef VR_DECLARE_LAUNCH
+inline cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count, int arith) {
+  typedef cudaError_t (*Fn)(const KernelParams &, int, int, cudaStream_t, int);
+  static const Fn lookup[3] = {launch_raymarch_lookup_a0, launch_raymarch_lookup_a1, launch_raymarch_lookup_a2};
+  static const Fn compute[3] = {launch_raymarch_compute_a0, launch_raymarch_compute_a1, launch_raymarch_compute_a2};
+  if (arith < 0 || arith > 2) return cudaErrorInvalidValue;
+  return (P.gradient_method ? lookup : compute)[arith](P, layout, dtype, stream, sm_count);
 }
 
 // resident_kernels.cu: everything that builds the resident representation of a volume.

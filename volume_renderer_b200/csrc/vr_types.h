@@ -128,6 +128,9 @@ struct KernelParams {
   // cell itself is not empty, 255 = at least 255)
   const uint8_t *dist;
   int ocx, ocy, ocz;
+  // the macro cell of a sample's low tap straight from the world position: floor(clamp(pos * cellA + cellB, 0, cellMax))
+  // per axis (= floor((x*N - 0.5) / 8) up to ~1e-4 voxels, far inside the grid's two-voxel dilation); see on_empty_cell
+  float cellA[3], cellB[3], cellMax[3];
 };
 
 }  // namespace vrb
