@@ -56,6 +56,7 @@ def parse():
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--skip", type=int, default=2)
     p.add_argument("--tile", type=int, default=64)
+    p.add_argument("--e2e-tile", type=int, default=32, help="N > 1, end-to-end leg: width of the tile columns dealt round-robin to the ranks")
     p.add_argument("--batch", type=int, default=16, help="frames per launch (one work queue per batch; clipped to --steps)")
     p.add_argument("--wshape", type=int, default=3, help="warp footprint (1<<s) x (32>>s) pixels")
     p.add_argument("--no-upload-probe", action="store_true", help="skip the host->resident upload measurement")
@@ -396,7 +397,6 @@ def run_b200(args):
         lights[i].color[:] = c
     B = frames_per_launch(args.steps, args.batch)
     npx = scene.W * scene.H * 3
-    h_img = torch.zeros(B * npx, dtype=torch.float32).pin_memory()
     resp = scene.res.ctypes.data_as(C.POINTER(C.c_uint64))
     p2p = world > 1 and args.exchange == "p2p"
     shared = token = d_img = None
@@ -473,34 +473,38 @@ def run_b200(args):
     # the reference, example2.m) + 'render' with host-side parameters and a device->host read of
     # the frame.  N > 1: partials are reduced to rank 0 first, rank 0 reads the frame back.
     stamp_sync = 100
-    h_np = h_img.numpy()
-    host_ptrs = (C.c_void_p * B)(*[h_np.ctypes.data + i * npx * 4 for i in range(B)])
+    # The frames land in ONE host buffer (a ring of two batches).  N = 1: pinned memory of this process.  N > 1: POSIX shared
+    # memory mapped and page-locked by every rank - with the column partition (VR_OPT_PART_MODE = 1) each rank's device copies
+    # exactly the pixel columns it rendered into the assembled frames over its own PCIe link, and the pipelined batches
+    # (vr_render_batch_begin / _end) let those copies run while the next batch is rendered.
+    host_frames = None
+    if world > 1:
+        host_frames = multigpu.SharedHostFrames(scene.H, scene.W, 2 * B, rank, world)
+        ring = host_frames.ptrs
+        multigpu.configure_partition(ctx, rank, world, args.e2e_tile, args.tile, mode=1)
+    else:
+        h_ring = torch.zeros(2 * B * npx, dtype=torch.float32).pin_memory()
+        ring = [h_ring.data_ptr() + i * npx * 4 for i in range(2 * B)]
 
-    def frame_e2e(step, nb):
+    def e2e_batch(step, nb, slot):
         _abi.check(lib.vr_sync_volumes(ctx, stamp_sync, C.byref(vE), C.byref(vR), C.byref(vA), *[C.byref(x) if x is not None else None for x in g]), ctx)
-        if world == 1:
-            rots = np.concatenate([scene.rot(step + i).reshape(-1, order="F") for i in range(nb)]).astype(np.float32)
-            _abi.check(lib.vr_render_batch(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
-                                           nb, f32p(rots), f32p(props_b), C.c_float(scene.thr), f32p(scene.color), host_ptrs), ctx)
-        else:
-            frame_device(step, nb)
-            if rank == 0:
-                if p2p:
-                    shared.download(h_np, nb)
-                else:
-                    h_img[: nb * npx].copy_(d_img[: nb * npx], non_blocking=True)
-            torch.cuda.synchronize()
-            if p2p:
-                multigpu.frame_barrier(token)  # nobody overwrites the shared images while rank 0 reads them
+        rots = np.concatenate([scene.rot(step + i).reshape(-1, order="F") for i in range(nb)]).astype(np.float32)
+        ptrs = (C.c_void_p * nb)(*ring[slot * B: slot * B + nb])
+        _abi.check(lib.vr_render_batch_begin(ctx, lights if nl else None, nl, C.byref(lutv) if nl else None, f32p(scene.factors), f32p(scene.es), resp,
+                                             nb, f32p(rots), f32p(props_b), C.c_float(scene.thr), f32p(scene.color), ptrs), ctx)
 
-    frame_e2e(-B, B)
+    def e2e_run(first, count):
+        """`count` frames from `first` in pipelined batches of B; returns the lattice samples of this rank's launches."""
+        for i, k in enumerate(range(0, count, B)):
+            e2e_batch(first + k, min(B, count - k), i & 1)
+        _abi.check(lib.vr_render_batch_end(ctx), ctx)  # every frame of this rank is in host memory
+        return stats().samples_marched
+
+    e2e_run(-2 * B, 2 * B)  # warm-up: both slots' device images, the pinned ring touched
     barrier()
-    e_samples = 0
     te = time.perf_counter()
-    for k in range(0, args.steps, B):
-        frame_e2e(k, min(B, args.steps - k))
-        e_samples += stats().samples_marched
-    barrier()
+    e_samples = e2e_run(0, args.steps)
+    barrier()  # N > 1: every rank's columns have landed in the shared frames
     te = time.perf_counter() - te
     e = torch.tensor([te, float(e_samples)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -542,6 +546,9 @@ def run_b200(args):
     d2h = scene.W * scene.H * 3 * 4
 
     def finish():
+        if host_frames is not None:
+            _abi.check(lib.vr_set_option(ctx, _abi.OPT_PART_MODE, 0), ctx)
+            host_frames.close(world)
         if shared is not None:
             torch.cuda.synchronize()
             dist.barrier()
@@ -603,7 +610,9 @@ def run_b200(args):
         "frames_per_s": args.steps / (ms * 1e-3), "gsamples_shaded_per_s": shaded_all / (ms * 1e-3) / 1e9,
         "samples_per_frame": samples_all / args.steps, "upload_s": t_up,
         "e2e": {"value": e2e_value, "unit": "Gsamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "frames_per_s": args.steps / te,
-                "note": "vr_sync_volumes + vr_render through the C ABI with host parameter/output buffers; volumes persistent (uploaded once, %0.2f s)" % t_up},
+                "note": ("vr_sync_volumes + vr_render_batch_begin/_end through the C ABI with host parameter and (page-locked) host image buffers, batches of %d frames, "
+                         "copies of batch k overlapped with the launch of batch k+1; volumes persistent (uploaded once, %0.2f s)" % (B, t_up)) +
+                        ("; N = %d: tile columns %d px wide dealt round-robin, each rank copies its own columns into frames in shared host memory" % (world, args.e2e_tile) if world > 1 else "")},
         "gpu_launches": launches_all, "clocks": clocks, "roofline": roofline,
     }
     if single is not None:

@@ -155,6 +155,30 @@ VR_API vr_status vr_render_batch_device(vr_ctx *ctx, const vr_light *lights, siz
                                         float opacity_threshold, const float color[3],
                                         float *const *d_out_images, void *cuda_stream);
 
+/* ---- several GPUs behind the same boundary (no reference counterpart; the reference renders on ONE device,
+ * volumeRender.cpp:77-87,153) ---------------------------------------------------------------------------------
+ * The context becomes the leader of a group with one member context per listed device (device_ids[0] must be the
+ * context's own device; n = 0 or 1 dissolves the group).  vr_sync_volumes then makes the volumes resident on every
+ * device (one host thread per device), and every render is cut into tile columns dealt round-robin to the devices:
+ * host-image renders (vr_render, vr_render_batch*) have each device copy its own columns into the caller's image over
+ * its own PCIe link, device-image renders have the kernels of all devices store into the caller's image over NVLink.
+ * Pixels are those of one device, bit for bit.  A MATLAB user adds one call after 'new':
+ * volumeRender('set_devices', handle, int32([0 1 2 3])).  Call it before the first vr_sync_volumes. */
+VR_API vr_status vr_set_devices(vr_ctx *ctx, uint32_t n, const int *device_ids);
+
+/* Pipelined movie batches (examples/example2.m:59-66 renders 360 frames of one scene): _begin enqueues the launch of a
+ * batch and the device->host copies of its frames (of the pixels this context owns when it is partitioned,
+ * VR_OPT_PART_MODE) and returns; the next _begin renders into a second set of device images while those copies are on the
+ * wire.  out_images must stay valid - and should be pinned, a pageable destination makes the copy synchronous - until
+ * vr_render_batch_end, which waits for everything begun; vr_get_stats then holds the counters summed over the batches
+ * (kernel_ms = sum of the launches).  Any other call on the context ends the pipeline first. */
+VR_API vr_status vr_render_batch_begin(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
+                                       const vr_volume *illumination, const float factors[3],
+                                       const float element_size_um[3], const uint64_t resolution[2],
+                                       size_t n_frames, const float *rotations, const float *props,
+                                       float opacity_threshold, const float color[3], float *const *out_images);
+VR_API vr_status vr_render_batch_end(vr_ctx *ctx);
+
 /* The same batch with host images (n_frames pointers to H*W*3 floats each), synchronous like vr_render. */
 VR_API vr_status vr_render_batch(vr_ctx *ctx, const vr_light *lights, size_t n_lights,
                                  const vr_volume *illumination, const float factors[3],
@@ -220,9 +244,18 @@ typedef enum vr_option {
                                    with the cosine in angle() as dot * rsqrt(|a|^2 |b|^2) and x / pi as a multiplication.  All three are
                                    held to the 1e-3 bar against the checker and to the measured envelope against the reference
                                    kernel's own images (tests/test_golden_refcuda.py); $VR_ARITHMETIC sets the default of new contexts */
+  VR_OPT_PART_MODE = 16,        /* image-space partition (VR_OPT_PART_RANK / _NRANKS): 0 (default) = tiles dealt round-robin, 1 = tile
+                                   COLUMNS dealt round-robin (tile tx belongs to rank tx % nranks).  With columns the pixels a rank
+                                   owns are, per image plane, runs of tile_w * H contiguous floats: a rank can copy exactly its own
+                                   pixels to the host (vr_render*, vr_render_batch_begin write only owned pixels of the host image
+                                   when nranks > 1), so the read-back of a frame is spread over the PCIe links of all GPUs */
   VR_OPT_COUNT_
 } vr_option;
-#define VR_DEFAULT_ARITHMETIC 0
+/* Default: 2.  Measured on a B200 against the reference kernel's OWN images (tests/golden/refcuda_*.npy, seven scenes): flavours 1
+ * and 2 agree with them to PSNR 112-125 dB, maximum 7.8e-5 ... 3.2e-4 of the image maximum, bit for bit on the scene without
+ * shading; flavour 0 - like the CPU checker - to 98-106 dB, maximum 3.6e-4 ... 1.5e-3 and one pixel at 2.5e-2
+ * (profiles/r02_arith_ab.md).  Flavour 2 renders the headline workload 12 % faster than flavour 0, 7 % faster than 1. */
+#define VR_DEFAULT_ARITHMETIC 2
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);
 VR_API vr_status vr_get_stats(vr_ctx *ctx, vr_stats *out);

@@ -7,7 +7,7 @@
 #include <stdint.h>
 typedef size_t mwSize;
 typedef size_t mwIndex;
-typedef enum { mxUNKNOWN_CLASS = 0, mxLOGICAL_CLASS = 3, mxDOUBLE_CLASS = 6, mxSINGLE_CLASS = 7, mxUINT64_CLASS = 15 } mxClassID;
+typedef enum { mxUNKNOWN_CLASS = 0, mxLOGICAL_CLASS = 3, mxDOUBLE_CLASS = 6, mxSINGLE_CLASS = 7, mxINT32_CLASS = 12, mxUINT64_CLASS = 15 } mxClassID;
 typedef enum { mxREAL = 0, mxCOMPLEX = 1 } mxComplexity;
 typedef struct mxArray_tag mxArray;
 #ifdef __cplusplus

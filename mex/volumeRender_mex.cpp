@@ -115,6 +115,11 @@ extern "C" void mexFunction(int nlhs, mxArray *plhs[], int nrhs, const mxArray *
     if (vr_set_option(ctx, (int)mxGetScalar(prhs[2]), (int64_t)mxGetScalar(prhs[3])) != VR_OK) fail(ctx, "set_option failed");
     return;
   }
+  if (!strcmp("set_devices", cmd)) {  // extension, no reference counterpart: volumeRender('set_devices', h, int32([0 1 2 3]))  (vr_set_devices)
+    if (nrhs != 3 || mxGetClassID(prhs[2]) != mxINT32_CLASS) mexErrMsgTxt("set_devices: device ids must be an int32 vector");
+    if (vr_set_devices(ctx, (uint32_t)mxGetNumberOfElements(prhs[2]), static_cast<const int *>(mxGetData(prhs[2]))) != VR_OK) fail(ctx, "set_devices failed");
+    return;
+  }
   if (!strcmp("render", cmd)) {  // render.cpp:134-277
     if (nrhs < 11) mexErrMsgTxt("insufficient parameter!");  // render.cpp:136-140
     // lights + illumination: skipped when either is a logical placeholder (render.cpp:145-146)

@@ -43,7 +43,7 @@ def lut():
 
 
 def _scene(cls, vol, lut, lights, grads=None, second_pass=False):
-    r = vrt.example1_scene(cls, vol, RES, lights=lights, lut=lut)
+    r = vrt.exact(vrt.example1_scene(cls, vol, RES, lights=lights, lut=lut))  # held to TOL against the oracle
     if grads is not None:
         r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = grads
     if second_pass:  # example1_grad.m:79-82
@@ -89,8 +89,8 @@ def test_bf16_storage_against_the_oracle_and_against_fp32_storage(lut, brick, gr
     assert m["max_abs_norm"] <= vrt.TOL, m
     a, b = gpu.stats()["samples_marched"], orc._backend.stats(orc.objectHandle).samples_marched
     assert abs(a - b) <= 1e-3 * b + 2, (a, b)
-    # the same values from fp32 storage, same options: identical bits
-    same_values = product(api.Volume(v32), grads32)
+    # the same values from fp32 storage, fetched the way this render fetched: identical bits
+    same_values = product(api.Volume(v32), grads32, [(_abi.OPT_TEXTURE_UNIT, gpu.stats()["fetch_mode"])])
     assert np.array_equal(same_values.render(), img)
     assert same_values.stats()["samples_shaded"] == gpu.stats()["samples_shaded"]
     # storage variants of the bf16 path are invisible: skipping modes, separate gradient volumes (load vs load3), per-texture kernels

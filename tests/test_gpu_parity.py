@@ -22,14 +22,20 @@ def brain64():
     return vrt.synth_brain((64, 64, 64))
 
 
-# Every test of this file runs in both fetch modes of the product (VR_OPT_TEXTURE_UNIT):
-#   "texture" - the default: fetches through the texture unit, checked against the oracle with the filter as measured on the
-#               B200 texture unit (ORC_OPT_FILTER_FRAC_BITS = 9, pinned by tests/test_oracle_ref.py and the golden images);
-#   "loads"   - loads + fp32 lerps, checked against the oracle with fp32 weights (the documented formula), bit-level.
+# Every test of this file runs in three configurations of the product (VR_OPT_TEXTURE_UNIT x VR_OPT_ARITHMETIC):
+#   "texture" - fetches through the texture unit, "exact" arithmetic: checked against the oracle with the filter as measured
+#               on the B200 texture unit (ORC_OPT_FILTER_FRAC_BITS = 9, pinned by tests/test_oracle_ref.py and the golden
+#               images), bar vrt.TOL;
+#   "loads"   - loads + fp32 lerps, "exact" arithmetic: checked against the oracle with fp32 weights (the documented
+#               formula), bit-level, bar vrt.TOL;
+#   "default" - the library's defaults (texture unit, the arithmetic flavour of VR_DEFAULT_ARITHMETIC - what nvcc makes of the
+#               reference's own source): against the oracle this flavour differs exactly as the reference's own kernel does,
+#               bar vrt.check_parity(exact_flavour=False); its tight pin is tests/test_golden_refcuda.py.
+# Bit-identity between configurations of the product (layouts, skipping, partitions, batches) is asserted in all three.
 _MODE = "texture"
 
 
-@pytest.fixture(params=["texture", "loads"], autouse=True)
+@pytest.fixture(params=["texture", "loads", "default"], autouse=True)
 def fetch_mode(request):
     global _MODE
     _MODE = request.param
@@ -38,6 +44,8 @@ def fetch_mode(request):
 
 
 def _apply_mode(gpu, orc=None):
+    if _MODE != "default":
+        gpu.setOption(_abi.OPT_ARITHMETIC, _abi.ARITH_EXACT)
     if _MODE == "loads":
         gpu.setOption(_abi.OPT_TEXTURE_UNIT, 0)
     elif orc is not None:
@@ -59,10 +67,11 @@ def _pair(vol, res, lights, lut, **kw):
 
 def _check(gpu, orc, tol=vrt.TOL, same_samples=True):
     img, ref = gpu.render(), orc.render()
-    m = vrt.compare(img, ref)
-    print(m)
     assert np.isfinite(img).all()
-    assert m["max_abs_norm"] <= tol, m
+    m = vrt.check_parity(img, ref, exact_flavour=_MODE != "default")
+    print(_MODE, m)
+    if _MODE != "default":
+        assert m["max_abs_norm"] <= tol, m
     if same_samples and isinstance(gpu, api.VolumeRender) and gpu.CameraXOffset == 0:
         # the CUDA build contracts to FMA, so a ray's tnear/tfar can differ from the oracle's by an
         # ulp and its sample count by one; totals agree to well under 0.1 %
@@ -552,6 +561,7 @@ def test_texture_unit_mode(brain64, lut):
             for r in (gpu, orc):
                 r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gx, gy, gz
         gpu.setOption(_abi.OPT_TEXTURE_UNIT, 1)
+        vrt.exact(gpu)
         img = gpu.render()
         assert np.isfinite(img).all()
         orc._backend.lib.orc_set_option(orc.objectHandle, vrt.ORC_OPT_FILTER_FRAC_BITS, 9)

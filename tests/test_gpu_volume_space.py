@@ -20,6 +20,7 @@ def _scene(vol, lut, grad, bricks=None, b=None, halo=0):
         r.setRegion(bricks[b][0], bricks[b][1], halo)  # before the volumes are assigned / synced
     r = vrt.example1_scene(lambda: r, vol, RES, lights=2, lut=lut)
     r.setOption(_abi.OPT_TEXTURE_UNIT, 0)  # region contexts fetch with loads: compare like with like
+    vrt.exact(r)  # held to TOL against the oracle
     r.FactorAbsorption = 30.0  # rays reach the 0.9 threshold inside the volume
     if grad:
         gx, gy, gz = api.Volume(vol).grad()

@@ -377,6 +377,33 @@ def compare(img, ref):
 TOL = 1e-3  # BASELINE.json north_star: max abs error <= 1e-3 on [0,1]-normalised RGB
 
 
+def exact(r):
+    """Select the "exact" arithmetic flavour (VR_OPT_ARITHMETIC = 0: no FMA contraction, IEEE sqrt / divide) on a product
+    renderer: the flavour that agrees with the CPU oracle bit for bit up to acosf, and is therefore held to TOL on every
+    scene.  (The default flavour reproduces what nvcc makes of the reference's own source and is pinned by the reference
+    kernel's golden images instead, tests/test_golden_refcuda.py.)  No-op on oracle-backed renderers."""
+    if type(r._backend).__name__ == "_CudaBackend":
+        r.setOption(_abi.OPT_ARITHMETIC, _abi.ARITH_EXACT)
+    return r
+
+
+def check_parity(img, ref, exact_flavour=True):
+    """The bar of a product image against the oracle's.  Exact flavour: max-abs <= TOL of the oracle image's maximum.
+    Other flavours differ from the oracle exactly as the reference's own CUDA kernel does (FMA contraction, rsqrtf; isolated
+    samples on the illumination's NaN discontinuity flip sides): they are held to the envelope the ORACLE is held to against
+    the reference kernel's golden images - PSNR >= 75 dB, >= 99.9 % of the pixels within 1e-3, median <= 1e-4, isolated
+    pixels <= 3e-2 - on the small test scenes, and to TOL itself at full size (bench.py `parity`)."""
+    m = compare(img, ref)
+    if exact_flavour:
+        assert m["max_abs_norm"] <= TOL, m
+        return m
+    d = np.abs(np.asarray(img, np.float64) - np.asarray(ref, np.float64)).max(axis=2) / m["peak"]
+    m["frac_within_1e-3"] = float((d <= 1e-3).mean())
+    m["median"] = float(np.median(d))
+    assert m["psnr_db"] >= 75.0 and m["frac_within_1e-3"] >= 0.999 and m["median"] <= 1e-4 and m["max_abs_norm"] <= 3e-2, m
+    return m
+
+
 # ---- the shimmed reference CUDA kernel (oracle/_ref/libref_cuda.so) -----------------------------------
 def ref_cuda():
     """The reference's own d_render + upload code on texture objects (oracle/ref_cuda), or None."""

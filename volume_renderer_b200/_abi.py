@@ -40,6 +40,7 @@ OPT_WARP_SHAPE = 12
 OPT_GRADIENT_INTERLEAVE = 13
 OPT_TEXTURE_UNIT = 14
 OPT_ARITHMETIC = 15
+OPT_PART_MODE = 16
 ARITH_EXACT, ARITH_REFERENCE, ARITH_FAST = 0, 1, 2
 IPC_HANDLE_BYTES = 64
 
@@ -102,6 +103,9 @@ def declare(lib):
         "vr_render_device": (render_args + [vp, vp], C.c_int),
         "vr_render_batch": ([vp, P(VrLight), C.c_size_t, P(VrVolume), f3, f3, u64p, C.c_size_t, f3, f3, C.c_float, f3, P(vp)], C.c_int),
         "vr_render_batch_device": ([vp, P(VrLight), C.c_size_t, P(VrVolume), f3, f3, u64p, C.c_size_t, f3, f3, C.c_float, f3, P(vp), vp], C.c_int),
+        "vr_render_batch_begin": ([vp, P(VrLight), C.c_size_t, P(VrVolume), f3, f3, u64p, C.c_size_t, f3, f3, C.c_float, f3, P(vp)], C.c_int),
+        "vr_render_batch_end": ([vp], C.c_int),
+        "vr_set_devices": ([vp, C.c_uint32, P(C.c_int)], C.c_int),
         "vr_henyey_greenstein": ([C.c_uint32, C.c_float, vp], C.c_int),
         "vr_timestamp_ms": ([C.c_int], C.c_uint64),
         "vr_last_error": ([vp], C.c_char_p),

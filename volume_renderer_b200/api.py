@@ -476,6 +476,13 @@ class VolumeRender:
         """vr_set_option; no MATLAB counterpart (defaults reproduce the reference as written)."""
         self._backend.set_option(self.objectHandle, option, value)
 
+    def setDevices(self, device_ids):
+        """vr_set_devices; no MATLAB counterpart in the reference (it renders on one device).  The gateway command is
+        volumeRender('set_devices', handle, int32 ids): this object then renders on all the listed GPUs - volumes resident on
+        each, tile columns dealt round-robin - and returns the same H x W x 3 image.  Call before the first render."""
+        ids = (C.c_int * len(device_ids))(*[int(d) for d in device_ids])
+        _abi.check(_abi.lib().vr_set_devices(self.objectHandle, len(device_ids), ids), self.objectHandle)
+
     def memClear(self):
         """VolumeRender.m:230-237: 'delete' on the handle; the later destructor hits a stale handle."""
         self._backend.delete(self.objectHandle)
@@ -612,6 +619,34 @@ class VolumeRender:
         boxes = multigpu.boxes_array(bricks)
         _abi.check(_abi.lib().vr_render_partial_device(self.objectHandle, *args, len(bricks), int(index), boxes.ctypes.data_as(C.POINTER(C.c_uint64)),
                                                        C.c_void_p(d_opacity_all), C.c_void_p(d_out), C.c_void_p(stream or 0)), self.objectHandle)
+
+    def renderMoviePipelined(self, rotations, batch=8, out=None):
+        """Extension: a long rotation movie (examples/example2.m:59-66) through vr_render_batch_begin / _end - batch k's
+        frames travel to the host while batch k+1 is rendered.  `out` (optional) is a list of page-locked H x W x 3 arrays."""
+        self._check_volumes()
+        self.syncVolumes()
+        H, W = int(self.ImageResolution[1]), int(self.ImageResolution[0])
+        n = len(rotations)
+        outs = out if out is not None else [np.zeros((H, W, 3), dtype=np.float32, order="F") for _ in range(n)]
+        lib, h = _abi.lib(), self.objectHandle
+        f32p = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+        keepalive = []
+        try:
+            for k in range(0, n, batch):
+                nb = min(batch, n - k)
+                args, keep = _render_args(self.LightSources if self.LightSources is not False else None,
+                                          self.VolumeIllumination if self.VolumeIllumination is not False else None,
+                                          [self.FactorEmission, self.FactorReflection, self.FactorAbsorption], self.ElementSizeUm, [H, W],
+                                          np.flipud(np.asarray(rotations[k])), [np.float32(self.CameraXOffset), self.FocalLength, self.DistanceToObject],
+                                          self.OpacityThreshold, self.Color)
+                R = np.concatenate([np.asfortranarray(np.flipud(np.asarray(r)).astype(np.float32)).reshape(-1, order="F") for r in rotations[k:k + nb]]).astype(np.float32)
+                Pp = np.tile(np.array([self.CameraXOffset, self.FocalLength, self.DistanceToObject], dtype=np.float32), nb)
+                ptrs = (C.c_void_p * nb)(*[o.ctypes.data for o in outs[k:k + nb]])
+                keepalive += [keep, R, Pp, ptrs]
+                _abi.check(lib.vr_render_batch_begin(h, args[0], args[1], args[2], args[3], args[4], args[5], nb, f32p(R), f32p(Pp), args[8], args[9], ptrs), h)
+        finally:
+            _abi.check(lib.vr_render_batch_end(h), h)
+        return outs
 
     def renderMovie(self, rotations):
         """Extension: the frames of a rotation movie (examples/example2.m:59-66) in one launch;

@@ -105,6 +105,26 @@ struct G4Geo {
   }
 };
 
+// Everything one launch owns while it is in flight.  The synchronous entry points use slot 0; the pipelined batches
+// (vr_render_batch_begin / _end) alternate between the two, so that the frames of batch k leave for the host while the
+// kernel of batch k+1 runs.
+struct LaunchSlot {
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the ray-march launch (timing)
+  cudaEvent_t ev_cost = nullptr;             // the launch's tile costs have reached h_tile_cost
+  cudaEvent_t ev_rendered = nullptr;         // launch + its counters complete (the copy stream waits on it)
+  cudaEvent_t ev_copied = nullptr;           // the frames of this slot have reached host memory
+  unsigned long long *d_stats = nullptr;     // 3 counters
+  unsigned long long *h_stats = nullptr;     // pinned
+  unsigned int *h_tile_cost = nullptr;       // pinned: measured cost per tile of this slot's last launch
+  size_t cost_tiles = 0;                     // capacity in tiles
+  uint64_t cost_sig = 0;                     // geometry the host copy belongs to (W, H, tile size)
+  bool cost_valid = false;
+  float *d_image = nullptr;                  // persistent output image(s) of the host-image entry points
+  size_t image_cap = 0;
+  bool stats_pending = false, timing_pending = false;
+  bool in_flight = false;                    // a pipelined batch of this slot has not been harvested yet
+};
+
 }  // namespace
 
 struct vr_ctx {
@@ -113,7 +133,19 @@ struct vr_ctx {
   int sm_count = 148;
   cudaStream_t stream = nullptr;
   bool own_stream = false;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evu0 = nullptr, evu1 = nullptr;
+  cudaEvent_t evu0 = nullptr, evu1 = nullptr;
+  LaunchSlot slot[2];
+  int cur = 0;                       // slot of the launch being set up
+  cudaStream_t copy_stream = nullptr;  // device->host copies of pipelined batches
+  bool pipe_open = false;            // between vr_render_batch_begin and vr_render_batch_end
+  uint64_t pipe_batches = 0;
+  vr_stats pipe_total{};             // counters summed over the batches of the open pipeline
+  // a group of contexts driven through this one (vr_set_devices): members[0] is this context itself
+  std::vector<vr_ctx *> members;
+  vr_ctx *leader = nullptr;          // set in the other members
+  bool ever_synced = false;
+  cudaEvent_t ev_group = nullptr;    // orders this member's stream against the leader's (device-image renders of a group)
+  bool group_peer = false;           // every pair of the group's devices has peer access
   cudaEvent_t ev_order = nullptr;  // orders a caller's stream behind work enqueued on the context's stream
   // mm::MManager state (mmanager.hxx:25-100)
   uint64_t timeLastMemSync = 0;
@@ -133,8 +165,6 @@ struct vr_ctx {
   float *d_lights_more = nullptr;
   size_t lights_more_cap = 0;
   // persistent buffers
-  float *d_image = nullptr;
-  size_t image_cap = 0;
   void *d_stage[kStageBufs] = {nullptr, nullptr, nullptr};  // device side of the upload staging
   void *h_stage[kStageBufs] = {nullptr, nullptr, nullptr};  // pinned host side
   cudaEvent_t ev_stage[kStageBufs] = {nullptr, nullptr, nullptr};
@@ -143,17 +173,12 @@ struct vr_ctx {
   uint32_t *d_tile_order = nullptr;       // owned tiles, heaviest first
   Camera *d_cams = nullptr;               // cameras of a batch
   // measured cost per tile of the previous launch (device counters, pinned host copy, completion event)
-  unsigned int *d_tile_cost = nullptr, *h_tile_cost = nullptr;
+  unsigned int *d_tile_cost = nullptr;
   size_t tile_cost_tiles = 0;     // capacity in tiles
-  uint64_t cost_sig = 0;          // geometry the host copy belongs to (W, H, tile size)
-  bool cost_valid = false;
-  cudaEvent_t ev_cost = nullptr;
   size_t cams_cap = 0;
   unsigned long long *d_warp_times = nullptr;  // debug buffer ($VR_WARP_TIMES=1): 2 x 8192 entries
   size_t tile_order_cap = 0;
   std::vector<uint32_t> h_tile_order;
-  unsigned long long *d_stats = nullptr;  // 3 counters
-  unsigned long long *h_stats = nullptr;  // pinned
   // volume-space mode: the voxel sub-box this context owns (region_on == false: everything)
   bool texhw_failed = false;  // VR_OPT_TEXTURE_UNIT = 2: the array copies did not fit; retried after the next upload
   bool region_on = false;
@@ -165,8 +190,6 @@ struct vr_ctx {
   int64_t opt[32];
   // bookkeeping
   vr_stats stats{};
-  bool stats_pending = false;
-  bool timing_pending = false;
   std::string err;
 };
 
@@ -222,7 +245,7 @@ void release(vr_ctx *c, Resident &r) {
 uint64_t resident_bytes(const vr_ctx *c) {
   uint64_t b = 0;
   for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes + c->tex[i].dist_bytes + c->tex[i].array_bytes;
-  b += c->image_cap + kStageBufs * c->stage_cap + c->lights_more_cap + c->g4_bytes;
+  b += c->slot[0].image_cap + c->slot[1].image_cap + kStageBufs * c->stage_cap + c->lights_more_cap + c->g4_bytes;
   return b;
 }
 
@@ -270,8 +293,40 @@ void parallel_copy(void *dst, const void *src, size_t bytes) {
 // MATLAB's mxArray is pageable; the driver stages such a copy itself at ~16 GB/s (3.1 ms for a 2048^2 frame, measured).
 // A pinned mirror filled in eight DMA pieces with four host threads moving piece k while piece k+1 is on the wire was
 // tried: 2.1 ms at best, but every few frames the copy threads were descheduled on the bench box and a frame took
-// 40-77 ms instead of 29 (gpurun_out r4).  A steady 3 ms beats a fragile 2: the plain copy stays.  Returns with the
-// stream drained.
+// 40-77 ms instead of 29 (gpurun_out r4).  A steady 3 ms beats a fragile 2: the plain copy stays.
+// Enqueues on `stream` the copy of the pixels THIS context renders: the whole frame for an unpartitioned context; with the
+// column partition (VR_OPT_PART_MODE = 1) the owned tile columns - per image plane `rows` runs of tile_w * H contiguous floats
+// at a pitch of nranks * tile_w * H floats, one 2-D copy per plane (plus the clipped last column).
+vr_status enqueue_download(vr_ctx *c, void *out, const void *d_src, uint64_t W, uint64_t H, cudaStream_t stream) {
+  const int64_t nranks = c->opt[VR_OPT_PART_NRANKS], rank = c->opt[VR_OPT_PART_RANK];
+  const size_t plane = (size_t)W * H;
+  if (nranks <= 1 || c->opt[VR_OPT_PART_MODE] != 1) {
+    // unpartitioned, or tiles dealt round-robin: the whole (cleared) image with this context's tiles in it
+    VR_CUDA(c, cudaMemcpyAsync(out, d_src, plane * 3 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    return VR_OK;
+  }
+  const size_t tw = (size_t)c->opt[VR_OPT_TILE_W];
+  const size_t ntx = (W + tw - 1) / tw;
+  const size_t run = tw * H * sizeof(float), pitch = (size_t)nranks * run;
+  // full columns owned: tx = rank, rank + nranks, ... with (tx + 1) * tw <= W; a clipped last column is copied on its own
+  size_t full = 0, clipped_tx = (size_t)-1;
+  for (size_t tx = (size_t)rank; tx < ntx; tx += (size_t)nranks) {
+    if ((tx + 1) * tw <= W) ++full;
+    else clipped_tx = tx;
+  }
+  for (int p = 0; p < 3; ++p) {
+    const size_t base = (size_t)p * plane * sizeof(float);
+    const char *src = static_cast<const char *>(d_src) + base;
+    char *dst = static_cast<char *>(out) + base;
+    if (full) VR_CUDA(c, cudaMemcpy2DAsync(dst + (size_t)rank * run, pitch, src + (size_t)rank * run, pitch, run, full, cudaMemcpyDeviceToHost, stream));
+    if (clipped_tx != (size_t)-1) {
+      const size_t o = clipped_tx * run, n = (W - clipped_tx * tw) * H * sizeof(float);
+      VR_CUDA(c, cudaMemcpyAsync(dst + o, src + o, n, cudaMemcpyDeviceToHost, stream));
+    }
+  }
+  return VR_OK;
+}
+// the same, and wait for it (the synchronous 'render')
 vr_status download_frame(vr_ctx *c, void *out, const void *d_src, size_t bytes) {
   VR_CUDA(c, cudaMemcpyAsync(out, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
   VR_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -688,20 +743,56 @@ vr_status set_device(vr_ctx *c) {
   return VR_OK;
 }
 
-vr_status collect(vr_ctx *c) {
-  if (!c->stats_pending && !c->timing_pending) return VR_OK;
-  VR_CUDA(c, cudaStreamSynchronize(c->stream));
-  if (c->timing_pending) {
+// Counters and timing of a finished launch of slot `S` (the stream has been synchronised or S.ev_rendered waited for).
+void read_slot(vr_ctx *c, LaunchSlot &S, vr_stats &into, bool accumulate) {
+  if (S.timing_pending) {
     float ms = 0;
-    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.kernel_ms = ms;
-    c->timing_pending = false;
+    if (cudaEventElapsedTime(&ms, S.ev0, S.ev1) == cudaSuccess) into.kernel_ms = accumulate ? into.kernel_ms + ms : ms;
+    S.timing_pending = false;
   }
-  if (c->stats_pending) {
-    c->stats.samples_marched = c->h_stats[0];
-    c->stats.samples_shaded = c->h_stats[1];
-    c->stats.rays_hit = c->h_stats[2];
-    c->stats_pending = false;
+  if (S.stats_pending) {
+    if (accumulate) {
+      into.samples_marched += S.h_stats[0], into.samples_shaded += S.h_stats[1], into.rays_hit += S.h_stats[2];
+    } else {
+      into.samples_marched = S.h_stats[0], into.samples_shaded = S.h_stats[1], into.rays_hit = S.h_stats[2];
+    }
+    S.stats_pending = false;
   }
+  (void)c;
+}
+
+// Pipelined batches: wait until the frames of slot `S` are in host memory and add its counters to the pipeline's totals.
+vr_status harvest(vr_ctx *c, LaunchSlot &S) {
+  if (!S.in_flight) return VR_OK;
+  VR_CUDA(c, cudaEventSynchronize(S.ev_copied));
+  read_slot(c, S, c->pipe_total, true);
+  c->pipe_total.kernel_launches += 1;
+  S.in_flight = false;
+  return VR_OK;
+}
+vr_status drain_pipeline(vr_ctx *c) {
+  if (!c->pipe_open) return VR_OK;
+  // oldest first
+  VR_TRY(harvest(c, c->slot[c->pipe_batches & 1]));
+  VR_TRY(harvest(c, c->slot[(c->pipe_batches + 1) & 1]));
+  const uint64_t resident = c->stats.bytes_resident;
+  const double upload_ms = c->stats.upload_ms;
+  const uint32_t uploads = c->stats.uploads, fetch = c->stats.fetch_mode, arith = c->stats.arithmetic;
+  const uint64_t uploaded = c->stats.bytes_uploaded;
+  c->stats = c->pipe_total;
+  c->stats.bytes_resident = resident, c->stats.upload_ms = upload_ms, c->stats.uploads = uploads, c->stats.bytes_uploaded = uploaded;
+  c->stats.fetch_mode = fetch, c->stats.arithmetic = arith;
+  c->pipe_open = false;
+  c->cur = 0;
+  return VR_OK;
+}
+
+vr_status collect(vr_ctx *c) {
+  if (c->pipe_open) return drain_pipeline(c);
+  LaunchSlot &S = c->slot[0];
+  if (!S.stats_pending && !S.timing_pending) return VR_OK;
+  VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  read_slot(c, S, c->stats, false);
   return VR_OK;
 }
 
@@ -943,7 +1034,16 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   P.ntx = (P.W + P.tile_w - 1) / P.tile_w, P.nty = (P.H + P.tile_h - 1) / P.tile_h;
   P.wt_x = P.tile_w / ww, P.wt_y = P.tile_h / wh;
   const uint64_t ntiles = (uint64_t)P.ntx * P.nty;
-  const uint64_t owned = ntiles > (uint64_t)P.part_rank ? (ntiles - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0;
+  // which tiles this context renders: tiles dealt round-robin (mode 0), or whole tile COLUMNS dealt round-robin (mode 1: the
+  // owned pixels of every image plane are then a few contiguous runs of tile_w * H floats - what a device->host copy wants)
+  const bool columns = c->opt[VR_OPT_PART_MODE] == 1 && P.part_nranks > 1;
+  const uint64_t own_cols = (uint64_t)P.ntx > (uint64_t)P.part_rank ? ((uint64_t)P.ntx - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0;
+  const uint64_t owned = columns ? own_cols * P.nty
+                                 : (ntiles > (uint64_t)P.part_rank ? (ntiles - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0);
+  auto owned_tile = [&](uint64_t j) -> uint32_t {
+    if (!columns) return (uint32_t)(P.part_rank + j * P.part_nranks);
+    return (uint32_t)((j / own_cols) * P.ntx + P.part_rank + (j % own_cols) * P.part_nranks);
+  };
   const uint64_t entries = owned * n_frames;  // (frame, owned tile) pairs of the launch
   P.num_owned = (uint32_t)entries;
   const uint64_t work = entries * P.wt_x * P.wt_y;
@@ -979,9 +1079,17 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   P.tile_order = nullptr;
   const bool ordered = c->opt[VR_OPT_TILE_ORDER] != 0;
   const uint64_t sig = ((uint64_t)P.W << 40) ^ ((uint64_t)P.H << 20) ^ ((uint64_t)P.tile_w << 8) ^ (uint64_t)P.tile_h;
-  const bool use_cost = c->cost_valid && c->cost_sig == sig && c->tile_cost_tiles >= ntiles && cudaEventQuery(c->ev_cost) == cudaSuccess;
-  cudaGetLastError();  // cudaErrorNotReady of the query is not an error
-  if ((ordered && entries > 1) || n_frames > 1) {
+  // measured tile costs: those of the most recent launch that has completed (this slot's, else the other slot's - a pipelined
+  // batch is set up while its predecessor still runs)
+  LaunchSlot &S = c->slot[c->cur];
+  const unsigned int *h_cost = nullptr;
+  for (int k = 0; k < 2 && !h_cost; ++k) {
+    LaunchSlot &Q = c->slot[(c->cur + 1 + k) & 1];  // the other slot holds the more recent launch
+    if (Q.cost_valid && Q.cost_sig == sig && Q.cost_tiles >= ntiles && cudaEventQuery(Q.ev_cost) == cudaSuccess) h_cost = Q.h_tile_cost;
+    cudaGetLastError();  // cudaErrorNotReady of the query is not an error
+  }
+  const bool use_cost = h_cost != nullptr;
+  if ((ordered && entries > 1) || n_frames > 1 || (columns && entries > 0)) {  // (the kernel's built-in hand-out is the tile round-robin)
     std::vector<std::pair<float, uint32_t>> key((size_t)entries);
     for (size_t f = 0; f < n_frames; ++f) {
       const Camera &C = cams[f];
@@ -999,16 +1107,16 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
         py = (b / cz * C.m[3][1] + ratio) / (2.f * ratio) * P.H;
       }
       for (uint64_t j = 0; j < owned; ++j) {
-        const uint32_t tile = (uint32_t)(P.part_rank + j * P.part_nranks);
+        const uint32_t tile = owned_tile(j);
         const float tx = ((tile % P.ntx) + 0.5f) * P.tile_w - px, ty = ((tile / P.ntx) + 0.5f) * P.tile_h - py;
         const uint32_t entry = (uint32_t)(f * ntiles + tile);
         float k = ordered ? tx * tx + ty * ty : (float)(f * owned + j);
         // measured beats guessed: the previous launch's shaded samples per tile (a movie turns slowly), most expensive first
         // key: the longest ray of the tile (= the duration of its longest item), then the tile's total
-        if (ordered && use_cost) k = -((float)c->h_tile_cost[ntiles + tile] * 1024.0f + fminf((float)c->h_tile_cost[tile] * (1.0f / 4096.0f), 1023.0f));
+        if (ordered && use_cost) k = -((float)h_cost[ntiles + tile] * 1024.0f + fminf((float)h_cost[tile] * (1.0f / 4096.0f), 1023.0f));
         // order 1: one heaviest-first list over all frames of the batch (measured best: 30.3 vs 31.3 ms per frame);
         // order 2: frame after frame, each heaviest-first
-        if (ordered && use_cost && c->opt[VR_OPT_TILE_ORDER] == 3) k = -(float)c->h_tile_cost[tile];  // A/B: by the tile's total
+        if (ordered && use_cost && c->opt[VR_OPT_TILE_ORDER] == 3) k = -(float)h_cost[tile];  // A/B: by the tile's total
         if (c->opt[VR_OPT_TILE_ORDER] == 2) k = (float)f * 4.0e9f + fminf(fmaxf(k, -1.9e9f), 1.9e9f);
         key[f * owned + j] = std::make_pair(k, entry);
       }
@@ -1026,16 +1134,20 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     VR_CUDA(c, cudaMemcpyAsync(c->d_tile_order, c->h_tile_order.data(), entries * 4, cudaMemcpyHostToDevice, stream));
     P.tile_order = c->d_tile_order;
   }
-  P.stats = c->d_stats;
+  P.stats = S.d_stats;
   P.tile_cost = nullptr;
   if (ordered && !vs) {
     if (c->tile_cost_tiles < ntiles) {
       if (c->d_tile_cost) cudaFree(c->d_tile_cost);
-      if (c->h_tile_cost) cudaFreeHost(c->h_tile_cost);
-      c->d_tile_cost = c->h_tile_cost = nullptr, c->tile_cost_tiles = 0, c->cost_valid = false;
+      c->d_tile_cost = nullptr, c->tile_cost_tiles = 0;
       VR_CUDA(c, cudaMalloc(&c->d_tile_cost, 2 * ntiles * sizeof(unsigned int)));  // [sum of shaded samples | longest ray] per tile
-      VR_CUDA(c, cudaMallocHost(&c->h_tile_cost, 2 * ntiles * sizeof(unsigned int)));
       c->tile_cost_tiles = ntiles;
+    }
+    if (S.cost_tiles < ntiles) {
+      if (S.h_tile_cost) cudaFreeHost(S.h_tile_cost);
+      S.h_tile_cost = nullptr, S.cost_tiles = 0, S.cost_valid = false;
+      VR_CUDA(c, cudaMallocHost(&S.h_tile_cost, 2 * ntiles * sizeof(unsigned int)));
+      S.cost_tiles = ntiles;
     }
     // the host copy of the previous launch is final before it is overwritten: same stream, and use_cost saw its event
     VR_CUDA(c, cudaMemsetAsync(c->d_tile_cost, 0, 2 * ntiles * sizeof(unsigned int), stream));
@@ -1046,26 +1158,50 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   if (c->opt[VR_OPT_CLEAR_IMAGE])
     for (size_t f = 0; f < n_frames; ++f) VR_CUDA(c, cudaMemsetAsync(d_outs[f], 0, (size_t)W * H * 3 * sizeof(float), stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
-  VR_CUDA(c, cudaMemsetAsync(c->d_stats, 0, 3 * sizeof(unsigned long long), stream));
-  VR_CUDA(c, cudaEventRecord(c->ev0, stream));
+  VR_CUDA(c, cudaMemsetAsync(S.d_stats, 0, 3 * sizeof(unsigned long long), stream));
+  VR_CUDA(c, cudaEventRecord(S.ev0, stream));
   const int arith = (int)c->opt[VR_OPT_ARITHMETIC];
   if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, stream, c->sm_count, arith));
   c->stats.arithmetic = (uint32_t)arith;
-  VR_CUDA(c, cudaEventRecord(c->ev1, stream));
+  VR_CUDA(c, cudaEventRecord(S.ev1, stream));
   if (P.tile_cost) {
-    VR_CUDA(c, cudaMemcpyAsync(c->h_tile_cost, c->d_tile_cost, 2 * ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
-    VR_CUDA(c, cudaEventRecord(c->ev_cost, stream));
-    c->cost_valid = true, c->cost_sig = sig;
+    VR_CUDA(c, cudaMemcpyAsync(S.h_tile_cost, c->d_tile_cost, 2 * ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+    VR_CUDA(c, cudaEventRecord(S.ev_cost, stream));
+    S.cost_valid = true, S.cost_sig = sig;
   }
   if (P.count) {
-    VR_CUDA(c, cudaMemcpyAsync(c->h_stats, c->d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
-    c->stats_pending = true;
+    VR_CUDA(c, cudaMemcpyAsync(S.h_stats, S.d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    S.stats_pending = true;
   }
-  c->timing_pending = true;
+  S.timing_pending = true;
   c->stats.kernel_launches = P.num_work > 0 ? 1 : 0;
   c->stats.fetch_mode = texhw ? 1u : 0u;
   return VR_OK;
 }
+
+// ---- device groups (vr_set_devices) ------------------------------------------------------------------------
+// the contexts a call on `c` drives: the group it leads, else itself
+std::vector<vr_ctx *> group_of(vr_ctx *c) { return c->members.empty() ? std::vector<vr_ctx *>{c} : c->members; }
+
+// counters of the whole group: sums, and the slowest member's times
+vr_stats merged_stats(vr_ctx *c) {
+  vr_stats t = c->stats;
+  for (size_t i = 1; i < c->members.size(); ++i) {
+    const vr_stats &m = c->members[i]->stats;
+    t.kernel_ms = std::max(t.kernel_ms, m.kernel_ms), t.upload_ms = std::max(t.upload_ms, m.upload_ms);
+    t.samples_marched += m.samples_marched, t.samples_shaded += m.samples_shaded, t.rays_hit += m.rays_hit;
+    t.bytes_resident += m.bytes_resident, t.bytes_uploaded += m.bytes_uploaded;
+    t.kernel_launches += m.kernel_launches, t.uploads += m.uploads;
+  }
+  return t;
+}
+#define VR_NOT_A_MEMBER(c) \
+  if ((c)->leader) return fail(c, VR_ERR_INVALID_ARGUMENT, "this context is a member of a device group: call its leader")
+#define VR_NOT_A_GROUP(c, what) \
+  if (!(c)->members.empty()) return fail(c, VR_ERR_UNSUPPORTED, what " is not available on a device group (vr_set_devices)")
+
+vr_status sync_volumes_one(vr_ctx *c, uint64_t T, const vr_volume *em, const vr_volume *re, const vr_volume *ab, const vr_volume *gx,
+                           const vr_volume *gy, const vr_volume *gz);
 
 }  // namespace
 
@@ -1112,17 +1248,23 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   cudaError_t ce = cudaSetDevice(device);
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   c->own_stream = ce == cudaSuccess;
-  if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev0);
-  if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
+  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  for (int k = 0; k < 2 && ce == cudaSuccess; ++k) {
+    LaunchSlot &S = c->slot[k];
+    ce = cudaEventCreate(&S.ev0);
+    if (ce == cudaSuccess) ce = cudaEventCreate(&S.ev1);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&S.ev_cost, cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&S.ev_rendered, cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&S.ev_copied, cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaMalloc(&S.d_stats, 64);
+    if (ce == cudaSuccess) ce = cudaMallocHost(&S.h_stats, 64);
+  }
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu0);
   if (ce == cudaSuccess) ce = cudaEventCreate(&c->evu1);
   for (int i = 0; i < kStageBufs && ce == cudaSuccess; ++i) ce = cudaEventCreateWithFlags(&c->ev_stage[i], cudaEventDisableTiming);
-  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&c->ev_cost, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&c->ev_order, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_counter, 64);
   if (ce == cudaSuccess && getenv("VR_WARP_TIMES")) ce = cudaMalloc(&c->d_warp_times, 2 * 8192 * sizeof(unsigned long long));
-  if (ce == cudaSuccess) ce = cudaMalloc(&c->d_stats, 64);
-  if (ce == cudaSuccess) ce = cudaMallocHost(&c->h_stats, 64);
   if (ce != cudaSuccess) {
     vr_status s = fail(nullptr, VR_ERR_CUDA, "vr_create: %s", cudaGetErrorString(ce));
     delete c;
@@ -1146,10 +1288,31 @@ vr_status vr_destroy(vr_ctx *c) {
     }
     g_registry.erase(c);
   }
+  if (c->leader) {  // a member destroyed on its own leaves its group
+    auto &mm = c->leader->members;
+    mm.erase(std::remove(mm.begin(), mm.end(), c), mm.end());
+    c->leader = nullptr;
+  }
+  for (size_t i = 1; i < c->members.size(); ++i) {
+    c->members[i]->leader = nullptr;
+    vr_destroy(c->members[i]);
+  }
+  c->members.clear();
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+  if (c->ev_group) cudaEventDestroy(c->ev_group);
   for (int i = 0; i < S_N; ++i) release(c, c->tex[i]);
-  if (c->d_image) cudaFree(c->d_image);
+  for (LaunchSlot &S : c->slot) {
+    if (S.d_image) cudaFree(S.d_image);
+    if (S.d_stats) cudaFree(S.d_stats);
+    if (S.h_stats) cudaFreeHost(S.h_stats);
+    if (S.h_tile_cost) cudaFreeHost(S.h_tile_cost);
+    cudaEvent_t evs[5] = {S.ev0, S.ev1, S.ev_cost, S.ev_rendered, S.ev_copied};
+    for (cudaEvent_t e : evs)
+      if (e) cudaEventDestroy(e);
+  }
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   for (int i = 0; i < kStageBufs; ++i) {
     if (c->d_stage[i]) cudaFree(c->d_stage[i]);
     if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
@@ -1160,14 +1323,10 @@ vr_status vr_destroy(vr_ctx *c) {
   if (c->d_tile_order) cudaFree(c->d_tile_order);
   if (c->d_cams) cudaFree(c->d_cams);
   if (c->d_tile_cost) cudaFree(c->d_tile_cost);
-  if (c->h_tile_cost) cudaFreeHost(c->h_tile_cost);
-  if (c->ev_cost) cudaEventDestroy(c->ev_cost);
   if (c->ev_order) cudaEventDestroy(c->ev_order);
   if (c->d_boxes) cudaFree(c->d_boxes);
   if (c->d_warp_times) cudaFree(c->d_warp_times);
-  if (c->d_stats) cudaFree(c->d_stats);
-  if (c->h_stats) cudaFreeHost(c->h_stats);
-  cudaEventDestroy(c->ev0), cudaEventDestroy(c->ev1), cudaEventDestroy(c->evu0), cudaEventDestroy(c->evu1);
+  cudaEventDestroy(c->evu0), cudaEventDestroy(c->evu1);
   if (c->own_stream) cudaStreamDestroy(c->stream);
   c->magic = 0;
   delete c;
@@ -1204,6 +1363,11 @@ vr_status vr_mem_info(vr_ctx *c, char *buf, size_t cap, size_t *needed) {
     add("\t\tfetch: %s; texture-unit copies (MB): %g\n",
         c->opt[VR_OPT_TEXTURE_UNIT] == 0 ? "loads + fp32 lerps" : (c->texhw_failed ? "loads (no room for the texture copies)" : "texture unit where possible"), arrays / MB);
   }
+  if (c->members.size() > 1) {
+    std::string ids;
+    for (vr_ctx *m : c->members) ids += (ids.empty() ? "" : ", ") + std::to_string(m->device);
+    add("\t\tdevice group: %zu members on devices [%s], tile columns dealt round-robin, peer access %s\n", c->members.size(), ids.c_str(), c->group_peer ? "yes" : "no");
+  }
   add("\t\trole -> texture: Em->%s Ab->%s Re->%s, gradient method: %s\n", names[c->idxEm], names[c->idxAb], names[c->idxRe],
       c->gradientMethod ? "lookup" : "compute");
   add("\n\t\tSimilarity of Volumes\n\t\t---------------------\n\t\t\tEm\tAb\tRe\n\t\tEm\t1\t\n\t\tAb\t%d\t1\n\t\tRe\t%d\t%d\t1\n\n",
@@ -1220,6 +1384,28 @@ vr_status vr_mem_info(vr_ctx *c, char *buf, size_t cap, size_t *needed) {
 vr_status vr_sync_volumes(vr_ctx *c, uint64_t T, const vr_volume *em, const vr_volume *re, const vr_volume *ab,
                           const vr_volume *gx, const vr_volume *gy, const vr_volume *gz) {
   VR_CHECK_HANDLE(c);
+  VR_NOT_A_MEMBER(c);
+  if (c->members.size() < 2) return sync_volumes_one(c, T, em, re, ab, gx, gy, gz);
+  // every device of the group holds all volumes (image-space mode): one host thread per device, each over its own PCIe link.
+  // A member that has never been synced gets everything (T = 0), whatever the caller's timestamp says.
+  std::vector<vr_status> st(c->members.size(), VR_OK);
+  std::vector<std::thread> th;
+  for (size_t i = 0; i < c->members.size(); ++i)
+    th.emplace_back([&, i] {
+      vr_ctx *m = c->members[i];
+      st[i] = sync_volumes_one(m, m->ever_synced ? T : 0, em, re, ab, gx, gy, gz);
+    });
+  for (auto &t : th) t.join();
+  cudaSetDevice(c->device);
+  for (size_t i = 0; i < st.size(); ++i)
+    if (st[i] != VR_OK) return i == 0 ? st[i] : fail(c, st[i], "device %d: %s", c->members[i]->device, c->members[i]->err.c_str());
+  return VR_OK;
+}
+
+extern "C++" {
+namespace {
+vr_status sync_volumes_one(vr_ctx *c, uint64_t T, const vr_volume *em, const vr_volume *re, const vr_volume *ab, const vr_volume *gx,
+                           const vr_volume *gy, const vr_volume *gz) {
   if (!em || !re || !ab) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
   const int ng = (gx != nullptr) + (gy != nullptr) + (gz != nullptr);
   if (ng != 0 && ng != 3) return fail(c, VR_ERR_INVALID_ARGUMENT, "gradient volumes: pass all three or none");
@@ -1252,19 +1438,59 @@ vr_status vr_sync_volumes(vr_ctx *c, uint64_t T, const vr_volume *em, const vr_v
   cudaEventElapsedTime(&ms, c->evu0, c->evu1);
   c->stats.upload_ms = ms;
   c->stats.bytes_resident = resident_bytes(c);
+  c->ever_synced = true;
   return VR_OK;
 }
+}  // namespace
+}  // extern "C++"
+
+extern "C++" {
+namespace {
+// Device-image render of a context or of a whole device group.  In a group every member launches on its own device and its
+// kernel stores the tiles it owns straight into the caller's image on the leader's device (peer stores over NVLink, misses
+// as 0, so nobody clears the image): the launch IS the gather.  The caller's stream continues only after every member's
+// launch, and no member starts before the work already queued on that stream.
+vr_status render_device_group(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination, const float factors[3],
+                              const float es[3], const uint64_t res[2], size_t n_frames, const float *rotations, const float *props,
+                              float thr, const float color[3], float *const *d_outs, void *cuda_stream) {
+  VR_TRY(set_device(c));
+  VR_TRY(collect(c));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->members.size() < 2) return render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_outs, s);
+  if (!c->group_peer) return fail(c, VR_ERR_UNSUPPORTED, "device-image renders of a group need peer access between its devices");
+  VR_CUDA(c, cudaEventRecord(c->ev_group, s));
+  for (size_t i = 0; i < c->members.size(); ++i) {
+    vr_ctx *m = c->members[i];
+    VR_TRY(set_device(m));
+    if (i) {
+      VR_TRY(collect(m));
+      VR_CUDA(m, cudaStreamWaitEvent(m->stream, c->ev_group, 0));
+    }
+    const int64_t clear = m->opt[VR_OPT_CLEAR_IMAGE];
+    m->opt[VR_OPT_CLEAR_IMAGE] = 0;  // every owned pixel is written by its owner
+    const vr_status st = render_common(m, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_outs, i ? m->stream : s);
+    m->opt[VR_OPT_CLEAR_IMAGE] = clear;
+    if (st != VR_OK) {
+      cudaSetDevice(c->device);
+      return i == 0 ? st : fail(c, st, "device %d: %s", m->device, m->err.c_str());
+    }
+    if (i) VR_CUDA(m, cudaEventRecord(m->ev_group, m->stream));
+  }
+  VR_TRY(set_device(c));
+  for (size_t i = 1; i < c->members.size(); ++i) VR_CUDA(c, cudaStreamWaitEvent(s, c->members[i]->ev_group, 0));
+  return VR_OK;
+}
+}  // namespace
+}  // extern "C++"
 
 vr_status vr_render_device(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
                            const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
                            const float props[3], float thr, const float color[3], float *d_out, void *cuda_stream) {
   VR_CHECK_HANDLE(c);
+  VR_NOT_A_MEMBER(c);
   if (!d_out) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: null output");
-  VR_TRY(set_device(c));
-  VR_TRY(collect(c));
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
-  if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
-  return render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &d_out, s);
+  return render_device_group(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &d_out, cuda_stream);
 }
 
 vr_status vr_render_batch_device(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
@@ -1272,15 +1498,93 @@ vr_status vr_render_batch_device(vr_ctx *c, const vr_light *lights, size_t n_lig
                                  const float *rotations, const float *props, float thr, const float color[3],
                                  float *const *d_out_images, void *cuda_stream) {
   VR_CHECK_HANDLE(c);
+  VR_NOT_A_MEMBER(c);
+  return render_device_group(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_out_images, cuda_stream);
+}
+
+// One process, several GPUs, behind the reference's own boundary (the reference picks ONE device, volumeRender.cpp:77-87): the
+// context becomes the leader of a group with one member context per device.  From then on vr_sync_volumes makes the volumes
+// resident on every device, and every render is cut into tile columns dealt round-robin to the devices (VR_OPT_PART_MODE = 1);
+// host-image renders have each device copy its own columns into the caller's image over its own PCIe link, device-image
+// renders have the kernels of all devices store into the caller's image over NVLink.  Pixels are those of one device, bit
+// for bit.  device_ids[0] must be the context's own device; a device may be listed more than once (members then share it).
+// n = 0 or 1 dissolves the group.  Call it before the first vr_sync_volumes: a member added later receives the volumes of
+// the next sync in full, but not the upload history that decides the role redirects (kernel.cu:739-867).
+vr_status vr_set_devices(vr_ctx *c, uint32_t n, const int *device_ids) {
+  VR_CHECK_HANDLE(c);
+  VR_NOT_A_MEMBER(c);
+  if (c->region_on) return fail(c, VR_ERR_UNSUPPORTED, "a context that owns a region (vr_set_region) cannot lead a device group");
   VR_TRY(set_device(c));
   VR_TRY(collect(c));
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
-  if (s != c->stream) VR_CUDA(c, cudaStreamSynchronize(c->stream));
-  return render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_out_images, s);
+  // dissolve what is there
+  for (size_t i = 1; i < c->members.size(); ++i) {
+    c->members[i]->leader = nullptr;
+    vr_destroy(c->members[i]);
+  }
+  c->members.clear();
+  VR_TRY(set_device(c));
+  c->opt[VR_OPT_PART_RANK] = 0, c->opt[VR_OPT_PART_NRANKS] = 1, c->opt[VR_OPT_PART_MODE] = 0;
+  if (n <= 1) {
+    if (n == 1 && device_ids && device_ids[0] != c->device) return fail(c, VR_ERR_INVALID_ARGUMENT, "set_devices: the first device must be the context's own (%d)", c->device);
+    return VR_OK;
+  }
+  if (!device_ids || n > 64) return fail(c, VR_ERR_INVALID_ARGUMENT, "set_devices: bad arguments");
+  if (device_ids[0] != c->device) return fail(c, VR_ERR_INVALID_ARGUMENT, "set_devices: the first device must be the context's own (%d)", c->device);
+  int ndev = 0;
+  VR_CUDA(c, cudaGetDeviceCount(&ndev));
+  for (uint32_t i = 0; i < n; ++i)
+    if (device_ids[i] < 0 || device_ids[i] >= ndev) return fail(c, VR_ERR_NO_DEVICE, "set_devices: device %d of %d does not exist", device_ids[i], ndev);
+  // peer access between every pair of distinct devices (kernels store into the leader's image, read device-memory sources)
+  c->group_peer = true;
+  for (uint32_t a = 0; a < n; ++a)
+    for (uint32_t b = 0; b < n; ++b) {
+      if (device_ids[a] == device_ids[b]) continue;
+      int can = 0;
+      cudaDeviceCanAccessPeer(&can, device_ids[a], device_ids[b]);
+      if (!can) {
+        c->group_peer = false;
+        continue;
+      }
+      cudaSetDevice(device_ids[a]);
+      const cudaError_t e = cudaDeviceEnablePeerAccess(device_ids[b], 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) c->group_peer = false;
+      cudaGetLastError();
+    }
+  VR_TRY(set_device(c));
+  if (!c->ev_group) VR_CUDA(c, cudaEventCreateWithFlags(&c->ev_group, cudaEventDisableTiming));
+  c->members.push_back(c);
+  for (uint32_t i = 1; i < n; ++i) {
+    vr_ctx *m = nullptr;
+    const vr_status st = vr_create_on_device(&m, device_ids[i]);
+    cudaError_t ce = cudaSuccess;
+    if (st == VR_OK) ce = cudaEventCreateWithFlags(&m->ev_group, cudaEventDisableTiming);
+    if (st != VR_OK || ce != cudaSuccess) {
+      const std::string why = st != VR_OK ? tl_error : std::string(cudaGetErrorString(ce));
+      if (m) vr_destroy(m);
+      for (size_t k = 1; k < c->members.size(); ++k) {
+        c->members[k]->leader = nullptr;
+        vr_destroy(c->members[k]);
+      }
+      c->members.clear();
+      cudaSetDevice(c->device);
+      return fail(c, st != VR_OK ? st : VR_ERR_CUDA, "set_devices: device %d: %s", device_ids[i], why.c_str());
+    }
+    m->leader = c;
+    memcpy(m->opt, c->opt, sizeof m->opt);
+    c->members.push_back(m);
+  }
+  for (uint32_t i = 0; i < n; ++i) {
+    vr_ctx *m = c->members[i];
+    m->opt[VR_OPT_PART_RANK] = i, m->opt[VR_OPT_PART_NRANKS] = n, m->opt[VR_OPT_PART_MODE] = 1;
+  }
+  VR_TRY(set_device(c));
+  return VR_OK;
 }
 
 vr_status vr_set_region(vr_ctx *c, const uint64_t lo[3], const uint64_t hi[3], uint32_t halo) {
   VR_CHECK_HANDLE(c);
+  VR_NOT_A_MEMBER(c);
+  VR_NOT_A_GROUP(c, "vr_set_region");
   VR_TRY(set_device(c));
   VR_TRY(collect(c));
   if (!lo || !hi || (hi[0] == 0 && hi[1] == 0 && hi[2] == 0)) {
@@ -1303,6 +1607,15 @@ vr_status vr_update_box(vr_ctx *c, int role, const vr_volume *vol, const uint64_
   VR_CHECK_HANDLE(c);
   if (!vol || !lo || !hi) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: null argument");
   if (role < 0 || role > S_DZ) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_update_box: role %d (0 emission, 1 absorption, 2 reflection, 3..5 gradient x,y,z)", role);
+  if (!c->leader && c->members.size() > 1) {  // a group: the box goes to every device
+    for (size_t i = 1; i < c->members.size(); ++i) {
+      vr_ctx *m = c->members[i];
+      m->leader = nullptr;
+      const vr_status st = vr_update_box(m, role, vol, lo, hi);
+      m->leader = c;
+      if (st != VR_OK) return fail(c, st, "device %d: %s", m->device, m->err.c_str());
+    }
+  }
   VR_TRY(set_device(c));
   VR_TRY(collect(c));
   // The slot that HOLDS this host volume: the role's own texture when one was uploaded for it (a distinct absorption
@@ -1352,6 +1665,8 @@ vr_status vr_render_opacity_device(vr_ctx *c, const vr_light *lights, size_t n_l
                                    const float props[3], float thr, const float color[3], float *d_opacity, void *cuda_stream) {
   VR_CHECK_HANDLE(c);
   if (!d_opacity) return fail(c, VR_ERR_INVALID_ARGUMENT, "opacity pass: null output");
+  VR_NOT_A_MEMBER(c);
+  VR_NOT_A_GROUP(c, "the volume-space opacity pass");
   VR_TRY(set_device(c));
   VR_TRY(collect(c));
   cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
@@ -1373,6 +1688,8 @@ vr_status vr_render_partial_device(vr_ctx *c, const vr_light *lights, size_t n_l
                                    const uint64_t *brick_boxes, const float *d_opacity_all, float *d_out, void *cuda_stream) {
   VR_CHECK_HANDLE(c);
   if (!d_out) return fail(c, VR_ERR_INVALID_ARGUMENT, "partial render: null output");
+  VR_NOT_A_MEMBER(c);
+  VR_NOT_A_GROUP(c, "the volume-space shading pass");
   VR_TRY(set_device(c));
   VR_TRY(collect(c));
   cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
@@ -1392,53 +1709,116 @@ vr_status vr_compose_partials_device(vr_ctx *c, uint32_t n, const float *const *
   return VR_OK;
 }
 
+extern "C++" {
+namespace {
+// the persistent device images of slot `S` for a batch of host-image frames
+vr_status slot_images(vr_ctx *c, LaunchSlot &S, size_t bytes, size_t n_frames, std::vector<float *> &d_outs) {
+  if (S.image_cap < bytes * n_frames) {
+    if (S.d_image) cudaFree(S.d_image);
+    S.d_image = nullptr, S.image_cap = 0;
+    VR_CUDA(c, cudaMalloc(&S.d_image, bytes * n_frames));
+    S.image_cap = bytes * n_frames;
+  }
+  d_outs.resize(n_frames);
+  for (size_t f = 0; f < n_frames; ++f) d_outs[f] = S.d_image + f * (bytes / sizeof(float));
+  return VR_OK;
+}
+
+// One pipelined batch on ONE context: launch on the context's stream into the images of the next slot, copies of the owned
+// pixels on the copy stream behind it.  Returns without waiting.
+vr_status batch_begin_one(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination, const float factors[3],
+                          const float es[3], const uint64_t res[2], size_t n_frames, const float *rotations, const float *props, float thr,
+                          const float color[3], float *const *out_images) {
+  if (!out_images || !res || n_frames == 0 || n_frames > 4096) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
+  for (size_t f = 0; f < n_frames; ++f)
+    if (!out_images[f]) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: null output");
+  VR_TRY(set_device(c));
+  const size_t bytes = (size_t)res[0] * res[1] * 3 * sizeof(float);
+  if (bytes == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: bad resolution");
+  if (!c->pipe_open) {
+    VR_TRY(collect(c));  // a synchronous render may still have counters pending
+    c->pipe_open = true, c->pipe_batches = 0;
+    c->pipe_total = vr_stats{};
+  }
+  const int k = (int)(c->pipe_batches & 1);
+  LaunchSlot &S = c->slot[k];
+  VR_TRY(harvest(c, S));  // batch k-2: its frames have left this slot's images (normally long ago)
+  c->cur = k;
+  std::vector<float *> d_outs;
+  vr_status st = slot_images(c, S, bytes, n_frames, d_outs);
+  if (st == VR_OK) st = render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_outs.data(), c->stream);
+  if (st != VR_OK) {
+    c->cur = 0;
+    return st;
+  }
+  VR_CUDA(c, cudaEventRecord(S.ev_rendered, c->stream));
+  VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, S.ev_rendered, 0));
+  for (size_t f = 0; f < n_frames; ++f) VR_TRY(enqueue_download(c, out_images[f], d_outs[f], res[1], res[0], c->copy_stream));
+  VR_CUDA(c, cudaEventRecord(S.ev_copied, c->copy_stream));
+  // the next launch into this slot's images (batch k+2) must not start before these copies are done
+  VR_CUDA(c, cudaStreamWaitEvent(c->stream, S.ev_copied, 0));
+  S.in_flight = true;
+  c->pipe_batches++;
+  c->cur = 0;
+  return VR_OK;
+}
+}  // namespace
+}  // extern "C++"
+
+// Pipelined movie frames (examples/example2.m:59-66 renders 360 frames of one scene): vr_render_batch_begin enqueues the
+// launch of a batch and the device->host copies of its frames and returns at once; the next begin renders into a second
+// set of device images while those copies are on the wire.  out_images must stay valid (and should be pinned: a pageable
+// destination makes the copy synchronous) until vr_render_batch_end, which waits for everything begun and leaves the summed
+// counters in vr_get_stats.  Any other call on the context ends the pipeline first.
+vr_status vr_render_batch_begin(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination, const float factors[3],
+                                const float es[3], const uint64_t res[2], size_t n_frames, const float *rotations, const float *props,
+                                float thr, const float color[3], float *const *out_images) {
+  VR_CHECK_HANDLE(c);
+  if (c->leader) return fail(c, VR_ERR_INVALID_ARGUMENT, "this context is a member of a device group: call its leader");
+  for (vr_ctx *m : group_of(c)) {
+    const vr_status st = batch_begin_one(m, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, out_images);
+    if (st != VR_OK) return m == c ? st : fail(c, st, "device %d: %s", m->device, m->err.c_str());
+  }
+  return VR_OK;
+}
+vr_status vr_render_batch_end(vr_ctx *c) {
+  VR_CHECK_HANDLE(c);
+  if (c->leader) return fail(c, VR_ERR_INVALID_ARGUMENT, "this context is a member of a device group: call its leader");
+  for (vr_ctx *m : group_of(c)) {
+    VR_TRY(set_device(m));
+    const vr_status st = drain_pipeline(m);
+    if (st != VR_OK) return m == c ? st : fail(c, st, "device %d: %s", m->device, m->err.c_str());
+  }
+  VR_TRY(set_device(c));
+  c->stats.bytes_resident = resident_bytes(c);
+  return VR_OK;
+}
+
+// The synchronous host-image renders are one pipelined batch, waited for.
 vr_status vr_render_batch(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
                           const float factors[3], const float es[3], const uint64_t res[2], size_t n_frames,
                           const float *rotations, const float *props, float thr, const float color[3], float *const *out_images) {
   VR_CHECK_HANDLE(c);
-  if (!out_images || !res || n_frames == 0 || n_frames > 4096) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
-  VR_TRY(set_device(c));
-  VR_TRY(collect(c));
-  const size_t bytes = (size_t)res[0] * res[1] * 3 * sizeof(float);
-  if (bytes == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: bad resolution");
-  if (c->image_cap < bytes * n_frames) {
-    if (c->d_image) cudaFree(c->d_image);
-    c->d_image = nullptr, c->image_cap = 0;
-    VR_CUDA(c, cudaMalloc(&c->d_image, bytes * n_frames));
-    c->image_cap = bytes * n_frames;
+  if (c->leader) return fail(c, VR_ERR_INVALID_ARGUMENT, "this context is a member of a device group: call its leader");
+  for (vr_ctx *m : group_of(c)) {
+    VR_TRY(set_device(m));
+    VR_TRY(collect(m));  // ends an open pipeline: this batch's counters stand alone
   }
-  std::vector<float *> d_outs(n_frames);
-  for (size_t f = 0; f < n_frames; ++f) d_outs[f] = c->d_image + f * (bytes / sizeof(float));
-  VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, d_outs.data(), c->stream));
-  for (size_t f = 0; f < n_frames; ++f)
-    if (!out_images[f]) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: null output");
-  for (size_t f = 0; f < n_frames; ++f) VR_TRY(download_frame(c, out_images[f], d_outs[f], bytes));
-  VR_TRY(collect(c));
-  c->stats.bytes_resident = resident_bytes(c);
-  return VR_OK;
+  const vr_status st = vr_render_batch_begin(c, lights, n_lights, illumination, factors, es, res, n_frames, rotations, props, thr, color, out_images);
+  const vr_status se = vr_render_batch_end(c);  // also after a failed begin: members that did start are waited for
+  return st != VR_OK ? st : se;
 }
 
 vr_status vr_render(vr_ctx *c, const vr_light *lights, size_t n_lights, const vr_volume *illumination,
                     const float factors[3], const float es[3], const uint64_t res[2], const float R[9],
                     const float props[3], float thr, const float color[3], float *out) {
-  VR_CHECK_HANDLE(c);
-  if (!out || !res) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
-  VR_TRY(set_device(c));
-  VR_TRY(collect(c));
-  const size_t bytes = (size_t)res[0] * res[1] * 3 * sizeof(float);
-  if (bytes == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "render: bad resolution");
-  if (c->image_cap < bytes) {
-    if (c->d_image) cudaFree(c->d_image);
-    c->d_image = nullptr, c->image_cap = 0;
-    VR_CUDA(c, cudaMalloc(&c->d_image, bytes));
-    c->image_cap = bytes;
+  if (!out) {
+    VR_CHECK_HANDLE(c);
+    return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
   }
-  VR_TRY(render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &c->d_image, c->stream));
   // cudaDeviceSynchronize + cudaMemcpy D2H (volumeRender.cpp:280-281)
-  VR_TRY(download_frame(c, out, c->d_image, bytes));
-  VR_TRY(collect(c));
-  c->stats.bytes_resident = resident_bytes(c);
-  return VR_OK;
+  float *outs[1] = {out};
+  return vr_render_batch(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, outs);
 }
 
 vr_status vr_henyey_greenstein(uint32_t n, float g, float *out) {
@@ -1484,6 +1864,11 @@ vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   if (option < 0 || option >= VR_OPT_COUNT_) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
   if (option == VR_OPT_ARITHMETIC && (value < 0 || value > 2)) return fail(c, VR_ERR_INVALID_ARGUMENT, "arithmetic flavour must be 0 (exact), 1 (reference) or 2 (fast)");
+  if (c->members.size() > 1) {
+    if (option == VR_OPT_PART_RANK || option == VR_OPT_PART_NRANKS || option == VR_OPT_PART_MODE)
+      return fail(c, VR_ERR_INVALID_ARGUMENT, "the partition of a device group is set by vr_set_devices");
+    for (size_t i = 1; i < c->members.size(); ++i) c->members[i]->opt[option] = value;
+  }
   c->opt[option] = value;
   return VR_OK;
 }
@@ -1496,10 +1881,13 @@ vr_status vr_get_option(vr_ctx *c, int option, int64_t *value) {
 vr_status vr_get_stats(vr_ctx *c, vr_stats *out) {
   VR_CHECK_HANDLE(c);
   if (!out) return fail(c, VR_ERR_INVALID_ARGUMENT, "null stats");
+  for (vr_ctx *m : group_of(c)) {
+    VR_TRY(set_device(m));
+    VR_TRY(collect(m));
+    m->stats.bytes_resident = resident_bytes(m);
+  }
   VR_TRY(set_device(c));
-  VR_TRY(collect(c));
-  c->stats.bytes_resident = resident_bytes(c);
-  *out = c->stats;
+  *out = merged_stats(c);
   return VR_OK;
 }
 vr_status vr_set_stream(vr_ctx *c, void *cuda_stream) {

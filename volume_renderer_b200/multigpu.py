@@ -26,19 +26,89 @@ def tile_grid(W, H, tile_w, tile_h):
     return (W + tile_w - 1) // tile_w, (H + tile_h - 1) // tile_h
 
 
-def owned_mask(H, W, tile_w, tile_h, rank, nranks):
+def owned_mask(H, W, tile_w, tile_h, rank, nranks, mode=0):
     """Boolean H x W mask of the pixels `rank` renders - the host twin of the kernel's
-    work-item -> pixel mapping (raymarch_kernel.cu): tile index = ty * ntx + tx."""
+    work-item -> pixel mapping (raymarch_kernel.cu): tile index = ty * ntx + tx.
+    mode 0: tiles dealt round-robin; mode 1 (VR_OPT_PART_MODE): tile COLUMNS dealt round-robin."""
     ntx, _ = tile_grid(W, H, tile_w, tile_h)
     ys, xs = np.mgrid[0:H, 0:W]
+    if mode == 1:
+        return ((xs // tile_w) % nranks) == rank
     tile = (ys // tile_h) * ntx + (xs // tile_w)
     return (tile % nranks) == rank
 
 
-def configure_partition(ctx, rank, nranks, tile_w=64, tile_h=64):
+def configure_partition(ctx, rank, nranks, tile_w=64, tile_h=64, mode=0):
     lib = _abi.lib()
-    for opt, val in ((_abi.OPT_TILE_W, tile_w), (_abi.OPT_TILE_H, tile_h), (_abi.OPT_PART_NRANKS, nranks), (_abi.OPT_PART_RANK, rank)):
+    for opt, val in ((_abi.OPT_TILE_W, tile_w), (_abi.OPT_TILE_H, tile_h), (_abi.OPT_PART_NRANKS, nranks), (_abi.OPT_PART_RANK, rank), (_abi.OPT_PART_MODE, mode)):
         _abi.check(lib.vr_set_option(ctx, opt, val), ctx)
+
+
+class SharedHostFrames:
+    """`count` H x W x 3 fp32 frames in ONE host buffer that every rank of the node maps (POSIX shared memory) and registers
+    with CUDA (page-locked), so that each rank's device copies the pixels it rendered straight into the assembled frames
+    over its own PCIe link (column partition, VR_OPT_PART_MODE = 1) - the read-back of a frame is spread over all GPUs.
+
+        frames = SharedHostFrames(H, W, count, rank, world)      # collective: rank 0 creates, the others attach
+        frames.ptrs[i]                                           # host pointer of frame i in THIS process
+        frames.array(i)                                          # numpy view (H, W, 3), Fortran order
+    """
+
+    def __init__(self, H, W, count, rank, world, group=None, name=None):
+        import torch
+        import torch.distributed as dist
+        from multiprocessing import shared_memory
+
+        self.H, self.W, self.count, self.rank = int(H), int(W), int(count), rank
+        self.frame_bytes = self.H * self.W * 3 * 4
+        nbytes = self.frame_bytes * self.count
+        box = [None]
+        if rank == 0:
+            self.shm = shared_memory.SharedMemory(create=True, size=nbytes, name=name)
+            box[0] = self.shm.name
+        if world > 1:
+            dist.broadcast_object_list(box, src=0, group=group)
+        if rank != 0:
+            self.shm = shared_memory.SharedMemory(name=box[0])
+            try:  # the creator unlinks; keep this process's resource tracker out of it
+                from multiprocessing import resource_tracker
+
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.buf = np.frombuffer(self.shm.buf, dtype=np.float32, count=nbytes // 4)
+        self.base = self.buf.ctypes.data
+        self._registered = False
+        if torch.cuda.is_available():
+            rc = torch.cuda.cudart().cudaHostRegister(self.base, nbytes, 0)
+            if int(rc) != 0:
+                raise RuntimeError("cudaHostRegister of the shared frames failed: %s" % rc)
+            self._registered = True
+        self.ptrs = [self.base + i * self.frame_bytes for i in range(self.count)]
+        if world > 1:
+            dist.barrier(group=group)
+
+    def array(self, i):
+        n = self.H * self.W * 3
+        return self.buf[i * n:(i + 1) * n].reshape((self.H, self.W, 3), order="F")
+
+    def close(self, world=1, group=None):
+        import torch
+
+        if self._registered:
+            torch.cuda.cudart().cudaHostUnregister(self.base)
+            self._registered = False
+        self.buf = None
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.barrier(group=group)
+        try:
+            self.shm.close()
+        except BufferError:
+            pass
+        if self.rank == 0:
+            self.shm.unlink()
 
 
 def combine_partials(partial, dst=0, group=None):
