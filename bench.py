@@ -43,13 +43,15 @@ DRAM_PROFILE = {
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=16)
+    p.add_argument("--steps", type=int, default=0, help="frames (default 16; example2: 360)")
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--size", type=int, default=1024, help="volume edge (default 1024 = the metric's config)")
-    p.add_argument("--image", type=int, default=2048, help="image edge (default 2048)")
-    p.add_argument("--gradient", default="lookup", choices=["lookup", "compute"])
-    p.add_argument("--lights", type=int, default=2)
+    p.add_argument("--config", default="example1_grad", choices=sorted(CONFIGS) + ["example3"],
+                   help="BASELINE.json configuration: example1_grad (default, the metric's), example1, example2 (360-frame 1920x1080 movie), example3 (two channels, stereo, partial updates)")
+    p.add_argument("--image", type=int, default=0, help="square image edge (default: the configuration's own resolution)")
+    p.add_argument("--gradient", default=None, choices=["lookup", "compute"], help="default: the configuration's")
+    p.add_argument("--lights", type=int, default=None, help="default: the configuration's")
     p.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
@@ -70,7 +72,15 @@ def parse():
                    help="image = tiles over replicated volumes (the metric's config); volume = bricks sharded over the ranks, sort-last composite (config 5)")
     p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                    help="N > 1: p2p = every rank's kernel stores its tiles into rank 0's image over NVLink (default); nccl = SUM-reduce of partial images")
-    return p.parse_args()
+    a = p.parse_args()
+    cfg = CONFIGS.get(a.config, {})
+    if a.gradient is None:
+        a.gradient = cfg.get("gradient", "compute")
+    if not a.steps:
+        a.steps = cfg.get("steps") or 16
+    if a.config in CONFIGS and cfg["volumes"] == "aliased" and a.gradient == "lookup":
+        p.error("--config %s renders with on-the-fly gradients" % a.config)
+    return a
 
 
 # ---- the scene (examples/example1_grad.m:36-51,79-82 on synthetic data) ---------------------------
@@ -84,18 +94,36 @@ def rotation(alpha, beta, gamma, R=None):
     return R @ Rx @ Ry @ Rz
 
 
+# BASELINE.json configs as bench workloads (--config).  "volumes": six = distinct E, R = E^2, A and Gx, Gy, Gz (configs[1]);
+# aliased = Em = Ab = E as one object, default 1x1x1 reflection volume (VolumeRender.m:131), on-the-fly gradient.
+EX1_LIGHTS = [([500, 1000, 550], [0, 1, 1]), ([550, 1000, 500], [1, 0, 1])]  # example1.m:36
+CONFIGS = {
+    # configs[1], examples/example1_grad.m:36-51,79-82 - the configuration the metric is quoted on (default)
+    "example1_grad": dict(image=(2048, 2048), gradient="lookup", lights=EX1_LIGHTS, factors=[0.1, 0.1, 0.4], thr=0.9, color=[1, 1, 1],
+                          focal=3.0, dist=6.0, R0=lambda: rotation(125, 25, 0), volumes="six", steps=None),
+    # configs[0], examples/example1.m:28-60: 1 HG light, on-the-fly gradients, 1024 x 1024 mono
+    "example1": dict(image=(1024, 1024), gradient="compute", lights=EX1_LIGHTS[:1], factors=[1.0, 0.4, 0.6], thr=0.9, color=[1, 1, 0],
+                     focal=3.0, dist=6.0, R0=lambda: rotation(125, 25, 0), volumes="aliased", steps=None),
+    # configs[2], examples/example2.m:28,53-66: 360-degree movie, 360 frames at 1920 x 1080, volumes resident
+    "example2": dict(image=(1920, 1080), gradient="compute", lights=[([1500, 1500, 0], [1, 1, 1])], factors=[10.0, 0.3, 1.0], thr=0.95, color=[1, 1, 1],
+                     focal=3.0, dist=6.0, R0=lambda: rotation(-15, -15, 15, rotation(90, 0, 0)), volumes="aliased", steps=360),
+}
+
+
 class Scene:
     def __init__(self, args):
-        self.W = self.H = args.image
-        self.factors = np.array([0.1, 0.1, 0.4], dtype=np.float32)  # [fEm, fRe, fAb] second pass of example1_grad.m:79-82
+        cfg = CONFIGS[args.config]
+        self.cfg = cfg
+        self.W, self.H = (args.image, args.image) if args.image else cfg["image"]  # ImageResolution = [W, H]
+        self.factors = np.array(cfg["factors"], dtype=np.float32)  # [fEm, fRe, fAb] (VolumeRender.m:558)
         self.es = np.array([1, 1, 1], dtype=np.float32)
         self.res = np.array([self.H, self.W], dtype=np.uint64)
-        self.props = np.array([0.0, 3.0, 6.0], dtype=np.float32)  # CameraXOffset, FocalLength, DistanceToObject
-        self.thr = 0.9
-        self.color = np.array([1, 1, 1], dtype=np.float32)
-        self.R0 = rotation(125, 25, 0)
-        lights = [([500, 1000, 550], [0, 1, 1]), ([550, 1000, 500], [1, 0, 1])][: args.lights]
-        self.lights = lights
+        self.props = np.array([0.0, cfg["focal"], cfg["dist"]], dtype=np.float32)  # CameraXOffset, FocalLength, DistanceToObject
+        self.thr = cfg["thr"]
+        self.color = np.array(cfg["color"], dtype=np.float32)
+        self.R0 = cfg["R0"]()
+        self.lights = cfg["lights"][: args.lights] if args.lights is not None else cfg["lights"]
+        self.aliased = cfg["volumes"] == "aliased"
 
     def rot(self, step):
         R = rotation(0, float(step), 0, self.R0)
@@ -253,6 +281,8 @@ def host_volumes_cpu(args):
     lib.orc_synth_volume.argtypes = [C.c_int, C.c_uint32, C.POINTER(C.c_uint64), C.c_void_p]
     lib.orc_volume_gradient.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)] + [C.c_void_p] * 3
     lib.orc_synth_volume(0, SEED, dims, E.ctypes.data)
+    if CONFIGS[args.config]["volumes"] == "aliased":
+        return {"E": E, "R": np.ones((1, 1, 1), dtype=np.float32, order="F"), "A": E}  # the SAME array: Em = Ab aliased
     A = np.asfortranarray(E[::2, ::2, ::2])  # distinct half-resolution absorption volume, normalised
     A = np.asfortranarray((A - A.min()) / (A.max() - A.min()))
     vols = {"E": E, "R": np.asfortranarray(E * E), "A": A}
@@ -304,8 +334,11 @@ def run_reference(args):
 def workload_config(args, scene, size=None):
     size = size or args.size
     return {
-        "workload": "example1_grad-shaped: %d^3 %s synthetic ViBE-Z-like E (+R=E^2, A, %s), %d HG light(s), %dx%d mono, F=3 D=6 thr=0.9, +1deg/step" % (
-            size, args.dtype, "Gx,Gy,Gz gradient lookup" if args.gradient == "lookup" else "on-the-fly gradient", len(scene.lights), scene.W, scene.H),
+        "workload": "%s-shaped: %d^3 %s synthetic ViBE-Z-like E (%s, %s), %d HG light(s), %dx%d mono, F=%g D=%g thr=%g, +1deg/step" % (
+            args.config, size, args.dtype, "Em = Ab aliased, constant reflection" if scene.aliased else "+R=E^2, A",
+            "Gx,Gy,Gz gradient lookup" if args.gradient == "lookup" else "on-the-fly gradient", len(scene.lights), scene.W, scene.H,
+            float(scene.props[1]), float(scene.props[2]), scene.thr),
+        "baseline_config": args.config,
         "volume": [size] * 3, "image": [scene.W, scene.H], "gradient": args.gradient, "lights": len(scene.lights),
         "multi_gpu": "image-space tiles %dx%d round-robin over replicated volumes; %s" % (
             args.tile, args.tile, "kernels store their tiles straight into rank 0's image over NVLink (CUDA IPC), one barrier per frame" if args.exchange == "p2p" else "NCCL sum-reduce of partial images to rank 0"),
@@ -354,11 +387,16 @@ def run_b200(args):
     # synthetic volumes generated straight into HBM (torch only owns the memory)
     E = torch.empty(n * n * n, dtype=tdt, device=dev)
     _abi.check(lib.vr_synth_volume(ctx, 0, SEED, dims, dt, C.c_void_p(E.data_ptr())), ctx)
-    Rv = E * E
     m = n // 2
-    A = E.view(n, n, n)[::2, ::2, ::2].contiguous().view(-1)  # distinct half-resolution absorption volume
-    A = (A - A.min()) / (A.max() - A.min())
-    keep = [E, Rv, A]
+    one_host = np.ones(1, dtype=np.float32)
+    if scene.aliased:
+        Rv = A = None
+        keep = [E]
+    else:
+        Rv = E * E
+        A = E.view(n, n, n)[::2, ::2, ::2].contiguous().view(-1)  # distinct half-resolution absorption volume
+        A = (A - A.min()) / (A.max() - A.min())
+        keep = [E, Rv, A]
 
     def vol(t, d, stamp):
         v = _abi.VrVolume()
@@ -369,7 +407,12 @@ def run_b200(args):
         v.memspace = _abi.MEM_DEVICE
         return v
 
-    vE, vR, vA = vol(E, (n, n, n), 1), vol(Rv, (n, n, n), 2), vol(A, (m, m, m), 3)
+    if scene.aliased:  # Em = Ab = the same Volume object (example1.m:53-54), default reflection volume = Volume(1)
+        vE = vol(E, (n, n, n), 1)
+        vA = vE
+        vR = _abi.volume_struct((one_host.ctypes.data, (1, 1, 1), _abi.DTYPE_F32, _abi.MEM_HOST), 2)
+    else:
+        vE, vR, vA = vol(E, (n, n, n), 1), vol(Rv, (n, n, n), 2), vol(A, (m, m, m), 3)
     g = [None, None, None]
     if args.gradient == "lookup":
         G = [torch.empty(n * n * n, dtype=tdt, device=dev) for _ in range(3)]
@@ -669,9 +712,29 @@ def run_b200(args):
         try:
             one(0)  # frame 0 of the movie through the mex path, for the full-size parity figure
             frame0 = pageable.reshape((scene.H, scene.W, 3), order="F").copy()
-            line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m, frame0, stats().fetch_mode)
-            if "parity" in line["cpu_baseline"]:
-                line["parity"] = line["cpu_baseline"].pop("parity")
+            arith_run, fetch_run = int(stats().arithmetic), int(stats().fetch_mode)
+            frame0_exact = None
+            if arith_run != _abi.ARITH_EXACT:  # the same frame once more in the "exact" arithmetic flavour (the one that agrees with the CPU oracle bit for bit)
+                _abi.check(lib.vr_set_option(ctx, _abi.OPT_ARITHMETIC, _abi.ARITH_EXACT), ctx)
+                one(0)
+                frame0_exact = pageable.reshape((scene.H, scene.W, 3), order="F").copy()
+                _abi.check(lib.vr_set_option(ctx, _abi.OPT_ARITHMETIC, arith_run), ctx)
+                one(0)  # (leaves the counters of the run's own flavour behind)
+            line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m, frame0, fetch_run, frame0_exact)
+            cb = line["cpu_baseline"]
+            par = {}
+            if isinstance(cb.get("reference_cuda"), dict) and cb["reference_cuda"].get("parity"):
+                par["reference_kernel"] = cb["reference_cuda"].pop("parity")
+            if "parity" in cb:
+                par["oracle"] = cb.pop("parity")
+            if "parity_exact" in cb:
+                par["oracle_exact_flavour"] = cb.pop("parity_exact")
+            if par:
+                # headline figures: against the reference's own kernel where it ran, else against the CPU oracle
+                head = par.get("reference_kernel") or par.get("oracle")
+                par.update({"max_abs_norm": head.get("max_abs_norm"), "psnr_db": head.get("psnr_db"), "window": head.get("window", "whole frame"),
+                            "arithmetic": int(stats().arithmetic), "against": "reference_kernel" if "reference_kernel" in par else "oracle"})
+                line["parity"] = par
             rcb = line["cpu_baseline"].get("reference_cuda", {})
             if "ms_per_frame" in rcb:  # same frames, same lattice: samples per frame from this run's counters
                 rcb["value"] = line["samples_per_frame"] / (rcb["ms_per_frame"] * 1e-3) / 1e9
@@ -779,10 +842,10 @@ def upload_probe(args):
     return out
 
 
-def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mode=1):
+def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mode=1, gpu_frame0_exact=None):
     import torch
 
-    need = (5 if G is not None else 2) * 4.0 * n ** 3 / 2 ** 30
+    need = (5 if G is not None else (1 if scene.aliased else 2)) * 4.0 * n ** 3 / 2 ** 30
     if mem_available_gib() < need * 1.3 + 8 or E.dtype != torch.float32:
         # not enough host memory for copies of the full volumes: same scene on a 512^3 twin
         a2 = argparse.Namespace(**vars(args))
@@ -793,7 +856,11 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mo
         def host(t, d):  # the flat tensors are in MATLAB order (dims[0] fastest)
             return t.cpu().numpy().reshape(d, order="F")
 
-        vols = {"E": host(E, (n, n, n)), "R": host(Rv, (n, n, n)), "A": host(A, (m, m, m))}
+        if scene.aliased:
+            hE = host(E, (n, n, n))
+            vols = {"E": hE, "R": np.ones((1, 1, 1), dtype=np.float32, order="F"), "A": hE}
+        else:
+            vols = {"E": host(E, (n, n, n)), "R": host(Rv, (n, n, n)), "A": host(A, (m, m, m))}
         if G is not None:
             vols.update({"Gx": host(G[0], (n, n, n)), "Gy": host(G[1], (n, n, n)), "Gz": host(G[2], (n, n, n))})
         note = "the same %d^3 volumes copied back from the GPU" % n
@@ -816,16 +883,22 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mo
             chk.render_window(0, ph)
             x0, x1, y0, y1 = chk.window
             ref_w = chk.out[y0:y1, x0:x1, :].astype(np.float64)
-            gpu_w = gpu_frame0[y0:y1, x0:x1, :].astype(np.float64)
             peak = float(chk.out.max()) or 1.0
-            d = np.abs(gpu_w - ref_w)
-            mse = float(np.mean((d / peak) ** 2))
-            out["parity"] = {"max_abs_norm": float(d.max() / peak), "psnr_db": (float("inf") if mse == 0 else 10.0 * math.log10(1.0 / mse)),
-                             "frac_within_1e-3": float((d.max(axis=2) / peak <= 1e-3).mean()), "window": [x0, x1, y0, y1], "pixels": int((x1 - x0) * (y1 - y0)),
-                             "normalised_by": "maximum of the oracle window (%.6g)" % peak, "tolerance": 1e-3,
-                             "checker": "oracle/liboracle.so (strict IEEE build), %s, frame 0 of this run's movie, %s" % (
-                                 "texture filter as measured on the B200 texture unit (ORC_OPT_FILTER_FRAC_BITS = 9)" if fetch_mode == 1 else "fp32 filter weights (documented formula)", note),
-                             "seconds": time.perf_counter() - t0}
+            secs = time.perf_counter() - t0
+
+            def diff(frame):
+                d = np.abs(frame[y0:y1, x0:x1, :].astype(np.float64) - ref_w)
+                mse = float(np.mean((d / peak) ** 2))
+                return {"max_abs_norm": float(d.max() / peak), "psnr_db": (float("inf") if mse == 0 else 10.0 * math.log10(1.0 / mse)),
+                        "frac_within_1e-3": float((d.max(axis=2) / peak <= 1e-3).mean()), "window": [x0, x1, y0, y1], "pixels": int((x1 - x0) * (y1 - y0)),
+                        "normalised_by": "maximum of the oracle window (%.6g)" % peak, "tolerance": 1e-3,
+                        "checker": "oracle/liboracle.so (strict IEEE build), %s, frame 0 of this run's movie, %s" % (
+                            "texture filter as measured on the B200 texture unit (ORC_OPT_FILTER_FRAC_BITS = 9)" if fetch_mode == 1 else "fp32 filter weights (documented formula)", note),
+                        "seconds": secs}
+
+            out["parity"] = diff(gpu_frame0)
+            if gpu_frame0_exact is not None:
+                out["parity_exact"] = diff(gpu_frame0_exact)
         except Exception as ex:
             out["parity"] = {"failed": repr(ex)[:300]}
     # north_star: "a baseline from the reference's CUDA kernel rebuilt standalone via nvcc is added where it builds" -
@@ -833,13 +906,13 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mo
     try:
         if note.startswith("512^3 twin"):
             raise RuntimeError("host memory too small for copies of the full volumes")
-        out["reference_cuda"] = reference_cuda_baseline(cpu, scene, vols)
+        out["reference_cuda"] = reference_cuda_baseline(cpu, scene, vols, gpu_frame0)
     except Exception as ex:
         out["reference_cuda"] = {"unavailable": repr(ex)}
     return out
 
 
-def reference_cuda_baseline(cpu, scene, vols):
+def reference_cuda_baseline(cpu, scene, vols, gpu_frame0=None):
     """Whole frames of the same scene through the reference's own vr::render (cudaMalloc + memset + d_render +
     sync + D2H, volumeRender.cpp:233-300) on this GPU; uploads (cudaMemcpy3D from pageable memory) not timed."""
     rc = cpu.vrt.ref_cuda()
@@ -853,6 +926,7 @@ def reference_cuda_baseline(cpu, scene, vols):
     n = len(scene.lights)
     out = np.zeros((scene.H, scene.W, 3), dtype=np.float32, order="F")
     times = []
+    parity = None
     for k in range(9):  # one warm-up + 8 timed frames, median
         rot = scene.rot(k)
         t = time.perf_counter()
@@ -860,10 +934,180 @@ def reference_cuda_baseline(cpu, scene, vols):
                                  scene.res.ctypes.data_as(C.POINTER(C.c_uint64)), f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color),
                                  out.ctypes.data) == 0
         times.append(time.perf_counter() - t)
+        if k == 0 and gpu_frame0 is not None:
+            # frame 0 of the movie: this library's image against the reference kernel's own, the WHOLE 2048^2 frame
+            peak = float(out.max()) or 1.0
+            d = np.abs(gpu_frame0.astype(np.float64) - out.astype(np.float64)) / peak
+            mse = float(np.mean(d ** 2))
+            parity = {"max_abs_norm": float(d.max()), "psnr_db": float("inf") if mse == 0 else 10.0 * math.log10(1.0 / mse),
+                      "frac_within_1e-3": float((d.max(axis=2) <= 1e-3).mean()), "pixels": int(out.shape[0] * out.shape[1]), "tolerance": 1e-3,
+                      "normalised_by": "maximum of the reference kernel's image (%.6g)" % peak,
+                      "checker": "the reference's own d_render (oracle/_ref/libref_cuda.so: volumeRender_kernel.cu on texture objects), same volumes, same camera, whole frame"}
     # the lattice of frame 0 is the one the oracle counted per pixel above; count it for the full frame with the same rule
     return {"kind": "shimmed reference: the reference's d_render/upload code on texture objects, nvcc sm_100a, unmodified launch shape (16x16 blocks)",
             "ms_per_frame": 1e3 * float(np.median(times[1:])), "ms_per_frame_min": 1e3 * min(times[1:]), "ms_per_frame_max": 1e3 * max(times[1:]),
-            "frames": len(times) - 1, "first_frame_ms": 1e3 * times[0], "statistic": "median of %d frames (camera +1 degree each) after one warm-up frame" % (len(times) - 1)}
+            "frames": len(times) - 1, "first_frame_ms": 1e3 * times[0], "statistic": "median of %d frames (camera +1 degree each) after one warm-up frame" % (len(times) - 1),
+            "parity": parity}
+
+
+def run_example3(args):
+    """BASELINE configs[3], examples/example3.m: a two-channel scene - the main channel E is faded on a half-space mask
+    every frame (example3.m:135-161: the reference re-uploads the whole volume, here vr_update_box moves the changed half),
+    the structure channel S (sparse tubes, green, fEm 0.5; :199-208) is rendered by a second renderer - as an off-axis stereo
+    pair (CameraXOffset 0.06, RedCyan; :105-108) with three lights (:76 + example1.m:36), 2048 x 2048 per eye.  Per frame:
+    update the half volume from host memory, render both eyes of both channels (one batch launch per channel), add the
+    channels (example3.m:239), crop + compose the anaglyph (VolumeRender.m:286-306) on the device, read the frame back."""
+    import torch
+
+    from volume_renderer_b200 import _abi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path")
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    lib = _abi.lib()
+    n, W = args.size, (args.image or 2048)
+    H = W
+    stream = torch.cuda.current_stream()
+    ctxs = []
+    for _ in range(2):
+        c = C.c_void_p()
+        _abi.check(lib.vr_create_on_device(C.byref(c), 0))
+        _abi.check(lib.vr_set_stream(c, C.c_void_p(stream.cuda_stream)), c)  # one stream: the channels' launches and the epilogue are ordered
+        if args.arith >= 0:
+            _abi.check(lib.vr_set_option(c, _abi.OPT_ARITHMETIC, args.arith), c)
+        ctxs.append(c)
+    main, struct = ctxs
+    dims = (C.c_uint64 * 3)(n, n, n)
+    E = torch.empty(n ** 3, dtype=torch.float32, device=dev)
+    S = torch.empty(n ** 3, dtype=torch.float32, device=dev)
+    _abi.check(lib.vr_synth_volume(main, 0, SEED, dims, _abi.DTYPE_F32, C.c_void_p(E.data_ptr())), main)
+    _abi.check(lib.vr_synth_volume(struct, 1, SEED, dims, _abi.DTYPE_F32, C.c_void_p(S.data_ptr())), struct)
+    # the main channel lives in HOST memory (MATLAB rewrites it there): two page-locked versions with different fade factors
+    # on the half space z < n/2 stand for the per-frame `Data(mask) = emission(mask) * factor` of example3.m:151
+    half = n ** 3 // 2
+    hosts = []
+    for factor in (0.8, 0.4):
+        h = E.cpu()
+        h[:half] *= factor  # z is the slowest axis: the first half of the buffer is the half space
+        hosts.append(h.pin_memory())
+    del E
+    one_host = np.ones(1, dtype=np.float32)
+
+    def hostvol(i, stamp):
+        return _abi.volume_struct((hosts[i].data_ptr(), (n, n, n), _abi.DTYPE_F32, _abi.MEM_HOST), stamp)
+
+    vR = _abi.volume_struct((one_host.ctypes.data, (1, 1, 1), _abi.DTYPE_F32, _abi.MEM_HOST), 2)
+    vS = _abi.volume_struct((S.data_ptr(), (n, n, n), _abi.DTYPE_F32, _abi.MEM_DEVICE), 3)
+    vM = hostvol(0, 10)
+    t_up = time.perf_counter()
+    _abi.check(lib.vr_sync_volumes(main, 0, C.byref(vM), C.byref(vR), C.byref(vM), None, None, None), main)
+    _abi.check(lib.vr_sync_volumes(struct, 0, C.byref(vS), C.byref(vR), C.byref(vS), None, None, None), struct)
+    torch.cuda.synchronize()
+    t_up = time.perf_counter() - t_up
+    lut = np.zeros(64 ** 3, dtype=np.float32)
+    _abi.check(lib.vr_henyey_greenstein(64, 0.8, lut.ctypes.data))
+    lutv = _abi.volume_struct((lut.ctypes.data, (64, 64, 64), _abi.DTYPE_F32, _abi.MEM_HOST), 9)
+    lights_spec = [([-15, 15, 0], [0.5, 0.5, 0.5])] + EX1_LIGHTS  # example3.m:76 + example1.m:36
+    lights = (_abi.VrLight * 3)()
+    for i, (p_, c_) in enumerate(lights_spec):
+        lights[i].position[:] = p_
+        lights[i].color[:] = c_
+    F, D, thr, base = 4.5, 6.0, 0.95, 0.06 / 2  # example3.m:66-73,105
+    delta = int(math.floor(base * W / 2.0 + 0.5))  # VolumeRender.m:277-282
+    Wp = W + delta
+    res_wide = np.array([H, Wp], dtype=np.uint64)
+    es = np.array([1, 1, 1], dtype=np.float32)
+    R0 = rotation(-15, 15, 15, rotation(90, 0, 0))
+    props = np.array([base, F, D, -base, F, D], dtype=np.float32)  # right eye, left eye (VolumeRender.m:284-285)
+    chan = {main: (np.array([1.0, 1.0, 1.0], dtype=np.float32), np.array([1, 1, 1], dtype=np.float32)),       # [fEm, fRe, fAb], color
+            struct: (np.array([0.5, 1.0, 1.0], dtype=np.float32), np.array([0, 1, 0], dtype=np.float32))}    # example3.m:199-208
+    npw = H * Wp * 3
+    eyes = {c: torch.zeros(2 * npw, dtype=torch.float32, device=dev) for c in ctxs}
+    summed = torch.zeros(2 * npw, dtype=torch.float32, device=dev)
+    out_dev = torch.zeros(H * W * 3, dtype=torch.float32, device=dev)
+    out_host = torch.zeros(H * W * 3, dtype=torch.float32).pin_memory()
+    lo, hi = (C.c_uint64 * 3)(0, 0, 0), (C.c_uint64 * 3)(n, n, n // 2)
+    resw = res_wide.ctypes.data_as(C.POINTER(C.c_uint64))
+    counters = {"samples": 0, "shaded": 0, "upload_ms": 0.0, "kernel_ms": 0.0, "launches": 0}
+
+    def frame(k, count=True):
+        nonlocal vM
+        vM = hostvol(k & 1, 100 + k)  # the other fade factor, a new timestamp
+        _abi.check(lib.vr_update_box(main, 0, C.byref(vM), lo, hi), main)
+        st = _abi.VrStats()
+        _abi.check(lib.vr_get_stats(main, C.byref(st)), main)
+        up_ms = st.upload_ms
+        rot = np.asfortranarray(np.flipud(rotation(0, float(k), 0, R0)).astype(np.float32)).reshape(-1, order="F")
+        rots = np.concatenate([rot, rot]).astype(np.float32)
+        for c, v in ((main, vM), (struct, vS)):
+            fac, col = chan[c]
+            _abi.check(lib.vr_sync_volumes(c, 100 + k, C.byref(v), C.byref(vR), C.byref(v), None, None, None), c)  # nothing dirty: moves nothing
+            outs = (C.c_void_p * 2)(eyes[c].data_ptr(), eyes[c].data_ptr() + 4 * npw)
+            _abi.check(lib.vr_render_batch_device(c, lights, 3, C.byref(lutv), f32p(fac), f32p(es), resw, 2, f32p(rots), f32p(props), C.c_float(thr), f32p(col), outs,
+                                                  C.c_void_p(stream.cuda_stream)), c)
+        pair = (C.c_void_p * 2)(eyes[main].data_ptr(), eyes[struct].data_ptr())
+        _abi.check(lib.vr_compose_partials_device(main, 2, pair, 2 * npw, C.c_void_p(summed.data_ptr()), C.c_void_p(stream.cuda_stream)), main)  # main + structure
+        _abi.check(lib.vr_compose_stereo_device(main, C.c_void_p(summed.data_ptr() + 4 * npw), C.c_void_p(summed.data_ptr()), resw, delta, 0,
+                                                C.c_void_p(out_dev.data_ptr()), C.c_void_p(stream.cuda_stream)), main)  # (left, right) -> red-cyan
+        out_host.copy_(out_dev, non_blocking=True)
+        torch.cuda.synchronize()
+        if count:
+            for c in ctxs:
+                _abi.check(lib.vr_get_stats(c, C.byref(st)), c)
+                counters["samples"] += st.samples_marched
+                counters["shaded"] += st.samples_shaded
+                counters["kernel_ms"] += st.kernel_ms
+                counters["launches"] += st.kernel_launches
+            counters["upload_ms"] += up_ms
+
+    for w in range(args.warmup):
+        frame(-1 - w, count=False)
+    sampler = ClockSampler(0)
+    t0 = time.time()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    tw = time.perf_counter()
+    for k in range(args.steps):
+        frame(k)
+    tw = time.perf_counter() - tw
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    K = args.steps
+    line = {
+        "metric": "Gsamples/s (two channels, stereo pair, %d^2 per eye, %d^3 vol)" % (W, n), "value": counters["samples"] / tw / 1e9, "unit": "Gsamples/s",
+        "n_gpus": 1, "steps": K, "warmup": args.warmup, "ms_per_step": 1e3 * tw / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "frames_per_s": K / tw, "gsamples_shaded_per_s": counters["shaded"] / tw / 1e9,
+        "kernel_ms_per_frame": counters["kernel_ms"] / K, "update_box_ms_per_frame": counters["upload_ms"] / K, "gpu_launches": counters["launches"] + 2 * K,
+        "e2e": {"value": counters["samples"] / tw / 1e9, "unit": "Gsamples/s", "h2d_bytes_per_step": n ** 3 * 2, "d2h_bytes_per_step": H * W * 3 * 4,
+                "note": "the step IS the end-to-end call sequence: vr_update_box from page-locked host memory, 2 x (vr_sync_volumes + vr_render_batch_device), "
+                        "vr_compose_partials_device, vr_compose_stereo_device, read-back of the anaglyph; wall clock"},
+        "config": {"workload": "example3-shaped: main channel %d^3 fp32 (host-resident, half of it rewritten every frame -> vr_update_box) + structure channel (sparse tubes, green), "
+                               "3 HG lights, on-the-fly gradient, off-axis stereo pair CameraXOffset 0.06 (delta %d px), %dx%d per eye, F=4.5 D=6 thr=0.95, RedCyan compose on the device" % (n, delta, W, H),
+                   "baseline_config": "example3", "volume": [n] * 3, "image": [W, H], "lights": 3, "gradient": "compute", "volume_upload_s": t_up,
+                   "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames"},
+        "clocks": clocks,
+    }
+    emit(line)
+    for c in ctxs:
+        _abi.check(lib.vr_destroy(c))
+    return 0
+
+
+def volume_cpu_baseline(args):
+    """The oracle on the 512^3 analogue of the huge volume (config 5 is CPU-timed on the 512^3 analogue): same
+    generator, same camera, 1 light, on-the-fly gradient, a centred window; all host cores."""
+    a2 = argparse.Namespace(**vars(args))
+    a2.size, a2.config, a2.gradient, a2.lights, a2.image = 512, "example1", "compute", 1, args.image
+    scene = Scene(a2)
+    cpu = CpuRender(scene, a2, host_volumes_cpu(a2))
+    half = cpu.calibrated_half(args.cpu_seconds)
+    nsm, sec, threads = cpu.render_window(0, half)
+    return {"value": nsm / sec / 1e9, "unit": "Gsamples/s (lattice)", "cores": int(threads), "kind": "port",
+            "sample": "512^3 fp32 analogue of the volume (same generator and camera), centred %dx%d window of the %dx%d image, %.1f s of CPU time, %d lattice samples" % (
+                2 * half, 2 * half, scene.W, scene.H, sec, nsm)}
 
 
 def run_volume(args):
@@ -880,6 +1124,7 @@ def run_volume(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    args.image = args.image or 2048
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -947,6 +1192,9 @@ def run_volume(args):
     sampler = ClockSampler(local) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     shaded = marched = 0
+    kernel_ms = 0.0
+    if world > 1:
+        vs.timing = []
     t0 = time.time()
     barrier()
     ev0.record()
@@ -955,31 +1203,92 @@ def run_volume(args):
         st = r.stats()  # counters of this rank's shading pass
         shaded += st["samples_shaded"]
         marched += st["samples_marched"]
+        kernel_ms += st["kernel_ms"]
     ev1.record()
     barrier()
     t1 = time.time()
     clocks = sampler.stop(t0, t1) if sampler else None
     ms = ev0.elapsed_time(ev1)
-    tot = torch.tensor([ms, float(shaded), float(marched)], dtype=torch.float64, device=dev)
+    phases = vs.phase_ms() if world > 1 else {"shading_pass": kernel_ms}
+    if world > 1:
+        vs.timing = None
+    fetch_mode, arith = r.stats()["fetch_mode"], r.stats()["arithmetic"]
+    names = ["opacity_pass", "all_gather", "shading_pass", "barrier_and_compose"]
+    tot = torch.tensor([ms, float(shaded), float(marched), kernel_ms] + [phases.get(p_, 0.0) for p_ in names], dtype=torch.float64, device=dev)
+    per_rank = None
     if world > 1:
         mx = tot.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        allr = [torch.zeros_like(tot) for _ in range(world)]
+        dist.all_gather(allr, tot)
+        per_rank = [{"rank": i, "shaded_per_frame": float(t[1]) / args.steps, "shading_kernel_ms_per_frame": float(t[3]) / args.steps,
+                     "opacity_pass_ms_per_frame": float(t[4]) / args.steps} for i, t in enumerate(allr)]
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         ms = float(mx[0])
+        kmax = float(mx[3])
+        phase_max = {p_: float(mx[4 + i]) / args.steps for i, p_ in enumerate(names)}
+    else:
+        kmax = kernel_ms
+        phase_max = {"shading_pass": kernel_ms / args.steps}
+    # ---- end to end: the same frames, each read back to host memory on rank 0 (wall clock, max over ranks) ----
+    barrier()
+    te = time.perf_counter()
+    e_shaded = 0
+    for k in range(args.steps):
+        if world > 1:
+            r.RotationMatrix = rotation(0, float(k), 0, R0)
+            img = vs.render(download=True)
+        else:
+            frame(k)
+            img = d_img.cpu()
+        e_shaded += r.stats()["samples_shaded"]
+    barrier()
+    te = time.perf_counter() - te
+    e = torch.tensor([te, float(e_shaded)], dtype=torch.float64, device=dev)
+    if world > 1:
+        emx = e.clone()
+        dist.all_reduce(emx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e, op=dist.ReduceOp.SUM)
+        te = float(emx[0])
     res_b = r.stats()["bytes_resident"]
     if rank == 0:
+        # roofline of the shading pass (the dominant kernel): trilinear fetches x 32 algorithmic bytes / the slowest rank's kernel time,
+        # against the fetch-only ceiling of the fetch path that ran (loads for bf16 / region contexts, else the texture unit)
+        fetches = 2 + 6 + 1  # emission, reflection, six central-difference taps, one LUT fetch (1 light)
+        achieved = float(tot[1]) * fetches * 32.0 / (kmax * 1e-3) / 1e9 / world  # per GPU: the slowest rank bounds the frame
+        roofline = {"bound": "gather", "achieved": achieved, "peak": None, "unit": "GB/s", "frac": None, "traffic": None, "kernel": "k_raymarch (shading pass)",
+                    "kernel_ms_avg": kmax / args.steps, "fetches_per_shaded_sample": fetches, "algorithmic_bytes_per_fetch": 32,
+                    "note": "per GPU: all ranks' shaded samples / ranks, over the SLOWEST rank's shading-pass time (ranks behind the opacity threshold idle)"}
+        try:
+            f_, m_ = C.c_double(), C.c_double()
+            _abi.check(lib.vr_probe_gather(ctx, 2 if fetch_mode == 1 else 0, 8, C.byref(f_), C.byref(m_)), ctx)
+            roofline["peak"] = f_.value * 32.0 / 1e9
+            roofline["frac"] = achieved / roofline["peak"]
+            roofline["peak_source"] = "live vr_probe_gather, %s, L2-resident footprint" % ("tex3D<float>" if fetch_mode == 1 else "eight 4-byte loads per fetch")
+        except Exception as ex:
+            roofline["peak_source"] = "probe failed: %r" % (ex,)
         line = {
             "metric": "Gsamples/s shaded (%d^2 image, %d^3 %s vol sharded over %d GPU(s))" % (args.image, n, args.dtype, world),
             "value": float(tot[1]) / (ms * 1e-3) / 1e9, "unit": "Gsamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
             "frames_per_s": args.steps / (ms * 1e-3), "samples_shaded_per_frame": float(tot[1]) / args.steps,
             "lattice_samples_visited_per_frame_all_ranks": float(tot[2]) / args.steps,
+            "phase_ms_per_frame_max_over_ranks": phase_max, "per_rank": per_rank, "fetch_mode": int(fetch_mode), "arithmetic": int(arith),
+            "e2e": {"value": float(e[1]) / te / 1e9, "unit": "Gsamples/s", "frames_per_s": args.steps / te, "h2d_bytes_per_step": 388, "d2h_bytes_per_step": args.image * args.image * 3 * 4,
+                    "note": "every frame composited on rank 0 and read back to host memory; wall clock, max over ranks"},
+            "roofline": roofline,
             "config": {"workload": "huge-volume-shaped: %d^3 %s synthetic ViBE-Z-like E (Em=Ab), bricks %s (+%d voxel halo) one per GPU, 1 HG light, on-the-fly gradient, %dx%d mono, F=3 D=6 thr=0.9, +1deg/step"
-                       % (n, args.dtype, "x".join(str(x) for x in multigpu.splits_for(world)), halo, args.image, args.image),
+                       % (n, args.dtype, "x".join(str(x) for x in multigpu.splits_for(world)), halo, args.image, args.image), "baseline_config": "huge volume (configs[4])",
                        "multi_gpu": "volume-space sort-last: opacity pass, all-gather of H*W floats per brick (NCCL), shading pass storing shares into rank 0 over NVLink (%s), composite kernel" % args.exchange,
-                       "brick_generate_s": t_gen, "brick_upload_s": t_up, "bytes_resident_rank0": res_b},
+                       "brick_generate_s": t_gen, "brick_upload_s": t_up, "bytes_resident_rank0": res_b,
+                       "l2": "inputs (resident bricks, GiBs) are larger than the 126 MB L2; no flush between frames"},
             "clocks": clocks, "gpu_launches": 2 * args.steps * world + args.steps,
         }
+        if not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = volume_cpu_baseline(args)
+            except Exception as ex:
+                line["cpu_baseline"] = {"value": None, "unit": "Gsamples/s", "cores": 0, "kind": "port", "sample": "failed: %r" % (ex,)}
         emit(line)
     if world > 1:
         torch.cuda.synchronize()
@@ -1015,4 +1324,6 @@ if __name__ == "__main__":
     if a.impl == "reference":
         os.environ["OMP_NUM_THREADS"] = str(host_cores())  # before libgomp loads: torchrun hands its workers OMP_NUM_THREADS=1
         sys.exit(run_reference(a))
+    if a.config == "example3":
+        sys.exit(run_example3(a))
     sys.exit(run_volume(a) if a.mode == "volume" else run_b200(a))

