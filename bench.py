@@ -1020,10 +1020,10 @@ def run_example3(args):
     es = np.array([1, 1, 1], dtype=np.float32)
     R0 = rotation(-15, 15, 15, rotation(90, 0, 0))
     props = np.array([base, F, D, -base, F, D], dtype=np.float32)  # right eye, left eye (VolumeRender.m:284-285)
-    chan = {main: (np.array([1.0, 1.0, 1.0], dtype=np.float32), np.array([1, 1, 1], dtype=np.float32)),       # [fEm, fRe, fAb], color
-            struct: (np.array([0.5, 1.0, 1.0], dtype=np.float32), np.array([0, 1, 0], dtype=np.float32))}    # example3.m:199-208
+    chan = [(np.array([1.0, 1.0, 1.0], dtype=np.float32), np.array([1, 1, 1], dtype=np.float32)),    # main: [fEm, fRe, fAb], color
+            (np.array([0.5, 1.0, 1.0], dtype=np.float32), np.array([0, 1, 0], dtype=np.float32))]    # structure: example3.m:199-208
     npw = H * Wp * 3
-    eyes = {c: torch.zeros(2 * npw, dtype=torch.float32, device=dev) for c in ctxs}
+    eyes = [torch.zeros(2 * npw, dtype=torch.float32, device=dev) for _ in ctxs]  # per channel: right eye, left eye
     summed = torch.zeros(2 * npw, dtype=torch.float32, device=dev)
     out_dev = torch.zeros(H * W * 3, dtype=torch.float32, device=dev)
     out_host = torch.zeros(H * W * 3, dtype=torch.float32).pin_memory()
@@ -1040,13 +1040,13 @@ def run_example3(args):
         up_ms = st.upload_ms
         rot = np.asfortranarray(np.flipud(rotation(0, float(k), 0, R0)).astype(np.float32)).reshape(-1, order="F")
         rots = np.concatenate([rot, rot]).astype(np.float32)
-        for c, v in ((main, vM), (struct, vS)):
-            fac, col = chan[c]
+        for ci, (c, v) in enumerate(((main, vM), (struct, vS))):
+            fac, col = chan[ci]
             _abi.check(lib.vr_sync_volumes(c, 100 + k, C.byref(v), C.byref(vR), C.byref(v), None, None, None), c)  # nothing dirty: moves nothing
-            outs = (C.c_void_p * 2)(eyes[c].data_ptr(), eyes[c].data_ptr() + 4 * npw)
+            outs = (C.c_void_p * 2)(eyes[ci].data_ptr(), eyes[ci].data_ptr() + 4 * npw)
             _abi.check(lib.vr_render_batch_device(c, lights, 3, C.byref(lutv), f32p(fac), f32p(es), resw, 2, f32p(rots), f32p(props), C.c_float(thr), f32p(col), outs,
                                                   C.c_void_p(stream.cuda_stream)), c)
-        pair = (C.c_void_p * 2)(eyes[main].data_ptr(), eyes[struct].data_ptr())
+        pair = (C.c_void_p * 2)(eyes[0].data_ptr(), eyes[1].data_ptr())
         _abi.check(lib.vr_compose_partials_device(main, 2, pair, 2 * npw, C.c_void_p(summed.data_ptr()), C.c_void_p(stream.cuda_stream)), main)  # main + structure
         _abi.check(lib.vr_compose_stereo_device(main, C.c_void_p(summed.data_ptr() + 4 * npw), C.c_void_p(summed.data_ptr()), resw, delta, 0,
                                                 C.c_void_p(out_dev.data_ptr()), C.c_void_p(stream.cuda_stream)), main)  # (left, right) -> red-cyan
