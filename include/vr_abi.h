@@ -190,6 +190,19 @@ VR_API vr_status vr_render_batch(vr_ctx *ctx, const vr_light *lights, size_t n_l
 /* n^3 floats, index k = c*n*n + a*n + b (HenyeyGreenstein.cc:86); evaluated on the GPU. */
 VR_API vr_status vr_henyey_greenstein(uint32_t n, float g, float *out_lut);
 
+/* The same LUT WITHOUT ANY ALLOCATION.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * vr_henyey_greenstein allocates and frees an n^3 device scratch per call; here that scratch is a file-scope
+ * `static __device__` array of the library, VR_HG_STATIC_MAX_N^3 floats = 1 MiB, which every GPU that loads the library
+ * holds until the process exits.  n > VR_HG_STATIC_MAX_N is rejected with VR_ERR_INVALID_ARGUMENT (64 is the size every
+ * example of the reference uses, example1.m:35).  The call runs on the CURRENT device, enqueues the kernel and the copy
+ * on `cuda_stream` (NULL = the legacy default stream), waits for them, and calls no cudaMalloc / cudaFree or any
+ * allocating library routine.  out_lut = n^3 floats in host OR device memory (same layout as above).  Every call shares
+ * the one array per device, which keeps the last call's contents (each call overwrites all it reads): calls that
+ * overlap on the GPU - two streams, two host threads - race; serialise them. */
+#define VR_HG_STATIC_MAX_N 64
+VR_API vr_status vr_henyey_greenstein_static(uint32_t n, float g, float *out_lut, void *cuda_stream);
+
 /* ---- timestamp() mex  (src/C/mex/timestamp.cpp:13-33) ---------------------------------- */
 /* Milliseconds since the epoch.  The reference stores them through an int* (timestamp.cpp:25,33),
  * i.e. only the low 32 bits reach MATLAB; truncate_like_reference != 0 reproduces that. */

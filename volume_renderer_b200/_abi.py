@@ -43,6 +43,7 @@ OPT_ARITHMETIC = 15
 OPT_PART_MODE = 16
 ARITH_EXACT, ARITH_REFERENCE, ARITH_FAST = 0, 1, 2
 IPC_HANDLE_BYTES = 64
+HG_STATIC_MAX_N = 64
 
 
 class VrVolume(C.Structure):
@@ -107,6 +108,7 @@ def declare(lib):
         "vr_render_batch_end": ([vp], C.c_int),
         "vr_set_devices": ([vp, C.c_uint32, P(C.c_int)], C.c_int),
         "vr_henyey_greenstein": ([C.c_uint32, C.c_float, vp], C.c_int),
+        "vr_henyey_greenstein_static": ([C.c_uint32, C.c_float, vp, vp], C.c_int),
         "vr_timestamp_ms": ([C.c_int], C.c_uint64),
         "vr_last_error": ([vp], C.c_char_p),
         "vr_status_string": ([C.c_int], C.c_char_p),

@@ -1837,6 +1837,26 @@ vr_status vr_henyey_greenstein(uint32_t n, float g, float *out) {
   return VR_OK;
 }
 
+// vr_henyey_greenstein without any allocation: the device scratch is a static array of the library (resident_kernels.cu).
+vr_status vr_henyey_greenstein_static(uint32_t n, float g, float *out, void *cuda_stream) {
+  static_assert(VR_HG_STATIC_MAX_N == HG_STATIC_MAX_N, "header and kernel file disagree on the scratch size");
+  if (!out || n == 0) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "HenyeyGreenstein: bad size");
+  if (n > VR_HG_STATIC_MAX_N)
+    return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_henyey_greenstein_static: n = %u exceeds the static scratch (n <= %d, %d^3 floats); use vr_henyey_greenstein",
+                n, (int)VR_HG_STATIC_MAX_N, (int)VR_HG_STATIC_MAX_N);
+  if (g > 1.0f || g < -1.0f) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "g must be in interval [-1,1]");  // HenyeyGreenstein.cc:44-45
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(nullptr, VR_ERR_NO_DEVICE, "no CUDA device; there is no CPU fallback");
+  cudaStream_t s = (cudaStream_t)cuda_stream;
+  float *d = nullptr;
+  cudaError_t e = launch_hg_lut_static(n, g, s, &d);
+  const size_t bytes = (size_t)n * n * n * sizeof(float);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, d, bytes, cudaMemcpyDefault, s);  // `out`: host or device memory of the caller
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) return fail(nullptr, VR_ERR_CUDA, "vr_henyey_greenstein_static: %s", cudaGetErrorString(e));
+  return VR_OK;
+}
+
 uint64_t vr_timestamp_ms(int truncate_like_reference) {
   const uint64_t ms = (uint64_t)std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::system_clock::now().time_since_epoch()).count();
   return truncate_like_reference ? (ms & 0xffffffffull) : ms;

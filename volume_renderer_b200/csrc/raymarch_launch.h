@@ -61,6 +61,10 @@ cudaError_t launch_distance(const uint32_t *occ, uint8_t *dist, uint8_t *tmp, in
 
 // Henyey-Greenstein LUT (HenyeyGreenstein.cc:47-91): n^3 floats on the device.
 cudaError_t launch_hg_lut(float *d_out, uint32_t n, float g, cudaStream_t stream);
+// The same LUT into the library's file-scope device scratch (no allocation; n <= HG_STATIC_MAX_N): enqueues the kernel on
+// `stream` for the CURRENT device and returns the scratch's device address in *d_lut (valid until the next call).
+enum { HG_STATIC_MAX_N = 64 };
+cudaError_t launch_hg_lut_static(uint32_t n, float g, cudaStream_t stream, float **d_lut);
 
 // synthetic ViBE-Z-shaped volumes; kind 0 = brain, 1 = tubes
 cudaError_t launch_synth(void *d_out, int kind, uint32_t seed, int w, int h, int d, int dtype, cudaStream_t stream);

@@ -7,6 +7,8 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "raymarch_core.h"
 #include "raymarch_launch.h"
 
@@ -299,6 +301,45 @@ cudaError_t launch_hg_lut(float *d_out, uint32_t n, float g, cudaStream_t stream
   if (blocks < 1) blocks = 1;
   k_hg_lut<<<(unsigned)blocks, 256, 0, stream>>>(d_out, n, g);
   return cudaGetLastError();
+}
+
+// ---- the same LUT without any allocation (vr_henyey_greenstein_static) ----------------------------
+// Scratch for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it): the n^3 device buffer of vr_henyey_greenstein lives in this file-scope array instead, 64^3 floats = 1 MiB, held by
+// every GPU that loads the library until the process exits.  In HOST code the name `g_hg_scratch` is only a stand-in for the
+// symbol, not a device address: a kernel handed it would fault (or, where the GPU can reach host memory, silently use the
+// wrong memory).  The address comes from cudaGetSymbolAddress, once per device with that device current.
+// Every call shares the array and it keeps the last call's contents; k_hg_lut writes every one of the n^3 elements the call
+// then reads, so nothing has to be cleared.  Calls that overlap on the GPU (two streams, two host threads) race on it.
+static __device__ __align__(256) float g_hg_scratch[HG_STATIC_MAX_N * HG_STATIC_MAX_N * HG_STATIC_MAX_N];
+
+namespace {
+enum { kMaxDevices = 64 };
+std::mutex g_hg_scratch_mutex;
+float *g_hg_scratch_addr[kMaxDevices];  // per device: the array's DEVICE address, resolved on first use
+}  // namespace
+
+cudaError_t launch_hg_lut_static(uint32_t n, float g, cudaStream_t stream, float **d_lut) {
+  if (!d_lut || n == 0 || n > HG_STATIC_MAX_N) return cudaErrorInvalidValue;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+  float *ptr = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_hg_scratch_mutex);
+    if (!g_hg_scratch_addr[dev]) {  // set-up, once per device, with that device current
+      void *p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_hg_scratch);
+      if (e != cudaSuccess) return e;
+      g_hg_scratch_addr[dev] = static_cast<float *>(p);
+    }
+    ptr = g_hg_scratch_addr[dev];
+  }
+  e = launch_hg_lut(ptr, n, g, stream);  // the kernel gets the device address, never the symbol's host-side name
+  if (e != cudaSuccess) return e;
+  *d_lut = ptr;
+  return cudaSuccess;
 }
 
 // ---- synthetic volumes ------------------------------------------------------------------------
