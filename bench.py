@@ -710,30 +710,27 @@ def run_b200(args):
     # ---- cpu_baseline: the oracle on host copies of the same volumes, bounded sample ----
     if world == 1 and not args.no_cpu_baseline:
         try:
-            one(0)  # frame 0 of the movie through the mex path, for the full-size parity figure
-            frame0 = pageable.reshape((scene.H, scene.W, 3), order="F").copy()
+            # frame 0 of the movie through the mex path in EVERY arithmetic flavour, for the full-size parity matrix
+            one(0)  # (the last render may have been the load-path leg: the counters must be those of this run's own configuration)
             arith_run, fetch_run = int(stats().arithmetic), int(stats().fetch_mode)
-            frame0_exact = None
-            if arith_run != _abi.ARITH_EXACT:  # the same frame once more in the "exact" arithmetic flavour (the one that agrees with the CPU oracle bit for bit)
-                _abi.check(lib.vr_set_option(ctx, _abi.OPT_ARITHMETIC, _abi.ARITH_EXACT), ctx)
+            frames = {}
+            for a_ in (0, 1, 2):
+                _abi.check(lib.vr_set_option(ctx, _abi.OPT_ARITHMETIC, a_), ctx)
                 one(0)
-                frame0_exact = pageable.reshape((scene.H, scene.W, 3), order="F").copy()
-                _abi.check(lib.vr_set_option(ctx, _abi.OPT_ARITHMETIC, arith_run), ctx)
-                one(0)  # (leaves the counters of the run's own flavour behind)
-            line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m, frame0, fetch_run, frame0_exact)
+                frames[a_] = pageable.reshape((scene.H, scene.W, 3), order="F").copy()
+            _abi.check(lib.vr_set_option(ctx, _abi.OPT_ARITHMETIC, arith_run), ctx)
+            one(0)  # (leaves the counters of the run's own flavour behind)
+            line["cpu_baseline"] = cpu_baseline(args, scene, keep, E, Rv, A, G if args.gradient == "lookup" else None, n, m, frames, fetch_run)
             cb = line["cpu_baseline"]
-            par = {}
-            if isinstance(cb.get("reference_cuda"), dict) and cb["reference_cuda"].get("parity"):
-                par["reference_kernel"] = cb["reference_cuda"].pop("parity")
             if "parity" in cb:
-                par["oracle"] = cb.pop("parity")
-            if "parity_exact" in cb:
-                par["oracle_exact_flavour"] = cb.pop("parity_exact")
-            if par:
-                # headline figures: against the reference's own kernel where it ran, else against the CPU oracle
-                head = par.get("reference_kernel") or par.get("oracle")
-                par.update({"max_abs_norm": head.get("max_abs_norm"), "psnr_db": head.get("psnr_db"), "window": head.get("window", "whole frame"),
-                            "arithmetic": int(stats().arithmetic), "against": "reference_kernel" if "reference_kernel" in par else "oracle"})
+                par = cb.pop("parity")
+                names = {0: "exact", 1: "reference", 2: "fast"}
+                mine = par.get("flavours", {}).get(names[arith_run], {})
+                # headline figures: this run's flavour against the reference's own kernel where it ran, else against the CPU oracle
+                head = mine.get("vs_reference_kernel") or mine.get("vs_oracle") or {}
+                par.update({"max_abs_norm": head.get("max_abs_norm"), "psnr_db": head.get("psnr_db"), "frac_within_1e-3": head.get("frac_within_1e-3"),
+                            "window": head.get("window", "whole frame"), "arithmetic": arith_run,
+                            "against": "reference_kernel" if mine.get("vs_reference_kernel") else "oracle", "tolerance": 1e-3})
                 line["parity"] = par
             rcb = line["cpu_baseline"].get("reference_cuda", {})
             if "ms_per_frame" in rcb:  # same frames, same lattice: samples per frame from this run's counters
@@ -842,7 +839,7 @@ def upload_probe(args):
     return out
 
 
-def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mode=1, gpu_frame0_exact=None):
+def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frames=None, fetch_mode=1):
     import torch
 
     need = (5 if G is not None else (1 if scene.aliased else 2)) * 4.0 * n ** 3 / 2 ** 30
@@ -872,47 +869,60 @@ def cpu_baseline(args, scene, keep, E, Rv, A, G, n, m, gpu_frame0=None, fetch_mo
         nsm, sec, threads = cpu.render_window(0, half)
     out = {"value": nsm / sec / 1e9, "unit": "Gsamples/s", "cores": int(threads), "kind": "port",
            "sample": "frame 0, centred %dx%d pixel window of the %dx%d image, %s; %.1f s of CPU time, %d samples; software tex3D by the documented filter formula (the model of the hardware filter is 30 %% slower on a CPU)" % (2 * half, 2 * half, scene.W, scene.H, note, sec, nsm)}
-    # ---- full-size parity: the checker build of the oracle (strict IEEE), filtering the way the product fetched, on a
-    # window of the very frame the GPU rendered (same volumes, same camera); north_star's bar is 1e-3 of the image maximum
-    if gpu_frame0 is not None and not note.startswith("512^3 twin"):
-        try:
-            chk = CpuRender(scene, args, vols, fast=False, filter_bits=9 if fetch_mode == 1 else 0)
-            # centred on the volume's silhouette where rays are long and shaded: cost ~ the timing window's per-pixel cost
-            ph = max(16, min(half, int(half * math.sqrt(8.0 / max(sec, 1e-3)))))
-            t0 = time.perf_counter()
-            chk.render_window(0, ph)
-            x0, x1, y0, y1 = chk.window
-            ref_w = chk.out[y0:y1, x0:x1, :].astype(np.float64)
-            peak = float(chk.out.max()) or 1.0
-            secs = time.perf_counter() - t0
-
-            def diff(frame):
-                d = np.abs(frame[y0:y1, x0:x1, :].astype(np.float64) - ref_w)
-                mse = float(np.mean((d / peak) ** 2))
-                return {"max_abs_norm": float(d.max() / peak), "psnr_db": (float("inf") if mse == 0 else 10.0 * math.log10(1.0 / mse)),
-                        "frac_within_1e-3": float((d.max(axis=2) / peak <= 1e-3).mean()), "window": [x0, x1, y0, y1], "pixels": int((x1 - x0) * (y1 - y0)),
-                        "normalised_by": "maximum of the oracle window (%.6g)" % peak, "tolerance": 1e-3,
-                        "checker": "oracle/liboracle.so (strict IEEE build), %s, frame 0 of this run's movie, %s" % (
-                            "texture filter as measured on the B200 texture unit (ORC_OPT_FILTER_FRAC_BITS = 9)" if fetch_mode == 1 else "fp32 filter weights (documented formula)", note),
-                        "seconds": secs}
-
-            out["parity"] = diff(gpu_frame0)
-            if gpu_frame0_exact is not None:
-                out["parity_exact"] = diff(gpu_frame0_exact)
-        except Exception as ex:
-            out["parity"] = {"failed": repr(ex)[:300]}
+    # ---- full-size parity matrix (north_star's bar: 1e-3 of the image maximum).  Checkers: (i) the reference's OWN kernel on
+    # this GPU (oracle/_ref/libref_cuda.so), the whole frame; (ii) the checker build of the oracle (strict IEEE), filtering the
+    # way the product fetched, on a window of the very frame the GPU rendered.  Every arithmetic flavour against both, and the
+    # two checkers against each other: what the reference's kernel differs from its own restated math by is the floor.
     # north_star: "a baseline from the reference's CUDA kernel rebuilt standalone via nvcc is added where it builds" -
     # oracle/_ref/libref_cuda.so = the reference's own d_render + upload code on texture objects (oracle/ref_cuda)
+    ref_frame = None
     try:
         if note.startswith("512^3 twin"):
             raise RuntimeError("host memory too small for copies of the full volumes")
-        out["reference_cuda"] = reference_cuda_baseline(cpu, scene, vols, gpu_frame0)
+        out["reference_cuda"], ref_frame = reference_cuda_baseline(cpu, scene, vols)
     except Exception as ex:
         out["reference_cuda"] = {"unavailable": repr(ex)}
+    if gpu_frames and not note.startswith("512^3 twin"):
+        try:
+            def metrics(a, b, peak, extra):
+                d = np.abs(a.astype(np.float64) - b.astype(np.float64)) / peak
+                mse = float(np.mean(d ** 2))
+                worst = d.max(axis=2)
+                m_ = {"max_abs_norm": float(d.max()), "psnr_db": (float("inf") if mse == 0 else 10.0 * math.log10(1.0 / mse)),
+                      "frac_within_1e-3": float((worst <= 1e-3).mean()), "pixels_beyond_1e-3": int((worst > 1e-3).sum()), "pixels": int(worst.size)}
+                m_.update(extra)
+                return m_
+
+            chk = CpuRender(scene, args, vols, fast=False, filter_bits=9 if fetch_mode == 1 else 0)
+            ph = max(16, min(half, int(half * math.sqrt(8.0 / max(sec, 1e-3)))))
+            t0 = time.perf_counter()
+            chk.render_window(0, ph)
+            secs = time.perf_counter() - t0
+            x0, x1, y0, y1 = chk.window
+            win = (slice(y0, y1), slice(x0, x1), slice(None))
+            orc_w = chk.out[win]
+            peak_o = float(chk.out.max()) or 1.0
+            names = {0: "exact", 1: "reference", 2: "fast"}
+            par = {"flavours": {}, "tolerance": 1e-3,
+                   "checkers": {"oracle": "oracle/liboracle.so (strict IEEE build), %s, frame 0 of this run's movie, %s; window [x0,x1,y0,y1] = %s, normalised by the window's maximum %.6g, %.1f s"
+                                          % ("texture filter as measured on the B200 texture unit (ORC_OPT_FILTER_FRAC_BITS = 9)" if fetch_mode == 1 else "fp32 filter weights (documented formula)",
+                                             note, [x0, x1, y0, y1], peak_o, secs),
+                                "reference_kernel": "the reference's own d_render (oracle/_ref/libref_cuda.so: volumeRender_kernel.cu on texture objects), same volumes and camera, whole frame, normalised by its maximum"}}
+            peak_r = (float(ref_frame.max()) or 1.0) if ref_frame is not None else None
+            for a_, fr in sorted(gpu_frames.items()):
+                e_ = {"vs_oracle": metrics(fr[win], orc_w, peak_o, {"window": [x0, x1, y0, y1]})}
+                if ref_frame is not None:
+                    e_["vs_reference_kernel"] = metrics(fr, ref_frame, peak_r, {"window": "whole frame"})
+                par["flavours"][names[a_]] = e_
+            if ref_frame is not None:
+                par["reference_kernel_vs_oracle"] = metrics(ref_frame[win], orc_w, peak_o, {"window": [x0, x1, y0, y1]})
+            out["parity"] = par
+        except Exception as ex:
+            out["parity"] = {"failed": repr(ex)[:300]}
     return out
 
 
-def reference_cuda_baseline(cpu, scene, vols, gpu_frame0=None):
+def reference_cuda_baseline(cpu, scene, vols):
     """Whole frames of the same scene through the reference's own vr::render (cudaMalloc + memset + d_render +
     sync + D2H, volumeRender.cpp:233-300) on this GPU; uploads (cudaMemcpy3D from pageable memory) not timed."""
     rc = cpu.vrt.ref_cuda()
@@ -926,7 +936,7 @@ def reference_cuda_baseline(cpu, scene, vols, gpu_frame0=None):
     n = len(scene.lights)
     out = np.zeros((scene.H, scene.W, 3), dtype=np.float32, order="F")
     times = []
-    parity = None
+    frame0 = None
     for k in range(9):  # one warm-up + 8 timed frames, median
         rot = scene.rot(k)
         t = time.perf_counter()
@@ -934,20 +944,12 @@ def reference_cuda_baseline(cpu, scene, vols, gpu_frame0=None):
                                  scene.res.ctypes.data_as(C.POINTER(C.c_uint64)), f32p(rot), f32p(scene.props), C.c_float(scene.thr), f32p(scene.color),
                                  out.ctypes.data) == 0
         times.append(time.perf_counter() - t)
-        if k == 0 and gpu_frame0 is not None:
-            # frame 0 of the movie: this library's image against the reference kernel's own, the WHOLE 2048^2 frame
-            peak = float(out.max()) or 1.0
-            d = np.abs(gpu_frame0.astype(np.float64) - out.astype(np.float64)) / peak
-            mse = float(np.mean(d ** 2))
-            parity = {"max_abs_norm": float(d.max()), "psnr_db": float("inf") if mse == 0 else 10.0 * math.log10(1.0 / mse),
-                      "frac_within_1e-3": float((d.max(axis=2) <= 1e-3).mean()), "pixels": int(out.shape[0] * out.shape[1]), "tolerance": 1e-3,
-                      "normalised_by": "maximum of the reference kernel's image (%.6g)" % peak,
-                      "checker": "the reference's own d_render (oracle/_ref/libref_cuda.so: volumeRender_kernel.cu on texture objects), same volumes, same camera, whole frame"}
+        if k == 0:
+            frame0 = out.copy()  # frame 0 of the movie as the reference's own kernel renders it
     # the lattice of frame 0 is the one the oracle counted per pixel above; count it for the full frame with the same rule
     return {"kind": "shimmed reference: the reference's d_render/upload code on texture objects, nvcc sm_100a, unmodified launch shape (16x16 blocks)",
             "ms_per_frame": 1e3 * float(np.median(times[1:])), "ms_per_frame_min": 1e3 * min(times[1:]), "ms_per_frame_max": 1e3 * max(times[1:]),
-            "frames": len(times) - 1, "first_frame_ms": 1e3 * times[0], "statistic": "median of %d frames (camera +1 degree each) after one warm-up frame" % (len(times) - 1),
-            "parity": parity}
+            "frames": len(times) - 1, "first_frame_ms": 1e3 * times[0], "statistic": "median of %d frames (camera +1 degree each) after one warm-up frame" % (len(times) - 1)}, frame0
 
 
 def run_example3(args):

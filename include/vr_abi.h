@@ -262,6 +262,10 @@ typedef enum vr_option {
                                    owns are, per image plane, runs of tile_w * H contiguous floats: a rank can copy exactly its own
                                    pixels to the host (vr_render*, vr_render_batch_begin write only owned pixels of the host image
                                    when nranks > 1), so the read-back of a frame is spread over the PCIe links of all GPUs */
+  VR_OPT_TEXTURE_SINGLE_COPY = 17, /* 1 (default): in texture-unit mode a volume is resident ONCE - when its cudaArray and the empty-space
+                                   grids stand, the padded brick storage they were built from is freed (4 instead of 8 GiB per 1024^3 fp32
+                                   volume) and rebuilt from the array only when something needs it: vr_update_box (such a volume keeps
+                                   both copies from then on), a switch to the load path, new skip grids.  0: keep both copies */
   VR_OPT_COUNT_
 } vr_option;
 /* Default: 2.  Measured on a B200 against the reference kernel's OWN images (tests/golden/refcuda_*.npy, seven scenes): flavours 1

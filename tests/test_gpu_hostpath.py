@@ -175,3 +175,75 @@ def test_plain_c_harness_equals_the_python_mirror(tmp_path, lut, flags, lights, 
     assert np.array_equal(img, want), np.abs(img - want).max()
     kernel_samples = int(p.stdout.split("samples marched")[0].split(",")[-1])
     assert kernel_samples == r.stats()["samples_marched"]
+
+
+def test_texture_unit_mode_keeps_one_copy_per_volume(lut):
+    """VR_OPT_TEXTURE_SINGLE_COPY (default on): once a texture-unit render has its cudaArrays and skip grids, the padded brick
+    storages they were built from are freed - bytes_resident ~ 1x the voxels, not 2x - and everything that needs a storage
+    again (the load path, vr_update_box, new skip grids) gets the bits an upload would have written."""
+    import torch
+
+    n = 128
+    E = vrt.synth_brain((n, n, n))
+    g = [np.asarray(v.Data) for v in api.Volume(E).grad()]
+    keep = []
+
+    def on_device(a):
+        t = torch.from_numpy(np.ascontiguousarray(a.reshape(-1, order="F"))).cuda()
+        keep.append(t)
+        return api.DeviceVolume(t.data_ptr(), a.shape, _abi.DTYPE_F32, _abi.MEM_DEVICE, keepalive=t)
+
+    def scene(single_copy=1, texture_unit=2):
+        r = vrt.example1_scene(api.VolumeRender, on_device(E), (160, 128), lights=2, lut=lut)  # device sources: no staging buffers
+        r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = [on_device(x) for x in g]
+        r.setOption(_abi.OPT_TEXTURE_SINGLE_COPY, single_copy)
+        r.setOption(_abi.OPT_TEXTURE_UNIT, texture_unit)
+        return r
+
+    voxels = 4 * n ** 3 * 4  # E, Gx, Gy, Gz
+    one, two = scene(1), scene(0)
+    img = one.render()
+    assert np.array_equal(two.render(), img)
+    b1, b2 = one.stats()["bytes_resident"], two.stats()["bytes_resident"]
+    print("resident bytes / voxel bytes: single copy %.3f, both copies %.3f" % (b1 / voxels, b2 / voxels))
+    assert b1 < 1.15 * voxels and b2 > 2.2 * voxels  # (both copies: the interleaved gradient storage is 4 elements per voxel)
+    assert one.stats()["fetch_mode"] == 1
+    # frames after the first change nothing (nothing left to drop, nothing rebuilt)
+    one.rotate(0, 10, 0), two.rotate(0, 10, 0)
+    assert np.array_equal(one.render(), two.render()) and one.stats()["bytes_resident"] == b1
+    # the load path needs the storages: rebuilt from the arrays, same bits as a context that never dropped them
+    loads = scene(1, texture_unit=0)
+    loads.rotate(0, 10, 0)
+    want_loads = loads.render()
+    one.setOption(_abi.OPT_TEXTURE_UNIT, 0)
+    assert np.array_equal(one.render(), want_loads) and one.stats()["fetch_mode"] == 0
+    assert one.stats()["bytes_resident"] > 2.2 * voxels
+    # ... and back: dropped again
+    one.setOption(_abi.OPT_TEXTURE_UNIT, 2)
+    assert np.array_equal(one.render(), two.render()) and one.stats()["bytes_resident"] == b1
+    # the skip grids are dropped by a partial update and rebuilt from a storage that was itself rebuilt from the array
+    for r in (one, two):
+        r.updateVolumeBox("emission", (0, 0, 0), (n, n, 8))  # same data: the image must not change
+    assert np.array_equal(one.render(), two.render())
+    assert one.stats()["bytes_resident"] > b1  # a volume that is updated in place keeps both copies from now on
+
+
+def test_plain_c_harness_on_several_gpus_equals_one_gpu(tmp_path):
+    """harness/vrbench --gpus G: vr_set_devices behind the same 'render' call, driven from plain C (no torch, no MPI)."""
+    import torch
+
+    g = torch.cuda.device_count()
+    if g < 2:
+        pytest.skip("one GPU visible (tests/test_gpu_group.py covers device groups whose members share a GPU)")
+    exe = os.path.join(ROOT, "harness", "vrbench")
+    imgs = []
+    for gpus in (1, g):
+        out = str(tmp_path / ("frame_%d.pfm" % gpus))
+        p = subprocess.run([exe, "--size", "96", "--image", "200", "120", "--frames", "2", "--grad", "--lights", "2", "--gpus", str(gpus), "--out", out],
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+        print(p.stdout)
+        assert p.returncode == 0, p.stdout
+        imgs.append(_read_pfm(out))
+        if gpus > 1:
+            assert "device group: %d members" % gpus in p.stdout and "peer access yes" in p.stdout
+    assert np.array_equal(imgs[0], imgs[1])

@@ -150,3 +150,55 @@ def test_volume_space_one_brick_per_gpu(tmp_path):
         m = vrt.compare(z[k], z["full"])
         print(k, m)
         assert m["max_abs_norm"] < 2e-5, (k, m)
+
+
+def _e2e_worker(rank, world, port, out_path):
+    """bench.py's end-to-end leg in small: every rank renders its tile COLUMNS of a movie in pipelined batches and its device
+    copies exactly those pixels into frames that live in ONE host buffer shared by the ranks (POSIX shared memory, page-locked
+    in every process)."""
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dev = rank % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    vol = vrt.synth_brain((48, 48, 48))
+    lut = vrt.oracle_lut(64)
+    r = api.VolumeRender()
+    r = vrt.example1_scene(lambda: r, vol, RES, lights=2, lut=lut)
+    frames = multigpu.SharedHostFrames(RES[1], RES[0], 5, rank, world)
+    for i in range(5):
+        if rank == 0:
+            frames.array(i)[...] = 7.0  # poisoned: every pixel must be written by exactly one rank
+    dist.barrier()
+    multigpu.configure_partition(r.objectHandle, rank, world, 32, 32, mode=1)
+    rots = []
+    for _ in range(5):
+        r.rotate(0, 13, 0)
+        rots.append(r.RotationMatrix.copy())
+    r.renderMoviePipelined(rots, batch=2, out=[frames.array(i) for i in range(5)])
+    dist.barrier()  # every rank's columns have landed
+    if rank == 0:
+        np.save(out_path, np.stack([np.array(frames.array(i)) for i in range(5)]))
+    frames.close(world)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_ranks_copy_their_own_columns_into_shared_host_frames(tmp_path, world):
+    import torch.multiprocessing as mp
+
+    vol = vrt.synth_brain((48, 48, 48))
+    single = _scene(vol, vrt.oracle_lut(64))
+    single.LightSources = [api.LightSource([500, 1000, 550], [0, 1, 1]), api.LightSource([550, 1000, 500], [1, 0, 1])]
+    want = []
+    for _ in range(5):
+        single.rotate(0, 13, 0)
+        want.append(single.render())
+    out = str(tmp_path / "frames.npy")
+    mp.spawn(_e2e_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    got = np.load(out)
+    for k in range(5):
+        assert np.array_equal(got[k], want[k]), (k, np.abs(got[k] - want[k]).max())

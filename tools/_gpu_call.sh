@@ -1,24 +1,22 @@
 set -x
 cd $GRAFT_REPO_ROOT
-python -m pytest tests -m gpu -q -x > gpurun_out/r2d_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2d_pytest.log
-tail -15 gpurun_out/r2d_pytest.log
-python bench.py --steps 20 --warmup 5 > gpurun_out/r2d_bench.json 2> gpurun_out/r2d_bench.err; echo "bench rc=$?"; tail -5 gpurun_out/r2d_bench.err
-Q="--steps 20 --warmup 5 --no-cpu-baseline --no-upload-probe --no-gather-probe --no-load-leg"
-for v in spec pairs specpairs; do
-VR_B200_LIB=$PWD/volume_renderer_b200/csrc/ab/libvr_b200_$v.so python bench.py $Q > gpurun_out/r2d_ab_${v}_l.json 2> gpurun_out/r2d_ab_${v}_l.err
-done
-VR_B200_LIB=$PWD/volume_renderer_b200/csrc/ab/libvr_b200_pairs.so python bench.py $Q --gradient compute --lights 2 > gpurun_out/r2d_ab_pairs_c2.json 2> gpurun_out/r2d_ab_pairs_c2.err
-python bench.py $Q --gradient compute --lights 2 > gpurun_out/r2d_ab_base_c2.json 2> gpurun_out/r2d_ab_base_c2.err
-for w in 2 4; do python bench.py $Q --wshape $w > gpurun_out/r2d_ab_wshape${w}_l.json 2> gpurun_out/r2d_ab_wshape${w}_l.err; done
-python bench.py --config example1 --steps 20 --warmup 5 --no-upload-probe --no-load-leg --cpu-seconds 8 > gpurun_out/r2d_cfg_example1.json 2> gpurun_out/r2d_cfg_example1.err; echo "ex1 rc=$?"
-python bench.py --config example2 --warmup 5 --no-upload-probe --no-load-leg --no-cpu-baseline > gpurun_out/r2d_cfg_example2.json 2> gpurun_out/r2d_cfg_example2.err; echo "ex2 rc=$?"
-python bench.py --config example3 --steps 8 --warmup 2 > gpurun_out/r2d_cfg_example3.json 2> gpurun_out/r2d_cfg_example3.err; echo "ex3 rc=$?"; tail -3 gpurun_out/r2d_cfg_example3.err
+mkdir -p gpurun_out
+nvidia-smi -L
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511"
+timeout 600 python -m pytest tests -m gpu -q > gpurun_out/r2i_pytest_2gpu.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/r2i_pytest_2gpu.log
+timeout 400 $TR bench.py --gpus 2 --steps 20 --warmup 5 > gpurun_out/r2i_bench_n2.json 2> gpurun_out/r2i_bench_n2.err; echo "bench n2 rc=$?"; tail -5 gpurun_out/r2i_bench_n2.err
+timeout 400 $TR bench.py --gpus 2 --mode volume --size 1024 --dtype f32 --steps 6 --warmup 2 --no-cpu-baseline > gpurun_out/r2i_vol_n2_f32.json 2> gpurun_out/r2i_vol_n2_f32.err; echo "vol f32 rc=$?"; tail -5 gpurun_out/r2i_vol_n2_f32.err
+timeout 600 $TR bench.py --gpus 2 --mode volume --size 2048 --dtype bf16 --steps 6 --warmup 2 --no-cpu-baseline > gpurun_out/r2i_vol_n2_bf16.json 2> gpurun_out/r2i_vol_n2_bf16.err; echo "vol bf16 rc=$?"; tail -5 gpurun_out/r2i_vol_n2_bf16.err
+timeout 300 ./harness/vrbench --gpus 2 --size 512 --image 2048 2048 --frames 6 --grad --lights 2 > gpurun_out/r2i_vrbench_g2.log 2>&1; echo "vrbench g2 rc=$?"; grep -E "frame|total|group" gpurun_out/r2i_vrbench_g2.log | tail -9
+timeout 300 ./harness/vrbench --gpus 1 --size 512 --image 2048 2048 --frames 6 --grad --lights 2 > gpurun_out/r2i_vrbench_g1.log 2>&1; grep -E "total" gpurun_out/r2i_vrbench_g1.log
+timeout 500 $TR bench.py --impl reference --gpus 2 --steps 2 --warmup 1 > gpurun_out/r2i_ref_n2.json 2> gpurun_out/r2i_ref_n2.err; echo "ref n2 rc=$?"
 python - <<'PY'
-import json,glob
-for f in sorted(glob.glob("gpurun_out/r2d_*.json")):
+import json
+for f in ("r2i_bench_n2","r2i_vol_n2_f32","r2i_vol_n2_bf16","r2i_ref_n2"):
     try:
-        d=json.load(open(f))
-        print(f, "ms/frame %.3f value %.1f shaded %.2f e2e %.1f" % (d["ms_per_step"], d["value"], d["gsamples_shaded_per_s"], d["e2e"]["value"]), d.get("parity",{}).get("max_abs_norm"))
+        d=json.load(open("gpurun_out/%s.json"%f))
+        print(f, "ms/step %.3f value %.2f e2e %.2f" % (d["ms_per_step"], d["value"], d["e2e"]["value"]), d.get("phase_ms_per_frame_max_over_ranks"), d.get("cpu_baseline",{}).get("cores"))
+        if d.get("per_rank"): print("   ", d["per_rank"])
     except Exception as ex:
-        print(f, "failed", ex)
+        print(f, "failed", repr(ex))
 PY

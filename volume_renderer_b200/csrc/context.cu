@@ -93,6 +93,10 @@ struct Resident {
   cudaTextureObject_t texobj = 0;
   size_t array_bytes = 0;
   bool array_valid = false;
+  // texture-unit mode keeps ONE copy: once the array and the empty-space grids exist the padded storage is freed
+  // (drop_storage) and rebuilt from the array only when something needs it (restore_storage); a volume that receives
+  // partial updates keeps both copies
+  bool keep_storage = false;
 };
 
 // geometry of the interleaved gradient storage: a gradient volume joins it when it matches
@@ -268,6 +272,7 @@ void geometry(int layout, uint64_t pw, uint64_t ph, uint64_t pd, uint32_t *sy, u
 }
 
 TexDesc describe(const Resident &r);
+vr_status restore_storage(vr_ctx *c, Resident &r, cudaStream_t stream);
 
 
 // memcpy with a few threads: one core copies ~10 GB/s, the PCIe 5 link takes 50
@@ -366,6 +371,7 @@ vr_status fill_resident(vr_ctx *c, Resident &r, const HostVol &v, const int box[
   uint32_t sy, sz;
   geometry(r.layout, (uint64_t)r.lw, (uint64_t)r.lh, (uint64_t)r.ld, &sy, &sz, &elems, &layers, &layer_elems);
   RepackArgs a;
+  a.src_surface = 0;
   a.dst = r.storage;
   a.w = r.w, a.h = r.h, a.d = r.d;
   a.lw = r.lw, a.lh = r.lh, a.ld = r.ld;
@@ -541,6 +547,7 @@ vr_status upload(vr_ctx *c, int slot, const HostVol &v) {
 // the bricks, a pass over the cells, three passes of the distance transform.
 vr_status ensure_skip_grids(vr_ctx *c, Resident &r, cudaStream_t stream) {
   if (r.kind != TEX_VOLUME || (r.occ && r.dist)) return VR_OK;
+  VR_TRY(restore_storage(c, r, stream));  // the grids are built from the padded storage
   r.ocx = (r.w + 7) / 8, r.ocy = (r.h + 7) / 8, r.ocz = (r.d + 7) / 8;
   const uint64_t ncell = (uint64_t)r.ocx * r.ocy * r.ocz;
   r.occ_bytes = (size_t)((ncell + 31) / 32) * 4;
@@ -601,6 +608,78 @@ vr_status ensure_array(vr_ctx *c, Resident &r, cudaStream_t stream) {
   cudaDestroySurfaceObject(surf);
   VR_CUDA(c, e);
   r.array_valid = true;
+  return VR_OK;
+}
+
+// ---- one copy per volume in texture-unit mode ----------------------------------------------------------------
+// The padded storage feeds the skip grids, the array fill, partial updates and the load kernels - none of which a
+// texture-unit render needs once the array and the grids stand.  Dropping it halves the resident bytes of the default mode
+// (8 -> 4 GiB per 1024^3 fp32 volume), so a scene that fits once into the 180 GB stays on the fast path.
+void drop_storage(vr_ctx *c, Resident &r) {
+  if (r.kind != TEX_VOLUME || !r.storage || !r.array_valid || r.keep_storage) return;
+  if (r.shared) {
+    // the interleaved gradient storage goes when all of its components have their arrays
+    for (int s = S_DX; s <= S_DZ; ++s) {
+      const Resident &q = c->tex[s];
+      if (q.shared && q.storage && (!q.array_valid || q.keep_storage)) return;
+    }
+    cudaFree(c->g4);
+    c->g4 = nullptr, c->g4_bytes = 0;
+    for (int s = S_DX; s <= S_DZ; ++s)
+      if (c->tex[s].shared) c->tex[s].storage = nullptr;
+    return;
+  }
+  cudaFree(r.storage);
+  r.storage = nullptr, r.storage_bytes = 0;
+}
+// Rebuilds a dropped storage from the volume's array: the very repack of an upload, its source read through a surface,
+// so the storage holds the bits an upload would have written.
+vr_status restore_storage(vr_ctx *c, Resident &r, cudaStream_t stream) {
+  if (r.kind != TEX_VOLUME || r.storage) return VR_OK;
+  if (!r.array || !r.array_valid) return fail(c, VR_ERR_CUDA, "internal: a volume has neither storage nor a valid array");
+  uint64_t elems, layers, layer_elems;
+  uint32_t sy, sz;
+  geometry(r.layout, (uint64_t)r.lw, (uint64_t)r.lh, (uint64_t)r.ld, &sy, &sz, &elems, &layers, &layer_elems);
+  const size_t es = elem_size(r.dtype);
+  if (r.shared) {
+    G4Geo geo;
+    geo.w = r.w, geo.h = r.h, geo.d = r.d, geo.lw = r.lw, geo.lh = r.lh, geo.ld = r.ld, geo.ox = r.ox, geo.oy = r.oy, geo.oz = r.oz;
+    geo.dtype = r.dtype, geo.layout = r.layout, geo.sy = sy, geo.sz = sz;
+    if (!c->g4) {
+      VR_CUDA(c, cudaMalloc(&c->g4, elems * es * 4));
+      VR_CUDA(c, cudaMemsetAsync(c->g4, 0, elems * es * 4, stream));
+      c->g4_bytes = elems * es * 4;
+      c->g4geo = geo;
+    }
+    if (c->g4geo == geo) {
+      r.storage = c->g4;
+    } else {  // the interleaved storage was re-made for another geometry meanwhile: this component lives on its own from now on
+      r.shared = false, r.estride = 1, r.ecomp = 0;
+      c->g4_users--;
+    }
+  }
+  if (!r.shared) {
+    VR_CUDA(c, cudaMalloc(&r.storage, elems * es));
+    r.storage_bytes = elems * es;
+  }
+  cudaResourceDesc rd = {};
+  rd.resType = cudaResourceTypeArray;
+  rd.res.array.array = r.array;
+  cudaSurfaceObject_t surf = 0;
+  VR_CUDA(c, cudaCreateSurfaceObject(&surf, &rd));
+  RepackArgs a;
+  a.dst = r.storage, a.src = nullptr, a.src_surface = (unsigned long long)surf;
+  a.w = r.w, a.h = r.h, a.d = r.d, a.lw = r.lw, a.lh = r.lh, a.ld = r.ld;
+  a.gx0 = r.ox - 1, a.gy0 = r.oy - 1, a.gz0 = r.oz - 1;
+  a.sx0 = 0, a.sy0 = 0, a.sw = r.w, a.sh = r.h, a.src_z0 = 0;
+  a.o0 = 0, a.o1 = elems;
+  a.sy = sy, a.sz = sz, a.estride = r.estride, a.ecomp = r.ecomp;
+  a.box[0] = a.box[1] = a.box[2] = 0, a.box[3] = r.w, a.box[4] = r.h, a.box[5] = r.d;
+  a.layout = r.layout, a.src_dtype = a.dst_dtype = r.dtype;
+  cudaError_t e = launch_repack(a, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);  // the kernel holds the surface handle by value
+  cudaDestroySurfaceObject(surf);
+  VR_CUDA(c, e);
   return VR_OK;
 }
 
@@ -869,11 +948,18 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
         if (tu == 1) return st;
         cudaGetLastError();  // auto: no room for the second copy -> loads, until the volumes change
         c->texhw_failed = true, texhw = false;
-        for (int s2 : need) drop_array(c->tex[s2]);
+        for (int s2 : need)
+          if (c->tex[s2].storage || c->tex[s2].kind != TEX_VOLUME) drop_array(c->tex[s2]);  // (an array that is the ONLY copy stays)
         break;
       }
     }
   }
+  // the load kernels read the padded storage: bring back what an earlier texture-unit render dropped
+  if (!texhw) {
+    const int need[] = {sEm, sAb, sRe, S_EM, S_DX, S_DY, S_DZ, S_LIGHT};
+    for (int sl : need) VR_TRY(restore_storage(c, c->tex[sl], stream));
+  }
+  if (c->opt[VR_OPT_EMPTY_SPACE_SKIP]) VR_TRY(ensure_skip_grids(c, c->tex[sAb], stream));  // (restores that storage if it must)
   P.em = describe(c->tex[sEm]);
   P.ab = describe(c->tex[sAb]);
   P.re = describe(c->tex[sRe]);
@@ -899,7 +985,6 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   }
   if (dtype < 0) dtype = VR_DTYPE_F32, layout = LAYOUT_LINEAR;
   Resident &rab = c->tex[sAb];
-  if (c->opt[VR_OPT_EMPTY_SPACE_SKIP]) VR_TRY(ensure_skip_grids(c, rab, stream));
   P.skip = (rab.kind == TEX_VOLUME && rab.occ && rab.dist) ? (int)c->opt[VR_OPT_EMPTY_SPACE_SKIP] : 0;
   P.occ = rab.occ, P.dist = rab.dist, P.ocx = rab.ocx, P.ocy = rab.ocy, P.ocz = rab.ocz;
   if (P.skip) {
@@ -1160,6 +1245,12 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
   VR_CUDA(c, cudaMemsetAsync(S.d_stats, 0, 3 * sizeof(unsigned long long), stream));
   VR_CUDA(c, cudaEventRecord(S.ev0, stream));
+  if (texhw && c->opt[VR_OPT_TEXTURE_SINGLE_COPY]) {
+    // texture-unit launches read arrays and grids only: the padded storages go (cudaFree waits for the grid builds that
+    // still read them; this happens on the first frame after an upload only)
+    const int need[] = {sEm, sAb, sRe, S_EM, S_DX, S_DY, S_DZ, S_LIGHT};
+    for (int sl : need) drop_storage(c, c->tex[sl]);
+  }
   const int arith = (int)c->opt[VR_OPT_ARITHMETIC];
   if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, stream, c->sm_count, arith));
   c->stats.arithmetic = (uint32_t)arith;
@@ -1243,6 +1334,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   c->opt[VR_OPT_TEXTURE_UNIT] = 2;
   // without touching the MATLAB classes: VR_TEXTURE_UNIT=0 (loads + fp32 lerps) / 1 / 2 in the environment of the MATLAB process
   if (const char *tu = getenv("VR_TEXTURE_UNIT")) c->opt[VR_OPT_TEXTURE_UNIT] = atoi(tu) < 0 ? 0 : (atoi(tu) > 2 ? 2 : atoi(tu));
+  c->opt[VR_OPT_TEXTURE_SINGLE_COPY] = 1;
   c->opt[VR_OPT_ARITHMETIC] = VR_DEFAULT_ARITHMETIC;
   if (const char *ar = getenv("VR_ARITHMETIC")) c->opt[VR_OPT_ARITHMETIC] = atoi(ar) < 0 ? 0 : (atoi(ar) > 2 ? 2 : atoi(ar));
   cudaError_t ce = cudaSetDevice(device);
@@ -1642,6 +1734,8 @@ vr_status vr_update_box(vr_ctx *c, int role, const vr_volume *vol, const uint64_
     box[i] = (int)lo[i], box[3 + i] = (int)hi[i];
   }
   c->stats.bytes_uploaded = 0;
+  VR_TRY(restore_storage(c, r, c->stream));  // (dropped by a texture-unit render: rebuilt from the array once)
+  r.keep_storage = true;                     // a volume that is updated in place keeps both copies from now on
   VR_CUDA(c, cudaEventRecord(c->evu0, c->stream));
   VR_TRY(fill_resident(c, r, v, box));
   // what the slot now holds: the caller's volume at its new timestamp (the next sync must not upload it again)

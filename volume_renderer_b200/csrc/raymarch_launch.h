@@ -46,6 +46,8 @@ struct RepackArgs {
   int layout;          // LAYOUT_*
   int src_dtype;       // vr_dtype of src
   int dst_dtype;       // vr_dtype of dst
+  unsigned long long src_surface;  // != 0: the source is the volume's own w x h x d fp32 cudaArray (a surface object) instead of
+                                   // `src` - rebuilds a padded storage that was dropped in texture-unit mode (context.cu)
 };
 cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream);
 

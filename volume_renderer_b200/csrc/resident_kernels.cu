@@ -57,7 +57,8 @@ __global__ void __launch_bounds__(256) k_repack(const RepackArgs a) {
       const int sy = min(max(Y + a.gy0, 0), a.h - 1);
       const int sz = min(max(Z + a.gz0, 0), a.d - 1);
       if (sx < a.box[0] || sx >= a.box[3] || sy < a.box[1] || sy >= a.box[4] || sz < a.box[2] || sz >= a.box[5]) continue;  // not part of this update
-      v = load_src(a.src, ((size_t)(sz - a.src_z0) * a.sh + (sy - a.sy0)) * a.sw + (sx - a.sx0), a.src_dtype);
+      if (a.src_surface) v = surf3Dread<float>((cudaSurfaceObject_t)a.src_surface, sx * (int)sizeof(float), sy, sz);
+      else v = load_src(a.src, ((size_t)(sz - a.src_z0) * a.sh + (sy - a.sy0)) * a.sw + (sx - a.sx0), a.src_dtype);
     } else if (a.box[0] > 0 || a.box[1] > 0 || a.box[2] > 0 || a.box[3] < a.w || a.box[4] < a.h || a.box[5] < a.d) {
       continue;  // brick filler beyond the padded extent: written once by the full upload
     }
