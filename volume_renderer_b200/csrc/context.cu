@@ -93,6 +93,7 @@ struct Resident {
   cudaTextureObject_t texobj = 0;
   size_t array_bytes = 0;
   bool array_valid = false;
+  int a0[3] = {0, 0, 0}, an[3] = {0, 0, 0};  // the voxel box [a0, a0 + an) the array holds: the resident box clipped to the volume
   // texture-unit mode keeps ONE copy: once the array and the empty-space grids exist the padded storage is freed
   // (drop_storage) and rebuilt from the array only when something needs it (restore_storage); a volume that receives
   // partial updates keeps both copies
@@ -567,26 +568,37 @@ vr_status ensure_skip_grids(vr_ctx *c, Resident &r, cudaStream_t stream) {
 // Texture-unit mode: the volume as a cudaArray behind a texture object with the reference's settings
 // (createTextureFromVolume, kernel.cu:522-554: normalized coordinates, linear filter, clamp, element type), filled from
 // the resident padded storage - one path whatever the source was (host, device, partial update, interleaved component).
+// The voxel box a context holds of a volume: everything for a whole volume, the owned region plus halo clipped to the
+// volume for a region context (vr_set_region).
+void array_box(const Resident &r, int a0[3], int an[3]) {
+  const int g0[3] = {r.ox - 1, r.oy - 1, r.oz - 1}, lext[3] = {r.lw, r.lh, r.ld}, dims[3] = {r.w, r.h, r.d};
+  for (int i = 0; i < 3; ++i) {
+    a0[i] = g0[i] < 0 ? 0 : g0[i];
+    const int hi = g0[i] + lext[i] > dims[i] ? dims[i] : g0[i] + lext[i];
+    an[i] = hi - a0[i];
+  }
+}
 bool array_eligible(const Resident &r) {
   if (r.kind != TEX_VOLUME) return true;  // constants and unbound slots need no array
-  return r.dtype == VR_DTYPE_F32 && !r.ox && !r.oy && !r.oz && r.lw == r.w + 2 && r.lh == r.h + 2 && r.ld == r.d + 2 && r.w <= 16384 &&
-         r.h <= 16384 && r.d <= 16384;
+  int a0[3], an[3];
+  array_box(r, a0, an);
+  return (r.dtype == VR_DTYPE_F32 || r.dtype == VR_DTYPE_BF16) && an[0] > 0 && an[1] > 0 && an[2] > 0 && an[0] <= 16384 && an[1] <= 16384 && an[2] <= 16384;
 }
 void drop_array(Resident &r) {
   if (r.texobj) cudaDestroyTextureObject(r.texobj);
   if (r.array) cudaFreeArray(r.array);
   r.texobj = 0, r.array = nullptr, r.array_bytes = 0, r.array_valid = false;
 }
+// fp32 arrays whatever the storage type: bf16 voxels widen exactly, and the texture unit has no bf16 element type (a half-float
+// array would round them).  A bf16 volume in texture-unit mode therefore holds 4 bytes per voxel once its storage is dropped.
 vr_status ensure_array(vr_ctx *c, Resident &r, cudaStream_t stream) {
   if (r.kind != TEX_VOLUME || r.array_valid) return VR_OK;
-  if (r.dtype != VR_DTYPE_F32) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode needs fp32 volumes (the filter has no bf16 element type)");
-  if (r.ox || r.oy || r.oz || r.lw != r.w + 2 || r.lh != r.h + 2 || r.ld != r.d + 2)
-    return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode needs whole volumes (no vr_set_region)");
-  if (r.w > 16384 || r.h > 16384 || r.d > 16384) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode: a 3D array holds at most 16384 voxels per axis");
+  if (!array_eligible(r)) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode: a 3D array holds at most 16384 voxels per axis");
   if (!r.array) {
+    array_box(r, r.a0, r.an);
     const cudaChannelFormatDesc cd = cudaCreateChannelDesc<float>();
-    VR_CUDA(c, cudaMalloc3DArray(&r.array, &cd, make_cudaExtent((size_t)r.w, (size_t)r.h, (size_t)r.d), cudaArraySurfaceLoadStore));
-    r.array_bytes = (size_t)r.w * r.h * r.d * sizeof(float);
+    VR_CUDA(c, cudaMalloc3DArray(&r.array, &cd, make_cudaExtent((size_t)r.an[0], (size_t)r.an[1], (size_t)r.an[2]), cudaArraySurfaceLoadStore));
+    r.array_bytes = (size_t)r.an[0] * r.an[1] * r.an[2] * sizeof(float);
     cudaResourceDesc rd = {};
     rd.resType = cudaResourceTypeArray;
     rd.res.array.array = r.array;
@@ -602,7 +614,7 @@ vr_status ensure_array(vr_ctx *c, Resident &r, cudaStream_t stream) {
   rd.res.array.array = r.array;
   cudaSurfaceObject_t surf = 0;
   VR_CUDA(c, cudaCreateSurfaceObject(&surf, &rd));
-  const cudaError_t e = launch_fill_array(describe(r), r.layout, (unsigned long long)surf, stream);
+  const cudaError_t e = launch_fill_array(describe(r), r.layout, r.dtype, r.a0, r.an, (unsigned long long)surf, stream);
   // the kernel has the handle by value; destroying the object after the launch is ordered behind it by the stream sync
   if (e == cudaSuccess) cudaStreamSynchronize(stream);
   cudaDestroySurfaceObject(surf);
@@ -671,7 +683,7 @@ vr_status restore_storage(vr_ctx *c, Resident &r, cudaStream_t stream) {
   a.dst = r.storage, a.src = nullptr, a.src_surface = (unsigned long long)surf;
   a.w = r.w, a.h = r.h, a.d = r.d, a.lw = r.lw, a.lh = r.lh, a.ld = r.ld;
   a.gx0 = r.ox - 1, a.gy0 = r.oy - 1, a.gz0 = r.oz - 1;
-  a.sx0 = 0, a.sy0 = 0, a.sw = r.w, a.sh = r.h, a.src_z0 = 0;
+  a.sx0 = r.a0[0], a.sy0 = r.a0[1], a.src_z0 = r.a0[2], a.sw = r.an[0], a.sh = r.an[1];  // the array's origin in the volume
   a.o0 = 0, a.o1 = elems;
   a.sy = sy, a.sz = sz, a.estride = r.estride, a.ecomp = r.ecomp;
   a.box[0] = a.box[1] = a.box[2] = 0, a.box[3] = r.w, a.box[4] = r.h, a.box[5] = r.d;
@@ -935,8 +947,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   // context can (fp32 whole volumes that fit twice), else loads
   const int64_t tu = c->opt[VR_OPT_TEXTURE_UNIT];
   bool texhw = false;
-  if (tu == 1 && vs) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode is not available for volume-space passes");
-  if (tu && !vs && !(tu == 2 && c->texhw_failed)) {
+  if (tu && !(tu == 2 && c->texhw_failed)) {
     const int need[] = {sEm, sAb, sRe, S_EM, S_DX, S_DY, S_DZ, S_LIGHT};
     bool eligible = true;
     for (int sl : need) eligible = eligible && array_eligible(c->tex[sl]);
@@ -951,6 +962,26 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
         for (int s2 : need)
           if (c->tex[s2].storage || c->tex[s2].kind != TEX_VOLUME) drop_array(c->tex[s2]);  // (an array that is the ONLY copy stays)
         break;
+      }
+      if (texhw && vs) {
+        // a region context's arrays hold its resident box only: one remap for all volume textures, so they must agree on it
+        const Resident *first = nullptr;
+        for (int sl : need) {
+          const Resident &q = c->tex[sl];
+          if (q.kind != TEX_VOLUME || sl == S_LIGHT) continue;
+          if (!first) first = &q;
+          if (memcmp(q.a0, first->a0, sizeof q.a0) || memcmp(q.an, first->an, sizeof q.an) || q.w != first->w || q.h != first->h || q.d != first->d) {
+            if (tu == 1) return fail(c, VR_ERR_UNSUPPORTED, "texture-unit mode: the volumes of a region context must share one resident box");
+            texhw = false;
+          }
+        }
+        if (texhw && first) {
+          const int dims[3] = {first->w, first->h, first->d};
+          for (int i = 0; i < 3; ++i) {
+            P.tex_cs[i] = (float)((double)dims[i] / (double)first->an[i]);
+            P.tex_co[i] = (float)(-(double)first->a0[i] / (double)first->an[i]);
+          }
+        }
       }
     }
   }
@@ -1037,7 +1068,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   if (c->opt[VR_OPT_KERNEL_VARIANT] == 3 && P.uniform == 1 && layout == LAYOUT_BRICK) P.uniform = 2;  // variant 3: force the 64-bit kernels (tests)
   if (P.frac_bits) P.uniform = 0;  // fixed-point weights (A/B option) are compiled into the per-texture kernels only
   if (texhw) {
-    P.uniform = 0, P.frac_bits = 0;  // the hardware filters (1.8 fixed-point weights by construction)
+    P.uniform = vs ? 1 : 0, P.frac_bits = 0;  // the hardware filters (1.8 fixed-point weights by construction); 1 = the region kernels
     layout = LAYOUT_TEXHW;
     P.tex_fast = (P.gx.kind == TEX_VOLUME && P.gy.kind == TEX_VOLUME && P.gz.kind == TEX_VOLUME ? 1 : 0) | (P.re.kind == TEX_VOLUME ? 2 : 0) |
                  (P.em_direct.kind == TEX_VOLUME ? 4 : 0) | (P.em.kind == TEX_VOLUME ? 8 : 0) | (P.lut.kind == TEX_VOLUME ? 16 : 0);
@@ -1773,7 +1804,12 @@ vr_status vr_render_opacity_device(vr_ctx *c, const vr_light *lights, size_t n_l
   float *dummy = d_opacity;  // no image is written in this pass; any non-null pointer passes the argument check
   const int64_t clear = c->opt[VR_OPT_CLEAR_IMAGE];
   c->opt[VR_OPT_CLEAR_IMAGE] = 0;
+  // The opacity pass counts into launch slot 1: the shading pass that follows (slot 0) then finds nothing pending and does not
+  // have to wait for this pass and the exchange behind it before it can be set up (the counters of slot 1 are never read).
+  c->cur = 1;
   const vr_status st = render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &dummy, s, &vs);
+  c->cur = 0;
+  c->slot[1].stats_pending = c->slot[1].timing_pending = false;
   c->opt[VR_OPT_CLEAR_IMAGE] = clear;
   return st;
 }
@@ -1999,6 +2035,9 @@ vr_status vr_get_stats(vr_ctx *c, vr_stats *out) {
   for (vr_ctx *m : group_of(c)) {
     VR_TRY(set_device(m));
     VR_TRY(collect(m));
+    // a synchronisation point by contract: everything the context has enqueued is complete when the counters are returned
+    // (an opacity pass counts into a slot nobody reads, so `collect` alone may find nothing to wait for)
+    VR_CUDA(m, cudaStreamSynchronize(m->stream));
     m->stats.bytes_resident = resident_bytes(m);
   }
   VR_TRY(set_device(c));

@@ -641,8 +641,12 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);  // kernel.cu:396
   const F3 ps = (r.pos - bmin) * bscale;                            // kernel.cu:437
   const int fb = UNI ? 0 : P.frac_bits;
-  // texture-unit launches are never volume-space passes (render_common): their kernels carry no region test
-  const int vs_mode = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW) ? 0 : P.vs_mode;
+  // UNI means "shared tap sets" for the load kernels; for the texture-unit kernels it marks the instantiation for contexts
+  // that own a region (volume-space passes): region test compiled in, coordinates remapped into the region's local arrays
+  constexpr bool TAPS = UNI != 0 && LAYOUT != LAYOUT_TEXHW;
+  constexpr bool TEXVS = UNI != 0 && LAYOUT == LAYOUT_TEXHW;
+  // plain texture-unit launches are never volume-space passes (render_common): their kernels carry no region test
+  const int vs_mode = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW && !TEXVS) ? 0 : P.vs_mode;
   if (vs_mode && !(ps.x >= P.reg_lo[0] && ps.x < P.reg_hi[0] && ps.y >= P.reg_lo[1] && ps.y < P.reg_hi[1] && ps.z >= P.reg_lo[2] &&
                      ps.z < P.reg_hi[2])) {
     r.n_marched++;  // a sample of the global lattice that another brick owns
@@ -657,25 +661,28 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   F3 spec_g = mk3(0.0f, 0.0f, 0.0f);
   float spec_re = 0.0f;
 #endif
-  if (UNI) {
+  // where the volume textures are fetched: the normalized volume coordinate, remapped for a region's local arrays
+  const F3 tcs = TEXVS ? ld3(P.tex_cs) : mk3(1.0f, 1.0f, 1.0f), tco = TEXVS ? ld3(P.tex_co) : mk3(0.0f, 0.0f, 0.0f);
+  const F3 pt = TEXVS ? mk3(fmaf(ps.x, tcs.x, tco.x), fmaf(ps.y, tcs.y, tco.y), fmaf(ps.z, tcs.z, tco.z)) : ps;
+  if (TAPS) {
     // (handing the skip phase's x*N - 0.5 and floors of this position over instead of computing
     // them again costs more in live registers than it saves: measured +2.5 %)
     axis_taps_from<LAYOUT>(P.geo, axis_coord(ps.x, P.geo.fw), axis_coord(ps.y, P.geo.fh), axis_coord(ps.z, P.geo.fd), fb, ax, ay, az);
     em_raw = taps_any<E>(P.em, ax, ay, az);
     ab_raw = P.ab_is_em ? em_raw : taps_any<E>(P.ab, ax, ay, az);
   } else if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 8)) {
-    em_raw = tex_raw(P.em, ps.x, ps.y, ps.z);
+    em_raw = tex_raw(P.em, pt.x, pt.y, pt.z);
 #if VR_TEX_SPECULATE
     if (GRAD == 1 && (P.tex_fast & 3) == 3 && P.n_lights > 0) {
       spec = true;
-      spec_g = mk3(tex_raw(P.gx, ps.x, ps.y, ps.z), tex_raw(P.gy, ps.x, ps.y, ps.z), tex_raw(P.gz, ps.x, ps.y, ps.z));
-      spec_re = P.re_is_em ? em_raw : tex_raw(P.re, ps.x, ps.y, ps.z);
+      spec_g = mk3(tex_raw(P.gx, pt.x, pt.y, pt.z), tex_raw(P.gy, pt.x, pt.y, pt.z), tex_raw(P.gz, pt.x, pt.y, pt.z));
+      spec_re = P.re_is_em ? em_raw : tex_raw(P.re, pt.x, pt.y, pt.z);
     }
 #endif
-    ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, ps.x, ps.y, ps.z, fb);
+    ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, pt.x, pt.y, pt.z, fb);
   } else {
-    em_raw = tex3d_any<LAYOUT, E>(P.em, ps.x, ps.y, ps.z, fb);
-    ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, ps.x, ps.y, ps.z, fb);
+    em_raw = tex3d_any<LAYOUT, E>(P.em, pt.x, pt.y, pt.z, fb);
+    ab_raw = P.ab_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.ab, pt.x, pt.y, pt.z, fb);
   }
 #if VR_EARLY_RE
   // The reflection taps are issued together with the emission taps, before the alpha test: nine of ten samples that
@@ -683,7 +690,7 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   // per sample is traded for a few wasted loads.  Measured: lookupGradient 23.9 -> 23.5 ms, computeGradient 27.5 -> 27.9
   // (hence per family, raymarch_kernel.cu).  Same operations on the same values.
   float re_early = 0.0f;
-  if (UNI && P.n_lights > 0 && !P.re_is_em) re_early = taps_any<E>(P.re, ax, ay, az);
+  if (TAPS && P.n_lights > 0 && !P.re_is_em) re_early = taps_any<E>(P.re, ax, ay, az);
 #endif
   // (the gradient taps issued here as well: 23.5 -> 25.1 ms, eight 16-byte loads in flight spill; the emission and
   // reflection loads all issued before the first lerp: +1.1 %.  Texture-unit launches: reflection + gradient fetches issued
@@ -709,7 +716,7 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
   if (P.n_lights > 0) {
     F3 g;
     float re_raw;
-    if (UNI) {
+    if (TAPS) {
       if (GRAD == 0) {
         // computeGradient: the six taps differ from the sample position in ONE coordinate each
         // ((pos.y + 0 - bmin.y) * bscale.y is ps.y bit for bit), so only that axis is set up anew.
@@ -746,16 +753,22 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
 #endif
       if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && GRAD == 1 && (P.tex_fast & 1)) {
         // straight-line: the three fetches (and the reflection fetch below) share the coordinate registers of ps
-        g = mk3(tex_raw(P.gx, ps.x, ps.y, ps.z), tex_raw(P.gy, ps.x, ps.y, ps.z), tex_raw(P.gz, ps.x, ps.y, ps.z));
+        g = mk3(tex_raw(P.gx, pt.x, pt.y, pt.z), tex_raw(P.gy, pt.x, pt.y, pt.z), tex_raw(P.gz, pt.x, pt.y, pt.z));
       } else if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && GRAD == 0 && (P.tex_fast & 4)) {
         const F3 gs = ld3(P.gstep);
         // the offset taps differ from ps in ONE coordinate each ((pos.y + 0 - bmin.y) * bscale.y is ps.y bit for bit)
         const float xp = (r.pos.x + gs.x - bmin.x) * bscale.x, xm = (r.pos.x - gs.x - bmin.x) * bscale.x;
         const float yp = (r.pos.y + gs.y - bmin.y) * bscale.y, ym = (r.pos.y - gs.y - bmin.y) * bscale.y;
         const float zp = (r.pos.z + gs.z - bmin.z) * bscale.z, zm = (r.pos.z - gs.z - bmin.z) * bscale.z;
+        if (TEXVS) {
+          g.x = tex_raw(P.em_direct, fmaf(xp, tcs.x, tco.x), pt.y, pt.z) - tex_raw(P.em_direct, fmaf(xm, tcs.x, tco.x), pt.y, pt.z);
+          g.y = tex_raw(P.em_direct, pt.x, fmaf(yp, tcs.y, tco.y), pt.z) - tex_raw(P.em_direct, pt.x, fmaf(ym, tcs.y, tco.y), pt.z);
+          g.z = tex_raw(P.em_direct, pt.x, pt.y, fmaf(zp, tcs.z, tco.z)) - tex_raw(P.em_direct, pt.x, pt.y, fmaf(zm, tcs.z, tco.z));
+        } else {
         g.x = tex_raw(P.em_direct, xp, ps.y, ps.z) - tex_raw(P.em_direct, xm, ps.y, ps.z);
         g.y = tex_raw(P.em_direct, ps.x, yp, ps.z) - tex_raw(P.em_direct, ps.x, ym, ps.z);
         g.z = tex_raw(P.em_direct, ps.x, ps.y, zp) - tex_raw(P.em_direct, ps.x, ps.y, zm);
+        }
         g = g * mk3(0.5f, 0.5f, 0.5f);
       } else if (GRAD == 0) {
         const F3 gs = ld3(P.gstep);
@@ -771,8 +784,8 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
         g.z = tex3d_any<LAYOUT, E>(P.em_direct, s1.x, s1.y, s1.z, fb) - tex3d_any<LAYOUT, E>(P.em_direct, s2.x, s2.y, s2.z, fb);
         g = g * mk3(0.5f, 0.5f, 0.5f);
       } else {
-        g = mk3(tex3d_any<LAYOUT, E>(P.gx, ps.x, ps.y, ps.z, fb), tex3d_any<LAYOUT, E>(P.gy, ps.x, ps.y, ps.z, fb),
-                tex3d_any<LAYOUT, E>(P.gz, ps.x, ps.y, ps.z, fb));
+        g = mk3(tex3d_any<LAYOUT, E>(P.gx, pt.x, pt.y, pt.z, fb), tex3d_any<LAYOUT, E>(P.gy, pt.x, pt.y, pt.z, fb),
+                tex3d_any<LAYOUT, E>(P.gz, pt.x, pt.y, pt.z, fb));
       }
       // the reflection fetch sits inside the reference's light loop (kernel.cu:342-344) but does
       // not depend on the light: fetched once
@@ -780,8 +793,8 @@ VR_HD void shade_sample(const KernelParams &P, F3 origin, Ray &r) {
       if (spec) re_raw = spec_re;
       else
 #endif
-      if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 2)) re_raw = P.re_is_em ? em_raw : tex_raw(P.re, ps.x, ps.y, ps.z);
-      else re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, ps.x, ps.y, ps.z, fb);
+      if (VR_TEX_FAST && LAYOUT == LAYOUT_TEXHW && (P.tex_fast & 2)) re_raw = P.re_is_em ? em_raw : tex_raw(P.re, pt.x, pt.y, pt.z);
+      else re_raw = P.re_is_em ? em_raw : tex3d_any<LAYOUT, E>(P.re, pt.x, pt.y, pt.z, fb);
     }
     illum = Lights<LAYOUT>::shade(P, g, P.fRe * re_raw, r.pos, origin, color, fb);
   }

@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     Ray r;
     bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, cam, x, y, origin, r);
     bool active = hit;
-    const int vs_mode = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW) ? 0 : P.vs_mode;
+    const int vs_mode = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW && UNI == 0) ? 0 : P.vs_mode;  // (TEXHW with UNI = 1: region contexts)
     if (vs_mode == 2 && hit) {  // start from the opacity of the bricks in front; nothing to do behind the threshold
       float a_in = 0.0f;
       active = vs_opacity_in(P, origin, r, (size_t)x * P.H + y, a_in);
@@ -240,7 +240,12 @@ cudaError_t VR_CAT3(launch_raymarch_lookup, _a, VR_ARITH)(const KernelParams &P,
 cudaError_t VR_CAT3(launch_raymarch_compute, _a, VR_ARITH)(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
 #endif
   // texture-unit launches: fp32 arrays, per-texture fetches (there are no tap sets to share)
-  if (layout == LAYOUT_TEXHW) return dtype == 0 && P.uniform == 0 ? launch_one<VR_GRAD, LAYOUT_TEXHW, ElemF32, 0>(P, stream, sm_count) : cudaErrorInvalidValue;
+  // (the arrays are fp32 whatever the storage type; uniform == 1 selects the instantiation for contexts that own a region)
+  if (layout == LAYOUT_TEXHW) {
+    if (P.uniform == 0) return launch_one<VR_GRAD, LAYOUT_TEXHW, ElemF32, 0>(P, stream, sm_count);
+    if (P.uniform == 1) return launch_one<VR_GRAD, LAYOUT_TEXHW, ElemF32, 1>(P, stream, sm_count);
+    return cudaErrorInvalidValue;
+  }
   if (dtype == 0) return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemF32>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemF32>(P, stream, sm_count);
   return layout == LAYOUT_BRICK ? launch_le<LAYOUT_BRICK, ElemBF16>(P, stream, sm_count) : launch_le<LAYOUT_LINEAR, ElemBF16>(P, stream, sm_count);
 }

@@ -88,7 +88,8 @@ cudaError_t launch_gradient(const void *d_in, int w, int h, int d, int dtype, vo
 
 // texture-unit mode (VR_OPT_TEXTURE_UNIT): copies the voxels of a whole resident fp32 volume (padded storage, any layout,
 // interleaved component or not) into a w x h x d cudaArray through a surface object
-cudaError_t launch_fill_array(const TexDesc &t, int layout, unsigned long long surface, cudaStream_t stream);
+// ... or of the voxel box [a0, a0 + an) of it (a region context's resident box clipped to the volume); dtype = vr_dtype of the storage
+cudaError_t launch_fill_array(const TexDesc &t, int layout, int dtype, const int a0[3], const int an[3], unsigned long long surface, cudaStream_t stream);
 
 // probe_kernels.cu: gather ceilings of the box with the march's access pattern; kind 0 = 8 x 4-byte
 // loads per fetch, 1 = 8 x 16-byte loads, 2 = tex3D<float> linear, 3 = tex3D<float4> linear; footprint (2^log2_edge)^3 voxels

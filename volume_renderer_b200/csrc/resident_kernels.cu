@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(256) k_repack(const RepackArgs a) {
       const int sy = min(max(Y + a.gy0, 0), a.h - 1);
       const int sz = min(max(Z + a.gz0, 0), a.d - 1);
       if (sx < a.box[0] || sx >= a.box[3] || sy < a.box[1] || sy >= a.box[4] || sz < a.box[2] || sz >= a.box[5]) continue;  // not part of this update
-      if (a.src_surface) v = surf3Dread<float>((cudaSurfaceObject_t)a.src_surface, sx * (int)sizeof(float), sy, sz);
+      if (a.src_surface) v = surf3Dread<float>((cudaSurfaceObject_t)a.src_surface, (sx - a.sx0) * (int)sizeof(float), sy - a.sy0, sz - a.src_z0);
       else v = load_src(a.src, ((size_t)(sz - a.src_z0) * a.sh + (sy - a.sy0)) * a.sw + (sx - a.sx0), a.src_dtype);
     } else if (a.box[0] > 0 || a.box[1] > 0 || a.box[2] > 0 || a.box[3] < a.w || a.box[4] < a.h || a.box[5] < a.d) {
       continue;  // brick filler beyond the padded extent: written once by the full upload
@@ -81,27 +81,39 @@ cudaError_t launch_repack(const RepackArgs &a, cudaStream_t stream) {
 // ---- texture-unit mode: padded storage -> cudaArray ---------------------------------------------
 // One thread per voxel, x fastest: a warp reads one or two brick rows and writes 128 contiguous bytes of the array's
 // row (the array's own tiling is the driver's business).  HBM bound: 4 bytes read + 4 written per voxel.
-template <int LAYOUT>
-__global__ void __launch_bounds__(256) k_fill_array(const TexDesc t, cudaSurfaceObject_t surf) {
-  const uint64_t n = (uint64_t)t.w * t.h * t.d;
+// The array holds the voxel box [a0, a0 + an) of the volume (the whole volume, or a region context's resident box clipped to
+// the volume); bf16 storage is widened exactly.
+struct Box6 {
+  int a0[3], an[3];
+};
+template <int LAYOUT, int DTYPE>
+__global__ void __launch_bounds__(256) k_fill_array(const TexDesc t, cudaSurfaceObject_t surf, const Box6 b) {
+  const uint64_t n = (uint64_t)b.an[0] * b.an[1] * b.an[2];
   const int es = t.estride > 1 ? t.estride : 1;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-    const int x = (int)(i % (uint64_t)t.w), y = (int)((i / (uint64_t)t.w) % (uint64_t)t.h), z = (int)(i / ((uint64_t)t.w * t.h));
+    const int x = (int)(i % (uint64_t)b.an[0]), y = (int)((i / (uint64_t)b.an[0]) % (uint64_t)b.an[1]), z = (int)(i / ((uint64_t)b.an[0] * b.an[1]));
     typedef Addr<LAYOUT> A;
-    const size_t off = A::z(z + 1 - t.oz, t.sz) + A::y(y + 1 - t.oy, t.sy) + A::x(x + 1 - t.ox);  // voxel v sits at padded index v + 1
-    const float v = __ldg(static_cast<const float *>(t.p) + off * (size_t)es + (size_t)t.ecomp);
+    // voxel v sits at padded index v + 1 (minus the local storage's origin)
+    const size_t off = A::z(z + b.a0[2] + 1 - t.oz, t.sz) + A::y(y + b.a0[1] + 1 - t.oy, t.sy) + A::x(x + b.a0[0] + 1 - t.ox);
+    const float v = load_src(t.p, off * (size_t)es + (size_t)t.ecomp, DTYPE);
     surf3Dwrite(v, surf, x * (int)sizeof(float), y, z);
   }
 }
-cudaError_t launch_fill_array(const TexDesc &t, int layout, unsigned long long surface, cudaStream_t stream) {
-  const uint64_t n = (uint64_t)t.w * t.h * t.d;
+cudaError_t launch_fill_array(const TexDesc &t, int layout, int dtype, const int a0[3], const int an[3], unsigned long long surface, cudaStream_t stream) {
+  Box6 b;
+  for (int i = 0; i < 3; ++i) b.a0[i] = a0[i], b.an[i] = an[i];
+  const uint64_t n = (uint64_t)an[0] * an[1] * an[2];
   if (n == 0) return cudaSuccess;
   uint64_t blocks = (n + 255) / 256;
   if (blocks > 148ull * 64) blocks = 148ull * 64;
-  if (layout == LAYOUT_BRICK)
-    k_fill_array<LAYOUT_BRICK><<<(unsigned)blocks, 256, 0, stream>>>(t, (cudaSurfaceObject_t)surface);
-  else
-    k_fill_array<LAYOUT_LINEAR><<<(unsigned)blocks, 256, 0, stream>>>(t, (cudaSurfaceObject_t)surface);
+  const cudaSurfaceObject_t s_ = (cudaSurfaceObject_t)surface;
+  if (layout == LAYOUT_BRICK) {
+    if (dtype == 0) k_fill_array<LAYOUT_BRICK, 0><<<(unsigned)blocks, 256, 0, stream>>>(t, s_, b);
+    else k_fill_array<LAYOUT_BRICK, 1><<<(unsigned)blocks, 256, 0, stream>>>(t, s_, b);
+  } else {
+    if (dtype == 0) k_fill_array<LAYOUT_LINEAR, 0><<<(unsigned)blocks, 256, 0, stream>>>(t, s_, b);
+    else k_fill_array<LAYOUT_LINEAR, 1><<<(unsigned)blocks, 256, 0, stream>>>(t, s_, b);
+  }
   return cudaGetLastError();
 }
 

@@ -131,6 +131,10 @@ struct KernelParams {
   // the macro cell of a sample's low tap straight from the world position: floor(clamp(pos * cellA + cellB, 0, cellMax))
   // per axis (= floor((x*N - 0.5) / 8) up to ~1e-4 voxels, far inside the grid's two-voxel dilation); see on_empty_cell
   float cellA[3], cellB[3], cellMax[3];
+  // texture-unit launches of a context that owns a REGION (k_raymarch<.., LAYOUT_TEXHW, .., UNI = 1>): the arrays hold the
+  // region's voxel box [a0, a0 + aw) only, so a normalized volume coordinate x becomes x * tex_cs + tex_co
+  // (= (x * N - a0) / aw: the same texel position x * N - 0.5 - a0 in the local array)
+  float tex_cs[3], tex_co[3];
 };
 
 }  // namespace vrb

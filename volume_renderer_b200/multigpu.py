@@ -316,8 +316,9 @@ class VolumeSpaceRank:
         import torch.distributed as dist
 
         stream = None  # = the context's stream = torch's current stream (set in __init__)
+        packed = self.r._packed_mono_args()  # one 'sync_volumes' + one marshalling per frame, shared by both passes
         self._mark("start")
-        self.r.renderOpacity(self.opac_mine.data_ptr(), stream)
+        self.r.renderOpacity(self.opac_mine.data_ptr(), stream, packed)
         self._mark("opacity_pass")
         if self.n > 1:
             dist.all_gather_into_tensor(self.opac_all, self.opac_mine, group=self.group)
@@ -325,14 +326,14 @@ class VolumeSpaceRank:
             self.opac_all.copy_(self.opac_mine)
         self._mark("all_gather")
         if self.shared is not None:
-            self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.shared.ptrs[self.rank].value, stream)
+            self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.shared.ptrs[self.rank].value, stream, packed)
             self._mark("shading_pass")
             frame_barrier(self.token, self.group)
             if self.rank == 0:
                 compose(self.r.objectHandle, [p.value for p in self.shared.ptrs], self.H * self.W * 3, self.out.data_ptr(), stream)
             self._mark("barrier_and_compose")
         else:
-            self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.part.data_ptr(), stream)
+            self.r.renderPartial(self.bricks, self.rank, self.opac_all.data_ptr(), self.part.data_ptr(), stream, packed)
             self._mark("shading_pass")
             if self.n > 1:
                 dist.reduce(self.part, dst=0, op=dist.ReduceOp.SUM, group=self.group)  # the sum IS the composite
