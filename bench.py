@@ -35,7 +35,7 @@ SEED = 0x5EED01BE
 # keyed by (volume edge, image edge, gradient method, dtype, texture unit on/off).  Not measured live: bench.py scales it to
 # the frames of its own launches and names the profile it came from.
 DRAM_PROFILE = {
-    (1024, 2048, "lookup", "f32", 1): {"bytes_per_frame": 1.67e9, "profile": "profiles/r01_v7_tex_summary.md"},
+    (1024, 2048, "lookup", "f32", 1): {"bytes_per_frame": 1.46e9, "profile": "profiles/r02_final_summary.md"},
     (1024, 2048, "lookup", "f32", 0): {"bytes_per_frame": 2.6e9, "profile": "profiles/r01_v5_summary.md"},
 }
 
@@ -58,8 +58,9 @@ def parse():
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--skip", type=int, default=2)
     p.add_argument("--tile", type=int, default=64)
+    p.add_argument("--e2e-batch", type=int, default=10, help="frames per pipelined batch of the end-to-end leg (the host ring holds two batches)")
     p.add_argument("--e2e-tile", type=int, default=32, help="N > 1, end-to-end leg: width of the tile columns dealt round-robin to the ranks")
-    p.add_argument("--batch", type=int, default=16, help="frames per launch (one work queue per batch; clipped to --steps)")
+    p.add_argument("--batch", type=int, default=32, help="frames per launch at most (one work queue per batch; the steps are cut into equal batches)")
     p.add_argument("--wshape", type=int, default=3, help="warp footprint (1<<s) x (32>>s) pixels")
     p.add_argument("--no-upload-probe", action="store_true", help="skip the host->resident upload measurement")
     p.add_argument("--no-gather-probe", action="store_true", help="skip the gather-ceiling microbenchmark (roofline.gather)")
@@ -521,6 +522,9 @@ def run_b200(args):
     # exactly the pixel columns it rendered into the assembled frames over its own PCIe link, and the pipelined batches
     # (vr_render_batch_begin / _end) let those copies run while the next batch is rendered.
     host_frames = None
+    Bd = B                                                   # frames per launch of the device-resident leg above
+    B = frames_per_launch(args.steps, min(args.e2e_batch, args.batch))  # ... and of this leg's pipelined batches
+    props_b = np.tile(scene.props, max(B, Bd)).astype(np.float32)
     if world > 1:
         host_frames = multigpu.SharedHostFrames(scene.H, scene.W, 2 * B, rank, world)
         ring = host_frames.ptrs

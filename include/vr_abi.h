@@ -245,11 +245,12 @@ typedef enum vr_option {
   VR_OPT_GRADIENT_INTERLEAVE = 13, /* 1 (default): the three gradient volumes of lookupGradient are stored interleaved
                                      (16-byte voxels Gx,Gy,Gz,-; one load per tap); 0: three separate volumes.  Takes
                                      effect at the next upload of the gradient volumes; pixels are bit-identical */
-  VR_OPT_TEXTURE_UNIT = 14,     /* how a trilinear fetch is done.  2 (default): through the texture unit on cudaArray copies of
+  VR_OPT_TEXTURE_UNIT = 14,     /* how a trilinear fetch is done.  2 (default): through the texture unit on fp32 cudaArray copies of
                                    the volumes, configured as the reference configures its textures (volumeRender_kernel.cu:
-                                   544-548) - the reference's own hardware filtering - where this context can (fp32 whole
-                                   volumes that fit twice), else as 0.  1: texture unit or VR_ERR_UNSUPPORTED.  0: eight loads +
-                                   fp32 lerps, the documented filter formula with fp32 weights (or VR_OPT_FILTER_FRAC_BITS) */
+                                   544-548) - the reference's own hardware filtering - where this context can (fp32 or bf16 volumes,
+                                   whole or a vr_set_region shard, whose arrays fit), else as 0.  1: texture unit or
+                                   VR_ERR_UNSUPPORTED.  0: eight loads + fp32 lerps, the documented filter formula with fp32 weights
+                                   (or VR_OPT_FILTER_FRAC_BITS) */
   VR_OPT_ARITHMETIC = 15,       /* arithmetic flavour of the ray-march kernels.  0 "exact": every fp32 operation individually rounded,
                                    IEEE square roots and divides - bit-equal to the CPU checker of the test suite.  1 "reference": what nvcc
                                    makes of the reference's own source - FMA contraction, normalize() by rsqrtf (helper_math.h:

@@ -108,17 +108,21 @@ def _vs_worker(rank, world, port, out_path):
     lut = vrt.oracle_lut(64)
     bricks = multigpu.brick_grid(vol.shape, multigpu.splits_for(world))
     imgs = {}
-    for exchange in ("p2p", "nccl"):
+    # both exchanges with the load path forced (bricks then fetch the very bits of a single pass), and the default - the
+    # texture unit on the brick's own arrays - once
+    for exchange, tu in (("p2p", 0), ("nccl", 0), ("p2p", 2)):
         r = api.VolumeRender()
         r.setRegion(*bricks[rank])
         r = vrt.example1_scene(lambda: r, vol, RES, lights=2, lut=lut)
+        r.setOption(_abi.OPT_TEXTURE_UNIT, tu)
         r.FactorAbsorption = 30.0
         vs = multigpu.VolumeSpaceRank(r, bricks, rank, exchange=exchange)
         for _ in range(2):  # a second frame reuses every buffer
             r.rotate(0, 10, 0)
             img = vs.render()
+        assert r.stats()["fetch_mode"] == (1 if tu else 0)
         if rank == 0:
-            imgs[exchange] = img
+            imgs["%s_tu%d" % (exchange, tu)] = img
         torch.cuda.synchronize()
         dist.barrier()
         if rank != 0:
@@ -127,11 +131,14 @@ def _vs_worker(rank, world, port, out_path):
         if rank == 0:
             vs.close()
     if rank == 0:
-        whole = vrt.example1_scene(api.VolumeRender, vol, RES, lights=2, lut=lut)
-        whole.setOption(_abi.OPT_TEXTURE_UNIT, 0)  # region contexts fetch with loads: compare like with like
-        whole.FactorAbsorption = 30.0
-        whole.rotate(0, 20, 0)
-        np.savez(out_path, full=whole.render(), **imgs)
+        full = {}
+        for tu in (0, 2):
+            whole = vrt.example1_scene(api.VolumeRender, vol, RES, lights=2, lut=lut)
+            whole.setOption(_abi.OPT_TEXTURE_UNIT, tu)  # compare like with like
+            whole.FactorAbsorption = 30.0
+            whole.rotate(0, 20, 0)
+            full["full_tu%d" % tu] = whole.render()
+        np.savez(out_path, **full, **imgs)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -146,10 +153,15 @@ def test_volume_space_one_brick_per_gpu(tmp_path):
     out = str(tmp_path / "vs.npz")
     mp.spawn(_vs_worker, args=(world, _free_port(), out), nprocs=world, join=True)
     z = np.load(out)
-    for k in ("p2p", "nccl"):
-        m = vrt.compare(z[k], z["full"])
+    for k in ("p2p_tu0", "nccl_tu0"):
+        m = vrt.compare(z[k], z["full_tu0"])
         print(k, m)
         assert m["max_abs_norm"] < 2e-5, (k, m)
+    # through the texture unit a brick's samples meet the filter's 8-bit weights a hair differently than the single pass's
+    # (remapped coordinate); at a rare pixel that moves the threshold break by a sample - isolated pixels within the bar
+    m = vrt.compare(z["p2p_tu2"], z["full_tu2"])
+    print("p2p_tu2", m)
+    assert m["max_abs_norm"] <= vrt.TOL and m["psnr_db"] >= 95.0, m
 
 
 def _e2e_worker(rank, world, port, out_path):

@@ -29,7 +29,7 @@ for nr in (1,2,8):
     rot=scene.rot(0)
     _abi.check(lib.vr_render_device(ctx,lights,2,C.byref(lutv),f(scene.factors),f(scene.es),resp,f(rot),f(scene.props),C.c_float(scene.thr),f(scene.color),C.c_void_p(img.data_ptr()),None),ctx)
     s=_abi.VrStats(); _abi.check(lib.vr_get_stats(ctx,C.byref(s)),ctx)
-  NW=148*28; wt=np.zeros(2*NW,dtype=np.uint64); _abi.check(lib.vr_debug_warp_times(ctx,wt.ctypes.data,NW),ctx)
+  NW=148*32; wt=np.zeros(2*NW,dtype=np.uint64); _abi.check(lib.vr_debug_warp_times(ctx,wt.ctypes.data,NW),ctx)
   st=wt[0::2].astype(np.int64); en=wt[1::2].astype(np.int64); t0=st.min()
   end=(en-t0)/1e6
   print("nranks",nr,"kernel_ms %.2f"%s.kernel_ms,"warp end ms: min %.2f p10 %.2f p50 %.2f p90 %.2f p99 %.2f max %.2f mean %.2f"%(end.min(),*np.percentile(end,[10,50,90,99]),end.max(),end.mean()), "still running at T-4,-3,-2,-1,-0.5 ms:", [int((end>end.max()-d).sum()) for d in (4,3,2,1,0.5)])
