@@ -765,7 +765,8 @@ def gather_probe(lib, ctx, args, n_lights, shaded_per_s):
     out = {"pattern": "8x4 bundles of parallel rays 0.7 voxel apart, 0.45-voxel steps, one trilinear fetch (8 taps) per step, 2048 threads/SM",
            "unit": "G trilinear fetches/s"}
     for name, kind, e in (("ldg4_L1_32^3", 0, 5), ("ldg4_L2_256^3", 0, 8), ("ldg4_HBM_1024^3", 0, 10), ("ldg16_L2_128^3", 1, 7), ("ldg16_HBM_512^3", 1, 9),
-                          ("tex_f32_L1_32^3", 2, 5), ("tex_f32_L2_256^3", 2, 8), ("tex_f32_HBM_1024^3", 2, 10), ("tex_f32x4_L2_128^3", 3, 7), ("tex_f32x4_HBM_512^3", 3, 9)):
+                          ("tex_f32_L1_32^3", 2, 5), ("tex_f32_L2_256^3", 2, 8), ("tex_f32_HBM_1024^3", 2, 10), ("tex_f32x4_L2_128^3", 3, 7), ("tex_f32x4_HBM_512^3", 3, 9),
+                          ("smem_taps_staging_free", 4, 8)):
         try:
             out[name] = probe(kind, e) / 1e9
         except Exception as ex:  # e.g. gather from layered arrays refused by the driver: the other probes still count

@@ -367,7 +367,9 @@ VR_API vr_status vr_device_download(vr_ctx *ctx, void *host_dst, const void *d_s
 /* Measurement only: the gather ceilings of this device with the march's access pattern (8x4 bundles of
  * parallel rays, one trilinear fetch = 8 taps per step; SURVEY 8(d) "BW_gather from a committed
  * microbenchmark").  kind 0 = eight 4-byte loads per fetch, 1 = eight 16-byte loads, 2 = one tex3D<float>
- * with hardware linear filtering (the reference's fetch, volumeRender_kernel.cu:544-548), 3 = tex3D<float4>.
+ * with hardware linear filtering (the reference's fetch, volumeRender_kernel.cu:544-548), 3 = tex3D<float4>,
+ * 4 = the taps read from shared memory, where a TMA-staged march would keep the voxel neighbourhood; the staging itself is left out, so the
+ * rate is the upper bound of that design.
  * Footprint (2^log2_edge)^3 voxels: 5 -> L1, 8 -> L2, 10 -> HBM.  Returns trilinear fetches per second. */
 VR_API vr_status vr_probe_gather(vr_ctx *ctx, int kind, int log2_edge, double *fetches_per_s, double *ms);
 

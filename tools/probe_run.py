@@ -11,7 +11,7 @@ from volume_renderer_b200 import _abi  # noqa: E402
 lib = _abi.lib()
 ctx = C.c_void_p()
 _abi.check(lib.vr_create(C.byref(ctx)))
-kinds = [int(k) for k in (sys.argv[1].split(",") if len(sys.argv) > 1 else ["2", "0"])]
+kinds = [int(k) for k in (sys.argv[1].split(",") if len(sys.argv) > 1 else ["2", "0", "4"])]  # 4 = TMA-staged neighbourhood, taps from shared memory
 for kind in kinds:
     for e in (5, 8, 10):
         f, ms = C.c_double(), C.c_double()

@@ -2168,7 +2168,7 @@ vr_status vr_device_upload(vr_ctx *c, void *d_dst, const void *host_src, size_t 
 }
 vr_status vr_probe_gather(vr_ctx *c, int kind, int log2_edge, double *fetches_per_s, double *ms) {
   VR_CHECK_HANDLE(c);
-  if (!fetches_per_s || !ms || kind < 0 || kind > 3 || log2_edge < 4 || log2_edge > 10) return fail(c, VR_ERR_INVALID_ARGUMENT, "probe_gather: bad arguments");
+  if (!fetches_per_s || !ms || kind < 0 || kind > 4 || log2_edge < 4 || log2_edge > 10) return fail(c, VR_ERR_INVALID_ARGUMENT, "probe_gather: bad arguments");
   VR_TRY(set_device(c));
   VR_CUDA(c, launch_probe_gather(kind, log2_edge, c->sm_count, c->stream, fetches_per_s, ms));
   return VR_OK;
