@@ -267,6 +267,17 @@ typedef enum vr_option {
                                    grids stand, the padded brick storage they were built from is freed (4 instead of 8 GiB per 1024^3 fp32
                                    volume) and rebuilt from the array only when something needs it: vr_update_box (such a volume keeps
                                    both copies from then on), a switch to the load path, new skip grids.  0: keep both copies */
+  VR_OPT_VS_SLICES = 18,        /* volume-space passes (vr_render_opacity / vr_render_partial): cut every ray's stretch inside the brick
+                                   into this many equal depth slices marched by DIFFERENT warps; 1 = whole rays; 0 (default) =
+                                   automatic: slices of at most ~2048 lattice samples on the brick's diagonal, at most 8; explicit values
+                                   up to 16; needs the closed-form empty-space skip, else whole rays.  A launch then ends with its
+                                   longest SLICE instead of its longest ray - what matters when a brick's rays are thousands of samples
+                                   long (a lone warp shades ~0.3 samples per microsecond).  Where each slice of each pixel starts - the
+                                   bit-exact state of the reference's recurrences there - is found once per frame by a small kernel of
+                                   the opacity pass and reused by the shading pass, which must follow with the same camera and value.
+                                   Every lattice sample is still shaded once, at its bit-exact position; a brick's opacity and colour
+                                   are folded from the slices' (1 - prod(1 - a_s); sum), so images agree with whole rays to float
+                                   rounding, not bit for bit.  Costs (S-1) * 16 + S * 16 bytes per pixel of scratch */
   VR_OPT_COUNT_
 } vr_option;
 /* Default: 2.  Measured on a B200 against the reference kernel's OWN images (tests/golden/refcuda_*.npy, seven scenes): flavours 1

@@ -52,6 +52,64 @@ def test_bricks_on_one_gpu_match_single_pass(splits, grad):
     assert vrt.compare(img, orc.render())["max_abs_norm"] <= vrt.TOL
 
 
+@pytest.mark.parametrize("splits,slices", [((1, 1, 1), 2), ((1, 1, 2), 3), ((2, 2, 2), 4), ((1, 2, 1), 16)])
+@pytest.mark.parametrize("grad", [0, 1])
+def test_depth_slices_shade_every_sample_once(splits, slices, grad):
+    """VR_OPT_VS_SLICES: the stretch of a ray inside a brick is marched by `slices` different warps.  Every lattice sample is
+    still shaded exactly once and at its bit-exact position - the counters say so - and the image agrees with whole rays to
+    float rounding (a slice's colour share is summed afterwards instead of in the loop)."""
+    vol = vrt.synth_brain((72, 64, 56))
+    lut = api.HenyeyGreenstein(64)
+    bricks = multigpu.brick_grid(vol.shape, splits)
+    imgs, shaded, marched = {}, {}, {}
+    for S in (1, slices):
+        rs = [_scene(vol, lut, grad, bricks, b) for b in range(len(bricks))]
+        for r in rs:
+            r.FactorAbsorption = 4.0  # translucent: no ray ends at the threshold, both passes shade the same samples
+            r.setOption(_abi.OPT_VS_SLICES, S)
+        imgs[S] = multigpu.render_bricks_one_gpu(rs, bricks)
+        shaded[S] = sum(r.stats()["samples_shaded"] for r in rs)  # (the shading pass: the last launch of each context)
+        marched[S] = sum(r.stats()["samples_marched"] for r in rs)
+    m = vrt.compare(imgs[slices], imgs[1])
+    print(splits, slices, grad, m, shaded)
+    assert m["max_abs_norm"] < 2e-6, m
+    assert shaded[slices] == shaded[1] and shaded[1] > 0
+    # ... and visited by one worker only: the fast-forward to a slice's start is not counted, a jump stops at its end
+    # (the two real steps a jump starts with may cross the slice's end: at most two samples per ray and border are counted twice)
+    assert 0 <= marched[slices] - marched[1] <= 2 * (slices - 1) * RES[0] * RES[1] * len(bricks), marched
+    full = _scene(vol, lut, grad)
+    full.FactorAbsorption = 4.0
+    assert vrt.compare(imgs[slices], full.render())["max_abs_norm"] < 2e-5
+    # opaque scene: rays end at the 0.9 threshold inside the volume - a slice behind the break must add nothing
+    for S in (1, slices):
+        rs = [_scene(vol, lut, grad, bricks, b) for b in range(len(bricks))]
+        for r in rs:
+            r.setOption(_abi.OPT_VS_SLICES, S)
+        imgs[S] = multigpu.render_bricks_one_gpu(rs, bricks)
+    m = vrt.compare(imgs[slices], imgs[1])
+    print("opaque", m)
+    assert m["max_abs_norm"] < 2e-5, m
+    assert vrt.compare(imgs[slices], _scene(vol, lut, grad).render())["max_abs_norm"] < 2e-5
+
+
+def test_depth_slices_need_the_same_cut_in_both_passes():
+    vol = vrt.synth_brain((40, 40, 40))
+    lut = api.HenyeyGreenstein(64)
+    bricks = multigpu.brick_grid(vol.shape, (1, 1, 1))
+    r = _scene(vol, lut, 0, bricks, 0)
+    r.setOption(_abi.OPT_VS_SLICES, 4)
+    import torch
+
+    op = torch.zeros(RES[0] * RES[1], dtype=torch.float32, device="cuda")
+    out = torch.zeros(RES[0] * RES[1] * 3, dtype=torch.float32, device="cuda")
+    r.renderOpacity(op.data_ptr())
+    r.setOption(_abi.OPT_VS_SLICES, 2)
+    with pytest.raises(_abi.VrError, match="depth slices"):
+        r.renderPartial(bricks, 0, op.data_ptr(), out.data_ptr())
+    with pytest.raises(_abi.VrError):
+        r.setOption(_abi.OPT_VS_SLICES, 17)
+
+
 def test_region_buffer_generated_on_the_device():
     """config 5 shape: each brick's voxels (+ halo) are generated straight into HBM and handed over
     as a VR_MEM_DEVICE_REGION source - the whole volume never exists anywhere."""

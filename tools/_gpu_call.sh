@@ -1,3 +1,4 @@
 set -x
 cd $GRAFT_REPO_ROOT
-timeout 120 python tools/probe_run.py 4 2>&1 | tail -6
+mkdir -p gpurun_out
+timeout 1700 python -m pytest tests -m gpu -q -x 2>&1 | tail -8

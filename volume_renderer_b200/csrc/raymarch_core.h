@@ -830,6 +830,38 @@ VR_HD bool vs_opacity_in(const KernelParams &P, F3 origin, const Ray &r, size_t 
   return true;
 }
 
+// Depth slices of the volume-space passes.  The ray's stretch inside this context's region box (from reg_lo / reg_hi, the
+// volume's faces where the region ends there) is cut into S equal parts of the ray parameter: slice s covers [bound(s), bound(s+1))
+// with bound(0) = -inf and bound(S) = +inf, so samples the box test puts a hair outside still have an owner.  Every kernel
+// evaluates the same expressions on the same values (the fma is spelled out: no contraction choices), and r.t itself is the
+// bit-exact serial recurrence, so each lattice sample falls into exactly one slice, in every pass alike.  A ray that never
+// enters the box has one slice, the first (ownership is decided per sample by the region test regardless).
+struct SliceCut {
+  float a, w;
+  bool inside;
+};
+VR_HD SliceCut vs_slice_cut(const KernelParams &P, F3 origin, const Ray &r, F3 bmin, F3 ext, int S) {
+  const F3 lo = mk3(P.reg_lo[0] > 0.0f ? bmin.x + ext.x * P.reg_lo[0] : bmin.x, P.reg_lo[1] > 0.0f ? bmin.y + ext.y * P.reg_lo[1] : bmin.y,
+                    P.reg_lo[2] > 0.0f ? bmin.z + ext.z * P.reg_lo[2] : bmin.z);
+  const F3 hi = mk3(P.reg_hi[0] < 1.0f ? bmin.x + ext.x * P.reg_hi[0] : bmin.x + ext.x, P.reg_hi[1] < 1.0f ? bmin.y + ext.y * P.reg_hi[1] : bmin.y + ext.y,
+                    P.reg_hi[2] < 1.0f ? bmin.z + ext.z * P.reg_hi[2] : bmin.z + ext.z);
+  float un = 0.0f, uf = 0.0f;  // in steps: pos = origin + step * u
+  SliceCut c;
+  c.inside = intersect_box(origin, r.step, lo, hi, un, uf);
+  c.a = un * P.tstep;
+  c.w = (uf * P.tstep - c.a) / (float)S;
+  return c;
+}
+VR_HD float vs_slice_bound(const SliceCut &c, int s, int S) {
+  if (s <= 0) return -3.0e38f;
+  if (s >= S || !c.inside) return 3.0e38f;
+#if defined(__CUDA_ARCH__)
+  return __fmaf_rn(c.w, (float)s, c.a);
+#else
+  return fmaf(c.w, (float)s, c.a);
+#endif
+}
+
 // Loop tail (kernel.cu:485-492).  Returns false when the ray is finished.
 VR_HD bool ray_advance(const KernelParams &P, Ray &r) {
   if (r.sw > P.thr) return false;
@@ -976,8 +1008,13 @@ VR_HD bool on_empty_cell(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale
 // counter - was tried: it saves the 38-instruction check per sample but lanes then reach the next
 // empty cell out of phase and run the jump below one by one: 27 -> 42 ms.  Checking every sample
 // keeps neighbouring rays in step.)
-VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale) {
+// t_until (depth slices): samples with r.t < t_until belong to an earlier slice of this ray - for this worker they are "empty"
+// whatever the grid says, and the fast-forward stops short of t_until (-inf: off).
+// t_stop (depth slices): the end of the worker's slice of the ray parameter - a jump does not go past it, so that every lattice
+// sample is visited (and counted) by exactly one worker; reaching it returns true (the caller retires the lane).
+VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, float t_stop = 3.0e38f) {
   for (;;) {
+    if (!(r.t < t_stop)) return true;
     const CellAt c = cell_at(P, r, bmin, bscale);
     const int dist = (int)VR_LDG(P.dist + c.cell);
     if (dist == 0) return true;  // something to shade here
@@ -1005,6 +1042,7 @@ VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale) {
     const float big = 3.0e38f;
     const F3 inv_dq = mk3(dq.x != 0.0f ? 1.0f / dq.x : big, dq.y != 0.0f ? 1.0f / dq.y : big, dq.z != 0.0f ? 1.0f / dq.z : big);
     float kf = ceilf(steps_to_exit(now, dist - 1, dq, inv_dq));
+    if (t_stop < 3.0e38f) kf = fminf(kf, fmaxf(ceilf((t_stop - r.t) / dt), 1.0f));
     kf = fminf(kf, fminf(fminf(binade_room(r.t, dt), binade_room(r.pos.x, d.x)), fminf(binade_room(r.pos.y, d.y), binade_room(r.pos.z, d.z))));
     kf = fminf(kf, 4194304.0f);
     if (!(kf >= 1.0f)) continue;
@@ -1025,6 +1063,48 @@ VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale) {
           one_binade(r.pos.z, r.pos.z, p_end.z)))
       continue;  // cannot happen with the conservative room; stay exact regardless
     r.n_marched += (uint32_t)kf;
+    r.t = t_end;
+    r.pos = p_end;
+  }
+}
+
+// Depth slices: run the reference's recurrences `t += tstep; pos += step` (kernel.cu:488-492) forward, EXACTLY, to the first
+// lattice sample with t >= t_until - whatever lies on the way (it is another worker's to shade).  The same binade argument as in
+// skip_empty_jump; no grid, no counting.  Returns false when the ray ends first.
+VR_HD bool fast_forward_to(const KernelParams &P, Ray &r, float t_until) {
+  for (;;) {
+    if (!(r.t < t_until)) return true;
+    if (!(r.t + 3.0f * P.tstep < t_until)) {  // within three samples: real steps, one at a time
+      r.t += P.tstep;
+      if (r.t > r.tfar) return false;
+      r.pos = r.pos + r.step;
+      continue;
+    }
+    const float t0 = r.t;
+    const F3 p0 = r.pos;
+    r.t += P.tstep;
+    if (r.t > r.tfar) return false;
+    r.pos = r.pos + r.step;
+    const float t1 = r.t;
+    const F3 p1 = r.pos;
+    r.t += P.tstep;
+    if (r.t > r.tfar) return false;
+    r.pos = r.pos + r.step;
+    if (!(one_binade(t0, t1, r.t) && one_binade(p0.x, p1.x, r.pos.x) && one_binade(p0.y, p1.y, r.pos.y) &&
+          one_binade(p0.z, p1.z, r.pos.z)))
+      continue;
+    const float dt = r.t - t1;
+    const F3 d = r.pos - p1;
+    float kf = floorf((t_until - r.t) / dt) - 1.0f;  // up to, not into, the slice: the last steps are real ones
+    kf = fminf(kf, fminf(fminf(binade_room(r.t, dt), binade_room(r.pos.x, d.x)), fminf(binade_room(r.pos.y, d.y), binade_room(r.pos.z, d.z))));
+    kf = fminf(kf, 4194304.0f);
+    if (!(kf >= 1.0f)) continue;
+    const float t_end = r.t + kf * dt;
+    if (t_end > r.tfar) return false;  // t_end < t_until: the ray ends before the slice starts
+    const F3 p_end = r.pos + kf * d;
+    if (!(one_binade(r.t, r.t, t_end) && one_binade(r.pos.x, r.pos.x, p_end.x) && one_binade(r.pos.y, r.pos.y, p_end.y) &&
+          one_binade(r.pos.z, r.pos.z, p_end.z)))
+      continue;
     r.t = t_end;
     r.pos = p_end;
   }

@@ -87,10 +87,20 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
   if (P.warp_times) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
 
   for (;;) {
+#ifdef VR_ITEM_PROFILE  // developer build (tools/build_ab.sh): the longest item of every warp, behind the warp times
+    unsigned long long it_start = 0;
+    unsigned it_loops = 0, it_jumps = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(it_start));
+#endif
     uint32_t w = 0;
     if (lane == 0) w = atomicAdd(P.work_counter, 1u);
     w = __shfl_sync(kFull, w, 0);
     if (w >= P.num_work) break;
+    // volume-space passes with depth slices: S consecutive work items are the S slices of one warp footprint
+    const int vs_mode_w = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW && UNI == 0) ? 0 : P.vs_mode;
+    const uint32_t S = (vs_mode_w && P.vs_slices > 1) ? (uint32_t)P.vs_slices : 1u;
+    const uint32_t slice = S > 1 ? w % S : 0u;
+    if (S > 1) w /= S;
     // work item -> frame, tile, pixel.  `entry` = frame * tiles_total + tile.
     const uint32_t owned = w / wt_per_tile, sub = w - owned * wt_per_tile;
     const uint32_t entry = P.tile_order ? VR_LDG(P.tile_order + owned) : (uint32_t)P.part_rank + owned * (uint32_t)P.part_nranks;
@@ -115,18 +125,37 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     Ray r;
     bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, cam, x, y, origin, r);
     bool active = hit;
-    const int vs_mode = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW && UNI == 0) ? 0 : P.vs_mode;  // (TEXHW with UNI = 1: region contexts)
+    const int vs_mode = vs_mode_w;  // (TEXHW with UNI = 1: region contexts)
+    float ts1 = 3.0e38f;  // where this item's slice of the ray parameter ends
+    if (S > 1 && hit) {
+      ts1 = vs_slice_bound(vs_slice_cut(P, origin, r, bmin, ext, (int)S), (int)slice + 1, (int)S);
+      if (slice > 0) {  // ... and its first sample, from k_slice_states
+        const float4 st = __ldg(reinterpret_cast<const float4 *>(P.vs_slice_state) + (size_t)(slice - 1) * ((size_t)P.W * P.H) + ((size_t)x * P.H + y));
+        r.t = st.x, r.pos = mk3(st.y, st.z, st.w);
+        if (!(st.x < 3.0e38f)) active = false;  // the ray ends before this slice
+      }
+    }
     if (vs_mode == 2 && hit) {  // start from the opacity of the bricks in front; nothing to do behind the threshold
       float a_in = 0.0f;
-      active = vs_opacity_in(P, origin, r, (size_t)x * P.H + y, a_in);
+      active = vs_opacity_in(P, origin, r, (size_t)x * P.H + y, a_in) && active;
+      if (S > 1 && active) {  // ... and of the slices of this brick in front of this one
+        float T = 1.0f - a_in;
+        const size_t plane = (size_t)P.W * P.H, pixel = (size_t)x * P.H + y;
+        for (uint32_t q = 0; q < slice; ++q) T = T * (1.0f - VR_LDG(P.vs_slice_opacity + q * plane + pixel));
+        a_in = 1.0f - T;
+      }
       r.sw = a_in;
       if (a_in > P.thr) active = false;
     }
     F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
     if (active && P.skip == 1) skip_setup(P, r, bscale, dq, inv_dq);
 
+    if (S > 1 && active && !(r.t < ts1)) active = false;  // (a ray that starts behind this item's slice)
     int waited = 0;  // warp-uniform: iterations the oldest postponed jump has been waiting
     while (__any_sync(kFull, active)) {
+#ifdef VR_ITEM_PROFILE
+      ++it_loops;
+#endif
       bool ready = active;  // shades a sample in this iteration
       if (P.skip == 2) {
         // The jump over empty space is ~290 instructions and is usually wanted by one or two lanes
@@ -140,7 +169,11 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
         if (wm) {
           const unsigned am = __ballot_sync(kFull, active);
           if (__popc(wm) >= VR_JUMP_LANES || wm == am || waited >= VR_JUMP_WAIT) {
-            if (want) ready = active = skip_empty_jump(P, r, bmin, bscale);
+#ifdef VR_ITEM_PROFILE
+            ++it_jumps;
+#endif
+            if (want) ready = active = skip_empty_jump(P, r, bmin, bscale, ts1);
+            if (S > 1 && active && !(r.t < ts1)) ready = active = false;  // jumped out of this item's slice
             waited = 0;
           } else {
             ++waited;
@@ -153,6 +186,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
       if (ready) {
         shade_sample<GRAD, LAYOUT, E, UNI>(P, origin, r);
         active = ray_advance(P, r);
+        if (S > 1 && active && !(r.t < ts1)) active = false;  // past this item's slice: the next slice's worker takes over
       }
     }
     if (x < (uint32_t)P.W && y < (uint32_t)P.H) {
@@ -162,11 +196,13 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
       // another GPU's memory (image-space direct send: each rank stores its tiles into the root's image).
       const size_t size = (size_t)P.W * P.H, k = (size_t)x * P.H + y;
       if (vs_mode == 1) {
-        P.vs_opacity_out[k] = hit ? r.sw : 0.0f;
+        if (S > 1) P.vs_slice_opacity[slice * size + k] = hit ? r.sw : 0.0f;
+        else P.vs_opacity_out[k] = hit ? r.sw : 0.0f;
       } else {
-        cam.out[k] = hit ? r.sx : 0.0f;
-        cam.out[k + size] = hit ? r.sy : 0.0f;
-        cam.out[k + 2 * size] = hit ? r.sz : 0.0f;
+        float *o = cam.out + (size_t)slice * 3 * size;  // (slice 0 of 1: the image itself)
+        o[k] = hit ? r.sx : 0.0f;
+        o[k + size] = hit ? r.sy : 0.0f;
+        o[k + 2 * size] = hit ? r.sz : 0.0f;
       }
     }
     if (P.tile_cost) {
@@ -181,6 +217,20 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
         atomicMax(P.tile_cost + P.tiles_total + tile, longest);
       }
     }
+#ifdef VR_ITEM_PROFILE
+    if (P.warp_times) {
+      unsigned long long it_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(it_end));
+      const unsigned ms = __reduce_max_sync(kFull, hit ? r.n_shaded : 0u), mm = __reduce_max_sync(kFull, hit ? r.n_marched : 0u);
+      const unsigned ss = __reduce_add_sync(kFull, hit ? r.n_shaded : 0u);
+      const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+      unsigned long long *rec = P.warp_times + 2 * 8192 + 6 * wid;
+      if (lane == 0 && it_end - it_start > rec[0]) {
+        rec[0] = it_end - it_start, rec[1] = (unsigned long long)x | ((unsigned long long)y << 16) | ((unsigned long long)slice << 32);
+        rec[2] = ms | ((unsigned long long)ss << 32), rec[3] = mm, rec[4] = it_loops, rec[5] = it_jumps;
+      }
+    }
+#endif
     if (hit) {
       tot_marched += r.n_marched;
       tot_shaded += r.n_shaded;
@@ -207,6 +257,41 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
   }
 }
 
+#define VR_CAT3_(a, b, c) a##b##c
+#define VR_CAT3(a, b, c) VR_CAT3_(a, b, c)
+#if !VR_GRAD
+// Depth slices: the first lattice sample of slices 1 .. S-1 of every pixel (vr_types.h), one thread per pixel.  Compiled with
+// the march kernels of its arithmetic flavour (ray_init must produce the very rays they march).
+template <int ARITH>
+__global__ void __launch_bounds__(128) k_slice_states(const __grid_constant__ KernelParams P) {
+  const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
+  const F3 origin = ray_origin(P.cam);
+  const size_t plane = (size_t)P.W * P.H;
+  const int S = P.vs_slices;
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < plane; k += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t x = (uint32_t)(k / (size_t)P.H), y = (uint32_t)(k - (size_t)x * P.H);
+    Ray r;
+    bool alive = ray_init(P, P.cam, x, y, origin, r);
+    SliceCut cut;
+    cut.a = cut.w = 0.0f, cut.inside = false;
+    if (alive) cut = vs_slice_cut(P, origin, r, bmin, ext, S);
+    alive = alive && cut.inside;
+    for (int s = 1; s < S; ++s) {
+      if (alive) alive = fast_forward_to(P, r, vs_slice_bound(cut, s, S));
+      reinterpret_cast<float4 *>(P.vs_slice_state)[(size_t)(s - 1) * plane + k] = alive ? make_float4(r.t, r.pos.x, r.pos.y, r.pos.z) : make_float4(3.0e38f, 0.0f, 0.0f, 0.0f);
+    }
+  }
+}
+cudaError_t VR_CAT3(launch_slice_states, _a, VR_ARITH)(const KernelParams &P, cudaStream_t stream, int sm_count) {
+  const size_t plane = (size_t)P.W * P.H;
+  size_t blocks = (plane + 127) / 128;
+  if (blocks > (size_t)sm_count * 16) blocks = (size_t)sm_count * 16;
+  if (blocks < 1) blocks = 1;
+  k_slice_states<VR_ARITH><<<(unsigned)blocks, 128, 0, stream>>>(P);
+  return cudaGetLastError();
+}
+#endif
+
 template <int GRAD, int LAYOUT, typename E, int UNI>
 static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
   constexpr int kBlockThreads = Tune<GRAD, LAYOUT>::threads;
@@ -232,8 +317,6 @@ static cudaError_t launch_le(const KernelParams &P, cudaStream_t stream, int sm_
   return P.uniform ? launch_one<VR_GRAD, LAYOUT, E, 1>(P, stream, sm_count) : launch_one<VR_GRAD, LAYOUT, E, 0>(P, stream, sm_count);
 }
 
-#define VR_CAT3_(a, b, c) a##b##c
-#define VR_CAT3(a, b, c) VR_CAT3_(a, b, c)
 #if VR_GRAD
 cudaError_t VR_CAT3(launch_raymarch_lookup, _a, VR_ARITH)(const KernelParams &P, int layout, int dtype, cudaStream_t stream, int sm_count) {
 #else

@@ -28,6 +28,17 @@ inline cudaError_t launch_raymarch(const KernelParams &P, int layout, int dtype,
   return (P.gradient_method ? lookup : compute)[arith](P, layout, dtype, stream, sm_count);
 }
 
+// depth slices of the volume-space passes: the first lattice sample of every slice (raymarch_kernel.cu: k_slice_states)
+cudaError_t launch_slice_states_a0(const KernelParams &P, cudaStream_t stream, int sm_count);
+cudaError_t launch_slice_states_a1(const KernelParams &P, cudaStream_t stream, int sm_count);
+cudaError_t launch_slice_states_a2(const KernelParams &P, cudaStream_t stream, int sm_count);
+inline cudaError_t launch_slice_states(const KernelParams &P, cudaStream_t stream, int sm_count, int arith) {
+  typedef cudaError_t (*Fn)(const KernelParams &, cudaStream_t, int);
+  static const Fn fn[3] = {launch_slice_states_a0, launch_slice_states_a1, launch_slice_states_a2};
+  if (arith < 0 || arith > 2) return cudaErrorInvalidValue;
+  return fn[arith](P, stream, sm_count);
+}
+
 // resident_kernels.cu: everything that builds the resident representation of a volume.
 struct RepackArgs {
   void *dst;           // padded (bricked) storage of the whole volume
@@ -78,6 +89,7 @@ cudaError_t launch_synth_region(void *d_out, int kind, uint32_t seed, const int 
 // Every partial is already weighted by the transmittance of the bricks in front of it, so the "under"
 // operator over depth-ordered partials reduces to an order-free sum.  Partials may live on peer GPUs.
 cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_floats, float *d_out, cudaStream_t stream);
+cudaError_t launch_fold_slices(const float *d_slices, int S, uint64_t n, float *d_out, int product, cudaStream_t stream);
 
 // image epilogue: stereo crop + compose (mode 0 RedCyan, 1 LeftRightHorizontal) and sequence normalisation
 cudaError_t launch_stereo(const float *left, const float *right, int H, int Wp, int delta, int mode, float *out, cudaStream_t stream);

@@ -506,6 +506,30 @@ cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_flo
   return cudaGetLastError();
 }
 
+// Depth slices of one brick (VR_OPT_VS_SLICES): S planes of n floats each -> one.  product = 1: opacities, 1 - prod(1 - a_s),
+// front to back (what a march through the whole brick accumulates: sum.w += (1 - sum.w) * alpha, kernel.cu:470-483);
+// product = 0: the additive colour shares, summed in slice order.
+__global__ void __launch_bounds__(256) k_fold_slices(const float *in, int S, uint64_t n, float *out, int product) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    if (product) {
+      float T = 1.0f;
+      for (int s = 0; s < S; ++s) T = T * (1.0f - __ldg(in + (uint64_t)s * n + i));
+      out[i] = 1.0f - T;
+    } else {
+      float a = __ldg(in + i);
+      for (int s = 1; s < S; ++s) a += __ldg(in + (uint64_t)s * n + i);
+      out[i] = a;
+    }
+  }
+}
+cudaError_t launch_fold_slices(const float *d_slices, int S, uint64_t n, float *d_out, int product, cudaStream_t stream) {
+  uint64_t blocks = (n + 255) / 256;
+  if (blocks > 148ull * 8) blocks = 148ull * 8;
+  if (blocks < 1) blocks = 1;
+  k_fold_slices<<<(unsigned)blocks, 256, 0, stream>>>(d_slices, S, n, d_out, product);
+  return cudaGetLastError();
+}
+
 // ---- image epilogue (what the reference does in MATLAB after the mex returns) ---------------------------
 // Stereo compose (VolumeRender.m:286-306): both eyes were rendered delta columns wider; the left image
 // keeps columns delta.., the right one columns ..Wp-delta; RedCyan takes R from the left eye and G,B from

@@ -115,6 +115,17 @@ struct KernelParams {
   int vs_mode;
   int vs_index, vs_count;          // this brick, number of bricks
   float reg_lo[3], reg_hi[3];      // owned region in normalized texture coordinates
+  // Depth slices (vs_slices > 1): the stretch of a ray inside this brick is cut into vs_slices equal parts handled by DIFFERENT
+  // work items (item = (tile, warp footprint, slice)), so that the longest chain of a launch is a slice, not a whole ray.  Pass 1
+  // writes the opacity of every slice to vs_slice_opacity[slice][pixel] (the brick's total, 1 - prod(1 - a_s), is derived from
+  // them and is what the bricks exchange); pass 2 starts slice s from the bricks in front AND the slices s' < s of this brick and
+  // writes its additive share to cam.out + slice * 3 * W * H (summed in slice order afterwards).
+  // Where slice s >= 1 of a pixel starts - (t, pos) of its first lattice sample, t = 3e38 when the ray ends before - is found ONCE
+  // per frame by k_slice_states (the exact fast-forward of the reference's recurrences) and read by both passes:
+  // entry (s - 1) * W * H + pixel of vs_slice_state.
+  int vs_slices;
+  float *vs_slice_opacity;
+  float *vs_slice_state;  // 4 floats per entry (16-byte aligned)
   float *vs_opacity_out;           // mode 1
   const float *vs_opacity_all;     // mode 2: vs_count planes of W*H floats (pixel k = x*H + y)
   const float *vs_boxes;           // mode 2: vs_count x 6 floats, world-space brick boxes (lo xyz, hi xyz)
