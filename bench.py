@@ -71,6 +71,8 @@ def parse():
     p.add_argument("--order", type=int, default=1, help="1 = tiles handed out centre-first (default), 0 = raster order")
     p.add_argument("--mode", default="image", choices=["image", "volume"],
                    help="image = tiles over replicated volumes (the metric's config); volume = bricks sharded over the ranks, sort-last composite (config 5)")
+    p.add_argument("--opt", action="append", default=[], metavar="K=V", help="--mode volume: extra vr_set_option(K, V) calls (A/B and debugging)")
+    p.add_argument("--vs-slices", type=int, default=0, help="--mode volume: VR_OPT_VS_SLICES (0 = the library's automatic choice, 1 = whole rays)")
     p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                    help="N > 1: p2p = every rank's kernel stores its tiles into rank 0's image over NVLink (default); nccl = SUM-reduce of partial images")
     a = p.parse_args()
@@ -1150,6 +1152,14 @@ def run_volume(args):
     _abi.check(lib.vr_set_stream(ctx, C.c_void_p(torch.cuda.current_stream().cuda_stream)), ctx)  # torch's stream, also for timing events
     if world > 1:
         r.setRegion(lo, hi, halo)
+        if args.vs_slices:
+            r.setOption(_abi.OPT_VS_SLICES, args.vs_slices)
+    r.setOption(_abi.OPT_TEXTURE_UNIT, args.texture_unit)
+    r.setOption(_abi.OPT_TILE_ORDER, args.order)
+    if args.arith >= 0:
+        r.setOption(_abi.OPT_ARITHMETIC, args.arith)
+    for kv in args.opt:
+        r.setOption(int(kv.split("=")[0]), int(kv.split("=")[1]))
     blo = [max(l - halo, 0) for l in lo] if world > 1 else [0, 0, 0]
     bhi = [min(h + halo, d) for h, d in zip(hi, dims)] if world > 1 else list(dims)
     nvox = int(np.prod([h - l for l, h in zip(blo, bhi)]))
@@ -1212,6 +1222,7 @@ def run_volume(args):
         shaded += st["samples_shaded"]
         marched += st["samples_marched"]
         kernel_ms += st["kernel_ms"]
+        vs_slices = int(st["vs_slices"])
     ev1.record()
     barrier()
     t1 = time.time()
@@ -1288,9 +1299,12 @@ def run_volume(args):
             "config": {"workload": "huge-volume-shaped: %d^3 %s synthetic ViBE-Z-like E (Em=Ab), bricks %s (+%d voxel halo) one per GPU, 1 HG light, on-the-fly gradient, %dx%d mono, F=3 D=6 thr=0.9, +1deg/step"
                        % (n, args.dtype, "x".join(str(x) for x in multigpu.splits_for(world)), halo, args.image, args.image), "baseline_config": "huge volume (configs[4])",
                        "multi_gpu": "volume-space sort-last: opacity pass, all-gather of H*W floats per brick (NCCL), shading pass storing shares into rank 0 over NVLink (%s), composite kernel" % args.exchange,
+                       "depth_slices": "%d per brick (VR_OPT_VS_SLICES = %d%s): a ray's stretch inside a brick is marched by that many warps" % (vs_slices, args.vs_slices, ", automatic" if args.vs_slices == 0 else ""),
                        "brick_generate_s": t_gen, "brick_upload_s": t_up, "bytes_resident_rank0": res_b,
                        "l2": "inputs (resident bricks, GiBs) are larger than the 126 MB L2; no flush between frames"},
-            "clocks": clocks, "gpu_launches": 2 * args.steps * world + args.steps,
+            "clocks": clocks,
+            # per rank and frame: two march kernels; with depth slices also the slice-start kernel and a fold kernel per pass
+            "gpu_launches": (5 if vs_slices > 1 else 2) * args.steps * world + args.steps,
         }
         if not args.no_cpu_baseline:
             try:

@@ -92,6 +92,8 @@ typedef struct vr_stats {
   uint32_t uploads;          /* volume uploads done by the last vr_sync_volumes */
   uint32_t fetch_mode;       /* how the last render fetched: 0 = loads + fp32 lerps, 1 = texture unit (VR_OPT_TEXTURE_UNIT) */
   uint32_t arithmetic;       /* arithmetic flavour of the last render's kernel (VR_OPT_ARITHMETIC) */
+  uint32_t vs_slices;        /* depth slices the last volume-space pass marched with (VR_OPT_VS_SLICES resolved); 1 otherwise */
+  uint32_t reserved_;
 } vr_stats;
 
 /* ---- 'new'  (render.cpp:58-65) -------------------------------------------------------- */
@@ -269,8 +271,10 @@ typedef enum vr_option {
                                    both copies from then on), a switch to the load path, new skip grids.  0: keep both copies */
   VR_OPT_VS_SLICES = 18,        /* volume-space passes (vr_render_opacity / vr_render_partial): cut every ray's stretch inside the brick
                                    into this many equal depth slices marched by DIFFERENT warps; 1 = whole rays; 0 (default) =
-                                   automatic: slices of at most ~2048 lattice samples on the brick's diagonal, at most 8; explicit values
-                                   up to 16; needs the closed-form empty-space skip, else whole rays.  A launch then ends with its
+                                   automatic: the context's first frame marches whole rays and its shading pass measures its own tail - the
+                                   part of the launch during which warps had already run out of work; 30 % or more -> 8 slices, less ->
+                                   whole rays (needs VR_OPT_COUNT_SAMPLES, else whole rays); explicit values up to 16; needs the closed-form
+                                   empty-space skip and kernels with one common volume geometry, else whole rays.  A launch then ends with its
                                    longest SLICE instead of its longest ray - what matters when a brick's rays are thousands of samples
                                    long (a lone warp shades ~0.3 samples per microsecond).  Where each slice of each pixel starts - the
                                    bit-exact state of the reference's recurrences there - is found once per frame by a small kernel of

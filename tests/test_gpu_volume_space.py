@@ -92,6 +92,69 @@ def test_depth_slices_shade_every_sample_once(splits, slices, grad):
     assert vrt.compare(imgs[slices], _scene(vol, lut, grad).render())["max_abs_norm"] < 2e-5
 
 
+def test_big_brick_whole_rays_and_depth_slices_agree():
+    """One brick of a 1024^3 volume at the benchmark's camera and image size (bench.py --mode volume, rank 0 of 2), whole rays
+    against five depth slices: the same opacity plane and colour share.  Also the frame on which a build of
+    this library once faulted: keep it at this size and camera."""
+    import os
+    import sys
+
+    import torch
+
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+
+    n, image, halo = 1024, 2048, 4
+    dims = (n, n, n)
+    bricks = multigpu.brick_grid(dims, multigpu.splits_for(2))
+    lo, hi = bricks[0]
+    lib = _abi.lib()
+    npx = image * image
+    got = {}
+    for slices in (1, 5):
+        r = api.VolumeRender()
+        ctx = r.objectHandle
+        r.setRegion(lo, hi, halo)
+        r.setOption(_abi.OPT_VS_SLICES, slices)
+        blo = [max(l - halo, 0) for l in lo]
+        bhi = [min(h + halo, d) for h, d in zip(hi, dims)]
+        nvox = int(np.prod([h - l for l, h in zip(blo, bhi)]))
+        buf = C.c_void_p()
+        _abi.check(lib.vr_device_alloc(ctx, nvox * 4, C.byref(buf)), ctx)
+        u3 = lambda v: (C.c_uint64 * 3)(*[int(x) for x in v])
+        _abi.check(lib.vr_synth_volume_region(ctx, 0, bench.SEED, u3(dims), u3(blo), u3(bhi), _abi.DTYPE_F32, buf), ctx)
+        E = api.DeviceVolume(buf.value, dims, _abi.DTYPE_F32, _abi.MEM_DEVICE_REGION)
+        r.VolumeIllumination = api.Volume(api.HenyeyGreenstein(64))
+        r.LightSources = [api.LightSource([500, 1000, 550], [0, 1, 1])]
+        r.ElementSizeUm = [1, 1, 1]
+        r.FocalLength, r.DistanceToObject, r.OpacityThreshold = 3.0, 6.0, 0.9
+        r.ImageResolution = [image, image]
+        r.VolumeEmission = E
+        r.VolumeAbsorption = E
+        r.FactorEmission, r.FactorAbsorption, r.FactorReflection = 1.0, 0.6, 0.4
+        r.Color = [1, 1, 0]
+        r.syncVolumes()
+        _abi.check(lib.vr_device_free(ctx, buf), ctx)
+        r.VolumeEmission.TimeLastUpdate = 1
+        r.VolumeAbsorption.TimeLastUpdate = 1
+        opac_all = torch.zeros(2 * npx, dtype=torch.float32, device="cuda")
+        out = torch.zeros(3 * npx, dtype=torch.float32, device="cuda")
+        R0 = bench.rotation(125, 25, 0)
+        for k in (0, 1):
+            r.RotationMatrix = bench.rotation(0, float(k), 0, R0)
+            packed = r._packed_mono_args()
+            r.renderOpacity(opac_all.data_ptr(), None, packed)  # plane 0 = this brick's; the other brick's stays 0
+            r.renderPartial(bricks, 0, opac_all.data_ptr(), out.data_ptr(), None, packed)
+            st = r.stats()
+        assert st["fetch_mode"] == 1 and st["vs_slices"] == slices, st
+        got[slices] = (opac_all[:npx].cpu().numpy(), out.cpu().numpy(), st["samples_shaded"])
+        del r
+    peak = got[1][1].max()
+    assert peak > 0 and got[1][2] == got[5][2]
+    assert np.abs(got[1][0] - got[5][0]).max() < 2e-6
+    assert np.abs(got[1][1] - got[5][1]).max() / peak < 2e-5
+
+
 def test_depth_slices_need_the_same_cut_in_both_passes():
     vol = vrt.synth_brain((40, 40, 40))
     lut = api.HenyeyGreenstein(64)

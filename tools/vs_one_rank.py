@@ -25,6 +25,9 @@ p.add_argument("--image", type=int, default=2048)
 p.add_argument("--frames", type=int, default=3)
 p.add_argument("--texture-unit", type=int, default=2)
 p.add_argument("--slices", type=int, default=1)
+p.add_argument("--part", type=int, nargs=2, default=None, metavar=("RANK", "NRANKS"), help="render only the tiles RANK + j * NRANKS (debugging)")
+p.add_argument("--tile", type=int, default=64)
+p.add_argument("--first", type=int, default=0, help="index of the first frame (the camera turns 1 degree per frame)")
 a = p.parse_args()
 lib = _abi.lib()
 n = a.size
@@ -39,6 +42,8 @@ ctx = r.objectHandle
 r.setRegion(lo, hi, halo)
 r.setOption(_abi.OPT_TEXTURE_UNIT, a.texture_unit)
 r.setOption(_abi.OPT_VS_SLICES, a.slices)
+if a.part:
+    multigpu.configure_partition(ctx, a.part[0], a.part[1], a.tile, a.tile)
 blo = [max(l - halo, 0) for l in lo]
 bhi = [min(h + halo, d) for h, d in zip(hi, dims)]
 nvox = int(np.prod([h - l for l, h in zip(blo, bhi)]))
@@ -65,16 +70,40 @@ npx = a.image * a.image
 opac_all = torch.zeros(a.world * npx, dtype=torch.float32, device="cuda")
 mine = torch.zeros(npx, dtype=torch.float32, device="cuda")
 out = torch.zeros(3 * npx, dtype=torch.float32, device="cuda")
-for k in range(a.frames):
+def dump_trace():
+    full = np.zeros(8 * 8192, dtype=np.uint64)
+    _abi.check(lib.vr_debug_warp_times(ctx, full.ctypes.data, 4 * 8192), ctx)
+    f = lambda u: float(np.array([u & 0xffffffff], dtype=np.uint32).view(np.float32)[0])
+    for slot in range(1, 65):
+        e = [int(v) for v in full[8 * slot : 8 * slot + 6]]
+        print("px +%d,+%d stage %d n %d t %.7g tfar %.7g pos %.7g %.7g %.7g marched %d a %d b %d" % (
+            (slot - 1) % 8, (slot - 1) // 8, e[0] & 0xff, e[0] >> 8, f(e[1]), f(e[1] >> 32), f(e[2]), f(e[2] >> 32), f(e[3]), e[3] >> 32, e[4], e[5]))
+
+
+if os.environ.get("VR_TRACE"):
+    import atexit
+    atexit.register(dump_trace)
+for k in range(a.first, a.first + a.frames):
     r.RotationMatrix = bench.rotation(0, float(k), 0, R0)
     packed = r._packed_mono_args()
     r.renderOpacity(mine.data_ptr(), None, packed)
     torch.cuda.synchronize()
     op_ms = r.stats()["kernel_ms"]
     r.renderPartial(bricks, a.rank, opac_all.data_ptr(), out.data_ptr(), None, packed)
+    if os.environ.get("VR_DEBUG_BOUNDS"):
+        torch.cuda.synchronize()
+        full = np.zeros(8 * 8192, dtype=np.uint64)
+        _abi.check(lib.vr_debug_warp_times(ctx, full.ctypes.data, 4 * 8192), ctx)
+        nlog = int(full[2 * 8192])
+        print("out-of-range cells logged:", nlog)
+        for i in range(min(nlog, 12)):
+            e = full[2 * 8192 + 8 + 6 * i : 2 * 8192 + 8 + 6 * i + 6]
+            f = lambda u: float(np.array([u & 0xffffffff], dtype=np.uint32).view(np.float32)[0])
+            print("   cell %d t %.6f tfar %.6f pos (%.6f %.6f %.6f) cx,cy,cz %d %d %d marched %d" % (
+                int(e[0]), f(int(e[1])), f(int(e[1]) >> 32), f(int(e[2])), f(int(e[2]) >> 32), f(int(e[3])), int(e[4]) & 0xfffff, (int(e[4]) >> 20) & 0xfffff, int(e[4]) >> 40, int(e[5])))
     st = r.stats()
-    print("frame %d rank %d/%d slices %d: opacity pass %.2f ms, shading pass %.2f ms, %d shaded samples (%.1f G/s), %d lattice samples visited, fetch_mode %d, resident %.1f GB" % (
-        k, a.rank, a.world, a.slices, op_ms, st["kernel_ms"], st["samples_shaded"], st["samples_shaded"] / st["kernel_ms"] / 1e6, st["samples_marched"], st["fetch_mode"], st["bytes_resident"] / 1e9), flush=True)
+    print("frame %d rank %d/%d slices %d -> %d: opacity pass %.2f ms, shading pass %.2f ms, %d shaded samples (%.1f G/s), %d lattice samples visited, fetch_mode %d, resident %.1f GB" % (
+        k, a.rank, a.world, a.slices, st["vs_slices"], op_ms, st["kernel_ms"], st["samples_shaded"], st["samples_shaded"] / st["kernel_ms"] / 1e6, st["samples_marched"], st["fetch_mode"], st["bytes_resident"] / 1e9), flush=True)
     if os.environ.get("VR_WARP_TIMES"):
         NW = 148 * 32
         full = np.zeros(8 * 8192, dtype=np.uint64)

@@ -75,6 +75,8 @@ class VrStats(C.Structure):
         ("uploads", C.c_uint32),
         ("fetch_mode", C.c_uint32),
         ("arithmetic", C.c_uint32),
+        ("vs_slices", C.c_uint32),
+        ("reserved_", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -132,6 +132,9 @@ struct LaunchSlot {
 
 }  // namespace
 
+#ifdef VR_TRACE_PIXEL
+static void *g_trace_host = nullptr;
+#endif
 // what the slice states of a region context (d_slice_state) were computed for
 struct SliceStateKey {
   float cam[4][3], box[3], tstep;
@@ -204,6 +207,9 @@ struct vr_ctx {
   size_t slice_opac_cap = 0, slice_img_cap = 0, slice_state_cap = 0;
   SliceStateKey key_of_states{};  // the frame d_slice_state belongs to
   int slices_of_opacity_pass = 0;  // what the planes in d_slice_opac hold (the shading pass must use the same cut)
+  int auto_slices = 0;             // VR_OPT_VS_SLICES = 0: the number decided from the first frames' measurements (0 = not yet)
+  double last_tail = -1.0;         // tail fraction of the last launch that measured it (-1: none)
+  uint64_t auto_slices_sig = 0;    // image and tiling that decision belongs to
   uint64_t pixels_of_opacity_pass = 0;
   size_t boxes_cap = 0;
   // options
@@ -862,9 +868,13 @@ void read_slot(vr_ctx *c, LaunchSlot &S, vr_stats &into, bool accumulate) {
     } else {
       into.samples_marched = S.h_stats[0], into.samples_shaded = S.h_stats[1], into.rays_hit = S.h_stats[2];
     }
+    c->last_tail = -1.0;  // the part of the launch during which warps had already run out of work (measured launches only)
+    if (S.h_stats[5]) {
+      const double t0 = (double)~S.h_stats[3], idle = (double)~S.h_stats[4], t1 = (double)S.h_stats[5];
+      if (t1 > t0) c->last_tail = (t1 - idle) / (t1 - t0);
+    }
     S.stats_pending = false;
   }
-  (void)c;
 }
 
 // Pipelined batches: wait until the frames of slot `S` are in host memory and add its counters to the pipeline's totals.
@@ -1092,6 +1102,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   // volume-space mode
   P.vs_mode = 0;
   int slices = 1;
+  bool measure_tail = false;
   if (vs) {
     if (n_frames != 1) return fail(c, VR_ERR_UNSUPPORTED, "volume-space passes render one frame per launch");
     const int64_t dims[3] = {(int64_t)E.w, (int64_t)E.h, (int64_t)E.d};
@@ -1133,20 +1144,23 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     // depth slices: the workers of a slice find its start with the exact fast-forward of the empty-space jump
     slices = (int)c->opt[VR_OPT_VS_SLICES];
     if (slices == 0) {
-      // automatic: slices of at most ~2048 lattice samples on the brick's longest ray (its diagonal).  A lone warp needs about
-      // 3 us per shaded sample (the loop is one dependent chain), so a ray of 6000 samples through dense matter alone lasts
-      // 18 ms whatever the other 4735 warps do - measured on a 2048^3 brick of a 4096^3 volume: 35.6 ms per frame for both
-      // passes with whole rays, 19.7 ms with 8 slices; bricks with short rays gain nothing and keep whole rays.
-      float diag2 = 0.0f;
-      for (int i = 0; i < 3; ++i) {
-        const float len = (P.boxmax[i] - P.boxmin[i]) * (float)(c->rhi[i] - c->rlo[i]) / (float)dims[i];
-        diag2 += len * len;
-      }
-      const float samples = P.tstep > 0.0f ? sqrtf(diag2) / P.tstep : 0.0f;
-      slices = (int)ceilf(samples / 2048.0f);
-      slices = slices < 1 ? 1 : (slices > 8 ? 8 : slices);
+      // Automatic.  A lone warp needs microseconds per shaded sample (the loop is one dependent chain), so a ray of 6000 samples
+      // through dense matter lasts 18 ms whatever the other 4735 warps do; slices pay when that chain is what the launch waits
+      // for, and cost about a millisecond per frame (slice starts, folds, S times the items) when it is not.  So the context
+      // MEASURES: its first frame marches whole rays and the shading pass records when its first warp ran out of work and when
+      // its last one finished.  A tail of 30 % of the launch or more -> 8 slices (measured on 2048^3 bricks of a 4096^3 volume:
+      // tails of 70 - 90 %, 35.6 -> 19.7 ms per frame); shorter tails -> whole rays (two bricks of 1024^3 / 2048^3: tails of
+      // 12 - 19 %, slices change the frame by -2 ... +7 %).  Decided again when the image or the tiling changes; needs
+      // VR_OPT_COUNT_SAMPLES (the read-back of the counters).
+      const uint64_t tw = (uint64_t)c->opt[VR_OPT_TILE_W], th = (uint64_t)c->opt[VR_OPT_TILE_H];
+      const uint64_t asig = (W << 40) ^ (H << 20) ^ (tw << 8) ^ th;
+      if (c->auto_slices_sig != asig) c->auto_slices = 0, c->auto_slices_sig = asig, c->last_tail = -1.0;
+      if (vs->mode == 1 && c->auto_slices == 0 && c->stats.vs_slices == 1 && c->last_tail >= 0.0) c->auto_slices = c->last_tail >= 0.3 ? 8 : 1;
+      measure_tail = vs->mode == 2 && c->auto_slices == 0 && P.count;
+      slices = vs->mode == 1 ? (c->auto_slices ? c->auto_slices : 1) : (c->slices_of_opacity_pass > 1 ? c->slices_of_opacity_pass : 1);
     }
-    if (slices < 1 || P.skip != 2) slices = 1;
+    // (the kernels with per-texture addressing, P.uniform == 0, are built for whole rays only)
+    if (slices < 1 || P.skip != 2 || P.uniform == 0) slices = 1;
     if (vs->mode == 2 && slices != (c->slices_of_opacity_pass > 1 ? c->slices_of_opacity_pass : 1))
       return fail(c, VR_ERR_INVALID_ARGUMENT, "partial render with %d depth slices after an opacity pass with %d", slices, c->slices_of_opacity_pass);
     if (slices > 1) {
@@ -1173,6 +1187,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       if (vs->mode == 2) P.cam.out = c->d_slice_img;
     }
     if (vs->mode == 1) c->slices_of_opacity_pass = slices, c->pixels_of_opacity_pass = W * H;
+    P.measure_tail = measure_tail && slices == 1;
   }
 
   // lights
@@ -1345,7 +1360,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   if (c->opt[VR_OPT_CLEAR_IMAGE])
     for (size_t f = 0; f < n_frames; ++f) VR_CUDA(c, cudaMemsetAsync(d_outs[f], 0, (size_t)W * H * 3 * sizeof(float), stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
-  VR_CUDA(c, cudaMemsetAsync(S.d_stats, 0, 3 * sizeof(unsigned long long), stream));
+  VR_CUDA(c, cudaMemsetAsync(S.d_stats, 0, 6 * sizeof(unsigned long long), stream));  // [marched, shaded, hits | tail measurement]
   VR_CUDA(c, cudaEventRecord(S.ev0, stream));
   if (texhw && c->opt[VR_OPT_TEXTURE_SINGLE_COPY]) {
     // texture-unit launches read arrays and grids only: the padded storages go (cudaFree waits for the grid builds that
@@ -1354,6 +1369,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     for (int sl : need) drop_storage(c, c->tex[sl]);
   }
   const int arith = (int)c->opt[VR_OPT_ARITHMETIC];
+  int slice_states_ran = 0;
   if (slices > 1) {
     // the slices' first samples: found by the opacity pass, reused by the shading pass of the same frame (same camera, same cut)
     SliceStateKey key;
@@ -1363,9 +1379,24 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     if (vs->mode == 1 || memcmp(&key, &c->key_of_states, sizeof key) != 0) {
       VR_CUDA(c, launch_slice_states(P, stream, c->sm_count, arith));
       c->key_of_states = key;
+      slice_states_ran = 1;
     }
   }
   if (P.num_work > 0) VR_CUDA(c, launch_raymarch(P, layout, dtype, stream, c->sm_count, arith));
+#ifdef VR_DEBUG_BOUNDS  // developer build: grid cells outside the grid that the jump asked for (logged and clamped by the kernel)
+  if (c->d_warp_times) {
+    std::vector<unsigned long long> log(8 + 6 * 16);
+    cudaError_t de = cudaStreamSynchronize(stream);
+    if (de == cudaSuccess) de = cudaMemcpy(log.data(), c->d_warp_times + 2 * 8192, log.size() * 8, cudaMemcpyDeviceToHost);
+    fprintf(stderr, "[bounds] device %d vs_mode %d: %s, %llu cells out of range\n", c->device, P.vs_mode, cudaGetErrorString(de), log[0]);
+    for (unsigned long long i = 0; i < log[0] && i < 16; ++i) {
+      const unsigned long long *e = log.data() + 8 + 6 * i;
+      auto f = [](unsigned long long u) { float v; unsigned w = (unsigned)u; memcpy(&v, &w, 4); return v; };
+      fprintf(stderr, "[bounds]   cell %llu t %.7g tfar %.7g pos %.7g %.7g %.7g c %llu %llu %llu marched %llu\n", e[0], f(e[1]), f(e[1] >> 32), f(e[2]),
+              f(e[2] >> 32), f(e[3]), e[4] & 0xfffff, (e[4] >> 20) & 0xfffff, e[4] >> 40, e[5]);
+    }
+  }
+#endif
   c->stats.arithmetic = (uint32_t)arith;
   if (slices > 1) {  // the brick's opacity plane / colour share from those of its slices
     if (vs->mode == 1) VR_CUDA(c, launch_fold_slices(c->d_slice_opac, slices, W * H, vs->opacity_out, 1, stream));
@@ -1378,11 +1409,12 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     S.cost_valid = true, S.cost_sig = sig;
   }
   if (P.count) {
-    VR_CUDA(c, cudaMemcpyAsync(S.h_stats, S.d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    VR_CUDA(c, cudaMemcpyAsync(S.h_stats, S.d_stats, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
     S.stats_pending = true;
   }
   S.timing_pending = true;
-  c->stats.kernel_launches = P.num_work > 0 ? 1 : 0;
+  c->stats.kernel_launches = (P.num_work > 0 ? 1 : 0) + (slices > 1 ? 1 + slice_states_ran : 0);  // march (+ fold, + slice starts)
+  c->stats.vs_slices = (uint32_t)slices;
   c->stats.fetch_mode = texhw ? 1u : 0u;
   return VR_OK;
 }
@@ -1475,7 +1507,12 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   for (int i = 0; i < kStageBufs && ce == cudaSuccess; ++i) ce = cudaEventCreateWithFlags(&c->ev_stage[i], cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&c->ev_order, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaMalloc(&c->d_counter, 64);
-  if (ce == cudaSuccess && getenv("VR_WARP_TIMES")) ce = cudaMalloc(&c->d_warp_times, 8 * 8192 * sizeof(unsigned long long));  // [start, end] per warp; item records of profile builds behind
+#ifdef VR_TRACE_PIXEL  // developer build: the buffer lives in host memory the kernels write through a mapping - it survives a fault
+  if (ce == cudaSuccess) ce = cudaHostAlloc(&g_trace_host, 8 * 8192 * sizeof(unsigned long long), cudaHostAllocMapped);
+  if (ce == cudaSuccess) ce = cudaHostGetDevicePointer((void **)&c->d_warp_times, g_trace_host, 0);
+#else
+  if (ce == cudaSuccess && getenv("VR_WARP_TIMES")) ce = cudaMalloc(&c->d_warp_times, 8 * 8192 * sizeof(unsigned long long));
+#endif  // [start, end] per warp; item records of profile builds behind
   if (ce != cudaSuccess) {
     vr_status s = fail(nullptr, VR_ERR_CUDA, "vr_create: %s", cudaGetErrorString(ce));
     delete c;
@@ -2280,6 +2317,11 @@ vr_status vr_device_free(vr_ctx *c, void *d_ptr) {
 }
 vr_status vr_debug_warp_times(vr_ctx *c, uint64_t *host_pairs, size_t max_warps) {
   VR_CHECK_HANDLE(c);
+#ifdef VR_TRACE_PIXEL
+  if (max_warps > 4 * 8192) max_warps = 4 * 8192;
+  memcpy(host_pairs, g_trace_host, max_warps * 16);  // no CUDA call: readable after a fault
+  return VR_OK;
+#endif
   if (!c->d_warp_times) return fail(c, VR_ERR_UNSUPPORTED, "set VR_WARP_TIMES=1 before vr_create");
   VR_TRY(set_device(c));
   if (max_warps > 4 * 8192) max_warps = 4 * 8192;  // (beyond 8192: the item records of a VR_ITEM_PROFILE build)

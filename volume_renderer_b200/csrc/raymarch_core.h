@@ -397,7 +397,30 @@ struct Ray {
   float t, tfar;
   float sx, sy, sz, sw;  // float4 sum
   uint32_t n_marched, n_shaded;
+#ifdef VR_TRACE_PIXEL
+  uint32_t trace_slot, trace_n;  // developer build: 0 = this lane is not traced
+#endif
 };
+// Developer build (-DVR_TRACE_PIXEL -DVR_TRACE_X0=.. -DVR_TRACE_Y0=..): the lanes of an 8x8 pixel box keep their latest state in
+// host-mapped memory (KernelParams::warp_times), so that it survives a fault of the kernel.
+#if defined(VR_TRACE_PIXEL) && defined(__CUDA_ARCH__)
+#define VR_TRACE(P, r, stage, a, b)                                                                                              \
+  do {                                                                                                                           \
+    if ((r).trace_slot) {                                                                                                        \
+      volatile unsigned long long *e_ = (P).warp_times + 8ull * (r).trace_slot;                                                  \
+      e_[1] = __float_as_uint((r).t) | ((unsigned long long)__float_as_uint((r).tfar) << 32);                                    \
+      e_[2] = __float_as_uint((r).pos.x) | ((unsigned long long)__float_as_uint((r).pos.y) << 32);                               \
+      e_[3] = __float_as_uint((r).pos.z) | ((unsigned long long)(r).n_marched << 32);                                            \
+      e_[4] = (unsigned long long)(a), e_[5] = (unsigned long long)(b);                                                          \
+      e_[0] = (unsigned long long)(stage) | ((unsigned long long)(++const_cast<Ray &>(r).trace_n) << 8);                                         \
+      __threadfence_system();                                                                                                    \
+    }                                                                                                                            \
+  } while (0)
+#else
+#define VR_TRACE(P, r, stage, a, b) \
+  do {                              \
+  } while (0)
+#endif
 
 // intersectBox (kernel.cu:155-199): Williams et al. slab test with sign-indexed bounds; relies
 // on IEEE inf/NaN semantics for axis-parallel rays exactly like the reference.
@@ -993,6 +1016,7 @@ VR_HD bool on_empty_cell(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale
   const int cx = __float_as_int(__fadd_rd(vx, 12582912.0f)) - 0x4B400000;
   const int cy = __float_as_int(__fadd_rd(vy, 12582912.0f)) - 0x4B400000;
   const int cz = __float_as_int(__fadd_rd(vz, 12582912.0f)) - 0x4B400000;
+  VR_TRACE(P, r, 2, (uint32_t)((cz * P.ocy + cy) * P.ocx + cx), 0);
   return VR_LDG(P.dist + (uint32_t)((cz * P.ocy + cy) * P.ocx + cx)) != 0;
 #else
   const CellAt c = cell_at(P, r, bmin, bscale);
@@ -1008,15 +1032,27 @@ VR_HD bool on_empty_cell(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale
 // counter - was tried: it saves the 38-instruction check per sample but lanes then reach the next
 // empty cell out of phase and run the jump below one by one: 27 -> 42 ms.  Checking every sample
 // keeps neighbouring rays in step.)
-// t_until (depth slices): samples with r.t < t_until belong to an earlier slice of this ray - for this worker they are "empty"
-// whatever the grid says, and the fast-forward stops short of t_until (-inf: off).
 // t_stop (depth slices): the end of the worker's slice of the ray parameter - a jump does not go past it, so that every lattice
 // sample is visited (and counted) by exactly one worker; reaching it returns true (the caller retires the lane).
 VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, float t_stop = 3.0e38f) {
   for (;;) {
     if (!(r.t < t_stop)) return true;
-    const CellAt c = cell_at(P, r, bmin, bscale);
+    CellAt c = cell_at(P, r, bmin, bscale);
+#if defined(VR_DEBUG_BOUNDS) && defined(__CUDA_ARCH__)
+    if (c.cell >= (uint32_t)(P.ocx * P.ocy * P.ocz) && P.warp_times) {
+      const unsigned long long slot = atomicAdd(P.warp_times + 2 * 8192, 1ull);
+      if (slot < 1000) {
+        unsigned long long *e = P.warp_times + 2 * 8192 + 8 + 6 * slot;
+        e[0] = c.cell, e[1] = __float_as_uint(r.t) | ((unsigned long long)__float_as_uint(r.tfar) << 32);
+        e[2] = __float_as_uint(r.pos.x) | ((unsigned long long)__float_as_uint(r.pos.y) << 32), e[3] = __float_as_uint(r.pos.z);
+        e[4] = (unsigned long long)c.cx | ((unsigned long long)c.cy << 20) | ((unsigned long long)c.cz << 40), e[5] = r.n_marched;
+      }
+      c.cell = 0;
+    }
+#endif
+    VR_TRACE(P, r, 3, c.cell, 0);
     const int dist = (int)VR_LDG(P.dist + c.cell);
+    VR_TRACE(P, r, 4, c.cell, dist);
     if (dist == 0) return true;  // something to shade here
     // two real steps: both samples are still less than one voxel past an empty cell
     const float t0 = r.t;
@@ -1065,6 +1101,7 @@ VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, fl
     r.n_marched += (uint32_t)kf;
     r.t = t_end;
     r.pos = p_end;
+    VR_TRACE(P, r, 5, (uint32_t)kf, dist);
   }
 }
 

@@ -76,7 +76,9 @@ static constexpr unsigned kFull = 0xffffffffu;
 #endif
 
 // ARITH (= VR_ARITH of this translation unit, raymarch_core.h) only keeps the kernels of the arithmetic flavours apart by name
-template <int GRAD, int LAYOUT, typename E, int UNI, int ARITH>
+// SL = 1: the instantiation for volume-space passes cut into depth slices (KernelParams::vs_slices > 1); whole rays - every other
+// launch - run the SL = 0 kernels, in which no slice code exists.
+template <int GRAD, int LAYOUT, typename E, int UNI, int ARITH, int SL>
 __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT>::min_blocks) k_raymarch(const __grid_constant__ KernelParams P) {
   const int lane = threadIdx.x & 31;
   const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
@@ -85,6 +87,10 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
   unsigned long long tot_marched = 0, tot_shaded = 0, tot_hits = 0;
   unsigned long long t_start = 0;
   if (P.warp_times) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+  // whole-ray volume-space passes can time their warps (KernelParams::measure_tail); compiled out of the plain texture-unit kernels
+  constexpr bool kTimed = SL == 0 && !(VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW && UNI == 0);
+  unsigned long long warp_start = 0;
+  if (kTimed && P.measure_tail) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(warp_start));
 
   for (;;) {
 #ifdef VR_ITEM_PROFILE  // developer build (tools/build_ab.sh): the longest item of every warp, behind the warp times
@@ -98,7 +104,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     if (w >= P.num_work) break;
     // volume-space passes with depth slices: S consecutive work items are the S slices of one warp footprint
     const int vs_mode_w = (VR_TEX_NO_VS && LAYOUT == LAYOUT_TEXHW && UNI == 0) ? 0 : P.vs_mode;
-    const uint32_t S = (vs_mode_w && P.vs_slices > 1) ? (uint32_t)P.vs_slices : 1u;
+    const uint32_t S = (SL && vs_mode_w && P.vs_slices > 1) ? (uint32_t)P.vs_slices : 1u;
     const uint32_t slice = S > 1 ? w % S : 0u;
     if (S > 1) w /= S;
     // work item -> frame, tile, pixel.  `entry` = frame * tiles_total + tile.
@@ -125,6 +131,11 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     Ray r;
     bool hit = (x < (uint32_t)P.W) && (y < (uint32_t)P.H) && ray_init(P, cam, x, y, origin, r);
     bool active = hit;
+#ifdef VR_TRACE_PIXEL
+    r.trace_slot = 0, r.trace_n = 0;
+    if (P.warp_times && x >= VR_TRACE_X0 && x < VR_TRACE_X0 + 8 && y >= VR_TRACE_Y0 && y < VR_TRACE_Y0 + 8) r.trace_slot = 1 + (x - VR_TRACE_X0) + 8 * (y - VR_TRACE_Y0);
+    if (hit) VR_TRACE(P, r, 1, P.vs_mode, slice);
+#endif
     const int vs_mode = vs_mode_w;  // (TEXHW with UNI = 1: region contexts)
     float ts1 = 3.0e38f;  // where this item's slice of the ray parameter ends
     if (S > 1 && hit) {
@@ -150,7 +161,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
     if (active && P.skip == 1) skip_setup(P, r, bscale, dq, inv_dq);
 
-    if (S > 1 && active && !(r.t < ts1)) active = false;  // (a ray that starts behind this item's slice)
+    if (SL && active && !(r.t < ts1)) active = false;  // a ray that starts behind this item's slice
     int waited = 0;  // warp-uniform: iterations the oldest postponed jump has been waiting
     while (__any_sync(kFull, active)) {
 #ifdef VR_ITEM_PROFILE
@@ -172,8 +183,8 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
 #ifdef VR_ITEM_PROFILE
             ++it_jumps;
 #endif
-            if (want) ready = active = skip_empty_jump(P, r, bmin, bscale, ts1);
-            if (S > 1 && active && !(r.t < ts1)) ready = active = false;  // jumped out of this item's slice
+            if (want) ready = active = SL ? skip_empty_jump(P, r, bmin, bscale, ts1) : skip_empty_jump(P, r, bmin, bscale);
+            if (SL && active && !(r.t < ts1)) ready = active = false;  // jumped out of this item's slice
             waited = 0;
           } else {
             ++waited;
@@ -184,9 +195,11 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
         if (active) ready = active = skip_empty_serial(P, r, bmin, bscale, dq, inv_dq);
       }
       if (ready) {
+        VR_TRACE(P, r, 6, 0, 0);
         shade_sample<GRAD, LAYOUT, E, UNI>(P, origin, r);
+        VR_TRACE(P, r, 7, __float_as_uint(r.sw), 0);
         active = ray_advance(P, r);
-        if (S > 1 && active && !(r.t < ts1)) active = false;  // past this item's slice: the next slice's worker takes over
+        if (SL && active && !(r.t < ts1)) active = false;  // past this item's slice: the next slice's worker takes over
       }
     }
     if (x < (uint32_t)P.W && y < (uint32_t)P.H) {
@@ -195,6 +208,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
       // the owner of the pixel writes that 0 itself, so the image needs no clear and cam.out may be
       // another GPU's memory (image-space direct send: each rank stores its tiles into the root's image).
       const size_t size = (size_t)P.W * P.H, k = (size_t)x * P.H + y;
+      if (hit) VR_TRACE(P, r, 8, k, 0);
       if (vs_mode == 1) {
         if (S > 1) P.vs_slice_opacity[slice * size + k] = hit ? r.sw : 0.0f;
         else P.vs_opacity_out[k] = hit ? r.sw : 0.0f;
@@ -205,6 +219,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
         o[k + 2 * size] = hit ? r.sz : 0.0f;
       }
     }
+    if (hit) VR_TRACE(P, r, 9, 0, 0);
     if (P.tile_cost) {
       // What this item cost: the next launch hands the tiles with the LONGEST items out first.  An item lasts as long
       // as its longest ray (lanes march in lockstep), and what must not start late is a long item - a tile half
@@ -236,6 +251,12 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
       tot_shaded += r.n_shaded;
       tot_hits += 1;
     }
+  }
+  if (kTimed && P.measure_tail && lane == 0) {
+    // when the first warp started, when the first warp found the queue empty, when the last one finished: the launch's tail
+    unsigned long long warp_end;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(warp_end));
+    atomicMax(P.stats + 3, ~warp_start), atomicMax(P.stats + 4, ~warp_end), atomicMax(P.stats + 5, warp_end);
   }
   if (P.warp_times && lane == 0) {
     unsigned long long t_end;
@@ -292,11 +313,11 @@ cudaError_t VR_CAT3(launch_slice_states, _a, VR_ARITH)(const KernelParams &P, cu
 }
 #endif
 
-template <int GRAD, int LAYOUT, typename E, int UNI>
-static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
+template <int GRAD, int LAYOUT, typename E, int UNI, int SL>
+static cudaError_t launch_sl(const KernelParams &P, cudaStream_t stream, int sm_count) {
   constexpr int kBlockThreads = Tune<GRAD, LAYOUT>::threads;
   int per_sm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E, UNI, VR_ARITH>, kBlockThreads, 0);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_raymarch<GRAD, LAYOUT, E, UNI, VR_ARITH, SL>, kBlockThreads, 0);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   // persistent grid: a whole number of waves, never more warps than work items
@@ -304,8 +325,17 @@ static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm
   const long long need = ((long long)P.num_work + (kBlockThreads / 32) - 1) / (kBlockThreads / 32);
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
-  k_raymarch<GRAD, LAYOUT, E, UNI, VR_ARITH><<<(unsigned)blocks, kBlockThreads, 0, stream>>>(P);
+  k_raymarch<GRAD, LAYOUT, E, UNI, VR_ARITH, SL><<<(unsigned)blocks, kBlockThreads, 0, stream>>>(P);
   return cudaGetLastError();
+}
+template <int GRAD, int LAYOUT, typename E, int UNI>
+static cudaError_t launch_one(const KernelParams &P, cudaStream_t stream, int sm_count) {
+  if (P.vs_mode && P.vs_slices > 1) {
+    // sliced passes exist for the kernels region contexts normally run (shared tap sets / region texture arrays)
+    if (UNI == 0) return cudaErrorInvalidValue;
+    return launch_sl<GRAD, LAYOUT, E, (UNI == 0 ? 1 : UNI), 1>(P, stream, sm_count);
+  }
+  return launch_sl<GRAD, LAYOUT, E, UNI, 0>(P, stream, sm_count);
 }
 
 template <int LAYOUT, typename E>
