@@ -1,10 +1,6 @@
 set -x
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
-timeout 300 python tools/vs_one_rank.py --rank 0 --world 2 --size 1024 --dtype f32 --slices 0 --frames 3 2>&1 | grep "VrError\|frame" | cut -c1-110
-timeout 300 python tools/vs_one_rank.py --rank 1 --world 2 --size 2048 --slices 0 --frames 3 2>&1 | grep "VrError\|frame" | cut -c1-110
-timeout 300 python tools/vs_one_rank.py --rank 1 --slices 0 --frames 3 2>&1 | grep "VrError\|frame" | cut -c1-110
-timeout 300 python tools/vs_one_rank.py --rank 6 --slices 0 --frames 3 2>&1 | grep "VrError\|frame" | cut -c1-110
-timeout 300 python tools/vs_one_rank.py --rank 7 --slices 0 --frames 3 2>&1 | grep "VrError\|frame" | cut -c1-110
-timeout 900 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
-python bench.py --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; tail -c 600 gpurun_out/bench_n1.json
+TR8="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517"
+timeout 400 $TR8 bench.py --gpus 8 --mode volume --size 4096 --dtype bf16 --steps 12 --warmup 3 --no-cpu-baseline > gpurun_out/vs8_auto.json 2> gpurun_out/vs8_auto.err; echo rc=$?
+tail -c 300 gpurun_out/vs8_auto.err
