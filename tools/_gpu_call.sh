@@ -1,6 +1,8 @@
 set -x
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
-TR8="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517"
-timeout 400 $TR8 bench.py --gpus 8 --mode volume --size 4096 --dtype bf16 --steps 12 --warmup 3 --no-cpu-baseline > gpurun_out/vs8_auto.json 2> gpurun_out/vs8_auto.err; echo rc=$?
-tail -c 300 gpurun_out/vs8_auto.err
+timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -4 > gpurun_out/pytest_1gpu.log; cat gpurun_out/pytest_1gpu.log
+timeout 300 python tools/vs_one_rank.py --rank 1 --frames 3 --slices 0 > gpurun_out/vs_one_rank.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/vs_launches.csv python tools/vs_one_rank.py --rank 1 --frames 3 --slices 0 > gpurun_out/vs_ncu.log 2>&1
+tail -2 gpurun_out/vs_one_rank.log | cut -c1-160
+grep -c . gpurun_out/vs_launches.csv
