@@ -282,6 +282,14 @@ typedef enum vr_option {
                                    Every lattice sample is still shaded once, at its bit-exact position; a brick's opacity and colour
                                    are folded from the slices' (1 - prod(1 - a_s); sum), so images agree with whole rays to float
                                    rounding, not bit for bit.  Costs (S-1) * 16 + S * 16 bytes per pixel of scratch */
+  VR_OPT_RAY_SLICES = 19,       /* latency mode of single frames (vr_render, vr_render_device, one-frame batches; also on device groups):
+                                   1 (default) = the plain march; 2 .. 16 = the frame is rendered as the two passes of the volume-space
+                                   mode on the whole volume - an opacity pass, then the shading pass - both cut into that many depth
+                                   slices, so that the launch no longer waits for its longest rays (what limits ONE frame spread over
+                                   several GPUs).  Costs the opacity pass (about a third of a frame on one GPU: not a throughput option),
+                                   agrees with the plain march to float rounding (the colour shares of the slices are summed afterwards).
+                                   Scenes the passes do not take - volumes of different sizes, no closed-form empty-space skip,
+                                   per-texture addressing - are rendered plainly */
   VR_OPT_COUNT_
 } vr_option;
 /* Default: 2.  Measured on a B200 against the reference kernel's OWN images (tests/golden/refcuda_*.npy, seven scenes): flavours 1

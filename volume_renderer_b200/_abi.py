@@ -43,6 +43,7 @@ OPT_ARITHMETIC = 15
 OPT_PART_MODE = 16
 OPT_TEXTURE_SINGLE_COPY = 17
 OPT_VS_SLICES = 18
+OPT_RAY_SLICES = 19
 ARITH_EXACT, ARITH_REFERENCE, ARITH_FAST = 0, 1, 2
 IPC_HANDLE_BYTES = 64
 HG_STATIC_MAX_N = 64

@@ -127,6 +127,7 @@ struct LaunchSlot {
   float *d_image = nullptr;                  // persistent output image(s) of the host-image entry points
   size_t image_cap = 0;
   bool stats_pending = false, timing_pending = false;
+  uint32_t launches = 1;  // kernels of the batch in flight (a latency-mode frame is several)
   bool in_flight = false;                    // a pipelined batch of this slot has not been harvested yet
 };
 
@@ -207,6 +208,8 @@ struct vr_ctx {
   size_t slice_opac_cap = 0, slice_img_cap = 0, slice_state_cap = 0;
   SliceStateKey key_of_states{};  // the frame d_slice_state belongs to
   int slices_of_opacity_pass = 0;  // what the planes in d_slice_opac hold (the shading pass must use the same cut)
+  float *d_self_opac = nullptr;    // VR_OPT_RAY_SLICES: the opacity plane of a plain frame rendered in two sliced passes
+  size_t self_opac_cap = 0;
   int auto_slices = 0;             // VR_OPT_VS_SLICES = 0: the number decided from the first frames' measurements (0 = not yet)
   double last_tail = -1.0;         // tail fraction of the last launch that measured it (-1: none)
   uint64_t auto_slices_sig = 0;    // image and tiling that decision belongs to
@@ -272,6 +275,7 @@ uint64_t resident_bytes(const vr_ctx *c) {
   uint64_t b = 0;
   for (int i = 0; i < S_N; ++i) b += c->tex[i].storage_bytes + c->tex[i].occ_bytes + c->tex[i].dist_bytes + c->tex[i].array_bytes;
   b += c->slot[0].image_cap + c->slot[1].image_cap + kStageBufs * c->stage_cap + c->lights_more_cap + c->g4_bytes;
+  b += c->slice_opac_cap + c->slice_img_cap + c->slice_state_cap + c->self_opac_cap;  // scratch of the depth slices (volume-space passes)
   return b;
 }
 
@@ -882,7 +886,7 @@ vr_status harvest(vr_ctx *c, LaunchSlot &S) {
   if (!S.in_flight) return VR_OK;
   VR_CUDA(c, cudaEventSynchronize(S.ev_copied));
   read_slot(c, S, c->pipe_total, true);
-  c->pipe_total.kernel_launches += 1;
+  c->pipe_total.kernel_launches += S.launches;
   S.in_flight = false;
   return VR_OK;
 }
@@ -893,11 +897,11 @@ vr_status drain_pipeline(vr_ctx *c) {
   VR_TRY(harvest(c, c->slot[(c->pipe_batches + 1) & 1]));
   const uint64_t resident = c->stats.bytes_resident;
   const double upload_ms = c->stats.upload_ms;
-  const uint32_t uploads = c->stats.uploads, fetch = c->stats.fetch_mode, arith = c->stats.arithmetic;
+  const uint32_t uploads = c->stats.uploads, fetch = c->stats.fetch_mode, arith = c->stats.arithmetic, vss = c->stats.vs_slices;
   const uint64_t uploaded = c->stats.bytes_uploaded;
   c->stats = c->pipe_total;
   c->stats.bytes_resident = resident, c->stats.upload_ms = upload_ms, c->stats.uploads = uploads, c->stats.bytes_uploaded = uploaded;
-  c->stats.fetch_mode = fetch, c->stats.arithmetic = arith;
+  c->stats.fetch_mode = fetch, c->stats.arithmetic = arith, c->stats.vs_slices = vss;
   c->pipe_open = false;
   c->cur = 0;
   return VR_OK;
@@ -919,6 +923,9 @@ struct VsArgs {
   float *opacity_out;          // mode 1
   const float *opacity_all;    // mode 2
   const uint64_t *boxes_vox;   // mode 2: count x {lo x,y,z, hi x,y,z} in voxels
+  // the two passes of ONE plain frame cut into depth slices (VR_OPT_RAY_SLICES): the "brick" is the whole volume of a context
+  // without a region; the pair is timed as one launch
+  bool self;
 };
 
 // 'render' minus the read-back: marshal like render.cpp:142-245, set up like vr::initRender
@@ -927,7 +934,35 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
                         const float factors[3], const float es[3], const uint64_t res[2], size_t n_frames, const float *R,
                         const float *props, float thr, const float color[3], float *const *d_outs, cudaStream_t stream,
                         const VsArgs *vs = nullptr) {
-  if (c->region_on != (vs != nullptr))
+  if (!vs && !c->region_on && n_frames == 1 && c->opt[VR_OPT_RAY_SLICES] > 1 && d_outs && d_outs[0] && res) {
+    // Latency mode of a single frame: an opacity pass and a shading pass, both cut into depth slices.  Scenes the
+    // passes do not take (volumes of different sizes, no closed-form skip ...) are rendered as ever.
+    const size_t need = (size_t)res[0] * res[1] * sizeof(float);
+    if (c->self_opac_cap < need) {
+      if (c->d_self_opac) cudaFree(c->d_self_opac);
+      c->d_self_opac = nullptr, c->self_opac_cap = 0;
+      VR_CUDA(c, cudaMalloc(&c->d_self_opac, need));
+      c->self_opac_cap = need;
+    }
+    VsArgs a{};
+    a.mode = 1, a.opacity_out = c->d_self_opac, a.self = true;
+    float *dummy = c->d_self_opac;
+    const int64_t clear = c->opt[VR_OPT_CLEAR_IMAGE];
+    c->opt[VR_OPT_CLEAR_IMAGE] = 0;
+    VR_CUDA(c, cudaEventRecord(c->slot[c->cur].ev0, stream));  // the frame's time: both passes (the opacity pass leaves the slot alone)
+    const vr_status st = render_common(c, lights, n_lights, illumination, factors, es, res, 1, R, props, thr, color, &dummy, stream, &a);
+    c->opt[VR_OPT_CLEAR_IMAGE] = clear;
+    if (st == VR_OK) {
+      const HostVol &E0 = c->host[S_EM];
+      const uint64_t box[6] = {0, 0, 0, E0.w, E0.h, E0.d};
+      VsArgs b{};
+      b.mode = 2, b.index = 0, b.count = 1, b.opacity_all = c->d_self_opac, b.boxes_vox = box, b.self = true;
+      return render_common(c, nullptr, 0, nullptr, factors, es, res, 1, R, props, thr, color, d_outs, stream, &b);  // (lights: set by pass 1)
+    }
+    if (st != VR_ERR_UNSUPPORTED) return st;
+    tl_error.clear();  // not a scene for the passes: the plain render below
+  }
+  if (c->region_on != (vs != nullptr && !vs->self))
     return fail(c, VR_ERR_INVALID_ARGUMENT, c->region_on ? "this context owns a region (vr_set_region): use vr_render_opacity_device / vr_render_partial_device"
                                                          : "volume-space passes need vr_set_region first");
   if (!factors || !es || !res || !R || !props || !color || !d_outs || n_frames == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "insufficient parameter!");
@@ -1028,7 +1063,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   P.re_is_em = sRe == sEm;
   P.gradient_method = c->gradientMethod;
   P.frac_bits = (int)c->opt[VR_OPT_FILTER_FRAC_BITS];
-  P.count = (int)c->opt[VR_OPT_COUNT_SAMPLES];
+  P.count = (vs && vs->self && vs->mode == 1) ? 0 : (int)c->opt[VR_OPT_COUNT_SAMPLES];
   // all volume textures of one launch must share element type and layout
   int dtype = -1, layout = -1;
   const int used[] = {sEm, sAb, sRe, S_EM, S_DX, S_DY, S_DZ};
@@ -1113,11 +1148,12 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     float reach = 1.5f;
     if (!P.gradient_method && !c->lights.empty())
       for (int i = 0; i < 3; ++i) reach = fmaxf(reach, 1.5f + 1.0f / (2.0f * P.boxmax[i]));
-    if ((float)c->halo < reach) return fail(c, VR_ERR_INVALID_ARGUMENT, "region halo %d too small: this scene needs %d voxels", c->halo, (int)ceilf(reach));
+    if (!vs->self && (float)c->halo < reach)
+      return fail(c, VR_ERR_INVALID_ARGUMENT, "region halo %d too small: this scene needs %d voxels", c->halo, (int)ceilf(reach));
     P.vs_mode = vs->mode, P.vs_index = vs->index, P.vs_count = vs->count;
     for (int i = 0; i < 3; ++i) {
-      P.reg_lo[i] = c->rlo[i] <= 0 ? -INFINITY : (float)c->rlo[i] / (float)dims[i];
-      P.reg_hi[i] = c->rhi[i] >= dims[i] ? INFINITY : (float)c->rhi[i] / (float)dims[i];
+      P.reg_lo[i] = (vs->self || c->rlo[i] <= 0) ? -INFINITY : (float)c->rlo[i] / (float)dims[i];
+      P.reg_hi[i] = (vs->self || c->rhi[i] >= dims[i]) ? INFINITY : (float)c->rhi[i] / (float)dims[i];
     }
     P.vs_opacity_out = vs->opacity_out, P.vs_opacity_all = vs->opacity_all;
     if (vs->mode == 2) {
@@ -1159,8 +1195,10 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       measure_tail = vs->mode == 2 && c->auto_slices == 0 && P.count;
       slices = vs->mode == 1 ? (c->auto_slices ? c->auto_slices : 1) : (c->slices_of_opacity_pass > 1 ? c->slices_of_opacity_pass : 1);
     }
+    if (vs->self) slices = (int)std::min<int64_t>(c->opt[VR_OPT_RAY_SLICES], 16);  // a plain frame in latency mode: explicit only
     // (the kernels with per-texture addressing, P.uniform == 0, are built for whole rays only)
     if (slices < 1 || P.skip != 2 || P.uniform == 0) slices = 1;
+    if (vs->self && vs->mode == 1 && slices == 1) return fail(c, VR_ERR_UNSUPPORTED, "this scene cannot be cut into depth slices");
     if (vs->mode == 2 && slices != (c->slices_of_opacity_pass > 1 ? c->slices_of_opacity_pass : 1))
       return fail(c, VR_ERR_INVALID_ARGUMENT, "partial render with %d depth slices after an opacity pass with %d", slices, c->slices_of_opacity_pass);
     if (slices > 1) {
@@ -1227,6 +1265,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
   // which tiles this context renders: tiles dealt round-robin (mode 0), or whole tile COLUMNS dealt round-robin (mode 1: the
   // owned pixels of every image plane are then a few contiguous runs of tile_w * H floats - what a device->host copy wants)
   const bool columns = c->opt[VR_OPT_PART_MODE] == 1 && P.part_nranks > 1;
+  P.part_columns = columns ? 1 : 0;
   const uint64_t own_cols = (uint64_t)P.ntx > (uint64_t)P.part_rank ? ((uint64_t)P.ntx - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0;
   const uint64_t owned = columns ? own_cols * P.nty
                                  : (ntiles > (uint64_t)P.part_rank ? (ntiles - P.part_rank + P.part_nranks - 1) / P.part_nranks : 0);
@@ -1291,7 +1330,7 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       // the point the long rays pass through: the box centre (the world origin) - or, for a context that owns a region, the
       // centre of ITS box: only the rays through that brick have work here
       float ctr[3] = {0.f, 0.f, 0.f};
-      if (vs)
+      if (vs && !vs->self)
         for (int i = 0; i < 3; ++i) {
           const float lo_n = (float)c->rlo[i] / (float)(i == 0 ? E.w : i == 1 ? E.h : E.d), hi_n = (float)c->rhi[i] / (float)(i == 0 ? E.w : i == 1 ? E.h : E.d);
           ctr[i] = P.boxmin[i] + (P.boxmax[i] - P.boxmin[i]) * 0.5f * (lo_n + hi_n);
@@ -1361,7 +1400,8 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     for (size_t f = 0; f < n_frames; ++f) VR_CUDA(c, cudaMemsetAsync(d_outs[f], 0, (size_t)W * H * 3 * sizeof(float), stream));
   VR_CUDA(c, cudaMemsetAsync(c->d_counter, 0, 64, stream));
   VR_CUDA(c, cudaMemsetAsync(S.d_stats, 0, 6 * sizeof(unsigned long long), stream));  // [marched, shaded, hits | tail measurement]
-  VR_CUDA(c, cudaEventRecord(S.ev0, stream));
+  const bool self1 = vs && vs->self && vs->mode == 1;  // the opacity pass of a latency-mode frame: no counters, no timing of its own
+  if (!(vs && vs->self)) VR_CUDA(c, cudaEventRecord(S.ev0, stream));  // (latency mode: recorded before the opacity pass)
   if (texhw && c->opt[VR_OPT_TEXTURE_SINGLE_COPY]) {
     // texture-unit launches read arrays and grids only: the padded storages go (cudaFree waits for the grid builds that
     // still read them; this happens on the first frame after an upload only)
@@ -1399,10 +1439,13 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
 #endif
   c->stats.arithmetic = (uint32_t)arith;
   if (slices > 1) {  // the brick's opacity plane / colour share from those of its slices
-    if (vs->mode == 1) VR_CUDA(c, launch_fold_slices(c->d_slice_opac, slices, W * H, vs->opacity_out, 1, stream));
-    else VR_CUDA(c, launch_fold_slices(c->d_slice_img, slices, 3 * W * H, d_outs[0], 0, stream));
+    FoldOwner own;
+    own.plane = W * H, own.H = (uint32_t)H, own.tile_w = (uint32_t)P.tile_w, own.tile_h = (uint32_t)P.tile_h, own.ntx = (uint32_t)P.ntx;
+    own.rank = (uint32_t)P.part_rank, own.nranks = (uint32_t)P.part_nranks, own.columns = columns ? 1u : 0u;
+    if (vs->mode == 1) VR_CUDA(c, launch_fold_slices(c->d_slice_opac, slices, W * H, vs->opacity_out, 1, own, stream));
+    else VR_CUDA(c, launch_fold_slices(c->d_slice_img, slices, 3 * W * H, d_outs[0], 0, own, stream));
   }
-  VR_CUDA(c, cudaEventRecord(S.ev1, stream));
+  if (!self1) VR_CUDA(c, cudaEventRecord(S.ev1, stream));
   if (P.tile_cost) {
     VR_CUDA(c, cudaMemcpyAsync(S.h_tile_cost, c->d_tile_cost, 2 * ntiles * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
     VR_CUDA(c, cudaEventRecord(S.ev_cost, stream));
@@ -1412,8 +1455,9 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
     VR_CUDA(c, cudaMemcpyAsync(S.h_stats, S.d_stats, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
     S.stats_pending = true;
   }
-  S.timing_pending = true;
+  if (!self1) S.timing_pending = true;
   c->stats.kernel_launches = (P.num_work > 0 ? 1 : 0) + (slices > 1 ? 1 + slice_states_ran : 0);  // march (+ fold, + slice starts)
+  if (vs && vs->self && vs->mode == 2) c->stats.kernel_launches += 3;  // the opacity pass of the same frame: slice starts, march, fold
   c->stats.vs_slices = (uint32_t)slices;
   c->stats.fetch_mode = texhw ? 1u : 0u;
   return VR_OK;
@@ -1485,6 +1529,7 @@ vr_status vr_create_on_device(vr_ctx **out, int device) {
   if (const char *tu = getenv("VR_TEXTURE_UNIT")) c->opt[VR_OPT_TEXTURE_UNIT] = atoi(tu) < 0 ? 0 : (atoi(tu) > 2 ? 2 : atoi(tu));
   c->opt[VR_OPT_TEXTURE_SINGLE_COPY] = 1;
   c->opt[VR_OPT_VS_SLICES] = 0;
+  c->opt[VR_OPT_RAY_SLICES] = 1;
   if (const char *sl = getenv("VR_VS_SLICES")) c->opt[VR_OPT_VS_SLICES] = atoi(sl) < 0 ? 0 : (atoi(sl) > 16 ? 16 : atoi(sl));
   c->opt[VR_OPT_ARITHMETIC] = VR_DEFAULT_ARITHMETIC;
   if (const char *ar = getenv("VR_ARITHMETIC")) c->opt[VR_OPT_ARITHMETIC] = atoi(ar) < 0 ? 0 : (atoi(ar) > 2 ? 2 : atoi(ar));
@@ -1576,6 +1621,7 @@ vr_status vr_destroy(vr_ctx *c) {
   if (c->d_slice_opac) cudaFree(c->d_slice_opac);
   if (c->d_slice_img) cudaFree(c->d_slice_img);
   if (c->d_slice_state) cudaFree(c->d_slice_state);
+  if (c->d_self_opac) cudaFree(c->d_self_opac);
   if (c->d_warp_times) cudaFree(c->d_warp_times);
   cudaEventDestroy(c->evu0), cudaEventDestroy(c->evu1);
   if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -2011,6 +2057,7 @@ vr_status batch_begin_one(vr_ctx *c, const vr_light *lights, size_t n_lights, co
     c->cur = 0;
     return st;
   }
+  S.launches = c->stats.kernel_launches;
   VR_CUDA(c, cudaEventRecord(S.ev_rendered, c->stream));
   VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, S.ev_rendered, 0));
   for (size_t f = 0; f < n_frames; ++f) VR_TRY(enqueue_download(c, out_images[f], d_outs[f], res[1], res[0], c->copy_stream));
@@ -2143,6 +2190,7 @@ vr_status vr_set_option(vr_ctx *c, int option, int64_t value) {
   if (option < 0 || option >= VR_OPT_COUNT_) return fail(c, VR_ERR_INVALID_ARGUMENT, "unknown option %d", option);
   if (option == VR_OPT_FILTER_FRAC_BITS && value != 0 && value != 8) return fail(c, VR_ERR_INVALID_ARGUMENT, "filter frac bits must be 0 or 8");
   if (option == VR_OPT_ARITHMETIC && (value < 0 || value > 2)) return fail(c, VR_ERR_INVALID_ARGUMENT, "arithmetic flavour must be 0 (exact), 1 (reference) or 2 (fast)");
+  if (option == VR_OPT_RAY_SLICES && (value < 1 || value > 16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "ray slices must be in [1, 16]");
   if (option == VR_OPT_VS_SLICES && (value < 0 || value > 16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "depth slices must be in [0, 16] (0 = automatic)");
   if (c->members.size() > 1) {
     if (option == VR_OPT_PART_RANK || option == VR_OPT_PART_NRANKS || option == VR_OPT_PART_MODE)

@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     if (hit) {
       tot_marched += r.n_marched;
       tot_shaded += r.n_shaded;
-      tot_hits += 1;
+      tot_hits += slice == 0 ? 1 : 0;  // (a pixel's slices are one ray)
     }
   }
   if (kTimed && P.measure_tail && lane == 0) {
@@ -291,6 +291,10 @@ __global__ void __launch_bounds__(128) k_slice_states(const __grid_constant__ Ke
   const int S = P.vs_slices;
   for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < plane; k += (size_t)gridDim.x * blockDim.x) {
     const uint32_t x = (uint32_t)(k / (size_t)P.H), y = (uint32_t)(k - (size_t)x * P.H);
+    if (P.part_nranks > 1) {  // an image-space partition: only this context's tiles are marched
+      const uint32_t tx = x / (uint32_t)P.tile_w, ty = y / (uint32_t)P.tile_h;
+      if ((P.part_columns ? tx : ty * (uint32_t)P.ntx + tx) % (uint32_t)P.part_nranks != (uint32_t)P.part_rank) continue;
+    }
     Ray r;
     bool alive = ray_init(P, P.cam, x, y, origin, r);
     SliceCut cut;

@@ -89,7 +89,12 @@ cudaError_t launch_synth_region(void *d_out, int kind, uint32_t seed, const int 
 // Every partial is already weighted by the transmittance of the bricks in front of it, so the "under"
 // operator over depth-ordered partials reduces to an order-free sum.  Partials may live on peer GPUs.
 cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_floats, float *d_out, cudaStream_t stream);
-cudaError_t launch_fold_slices(const float *d_slices, int S, uint64_t n, float *d_out, int product, cudaStream_t stream);
+// which pixels of a plane a context owns under an image-space partition (nranks <= 1: all of them)
+struct FoldOwner {
+  uint64_t plane;  // W * H
+  uint32_t H, tile_w, tile_h, ntx, rank, nranks, columns;
+};
+cudaError_t launch_fold_slices(const float *d_slices, int S, uint64_t n, float *d_out, int product, const FoldOwner &own, cudaStream_t stream);
 
 // image epilogue: stereo crop + compose (mode 0 RedCyan, 1 LeftRightHorizontal) and sequence normalisation
 cudaError_t launch_stereo(const float *left, const float *right, int H, int Wp, int delta, int mode, float *out, cudaStream_t stream);

@@ -509,8 +509,15 @@ cudaError_t launch_compose(const float *const *d_partials, int n, uint64_t n_flo
 // Depth slices of one brick (VR_OPT_VS_SLICES): S planes of n floats each -> one.  product = 1: opacities, 1 - prod(1 - a_s),
 // front to back (what a march through the whole brick accumulates: sum.w += (1 - sum.w) * alpha, kernel.cu:470-483);
 // product = 0: the additive colour shares, summed in slice order.
-__global__ void __launch_bounds__(256) k_fold_slices(const float *in, int S, uint64_t n, float *out, int product) {
+__global__ void __launch_bounds__(256) k_fold_slices(const float *in, int S, uint64_t n, float *out, int product, const FoldOwner own) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    if (own.nranks > 1) {  // an image-space partition: only the pixels of this context's tiles hold anything (k = x * H + y)
+      const uint64_t k = i % own.plane;
+      const uint32_t x = (uint32_t)(k / own.H), y = (uint32_t)(k - (uint64_t)x * own.H);
+      const uint32_t tx = x / own.tile_w, ty = y / own.tile_h;
+      const uint32_t key = own.columns ? tx : ty * own.ntx + tx;
+      if (key % own.nranks != own.rank) continue;
+    }
     if (product) {
       float T = 1.0f;
       for (int s = 0; s < S; ++s) T = T * (1.0f - __ldg(in + (uint64_t)s * n + i));
@@ -522,11 +529,11 @@ __global__ void __launch_bounds__(256) k_fold_slices(const float *in, int S, uin
     }
   }
 }
-cudaError_t launch_fold_slices(const float *d_slices, int S, uint64_t n, float *d_out, int product, cudaStream_t stream) {
+cudaError_t launch_fold_slices(const float *d_slices, int S, uint64_t n, float *d_out, int product, const FoldOwner &own, cudaStream_t stream) {
   uint64_t blocks = (n + 255) / 256;
   if (blocks > 148ull * 8) blocks = 148ull * 8;
   if (blocks < 1) blocks = 1;
-  k_fold_slices<<<(unsigned)blocks, 256, 0, stream>>>(d_slices, S, n, d_out, product);
+  k_fold_slices<<<(unsigned)blocks, 256, 0, stream>>>(d_slices, S, n, d_out, product, own);
   return cudaGetLastError();
 }
 

@@ -124,6 +124,7 @@ struct KernelParams {
   // per frame by k_slice_states (the exact fast-forward of the reference's recurrences) and read by both passes:
   // entry (s - 1) * W * H + pixel of vs_slice_state.
   int vs_slices;
+  int part_columns;  // 1: the image-space partition deals tile COLUMNS (VR_OPT_PART_MODE); only k_slice_states needs to know
   int measure_tail;  // whole-ray shading pass: stats[3..5] = ~(first warp start), ~(first warp end), last warp end, ns (the automatic choice of slices)
   float *vs_slice_opacity;
   float *vs_slice_state;  // 4 floats per entry (16-byte aligned)
