@@ -479,10 +479,14 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     # ---- device-resident leg: `value` ----
+    # (the sampler is started BEFORE the warm-up: nvidia-smi takes a few hundred ms to initialise NVML and holds driver locks
+    # meanwhile - inside the timed region that stalls launches; its rows are filtered by time stamp to the timed region)
+    sampler = ClockSampler(local) if rank == 0 else None
     for w in range(0, args.warmup, B):
         frame_device(-args.warmup + w, min(B, args.warmup - w))
+    if sampler:
+        time.sleep(0.3)  # nvidia-smi's start-up ends outside the timed region
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
     samples = shaded = 0
     kernel_ms = []
     launches = 0
@@ -1071,9 +1075,9 @@ def run_example3(args):
                 counters["launches"] += st.kernel_launches
             counters["upload_ms"] += up_ms
 
+    sampler = ClockSampler(0)  # before the warm-up, see run_b200
     for w in range(args.warmup):
         frame(-1 - w, count=False)
-    sampler = ClockSampler(0)
     t0 = time.time()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
@@ -1204,10 +1208,13 @@ def run_volume(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local) if rank == 0 else None  # before the warm-up, see run_b200
     for w in range(args.warmup):
         frame(-1 - w)
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        time.sleep(0.3)  # let nvidia-smi finish its start-up outside the timed region (three warm-up frames are 70 ms)
+    barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     shaded = marched = 0
     kernel_ms = 0.0
@@ -1216,9 +1223,14 @@ def run_volume(args):
     t0 = time.time()
     barrier()
     ev0.record()
+    dbg = os.environ.get("BENCH_DEBUG_TIMES")
     for k in range(args.steps):
+        tf0 = time.perf_counter()
         frame(k)
+        tf1 = time.perf_counter()
         st = r.stats()  # counters of this rank's shading pass
+        if dbg:
+            print("[times] rank %d frame %d: frame() %.2f ms, stats() %.2f ms, kernel %.2f ms, slices %d" % (rank, k, (tf1 - tf0) * 1e3, (time.perf_counter() - tf1) * 1e3, st["kernel_ms"], st["vs_slices"]), file=sys.stderr, flush=True)
         shaded += st["samples_shaded"]
         marched += st["samples_marched"]
         kernel_ms += st["kernel_ms"]

@@ -2,10 +2,12 @@
  * synthetic ViBE-Z-like volume without MATLAB.  It performs the same call sequence the MATLAB
  * class does per frame (VolumeRender.m:497-583): 'sync_volumes' then 'render'.
  *
- *   vrbench [--size N] [--image W H] [--frames K] [--lights L] [--grad] [--bf16] [--stereo] [--gpus G] [--out file.pfm]
+ *   vrbench [--size N] [--image W H] [--frames K] [--lights L] [--grad] [--bf16] [--stereo] [--gpus G] [--ray-slices S] [--out file.pfm]
  *
  * --gpus G: the context leads a group of devices 0..G-1 (vr_set_devices): volumes resident on each, tile columns dealt
  * round-robin, the same H x W x 3 image comes back - several GPUs behind the one 'render' call, no torch, no MPI.
+ *
+ * --ray-slices S: VR_OPT_RAY_SLICES, the latency mode of single frames (every frame here is one 'render' call).
  *
  * Links only against libvr_b200.so (no CPU fallback, no checker code).
  */
@@ -57,7 +59,7 @@ static int write_pfm(const char *path, const float *img, uint64_t H, uint64_t W)
 
 int main(int argc, char **argv) {
   uint64_t n = 256, W = 512, H = 512;
-  int frames = 3, nl = 1, grad = 0, bf16 = 0, stereo = 0, gpus = 1;
+  int frames = 3, nl = 1, grad = 0, bf16 = 0, stereo = 0, gpus = 1, ray_slices = 1;
   const char *out = NULL;
   for (int i = 1; i < argc; ++i) {
     if (!strcmp(argv[i], "--size") && i + 1 < argc) n = strtoull(argv[++i], NULL, 10);
@@ -68,6 +70,7 @@ int main(int argc, char **argv) {
     else if (!strcmp(argv[i], "--bf16")) bf16 = 1;
     else if (!strcmp(argv[i], "--stereo")) stereo = 1;
     else if (!strcmp(argv[i], "--gpus") && i + 1 < argc) gpus = atoi(argv[++i]);
+    else if (!strcmp(argv[i], "--ray-slices") && i + 1 < argc) ray_slices = atoi(argv[++i]);
     else if (!strcmp(argv[i], "--out") && i + 1 < argc) out = argv[++i];
     else { fprintf(stderr, "usage: vrbench [--size N] [--image W H] [--frames K] [--lights L] [--grad] [--bf16] [--stereo] [--gpus G] [--out f.pfm]\n"); return 2; }
   }
@@ -80,6 +83,7 @@ int main(int argc, char **argv) {
     for (int i = 0; i < gpus; ++i) ids[i] = i;
     CHECK(vr_set_devices(ctx, (uint32_t)gpus, ids));
   }
+  if (ray_slices > 1) CHECK(vr_set_option(ctx, VR_OPT_RAY_SLICES, ray_slices));
   const int dt = bf16 ? VR_DTYPE_BF16 : VR_DTYPE_F32;
   const size_t vbytes = (size_t)n * n * n * (bf16 ? 2 : 4);
   const uint64_t dims[3] = {n, n, n};

@@ -247,3 +247,17 @@ def test_plain_c_harness_on_several_gpus_equals_one_gpu(tmp_path):
         if gpus > 1:
             assert "device group: %d members" % gpus in p.stdout and "peer access yes" in p.stdout
     assert np.array_equal(imgs[0], imgs[1])
+
+
+def test_plain_c_harness_latency_mode(tmp_path):
+    """harness/vrbench --ray-slices S: VR_OPT_RAY_SLICES from plain C - every frame of the harness is one 'render' call."""
+    exe = os.path.join(ROOT, "harness", "vrbench")
+    imgs = []
+    for extra in ([], ["--ray-slices", "4"]):
+        out = str(tmp_path / ("frame_%d.pfm" % len(extra)))
+        p = subprocess.run([exe, "--size", "96", "--image", "200", "120", "--frames", "2", "--grad", "--lights", "2", "--out", out] + extra,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+        assert p.returncode == 0, p.stdout
+        imgs.append(_read_pfm(out))
+    assert imgs[0].max() > 0 and not np.array_equal(imgs[0], imgs[1])  # (the folds round differently: the option did something)
+    assert np.abs(imgs[0] - imgs[1]).max() / imgs[0].max() < 2e-5

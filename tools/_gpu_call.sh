@@ -1,6 +1,6 @@
 set -x
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
-timeout 300 python tools/latency_mode.py --gpus 8 --slices 1,4,8,16 2>&1 | tail -4 | tee gpurun_out/latency_8.log
-timeout 300 python tools/latency_mode.py --gpus 4 --slices 1,8,16 2>&1 | tail -3 | tee gpurun_out/latency_4.log
-timeout 300 python tools/latency_mode.py --gpus 2 --slices 1,8 2>&1 | tail -2 | tee gpurun_out/latency_2.log
+TR2="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517"
+timeout 600 $TR2 bench.py --gpus 2 --mode volume --size 2048 --dtype bf16 --steps 12 --warmup 3 --no-cpu-baseline > gpurun_out/vs2_2048_final.json 2> gpurun_out/vs2_2048_final.err; echo rc=$?
+timeout 600 $TR2 bench.py --gpus 2 --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/bench_n2.json 2> gpurun_out/bench_n2.err; echo rc=$?
