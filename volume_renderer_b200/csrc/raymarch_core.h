@@ -873,6 +873,8 @@ VR_HD SliceCut vs_slice_cut(const KernelParams &P, F3 origin, const Ray &r, F3 b
   c.inside = intersect_box(origin, r.step, lo, hi, un, uf);
   c.a = un * P.tstep;
   c.w = (uf * P.tstep - c.a) / (float)S;
+  // (a ray that lies IN a face of the box gives 0 * inf = NaN in the slab test, as in the reference's intersectBox: one slice then)
+  c.inside = c.inside && c.w >= 0.0f && c.a == c.a;
   return c;
 }
 VR_HD float vs_slice_bound(const SliceCut &c, int s, int S) {
