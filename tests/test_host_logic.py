@@ -194,3 +194,29 @@ def test_acos_polynomial_accuracy_and_nan_rule():
     assert lib.emul_acos_poly(1.0) == 0.0 and lib.emul_acos_poly(-1.0) == np.float32(np.pi)
     for bad in (1.0000001, -1.0000001, 2.0, float("nan"), float("inf")):
         assert np.isnan(lib.emul_acos_poly(bad))
+
+
+def test_python_constants_and_structs_match_the_header(tmp_path):
+    """volume_renderer_b200/_abi.py restates include/vr_abi.h by hand: every VR_OPT_* value, and vr_stats field by field
+    (size and offsets from a C program compiled against the header itself)."""
+    import ctypes
+    import re
+    import subprocess
+
+    from volume_renderer_b200 import _abi
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "vr_abi.h")).read()
+    opts = dict(re.findall(r"\bVR_OPT_([A-Z0-9_]+)\s*=\s*(\d+)", hdr))
+    assert len(opts) >= 20
+    for name, value in opts.items():
+        assert getattr(_abi, "OPT_" + name) == int(value), name
+    fields = [f for f, _ in _abi.VrStats._fields_]
+    src = tmp_path / "layout.c"
+    src.write_text('#include <stddef.h>\n#include <stdio.h>\n#include "vr_abi.h"\nint main(void) {\n  printf("%zu\\n", sizeof(vr_stats));\n'
+                   + "".join('  printf("%%zu\\n", offsetof(vr_stats, %s));\n' % f for f in fields) + "  return 0;\n}\n")
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c11", "-I", os.path.join(root, "include"), "-o", str(exe), str(src)], check=True)
+    out = [int(x) for x in subprocess.run([str(exe)], check=True, stdout=subprocess.PIPE, text=True).stdout.split()]
+    assert out[0] == ctypes.sizeof(_abi.VrStats)
+    assert out[1:] == [getattr(_abi.VrStats, f).offset for f in fields]
