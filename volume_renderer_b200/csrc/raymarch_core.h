@@ -943,6 +943,13 @@ VR_HD float u2f(uint32_t u) {
   return f;
 #endif
 }
+// the largest float below x (x finite): t > float_below(x)  <=>  t >= x
+VR_HD float float_below(float x) {
+  const uint32_t u = f2u(x);
+  if (x > 0.0f) return u2f(u - 1u);
+  if (x < 0.0f) return u2f(u + 1u);
+  return u2f(0x80000001u);  // below +-0: the smallest negative denormal
+}
 // v0, v1, v2 are normal numbers of one binade (same sign, same exponent), or all equal
 VR_HD bool one_binade(float v0, float v1, float v2) {
   const uint32_t e0 = f2u(v0) >> 23, e1 = f2u(v1) >> 23, e2 = f2u(v2) >> 23;
@@ -1034,11 +1041,15 @@ VR_HD bool on_empty_cell(const KernelParams &P, const Ray &r, F3 bmin, F3 bscale
 // counter - was tried: it saves the 38-instruction check per sample but lanes then reach the next
 // empty cell out of phase and run the jump below one by one: 27 -> 42 ms.  Checking every sample
 // keeps neighbouring rays in step.)
-// t_stop (depth slices): the end of the worker's slice of the ray parameter - a jump does not go past it, so that every lattice
-// sample is visited (and counted) by exactly one worker; reaching it returns true (the caller retires the lane).
-VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, float t_stop = 3.0e38f) {
+// (Depth slices need nothing here: a slice's end is the ray's tfar - see the kernel - and the jump stops there as it does at the
+// end of a whole ray, counting every lattice sample up to it once.)
+// STOP = 1 keeps an earlier formulation - an explicit end t_stop of the lane's stretch, 3e38 = none - alive for the WHOLE-RAY
+// kernels only, which pass 3e38: with it they compile to the very machine code that ran every test, benchmark and the 360-frame
+// turns of this round (checked by comparing the SASS); the sliced kernels use STOP = 0.  See DESIGN 4.5 for why that matters here.
+template <int STOP>
+VR_HD bool skip_empty_jump_t(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, float t_stop) {
   for (;;) {
-    if (!(r.t < t_stop)) return true;
+    if (STOP && !(r.t < t_stop)) return true;
     CellAt c = cell_at(P, r, bmin, bscale);
 #if defined(VR_DEBUG_BOUNDS) && defined(__CUDA_ARCH__)
     if (c.cell >= (uint32_t)(P.ocx * P.ocy * P.ocz) && P.warp_times) {
@@ -1080,7 +1091,7 @@ VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, fl
     const float big = 3.0e38f;
     const F3 inv_dq = mk3(dq.x != 0.0f ? 1.0f / dq.x : big, dq.y != 0.0f ? 1.0f / dq.y : big, dq.z != 0.0f ? 1.0f / dq.z : big);
     float kf = ceilf(steps_to_exit(now, dist - 1, dq, inv_dq));
-    if (t_stop < 3.0e38f) kf = fminf(kf, fmaxf(ceilf((t_stop - r.t) / dt), 1.0f));
+    if (STOP && t_stop < 3.0e38f) kf = fminf(kf, fmaxf(ceilf((t_stop - r.t) / dt), 1.0f));
     kf = fminf(kf, fminf(fminf(binade_room(r.t, dt), binade_room(r.pos.x, d.x)), fminf(binade_room(r.pos.y, d.y), binade_room(r.pos.z, d.z))));
     kf = fminf(kf, 4194304.0f);
     if (!(kf >= 1.0f)) continue;
@@ -1147,6 +1158,10 @@ VR_HD bool fast_forward_to(const KernelParams &P, Ray &r, float t_until) {
     r.t = t_end;
     r.pos = p_end;
   }
+}
+
+VR_HD bool skip_empty_jump(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, float t_stop = 3.0e38f) {
+  return skip_empty_jump_t<1>(P, r, bmin, bscale, t_stop);
 }
 
 VR_HD bool skip_empty(const KernelParams &P, Ray &r, F3 bmin, F3 bscale, F3 dq, F3 inv_dq) {

@@ -137,14 +137,18 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     if (hit) VR_TRACE(P, r, 1, P.vs_mode, slice);
 #endif
     const int vs_mode = vs_mode_w;  // (TEXHW with UNI = 1: region contexts)
-    float ts1 = 3.0e38f;  // where this item's slice of the ray parameter ends
     if (S > 1 && hit) {
-      ts1 = vs_slice_bound(vs_slice_cut(P, origin, r, bmin, ext, (int)S), (int)slice + 1, (int)S);
-      if (slice > 0) {  // ... and its first sample, from k_slice_states
+      // This item's slice [bound(slice), bound(slice + 1)) of the ray parameter.  Its END becomes the ray's far end - the largest
+      // float below the bound, so that `t > tfar` (kernel.cu:489-490) is exactly `t >= bound` - and the march below is the
+      // whole-ray march, instruction for instruction: the loop tail and the empty-space jump already stop at tfar.
+      const float ts1 = vs_slice_bound(vs_slice_cut(P, origin, r, bmin, ext, (int)S), (int)slice + 1, (int)S);
+      if (slice > 0) {  // its first sample, from k_slice_states
         const float4 st = __ldg(reinterpret_cast<const float4 *>(P.vs_slice_state) + (size_t)(slice - 1) * ((size_t)P.W * P.H) + ((size_t)x * P.H + y));
         r.t = st.x, r.pos = mk3(st.y, st.z, st.w);
         if (!(st.x < 3.0e38f)) active = false;  // the ray ends before this slice
       }
+      if (ts1 < 3.0e38f) r.tfar = fminf(r.tfar, float_below(ts1));
+      if (r.t > r.tfar) active = false;  // an empty slice
     }
     if (vs_mode == 2 && hit) {  // start from the opacity of the bricks in front; nothing to do behind the threshold
       float a_in = 0.0f;
@@ -161,7 +165,6 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
     F3 dq = mk3(0, 0, 0), inv_dq = mk3(0, 0, 0);
     if (active && P.skip == 1) skip_setup(P, r, bscale, dq, inv_dq);
 
-    if (SL && active && !(r.t < ts1)) active = false;  // a ray that starts behind this item's slice
     int waited = 0;  // warp-uniform: iterations the oldest postponed jump has been waiting
     while (__any_sync(kFull, active)) {
 #ifdef VR_ITEM_PROFILE
@@ -183,8 +186,7 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
 #ifdef VR_ITEM_PROFILE
             ++it_jumps;
 #endif
-            if (want) ready = active = SL ? skip_empty_jump(P, r, bmin, bscale, ts1) : skip_empty_jump(P, r, bmin, bscale);
-            if (SL && active && !(r.t < ts1)) ready = active = false;  // jumped out of this item's slice
+            if (want) ready = active = SL ? skip_empty_jump_t<0>(P, r, bmin, bscale, 3.0e38f) : skip_empty_jump(P, r, bmin, bscale);
             waited = 0;
           } else {
             ++waited;
@@ -199,7 +201,6 @@ __global__ void __launch_bounds__(Tune<GRAD, LAYOUT>::threads, Tune<GRAD, LAYOUT
         shade_sample<GRAD, LAYOUT, E, UNI>(P, origin, r);
         VR_TRACE(P, r, 7, __float_as_uint(r.sw), 0);
         active = ray_advance(P, r);
-        if (SL && active && !(r.t < ts1)) active = false;  // past this item's slice: the next slice's worker takes over
       }
     }
     if (x < (uint32_t)P.W && y < (uint32_t)P.H) {
