@@ -244,3 +244,67 @@ extern "C" uint64_t emul_div_pi_mismatches(uint32_t first_bits, uint32_t last_bi
   }
   return bad;
 }
+
+// Depth slices: fast_forward_to must land on the very (t, pos) the reference's serial recurrences
+// `t += tstep; pos += step` (volumeRender_kernel.cu:488-492) reach at the first sample with t >= t_until - bit for bit.
+// Random rays through the box [-1,1]^3 (directions with tiny and zero components, starts on a face so that coordinates cross
+// zero and many binades); returns the number of rays on which the two disagree (state or "the ray ended first").
+static uint32_t lcg(uint32_t &s) { return s = s * 1664525u + 1013904223u; }
+static float urand(uint32_t &s) { return (float)(lcg(s) >> 8) * (1.0f / 16777216.0f); }
+extern "C" uint64_t emul_fast_forward_mismatches(uint32_t seed, uint32_t n_rays) {
+  uint64_t bad = 0;
+  uint32_t s = seed;
+  for (uint32_t i = 0; i < n_rays; ++i) {
+    KernelParams P;
+    memset(&P, 0, sizeof P);
+    const int n = 64 << (lcg(s) % 7u);  // 64 .. 4096 voxels across
+    P.tstep = 1.0f / (2.2f * (float)n * 1.41421356f);
+    float d[3] = {urand(s) * 2.0f - 1.0f, urand(s) * 2.0f - 1.0f, urand(s) * 2.0f - 1.0f};
+    const uint32_t kind = lcg(s) % 8u;
+    if (kind == 0) d[lcg(s) % 3u] = 0.0f;          // axis-parallel in one coordinate
+    if (kind == 1) d[lcg(s) % 3u] *= 1.0e-6f;      // ... nearly
+    if (kind == 2) d[lcg(s) % 3u] *= 1.0e-3f;
+    const float len = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    if (!(len > 1.0e-3f)) continue;
+    Ray r;
+    memset(&r, 0, sizeof r);
+    r.step = mk3(d[0] / len * P.tstep, d[1] / len * P.tstep, d[2] / len * P.tstep);
+    r.pos = mk3(urand(s) * 2.0f - 1.0f, urand(s) * 2.0f - 1.0f, urand(s) * 2.0f - 1.0f);
+    const uint32_t face = lcg(s) % 3u;  // start on a face of the box
+    (face == 0 ? r.pos.x : face == 1 ? r.pos.y : r.pos.z) = (lcg(s) & 1u) ? 1.0f : -1.0f;
+    r.t = 3.0f + urand(s) * 3.0f;  // the examples' distances: t in the binades [2,4) and [4,8)
+    const uint32_t steps_total = 1u + lcg(s) % (uint32_t)(4 * n);
+    r.tfar = r.t + (float)steps_total * P.tstep;
+    const float t_until = r.t + urand(s) * 1.2f * (r.tfar - r.t);  // sometimes beyond the ray's end
+    Ray a = r, b = r;
+    bool alive_a = true;
+    while (a.t < t_until) {  // the reference's loop tail, one sample at a time
+      a.t += P.tstep;
+      if (a.t > a.tfar) {
+        alive_a = false;
+        break;
+      }
+      a.pos = a.pos + a.step;
+    }
+    const bool alive_b = fast_forward_to(P, b, t_until);
+    if (alive_a != alive_b) {
+      ++bad;
+      continue;
+    }
+    if (alive_a && (f2u(a.t) != f2u(b.t) || f2u(a.pos.x) != f2u(b.pos.x) || f2u(a.pos.y) != f2u(b.pos.y) || f2u(a.pos.z) != f2u(b.pos.z))) ++bad;
+  }
+  return bad;
+}
+extern "C" uint64_t emul_float_below_mismatches(uint32_t seed, uint32_t n) {
+  uint64_t bad = 0;
+  uint32_t s = seed;
+  for (uint32_t i = 0; i < n; ++i) {
+    float x = u2f(lcg(s));
+    if (!(x == x) || std::isinf(x)) continue;
+    if (float_below(x) != nextafterf(x, -INFINITY)) ++bad;
+  }
+  const float special[] = {0.0f, -0.0f, 1.0f, 1.17549435e-38f, 1.4e-45f, -1.4e-45f, 3.0e38f};
+  for (float x : special)
+    if (float_below(x) != nextafterf(x, -INFINITY)) ++bad;
+  return bad;
+}

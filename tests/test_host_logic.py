@@ -220,3 +220,21 @@ def test_python_constants_and_structs_match_the_header(tmp_path):
     out = [int(x) for x in subprocess.run([str(exe)], check=True, stdout=subprocess.PIPE, text=True).stdout.split()]
     assert out[0] == ctypes.sizeof(_abi.VrStats)
     assert out[1:] == [getattr(_abi.VrStats, f).offset for f in fields]
+
+
+def test_slice_starts_are_the_serial_recurrences_bit_for_bit():
+    """Depth slices: the exact fast-forward that finds where a slice starts (raymarch_core.h: fast_forward_to,
+    run here on the host) lands on the very float state the reference's `t += tstep; pos += step` loop reaches, on 20 000 random
+    rays with coordinates that cross zero, tiny and zero direction components and ends before / behind the ray's end; and
+    float_below - which turns a slice's end into the ray's tfar - is nextafter(x, -inf)."""
+    import ctypes as C
+
+    import vrt
+
+    lib = vrt.host_emul()
+    lib.emul_fast_forward_mismatches.restype = C.c_uint64
+    lib.emul_fast_forward_mismatches.argtypes = [C.c_uint32] * 2
+    assert lib.emul_fast_forward_mismatches(vrt.SEED, 20000) == 0
+    lib.emul_float_below_mismatches.restype = C.c_uint64
+    lib.emul_float_below_mismatches.argtypes = [C.c_uint32] * 2
+    assert lib.emul_float_below_mismatches(vrt.SEED, 200000) == 0
