@@ -102,6 +102,66 @@ void build(HostTex &T, const float *src, int w, int h, int d, bool with_occ) {
   }
 }
 
+// Depth slices of the volume-space passes, lane-serial: what the workers of one pixel's S slices do in
+// raymarch_kernel.cu - slice starts by the exact fast-forward (k_slice_states), the slice's end as the ray's tfar, pass 1 one
+// opacity per slice folded as 1 - prod(1 - a_s), pass 2 every slice started from the bricks in front and the slices in front and
+// the shares summed in slice order - with the product's own helpers.
+int g_slices = 1;
+template <int GRAD, int LAYOUT, int UNI>
+bool march_pixel_sliced(const KernelParams &P, uint32_t x, uint32_t y, float rgba[4], uint32_t &marched, uint32_t &shaded) {
+  const int S = P.vs_slices;
+  const F3 origin = ray_origin(P.cam);
+  Ray r0;
+  if (!ray_init(P, P.cam, x, y, origin, r0)) return false;
+  const F3 bmin = ld3(P.boxmin), ext = ld3(P.boxmax) - bmin;
+  const F3 bscale = mk3(1.0f / ext.x, 1.0f / ext.y, 1.0f / ext.z);
+  const size_t plane = (size_t)P.W * P.H, pixel = (size_t)x * P.H + y;
+  float a_front = 0.0f;
+  const bool in_brick = P.vs_mode == 2 ? vs_opacity_in(P, origin, r0, pixel, a_front) : true;
+  const SliceCut cut = vs_slice_cut(P, origin, r0, bmin, ext, S);
+  Ray walker = r0;
+  bool walker_alive = cut.inside;
+  float T1 = 1.0f, sum[3] = {0.0f, 0.0f, 0.0f};
+  marched = shaded = 0;
+  for (int s = 0; s < S; ++s) {
+    Ray r = r0;
+    bool active = true;
+    if (s > 0) {
+      if (walker_alive) walker_alive = fast_forward_to(P, walker, vs_slice_bound(cut, s, S));
+      if (walker_alive) r.t = walker.t, r.pos = walker.pos;
+      else active = false;
+    }
+    const float ts1 = vs_slice_bound(cut, s + 1, S);
+    if (ts1 < 3.0e38f) r.tfar = fminf(r.tfar, float_below(ts1));
+    if (r.t > r.tfar) active = false;
+    if (P.vs_mode == 2) {
+      float T = 1.0f - a_front;
+      for (int q = 0; q < s; ++q) T = T * (1.0f - P.vs_slice_opacity[(size_t)q * plane + pixel]);
+      r.sw = 1.0f - T;
+      if (!in_brick || r.sw > P.thr) active = false;
+    }
+    F3 dq, inv_dq;
+    skip_setup(P, r, bscale, dq, inv_dq);
+    while (active) {
+      if (P.skip) active = skip_empty(P, r, bmin, bscale, dq, inv_dq);
+      if (!active) break;
+      shade_sample<GRAD, LAYOUT, ElemF32, UNI>(P, origin, r);
+      active = ray_advance(P, r);
+    }
+    if (P.vs_mode == 1) {
+      P.vs_slice_opacity[(size_t)s * plane + pixel] = r.sw;
+      T1 = T1 * (1.0f - r.sw);
+    } else if (s == 0) {
+      sum[0] = r.sx, sum[1] = r.sy, sum[2] = r.sz;
+    } else {
+      sum[0] += r.sx, sum[1] += r.sy, sum[2] += r.sz;
+    }
+    marched += r.n_marched, shaded += r.n_shaded;
+  }
+  rgba[0] = sum[0], rgba[1] = sum[1], rgba[2] = sum[2], rgba[3] = 1.0f - T1;
+  return true;
+}
+
 template <int GRAD, int LAYOUT, int UNI>
 void run(const KernelParams &P, float *out, uint64_t *stats) {
   const size_t size = (size_t)P.W * P.H;
@@ -115,7 +175,9 @@ void run(const KernelParams &P, float *out, uint64_t *stats) {
     for (int y = 0; y < P.H; ++y) {
       float rgb[4];
       uint32_t m = 0, s = 0;
-      if (!march_pixel<GRAD, LAYOUT, ElemF32, UNI>(P, (uint32_t)x, (uint32_t)y, rgb, m, s)) continue;
+      const bool hit = (P.vs_mode && P.vs_slices > 1) ? march_pixel_sliced<GRAD, LAYOUT, UNI>(P, (uint32_t)x, (uint32_t)y, rgb, m, s)
+                                                        : march_pixel<GRAD, LAYOUT, ElemF32, UNI>(P, (uint32_t)x, (uint32_t)y, rgb, m, s);
+      if (!hit) continue;
       const size_t k = (size_t)x * P.H + y;
       if (P.vs_mode == 1) {
         P.vs_opacity_out[k] = rgb[3];
@@ -187,6 +249,10 @@ int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr
   const size_t plane = (size_t)P.W * P.H;
   const int64_t dims[3] = {(int64_t)em->dims[0], (int64_t)em->dims[1], (int64_t)em->dims[2]};
   std::vector<float> opac((size_t)n_bricks * plane, 0.f), boxes((size_t)n_bricks * 6), part(plane * 3);
+  // depth slices (emul_set_slices): one set of per-slice opacity planes per brick, written by pass 1, read by pass 2
+  const int S = g_slices > 1 && P.skip == 2 ? g_slices : 1;
+  std::vector<float> slice_opac(S > 1 ? (size_t)n_bricks * S * plane : 0, 0.f);
+  P.vs_slices = S;
   for (int b = 0; b < n_bricks; ++b)
     for (int i = 0; i < 3; ++i) {
       const float ext = P.boxmax[i] - P.boxmin[i];
@@ -205,15 +271,20 @@ int emul(const vr_volume *em, const vr_volume *re, const vr_volume *gx, const vr
     region(b);
     P.vs_mode = 1;
     P.vs_opacity_out = opac.data() + (size_t)b * plane;
+    P.vs_slice_opacity = S > 1 ? slice_opac.data() + (size_t)b * S * plane : nullptr;
     go(nullptr, nullptr);
   }
   memset(out, 0, plane * 3 * sizeof(float));
+  if (stats) stats[0] = stats[1] = stats[2] = 0;
   P.vs_opacity_all = opac.data(), P.vs_boxes = boxes.data();
   for (int b = 0; b < n_bricks; ++b) {
     region(b);
     P.vs_mode = 2;
-    go(part.data(), nullptr);
+    P.vs_slice_opacity = S > 1 ? slice_opac.data() + (size_t)b * S * plane : nullptr;
+    uint64_t st[3] = {0, 0, 0};
+    go(part.data(), st);
     for (size_t i = 0; i < plane * 3; ++i) out[i] += part[i];
+    if (stats) stats[0] += st[0], stats[1] += st[1], stats[2] += st[2];  // the shading passes of all bricks
   }
   return 0;
 }
@@ -230,6 +301,8 @@ extern "C" int emul_render(const vr_volume *em, const vr_volume *re, const vr_vo
     return emul<LAYOUT_BRICK>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, n_bricks, boxes_vox, out, stats);
   return emul<LAYOUT_LINEAR>(em, re, gx, gy, gz, lut, lights, n_lights, factors, es, res, R, props, thr, color, skip, frac_bits, variant, n_bricks, boxes_vox, out, stats);
 }
+
+extern "C" void emul_set_slices(int slices) { g_slices = slices; }
 
 // unit-test hooks for the small numeric helpers of raymarch_core.h
 extern "C" float emul_acos_poly(float x) { return acos_poly(x); }

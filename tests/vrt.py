@@ -191,10 +191,14 @@ def host_emul():
     return _emul
 
 
-def emul_render(r, layout=1, skip=2, frac_bits=0, resolution=None, xoffset=0.0, variant=0, bricks=None):
+def emul_render(r, layout=1, skip=2, frac_bits=0, resolution=None, xoffset=0.0, variant=0, bricks=None, slices=1):
     """Run a configured api.VolumeRender-like scene `r` (Em = Ab aliased) through the host
-    emulation of the device code.  Returns (image HxWx3, stats[3])."""
+    emulation of the device code.  Returns (image HxWx3, stats[3]).  `slices` > 1 (with bricks): the volume-space passes
+    cut into depth slices (VR_OPT_VS_SLICES)."""
     lib = host_emul()
+    lib.emul_set_slices.argtypes = [C.c_int]
+    lib.emul_set_slices.restype = None
+    lib.emul_set_slices(int(slices))
     keep = []
 
     def vs(v):
@@ -216,6 +220,7 @@ def emul_render(r, layout=1, skip=2, frac_bits=0, resolution=None, xoffset=0.0, 
     bv = (C.c_uint64 * (6 * max(nb, 1)))(*[int(v) for box in (bricks or []) for v in (list(box[0]) + list(box[1]))])
     rc = lib.emul_render(vs(r.VolumeEmission), vs(r.VolumeReflection), vs(g[0]), vs(g[1]), vs(g[2]), args[2], args[0], args[1],
                          *args[3:], layout, skip, frac_bits, variant, nb, bv, out.ctypes.data, stats)
+    lib.emul_set_slices(1)
     assert rc == 0, rc
     return out, list(stats)
 
