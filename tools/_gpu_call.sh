@@ -1,3 +1,4 @@
 set -x
 cd $GRAFT_REPO_ROOT
-timeout 80 python tools/vs_one_rank.py --rank 1 --slices 0 --frames 120 2>&1 | grep "^frame" | sed -n '1p;3p;60p;120p' | cut -c1-140
+timeout 40 python tools/vs_one_rank.py --rank 0 --world 2 --size 1024 --dtype f32 --slices 16 --frames 360 2>&1 | grep -c "^frame"
+timeout 40 python -m pytest tests/test_gpu_hostpath.py -m gpu -q -k "harness" 2>&1 | tail -2
