@@ -271,8 +271,8 @@ typedef enum vr_option {
                                    both copies from then on), a switch to the load path, new skip grids.  0: keep both copies */
   VR_OPT_VS_SLICES = 18,        /* volume-space passes (vr_render_opacity / vr_render_partial): cut every ray's stretch inside the brick
                                    into this many equal depth slices marched by DIFFERENT warps; 1 = whole rays; 0 (default) =
-                                   automatic: the context's first frame marches whole rays and its shading pass measures its own tail - the
-                                   part of the launch during which warps had already run out of work; 30 % or more -> 8 slices, less ->
+                                   automatic: frames march whole rays and their shading pass measures its own tail - the part of the
+                                   launch during which warps had already run out of work; 30 % or more -> 8 slices from then on, less ->
                                    whole rays (needs VR_OPT_COUNT_SAMPLES, else whole rays); explicit values up to 16; needs the closed-form
                                    empty-space skip and kernels with one common volume geometry, else whole rays.  A launch then ends with its
                                    longest SLICE instead of its longest ray - what matters when a brick's rays are thousands of samples

@@ -1184,15 +1184,16 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       // through dense matter lasts 18 ms whatever the other 4735 warps do; slices pay when that chain is what the launch waits
       // for, and cost about a millisecond per frame (slice starts, folds, S times the items) when it is not.  So the context
       // MEASURES: its first frame marches whole rays and the shading pass records when its first warp ran out of work and when
-      // its last one finished.  A tail of 30 % of the launch or more -> 8 slices (measured on 2048^3 bricks of a 4096^3 volume:
+      // its last one finished - on every whole-ray frame.  A tail of 30 % of the launch or more -> 8 slices from then on (measured on 2048^3 bricks of a 4096^3 volume:
       // tails of 70 - 90 %, 35.6 -> 19.7 ms per frame); shorter tails -> whole rays (two bricks of 1024^3 / 2048^3: tails of
       // 12 - 19 %, slices change the frame by -2 ... +7 %).  Decided again when the image or the tiling changes; needs
       // VR_OPT_COUNT_SAMPLES (the read-back of the counters).
       const uint64_t tw = (uint64_t)c->opt[VR_OPT_TILE_W], th = (uint64_t)c->opt[VR_OPT_TILE_H];
       const uint64_t asig = (W << 40) ^ (H << 20) ^ (tw << 8) ^ th;
       if (c->auto_slices_sig != asig) c->auto_slices = 0, c->auto_slices_sig = asig, c->last_tail = -1.0;
-      if (vs->mode == 1 && c->auto_slices == 0 && c->stats.vs_slices == 1 && c->last_tail >= 0.0) c->auto_slices = c->last_tail >= 0.3 ? 8 : 1;
-      measure_tail = vs->mode == 2 && c->auto_slices == 0 && P.count;
+      // (whole rays keep measuring, a cut is kept: a scene that turns a long tail towards the camera later is still cut then)
+      if (vs->mode == 1 && c->auto_slices <= 1 && c->stats.vs_slices == 1 && c->last_tail >= 0.0) c->auto_slices = c->last_tail >= 0.3 ? 8 : 1;
+      measure_tail = vs->mode == 2 && c->auto_slices <= 1 && P.count;
       slices = vs->mode == 1 ? (c->auto_slices ? c->auto_slices : 1) : (c->slices_of_opacity_pass > 1 ? c->slices_of_opacity_pass : 1);
     }
     if (vs->self) slices = (int)std::min<int64_t>(c->opt[VR_OPT_RAY_SLICES], 16);  // a plain frame in latency mode: explicit only
