@@ -1183,10 +1183,10 @@ vr_status render_common(vr_ctx *c, const vr_light *lights, size_t n_lights, cons
       // Automatic.  A lone warp needs microseconds per shaded sample (the loop is one dependent chain), so a ray of 6000 samples
       // through dense matter lasts 18 ms whatever the other 4735 warps do; slices pay when that chain is what the launch waits
       // for, and cost about a millisecond per frame (slice starts, folds, S times the items) when it is not.  So the context
-      // MEASURES: its first frame marches whole rays and the shading pass records when its first warp ran out of work and when
-      // its last one finished - on every whole-ray frame.  A tail of 30 % of the launch or more -> 8 slices from then on (measured on 2048^3 bricks of a 4096^3 volume:
-      // tails of 70 - 90 %, 35.6 -> 19.7 ms per frame); shorter tails -> whole rays (two bricks of 1024^3 / 2048^3: tails of
-      // 12 - 19 %, slices change the frame by -2 ... +7 %).  Decided again when the image or the tiling changes; needs
+      // MEASURES: frames march whole rays, and their shading pass records when its first warp ran out of work and when its last
+      // one finished.  A tail of 30 % of the launch or more -> 8 slices from then on (measured on 2048^3 bricks of a 4096^3
+      // volume: tails of 70 - 90 %, 35.6 -> 19.7 ms per frame); shorter tails -> whole rays (two bricks of 1024^3 / 2048^3: tails
+      // of 12 - 19 %, slices change the frame by -2 ... +7 %).  Starts over when the image or the tiling changes; needs
       // VR_OPT_COUNT_SAMPLES (the read-back of the counters).
       const uint64_t tw = (uint64_t)c->opt[VR_OPT_TILE_W], th = (uint64_t)c->opt[VR_OPT_TILE_H];
       const uint64_t asig = (W << 40) ^ (H << 20) ^ (tw << 8) ^ th;
